@@ -1,0 +1,272 @@
+// Weight preparation, activation producers (reduce + RMSNorm + Q80), embedding, argmax,
+// error plumbing.
+#include <stdarg.h>
+#include <stdio.h>
+#include "epilogue.cuh"
+
+static thread_local char g_err[512] = "";
+void dl_set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+extern "C" const char* dl_last_error(void) { return g_err; }
+
+#define CHECK_LAUNCH(name)                                                              \
+    do {                                                                                \
+        cudaError_t e__ = cudaGetLastError();                                           \
+        if (e__ != cudaSuccess) {                                                       \
+            dl_set_error("%s: %s", name, cudaGetErrorString(e__));                      \
+            return -(int)e__;                                                           \
+        }                                                                               \
+    } while (0)
+
+extern "C" int dl_device_sm_count(void) {
+    int dev = 0, n = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return -1;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return -1;
+    return n;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Q40 file rows -> Q40T tiles
+// ------------------------------------------------------------------------------------------------
+extern "C" long long dl_q40t_bytes(int d, int n) {
+    long long d_pad = ((long long)d + Q40T_TILE_ROWS - 1) / Q40T_TILE_ROWS * Q40T_TILE_ROWS;
+    return d_pad / Q40T_TILE_ROWS * (long long)(n / Q40T_TILE_K) * Q40T_TILE_BYTES;
+}
+
+__global__ void q40_repack_kernel(const uint8_t* __restrict__ raw, int rows, int nb, uint8_t* __restrict__ out, int KT,
+                                  int dst_row0, int dst_row_step) {
+    // one thread per (source row, block); 18-byte source blocks are only 2-byte aligned
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (long long)rows * nb) return;
+    const int r = (int)(idx / nb), b = (int)(idx % nb);
+    const uint16_t* src = reinterpret_cast<const uint16_t*>(raw + ((size_t)r * nb + b) * 18);
+    uint16_t v[9];
+#pragma unroll
+    for (int i = 0; i < 9; i++) v[i] = src[i];
+    const int drow = dst_row0 + r * dst_row_step;
+    const int rt = drow >> 7, rr = drow & 127;
+    const int kt = b >> 2, kb = b & 3;
+    uint8_t* tile = out + ((size_t)rt * KT + kt) * Q40T_TILE_BYTES;
+    uint4 q;
+    q.x = (uint32_t)v[1] | ((uint32_t)v[2] << 16);
+    q.y = (uint32_t)v[3] | ((uint32_t)v[4] << 16);
+    q.z = (uint32_t)v[5] | ((uint32_t)v[6] << 16);
+    q.w = (uint32_t)v[7] | ((uint32_t)v[8] << 16);
+    *reinterpret_cast<uint4*>(tile + rr * 64 + (((kb + (rr >> 1)) & 3) << 4)) = q;
+    *reinterpret_cast<uint16_t*>(tile + Q40T_SCALE_OFF + rr * 8 + kb * 2) = v[0];
+}
+
+extern "C" int dl_q40_repack(const uint8_t* raw, int rows, int n, uint8_t* q40t, int d_pad, int dst_row0,
+                             int dst_row_step, void* stream) {
+    if (n % Q40T_TILE_K != 0) { dl_set_error("dl_q40_repack: n=%d not a multiple of 128", n); return -1; }
+    if (dst_row0 + (rows - 1) * dst_row_step >= d_pad) { dl_set_error("dl_q40_repack: rows exceed destination"); return -1; }
+    const int nb = n / 32;
+    const long long total = (long long)rows * nb;
+    const int threads = 256;
+    const unsigned blocks = (unsigned)((total + threads - 1) / threads);
+    q40_repack_kernel<<<blocks, threads, 0, (cudaStream_t)stream>>>(raw, rows, nb, q40t, n / Q40T_TILE_K, dst_row0,
+                                                                    dst_row_step);
+    CHECK_LAUNCH("dl_q40_repack");
+    return 0;
+}
+
+__global__ void q40t_dequant_kernel(const uint8_t* __restrict__ w, int d, int n, float* __restrict__ out) {
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;   // one thread per (row, block)
+    const int nb = n / 32;
+    if (idx >= (long long)d * nb) return;
+    const int r = (int)(idx / nb), b = (int)(idx % nb);
+    const int rt = r >> 7, rr = r & 127, kt = b >> 2, kb = b & 3;
+    const uint8_t* tile = w + ((size_t)rt * (n / Q40T_TILE_K) + kt) * Q40T_TILE_BYTES;
+    const uint8_t* q = tile + rr * 64 + (((kb + (rr >> 1)) & 3) << 4);
+    const float dw = __half2float(*reinterpret_cast<const __half*>(tile + Q40T_SCALE_OFF + rr * 8 + kb * 2));
+    float* o = out + (size_t)r * n + (size_t)b * 32;
+    for (int j = 0; j < 16; j++) {
+        o[j] = (float)((int)(q[j] & 0xF) - 8) * dw;
+        o[j + 16] = (float)((int)(q[j] >> 4) - 8) * dw;
+    }
+}
+
+extern "C" int dl_q40t_dequant(const uint8_t* q40t, int d, int n, float* out, void* stream) {
+    const long long total = (long long)d * (n / 32);
+    q40t_dequant_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(q40t, d, n, out);
+    CHECK_LAUNCH("dl_q40t_dequant");
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// embedding gather (+ per-forward step counter used as the epoch base of all peer flags)
+// ------------------------------------------------------------------------------------------------
+__global__ void embedding_kernel(const float* __restrict__ table, const int* __restrict__ tokens, float* __restrict__ x,
+                                 int dim, uint32_t* step_counter) {
+    pdl_launch_dependents();
+    pdl_wait();
+    const int m = blockIdx.x;
+    const float4* src = reinterpret_cast<const float4*>(table + (size_t)tokens[m] * dim);
+    float4* dst = reinterpret_cast<float4*>(x + (size_t)m * dim);
+    for (int i = threadIdx.x; i < dim / 4; i += blockDim.x) dst[i] = src[i];
+    if (step_counter != nullptr && m == 0 && threadIdx.x == 0) *step_counter = *step_counter + 1u;
+}
+
+extern "C" int dl_embedding(const float* table, const int* tokens, float* x, int M, int dim, uint32_t* step_counter,
+                            void* stream) {
+    embedding_kernel<<<M, 256, 0, (cudaStream_t)stream>>>(table, tokens, x, dim, step_counter);
+    CHECK_LAUNCH("dl_embedding");
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// reduce (merge-add of the peers' partial sums) + residual + RMSNorm + Q80 cast
+// one CTA per activation row; dim <= 16384
+// ------------------------------------------------------------------------------------------------
+#define RNQ_THREADS 512
+#define RNQ_MAX_PER_THREAD 32     // dim <= 512*32 = 16384
+
+struct RnqArgs {
+    const float* x_in;
+    float* x_out;
+    const float* partials;      // [n_src][mcap_p][dim] with src_stride elements between sources
+    int n_src;
+    long long src_stride;
+    const uint32_t* flags;
+    const uint32_t* step_counter;
+    uint32_t flag_mul, flag_add;
+    const float* norm_w;
+    float eps;
+    int dim, M, mcap;
+    uint8_t* xq_out;
+    uint8_t* xh_out;
+    float* y_out;
+};
+
+__global__ void __launch_bounds__(RNQ_THREADS) reduce_norm_quant_kernel(const __grid_constant__ RnqArgs a) {
+    __shared__ float s_part[RNQ_THREADS / 32];
+    __shared__ float s_inv;
+    pdl_launch_dependents();
+    pdl_wait();
+    const int m = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (a.flags != nullptr && a.n_src > 0) {
+        if (tid < a.n_src) {
+            const uint32_t epoch = ld_volatile_u32(a.step_counter) * a.flag_mul + a.flag_add;
+            wait_flag_ge(a.flags + tid, epoch);
+        }
+        __syncthreads();
+    }
+    // 32-element blocks are dealt round-robin to warps: block b -> warp b % nwarps (lane = element)
+    const int nblocks = a.dim / 32;
+    constexpr int nwarps = RNQ_THREADS / 32;
+    float vals[RNQ_MAX_PER_THREAD];
+    float ss = 0.0f;
+#pragma unroll
+    for (int c = 0; c < RNQ_MAX_PER_THREAD; c++) {
+        const int b = warp + c * nwarps;
+        vals[c] = 0.0f;
+        if (b < nblocks) {
+            const int i = b * 32 + lane;
+            float v = (a.x_in != nullptr) ? a.x_in[(size_t)m * a.dim + i] : 0.0f;
+            for (int s = 0; s < a.n_src; s++) v += a.partials[(size_t)s * a.src_stride + (size_t)m * a.dim + i];
+            if (a.x_out != nullptr) a.x_out[(size_t)m * a.dim + i] = v;
+            vals[c] = v;
+            ss += v * v;
+        }
+    }
+    ss = warp_sum(ss);
+    if (lane == 0) s_part[warp] = ss;
+    __syncthreads();
+    if (warp == 0) {
+        float t = (lane < nwarps) ? s_part[lane] : 0.0f;
+        t = warp_sum(t);
+        if (lane == 0) s_inv = 1.0f / sqrtf(t / (float)a.dim + a.eps);
+    }
+    __syncthreads();
+    const float inv = s_inv;
+#pragma unroll
+    for (int c = 0; c < RNQ_MAX_PER_THREAD; c++) {
+        const int b = warp + c * nwarps;
+        if (b < nblocks) {
+            const int i = b * 32 + lane;
+            float y = vals[c];
+            if (a.norm_w != nullptr) y = a.norm_w[i] * (inv * y);
+            if (a.y_out != nullptr) a.y_out[(size_t)m * a.dim + i] = y;
+            if (a.xq_out != nullptr || a.xh_out != nullptr) q80_block_store(y, lane, m, b, a.mcap, a.xq_out, a.xh_out);
+        }
+    }
+}
+
+extern "C" int dl_reduce_norm_quant(const float* x_in, float* x_out, const float* partials, int n_src, int src_stride,
+                                    const uint32_t* flags, const uint32_t* step_counter, uint32_t flag_mul,
+                                    uint32_t flag_add, const float* norm_w, float eps, int dim, int M, int mcap,
+                                    uint8_t* xq_out, uint8_t* xh_out, float* y_out, int pdl, void* stream) {
+    if (dim % 32 != 0 || dim > RNQ_THREADS * RNQ_MAX_PER_THREAD) { dl_set_error("dl_reduce_norm_quant: bad dim %d", dim); return -1; }
+    if (n_src > DL_MAX_PEERS) { dl_set_error("dl_reduce_norm_quant: n_src > 8"); return -1; }
+    RnqArgs a;
+    a.x_in = x_in; a.x_out = x_out; a.partials = partials; a.n_src = n_src; a.src_stride = src_stride;
+    a.flags = flags; a.step_counter = step_counter; a.flag_mul = flag_mul; a.flag_add = flag_add;
+    a.norm_w = norm_w; a.eps = eps; a.dim = dim; a.M = M; a.mcap = mcap;
+    a.xq_out = xq_out; a.xh_out = xh_out; a.y_out = y_out;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(M);
+    cfg.blockDim = dim3(RNQ_THREADS);
+    cfg.stream = (cudaStream_t)stream;
+    cudaLaunchAttribute attr[1];
+    if (pdl) {
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+    }
+    cudaError_t e = cudaLaunchKernelEx(&cfg, reduce_norm_quant_kernel, a);
+    if (e != cudaSuccess) { dl_set_error("dl_reduce_norm_quant: %s", cudaGetErrorString(e)); return -(int)e; }
+    return 0;
+}
+
+extern "C" int dl_quant_q80(const float* x, int M, int K, int mcap, uint8_t* xq_out, uint8_t* xh_out, void* stream) {
+    // the same kernel with no residual/partials/norm: y = x
+    return dl_reduce_norm_quant(x, nullptr, nullptr, 0, 0, nullptr, nullptr, 0, 0, nullptr, 0.0f, K, M, mcap, xq_out,
+                                xh_out, nullptr, 0, stream);
+}
+
+// ------------------------------------------------------------------------------------------------
+// argmax (greedy sampling on device)
+// ------------------------------------------------------------------------------------------------
+__global__ void argmax_kernel(const float* __restrict__ logits, int vocab, int ld, int* __restrict__ out) {
+    __shared__ float s_v[32];
+    __shared__ int s_i[32];
+    pdl_launch_dependents();
+    pdl_wait();
+    const int m = blockIdx.x;
+    const float* row = logits + (size_t)m * ld;
+    float best = -INFINITY;
+    int bi = 0x7fffffff;
+    for (int i = threadIdx.x; i < vocab; i += blockDim.x) {
+        float v = row[i];
+        if (v > best || (v == best && i < bi)) { best = v; bi = i; }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        float ov = __shfl_xor_sync(0xffffffffu, best, o);
+        int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+        if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
+    }
+    if ((threadIdx.x & 31) == 0) { s_v[threadIdx.x >> 5] = best; s_i[threadIdx.x >> 5] = bi; }
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        const int nw = blockDim.x >> 5;
+        best = (threadIdx.x < nw) ? s_v[threadIdx.x] : -INFINITY;
+        bi = (threadIdx.x < nw) ? s_i[threadIdx.x] : 0x7fffffff;
+        for (int o = 16; o > 0; o >>= 1) {
+            float ov = __shfl_xor_sync(0xffffffffu, best, o);
+            int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
+        }
+        if (threadIdx.x == 0) out[m] = bi;
+    }
+}
+
+extern "C" int dl_argmax(const float* logits, int M, int vocab, int ld, int* tokens_out, void* stream) {
+    argmax_kernel<<<M, 1024, 0, (cudaStream_t)stream>>>(logits, vocab, ld, tokens_out);
+    CHECK_LAUNCH("dl_argmax");
+    return 0;
+}

@@ -1,0 +1,122 @@
+/* b200-dllama C ABI: every CUDA entry point of libdllama_b200_cuda.so.
+ *
+ * All pointers are device pointers unless stated otherwise; `stream` is a cudaStream_t.  Functions
+ * return 0 on success or a negative/CUDA error code; dl_last_error() gives the message.
+ * Citations name the reference component each entry point replaces (paths relative to the
+ * reference tree).
+ */
+#ifndef DLLAMA_B200_H
+#define DLLAMA_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DL_MAX_PEERS 8
+
+/* ---- epilogue selector for the Q40 GEMV / GEMM kernels ---------------------------------- */
+enum {
+    DL_EPI_STORE = 0,     /* f32 store (optionally Q80 round-trip) to 1..8 (peer) buffers + flags  */
+    DL_EPI_QKV_ROPE = 1,  /* RoPE on q,k rows; q -> buffer; k,v -> paged KV cache                   */
+    DL_EPI_SILU_MUL = 2,  /* rows interleaved (gate,up): act(g)*u -> Q80 activation slabs           */
+};
+
+typedef struct {
+    int kind;
+    /* DL_EPI_STORE: dst[p][dst_off + m*ld + row] for p < n_dst  (reference: OP_CAST y->ZQ slice +
+     * SYNC_NODE_SLICES, src/llm.cpp:308-314,381-387; logits gather :426-432) */
+    float* dst[DL_MAX_PEERS];
+    int n_dst;
+    int ld;
+    long long dst_off;
+    int q80_roundtrip;
+    uint32_t* flag[DL_MAX_PEERS];     /* flag word to release on each destination (NULL: none) */
+    const uint32_t* step_counter;     /* epoch = *step_counter * flag_mul + flag_add           */
+    uint32_t flag_mul, flag_add;
+    uint32_t* cta_counter;            /* zero-initialised, self-resetting completion counter   */
+    /* DL_EPI_QKV_ROPE (reference: OP_ROPE_LLAMA + OP_SHIFT, src/llm.cpp:259-286) */
+    float* q_out;                     /* [M][q_dim] */
+    int q_dim, kv_dim, head_size;
+    const float* rope_freqs;          /* [head_size/2] */
+    const int* pos;                   /* [M] */
+    const int* slot;                  /* [M] */
+    const int* block_table;           /* [n_slots][max_pages] */
+    int max_pages, page_size, n_kv_heads;
+    void* k_cache;                    /* [n_pages][n_kv_heads][page_size][head_size] */
+    void* v_cache;
+    int kv_f32;                       /* 1: f32 cache, 0: fp16 cache */
+    /* DL_EPI_SILU_MUL (reference: OP_SILU + OP_MUL + OP_CAST d->dq, src/llm.cpp:355-374) */
+    uint8_t* xq_out;                  /* XQ slabs of the hidden activation (may be NULL) */
+    uint8_t* xh_out;                  /* XH slabs (may be NULL) */
+    int out_mcap;                     /* row capacity of the XQ/XH slabs */
+    int act_gelu;                     /* 0 = SiLU, 1 = tanh-GELU */
+} DlEpilogue;
+
+const char* dl_last_error(void);
+int dl_device_sm_count(void);
+
+/* ---- weight preparation ------------------------------------------------------------------ */
+/* bytes of a Q40T image of a [d][n] matrix (d padded to 128) */
+long long dl_q40t_bytes(int d, int n);
+/* scatter `rows` raw Q40 rows (file layout, n/32 blocks of 18 B each) into a Q40T image at
+ * destination rows dst_row0 + i*dst_row_step.  (reference: splitRowMatmulWeight /
+ * splitColMatmulWeight + NnCpuDevice weight copy, src/nn/nn-core.cpp:270-303) */
+int dl_q40_repack(const uint8_t* raw, int rows, int n, uint8_t* q40t, int d_pad, int dst_row0,
+                  int dst_row_step, void* stream);
+/* Q40T -> f32 [d][n] (tests, cuBLAS baseline path) */
+int dl_q40t_dequant(const uint8_t* q40t, int d, int n, float* out, void* stream);
+
+/* ---- activation producers ---------------------------------------------------------------- */
+/* x_out = x_in + sum_src partial[src] ; y = rmsnorm(x_out)*w ; y -> Q80 -> XQ and/or XH slabs.
+ * Waits (acquire.sys) on flags[src] >= epoch before reading partials when flags != NULL.
+ * (reference: OP_MERGE_ADD + OP_INV_RMS + OP_RMS_NORM + OP_CAST, src/llm.cpp:204-239,317-342) */
+int dl_reduce_norm_quant(const float* x_in, float* x_out, const float* partials, int n_src, int src_stride,
+                         const uint32_t* flags, const uint32_t* step_counter, uint32_t flag_mul,
+                         uint32_t flag_add, const float* norm_w, float eps, int dim, int M, int mcap,
+                         uint8_t* xq_out, uint8_t* xh_out, float* y_out, int pdl, void* stream);
+/* plain f32 [M][K] -> XQ / XH (no norm); (reference: OP_CAST F32->Q80, nn-cpu-ops.cpp:1221-1235) */
+int dl_quant_q80(const float* x, int M, int K, int mcap, uint8_t* xq_out, uint8_t* xh_out, void* stream);
+/* embedding gather: x[m][:] = table[token[m]][:]  (reference: OP_EMBEDDING, nn-cpu-ops.cpp:880-892) */
+int dl_embedding(const float* table, const int* tokens, float* x, int M, int dim, uint32_t* step_counter,
+                 void* stream);
+
+/* ---- Q40 x Q80 matmuls ------------------------------------------------------------------- */
+/* dp4a GEMV, M <= 8 rows: bulk-copy fed, cluster split-K (reference: matmul_Q80_Q40_F32,
+ * src/nn/nn-cpu-ops.cpp:222-440) */
+int dl_gemv_q40(const uint8_t* w_q40t, int d, int n, const uint8_t* xq, int mcap, int M, int row_split,
+                int k_split, const DlEpilogue* epi /*host*/, int pdl, void* stream);
+/* tcgen05 GEMM, M up to 256 per tile: Q40 dequantised to fp16 in the smem pipeline, UMMA with
+ * TMEM accumulators (reference: llamafile_sgemm Q40xQ80, src/nn/llamafile/sgemm.cpp:593-783) */
+int dl_gemm_q40_tc(const uint8_t* w_q40t, int d, int n, const uint8_t* xh, int ncap, int M, int k_split,
+                   const DlEpilogue* epi /*host*/, int pdl, void* stream);
+
+/* ---- attention ---------------------------------------------------------------------------- */
+/* per-row paged GQA attention over positions 0..pos[m] (decode rows and prefill-chunk rows alike);
+ * output Q80-quantised into XQ/XH slabs for the wo matmul and/or f32.
+ * scratch: >= dl_attention_scratch_bytes(); (reference: OP_MULTIHEAD_ATT, nn-cpu-ops.cpp:749-784,1135-1161) */
+long long dl_attention_scratch_bytes(int M, int n_heads, int head_size, int max_splits);
+int dl_attention(const float* q, int M, int n_heads, int n_kv_heads, int head_size, const void* k_cache,
+                 const void* v_cache, int kv_f32, const int* pos, const int* slot, const int* block_table,
+                 int max_pages, int page_size, int n_splits, void* scratch, uint8_t* xq_out, uint8_t* xh_out,
+                 int out_mcap, float* y_out, int pdl, void* stream);
+
+/* ---- sampling helpers --------------------------------------------------------------------- */
+/* argmax over logits[m][0..vocab) -> tokens[m]  (reference: Sampler::sample temperature==0,
+ * src/tokenizer.cpp:472-502) */
+int dl_argmax(const float* logits, int M, int vocab, int ld, int* tokens_out, void* stream);
+
+/* ---- peer memory (symmetric buffers over NVLink) ------------------------------------------ */
+int dl_ipc_alloc(void** dev_ptr, long long bytes, uint8_t* handle_out /*64 B host*/);
+int dl_ipc_open(const uint8_t* handle /*64 B host*/, void** dev_ptr);
+int dl_ipc_close(void* dev_ptr);
+int dl_ipc_free(void* dev_ptr);
+/* all ranks: flag barrier over peer memory (one CTA) */
+int dl_peer_barrier(uint32_t* const* flags_on_peers /*host array*/, uint32_t* my_flags, int rank, int world,
+                    uint32_t epoch, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
