@@ -230,18 +230,39 @@ extern "C" int dl_quant_q80(const float* x, int M, int K, int mcap, uint8_t* xq_
 }
 
 // ------------------------------------------------------------------------------------------------
-// argmax (greedy sampling on device)
+// greedy sampling on device (+ optional wait for the peers' logits slices, + device-resident
+// decode loop support: feed the token back, advance the position, record a history)
 // ------------------------------------------------------------------------------------------------
-__global__ void argmax_kernel(const float* __restrict__ logits, int vocab, int ld, int* __restrict__ out) {
+struct ArgmaxArgs {
+    const float* logits;
+    int vocab, ld;
+    int* tokens_out;
+    const uint32_t* flags;
+    int n_flags;
+    const uint32_t* step_counter;
+    uint32_t flag_mul, flag_add;
+    int* pos_inc;
+    int* history;
+    int history_cap;
+};
+
+__global__ void argmax_kernel(const __grid_constant__ ArgmaxArgs a) {
     __shared__ float s_v[32];
     __shared__ int s_i[32];
     pdl_launch_dependents();
     pdl_wait();
+    if (a.flags != nullptr) {
+        if ((int)threadIdx.x < a.n_flags) {
+            const uint32_t epoch = ld_volatile_u32(a.step_counter) * a.flag_mul + a.flag_add;
+            wait_flag_ge(a.flags + threadIdx.x, epoch);
+        }
+        __syncthreads();
+    }
     const int m = blockIdx.x;
-    const float* row = logits + (size_t)m * ld;
+    const float* row = a.logits + (size_t)m * a.ld;
     float best = -INFINITY;
     int bi = 0x7fffffff;
-    for (int i = threadIdx.x; i < vocab; i += blockDim.x) {
+    for (int i = threadIdx.x; i < a.vocab; i += blockDim.x) {
         float v = row[i];
         if (v > best || (v == best && i < bi)) { best = v; bi = i; }
     }
@@ -254,19 +275,62 @@ __global__ void argmax_kernel(const float* __restrict__ logits, int vocab, int l
     __syncthreads();
     if (threadIdx.x < 32) {
         const int nw = blockDim.x >> 5;
-        best = (threadIdx.x < nw) ? s_v[threadIdx.x] : -INFINITY;
-        bi = (threadIdx.x < nw) ? s_i[threadIdx.x] : 0x7fffffff;
+        best = ((int)threadIdx.x < nw) ? s_v[threadIdx.x] : -INFINITY;
+        bi = ((int)threadIdx.x < nw) ? s_i[threadIdx.x] : 0x7fffffff;
         for (int o = 16; o > 0; o >>= 1) {
             float ov = __shfl_xor_sync(0xffffffffu, best, o);
             int oi = __shfl_xor_sync(0xffffffffu, bi, o);
             if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
         }
-        if (threadIdx.x == 0) out[m] = bi;
+        if (threadIdx.x == 0) {
+            if (bi == 0x7fffffff) bi = 0;      // all-NaN row: stay in range
+            a.tokens_out[m] = bi;
+            if (a.pos_inc != nullptr) a.pos_inc[m] += 1;
+            if (a.history != nullptr) {
+                const uint32_t c = ld_volatile_u32(a.step_counter);
+                a.history[(size_t)((c - 1u) % (uint32_t)a.history_cap) * gridDim.x + m] = bi;
+            }
+        }
     }
 }
 
-extern "C" int dl_argmax(const float* logits, int M, int vocab, int ld, int* tokens_out, void* stream) {
-    argmax_kernel<<<M, 1024, 0, (cudaStream_t)stream>>>(logits, vocab, ld, tokens_out);
-    CHECK_LAUNCH("dl_argmax");
+extern "C" int dl_argmax(const float* logits, int M, int vocab, int ld, int* tokens_out, const uint32_t* flags,
+                         int n_flags, const uint32_t* step_counter, uint32_t flag_mul, uint32_t flag_add, int* pos_inc,
+                         int* history, int history_cap, int pdl, void* stream) {
+    ArgmaxArgs a;
+    a.logits = logits; a.vocab = vocab; a.ld = ld; a.tokens_out = tokens_out;
+    a.flags = flags; a.n_flags = n_flags; a.step_counter = step_counter; a.flag_mul = flag_mul; a.flag_add = flag_add;
+    a.pos_inc = pos_inc; a.history = history; a.history_cap = history_cap;
+    if (history != nullptr && step_counter == nullptr) { dl_set_error("dl_argmax: history needs step_counter"); return -1; }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(M);
+    cfg.blockDim = dim3(1024);
+    cfg.stream = (cudaStream_t)stream;
+    cudaLaunchAttribute attr[1];
+    if (pdl) {
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+    }
+    cudaError_t e = cudaLaunchKernelEx(&cfg, argmax_kernel, a);
+    if (e != cudaSuccess) { dl_set_error("dl_argmax: %s", cudaGetErrorString(e)); return -(int)e; }
+    return 0;
+}
+
+// wait until flags[i] >= epoch for i < n (orders later stream work after the peers' pushes)
+__global__ void wait_flags_kernel(const uint32_t* flags, int n, const uint32_t* step_counter, uint32_t mul, uint32_t add) {
+    pdl_launch_dependents();
+    pdl_wait();
+    if ((int)threadIdx.x < n) {
+        const uint32_t epoch = ld_volatile_u32(step_counter) * mul + add;
+        wait_flag_ge(flags + threadIdx.x, epoch);
+    }
+}
+
+extern "C" int dl_wait_flags(const uint32_t* flags, int n, const uint32_t* step_counter, uint32_t flag_mul,
+                             uint32_t flag_add, void* stream) {
+    wait_flags_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(flags, n, step_counter, flag_mul, flag_add);
+    CHECK_LAUNCH("dl_wait_flags");
     return 0;
 }

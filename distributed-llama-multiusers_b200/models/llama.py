@@ -1,0 +1,447 @@
+"""GPU inference engine: Llama forward on sm_100a kernels, tensor-parallel over peer memory.
+
+This replaces the reference's graph builder + executor + device (buildLlmNet, src/llm.cpp:126-438;
+NnExecutor::forward, src/nn/nn-executor.cpp:57-192; NnCpuDevice, src/nn/nn-cpu.cpp) with a fixed
+sequence of five fused kernels per layer, captured once per batch shape into a CUDA graph:
+
+    K1 reduce_norm_quant   merge-add of the peers' partial sums + residual + RMSNorm + Q80 cast
+    K2 qkv matmul          merged q|k|v weight; epilogue: RoPE + paged KV-cache write
+    K3 attention           paged GQA flash-decode; epilogue: Q80 cast
+    K4 wo matmul           epilogue: Q80-cast partial sum pushed to every peer GPU + release flags
+    K5 (K1 again for ffn)  ... w1|w3 matmul (epilogue SiLU*mul + Q80) ... w2 matmul (push)
+
+Tensor parallelism follows the reference's slicing (src/llm.cpp:131-142): q/k/v/w1/w3/wcls are
+split along the output dim, wo/w2 along the input dim, KV cache by kv head; the residual stream is
+replicated.  The socket all-gather + merge-add (SYNC_NODE_SLICES + OP_MERGE_ADD) becomes peer
+stores from the matmul epilogue plus a flag wait in the next kernel's prologue.
+"""
+from __future__ import annotations
+
+import math
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from ..formats.mfile import ModelFile, HIDDEN_ACT_SILU
+from ..ops import kernels as K
+from ..ops import quant
+from ..ops.lib import EPI_QKV_ROPE, EPI_SILU_MUL, EPI_STORE
+from ..parallel.symm import SymmetricBuffer, validate_tp
+from .oracle import rope_frequencies
+
+GEMV_MAX_M = 8
+PAGE = K.PAGE_SIZE
+
+
+def _round_up(x: int, m: int) -> int:
+    return (x + m - 1) // m * m
+
+
+class PageAllocator:
+    """Host-side KV page allocator: per-slot page lists over one shared pool (per-user KV caches;
+    the reference has a single cache shared by all users, src/llm.cpp:197-198)."""
+
+    def __init__(self, n_pages: int, n_slots: int, max_pages_per_seq: int):
+        self.free_pages = list(range(n_pages - 1, -1, -1))
+        self.free_slots = list(range(n_slots - 1, -1, -1))
+        self.max_pages = max_pages_per_seq
+        self.table = np.zeros((n_slots, max_pages_per_seq), dtype=np.int32)
+        self.n_used = np.zeros(n_slots, dtype=np.int32)
+        self.dirty = True
+
+    def alloc_slot(self) -> int:
+        if not self.free_slots:
+            raise RuntimeError("no free sequence slot")
+        return self.free_slots.pop()
+
+    def free_slot(self, slot: int):
+        for i in range(int(self.n_used[slot])):
+            self.free_pages.append(int(self.table[slot, i]))
+        self.n_used[slot] = 0
+        self.free_slots.append(slot)
+
+    def ensure(self, slot: int, n_tokens: int):
+        need = (n_tokens + PAGE - 1) // PAGE
+        if need > self.max_pages:
+            raise RuntimeError(f"sequence of {n_tokens} tokens exceeds max_seq_len")
+        while self.n_used[slot] < need:
+            if not self.free_pages:
+                raise RuntimeError("KV cache exhausted")
+            self.table[slot, self.n_used[slot]] = self.free_pages.pop()
+            self.n_used[slot] += 1
+            self.dirty = True
+
+
+class LlamaEngine:
+    def __init__(self, model_path: str, rank: int = 0, world: int = 1, group=None, max_rows: int = 32,
+                 n_slots: int = 4, max_seq_len: int = 2048, kv_dtype: torch.dtype = torch.float16,
+                 sync_q80: bool = True, use_pdl: bool = True, use_graphs: bool = True, n_pages: Optional[int] = None,
+                 device: Optional[torch.device] = None, verbose: bool = False):
+        self.mf = ModelFile(model_path, max_seq_len=max_seq_len)
+        h = self.h = self.mf.header
+        if h.weight_type != quant.Q40:
+            raise NotImplementedError("GPU engine: only Q40 weights (+Q80 activations) are wired up; "
+                                      "f32 models run through models.oracle")
+        validate_tp(world, h.n_kv_heads, h.dim, h.hidden_dim, h.n_heads, h.vocab_size)
+        self.rank, self.world, self.group = rank, world, group
+        self.device = device or torch.device("cuda", torch.cuda.current_device())
+        self.max_rows = max_rows
+        self.use_pdl, self.use_graphs = use_pdl, use_graphs
+        self.sync_q80 = sync_q80
+        self.seq_len = min(h.seq_len, max_seq_len)
+        self.n_sms = K.cuda_lib().dl_device_sm_count()
+        dev = self.device
+
+        # ---- per-rank geometry (reference: sliceRowMatmul / sliceColMatmul / sliceKvCache) -------
+        N = world
+        self.dim, self.hs = h.dim, h.head_size
+        self.n_heads_loc = h.n_heads // N
+        self.n_kv_loc = h.n_kv_heads // N
+        self.q_loc = self.n_heads_loc * self.hs
+        self.kv_loc = self.n_kv_loc * self.hs
+        self.hid_loc = h.hidden_dim // N
+        self.vocab_loc = h.vocab_size // N
+        self.qkv_d = self.q_loc + 2 * self.kv_loc
+
+        # ---- weights ---------------------------------------------------------------------------
+        self._load_weights(verbose)
+
+        # ---- activations -----------------------------------------------------------------------
+        R = max_rows
+        self.ncap = max(16, _round_up(R, 128) if R > 64 else (16 if R <= 16 else 32 if R <= 32 else 64))
+        self.desc = torch.zeros(3, R, dtype=torch.int32, device=dev)      # tokens | pos | slot
+        self.h_desc = torch.zeros(3, R, dtype=torch.int32).pin_memory()
+        self.tokens, self.pos, self.slot = self.desc[0], self.desc[1], self.desc[2]
+        self.x = [torch.zeros(R, h.dim, dtype=torch.float32, device=dev) for _ in range(2)]
+        self.q = torch.zeros(R, self.q_loc, dtype=torch.float32, device=dev)
+        self.xq_dim = K.alloc_xq(h.dim, GEMV_MAX_M, dev)
+        self.xq_att = K.alloc_xq(self.q_loc, GEMV_MAX_M, dev)
+        self.xq_hid = K.alloc_xq(self.hid_loc, GEMV_MAX_M, dev)
+        self.xh_dim = K.alloc_xh(h.dim, self.ncap, dev)
+        self.xh_att = K.alloc_xh(self.q_loc, self.ncap, dev)
+        self.xh_hid = K.alloc_xh(self.hid_loc, self.ncap, dev)
+        self.rope_freqs = rope_frequencies(h).to(dev)
+        self.out_tokens = torch.zeros(R, dtype=torch.int32, device=dev)
+        self.h_out_tokens = torch.zeros(R, dtype=torch.int32).pin_memory()
+        self.history_cap = 4096
+        self.history = torch.zeros(self.history_cap * R, dtype=torch.int32, device=dev)
+
+        # ---- symmetric exchange area: partial sums, logits, flags, counters ------------------------
+        part_bytes = N * R * h.dim * 4
+        logit_bytes = R * h.vocab_size * 4
+        self._off_att, self._off_ffn = 0, part_bytes
+        self._off_logits = 2 * part_bytes
+        self._off_flags = _round_up(self._off_logits + logit_bytes, 256)
+        total = self._off_flags + 4096
+        self.symm = SymmetricBuffer(total, rank, world, group)
+        sp = self.symm.ptrs
+        self.part_att = [p + self._off_att for p in sp]
+        self.part_ffn = [p + self._off_ffn for p in sp]
+        self.logits_ptrs = [p + self._off_logits for p in sp]
+        # flag words: [att: 8][ffn: 8][logits: 8][step counter][cta counters: 8]
+        fl = [p + self._off_flags for p in sp]
+        self.flags_att_local, self.flags_ffn_local, self.flags_log_local = fl[rank], fl[rank] + 32, fl[rank] + 64
+        self.flags_att_peer = [p + 4 * rank for p in fl]
+        self.flags_ffn_peer = [p + 32 + 4 * rank for p in fl]
+        self.flags_log_peer = [p + 64 + 4 * rank for p in fl]
+        self.step_counter = fl[rank] + 96
+        self.cta_counters = [fl[rank] + 128 + 4 * i for i in range(8)]
+        self.logits = self.symm.tensor(self._off_logits, (R, h.vocab_size), torch.float32)
+
+        # ---- KV cache ----------------------------------------------------------------------------
+        self.max_pages = (self.seq_len + PAGE - 1) // PAGE
+        self.n_slots = n_slots
+        self.n_pages = n_pages or n_slots * self.max_pages
+        self.pages = PageAllocator(self.n_pages, n_slots, self.max_pages)
+        self.block_table = torch.zeros(n_slots, self.max_pages, dtype=torch.int32, device=dev)
+        self.h_block_table = torch.zeros(n_slots, self.max_pages, dtype=torch.int32).pin_memory()
+        kv_shape = (self.n_pages, self.n_kv_loc, PAGE, self.hs)
+        self.k_cache = [torch.zeros(kv_shape, dtype=kv_dtype, device=dev) for _ in range(h.n_layers)]
+        self.v_cache = [torch.zeros(kv_shape, dtype=kv_dtype, device=dev) for _ in range(h.n_layers)]
+        self.max_splits = 32
+        self.att_scratch = torch.zeros(K.attention_scratch_bytes(R, self.n_heads_loc, self.hs, self.max_splits),
+                                       dtype=torch.uint8, device=dev)
+        self._graphs: Dict[Tuple, torch.cuda.CUDAGraph] = {}
+        self._graph_launches: Dict[Tuple, int] = {}
+        self._graph_stream = torch.cuda.Stream(device=dev)
+        torch.cuda.synchronize()
+
+    # ------------------------------------------------------------------------------------------------
+    def _load_weights(self, verbose: bool):
+        h, mf, dev, r, N = self.h, self.mf, self.device, self.rank, self.world
+        nb_dim = h.dim // 32
+
+        def up(arr: np.ndarray) -> torch.Tensor:
+            t = torch.empty(arr.size, dtype=torch.uint8)
+            t.numpy()[:] = arr.reshape(-1)
+            return t.to(dev, non_blocking=False)
+
+        def rows(name, l, row0, nrows):
+            return up(mf.raw_rows(name, l, row0, nrows))
+
+        def cols(name, l, col0, ncols):
+            e = mf.entry(name, l)
+            nb = e.cols // 32
+            v = mf.raw(name, l).reshape(e.rows, nb, 18)[:, col0 // 32:(col0 + ncols) // 32, :]
+            return up(np.ascontiguousarray(v))
+
+        def f32(name, l=-1):
+            return torch.from_numpy(mf.f32(name, l).reshape(-1).copy()).to(dev)
+
+        self.embedding = torch.empty(h.vocab_size, h.dim, dtype=torch.float32, device=dev)
+        e = mf.entry("embedding")
+        chunk = 16384
+        for r0 in range(0, h.vocab_size, chunk):
+            n = min(chunk, h.vocab_size - r0)
+            a = mf.data[e.offset + r0 * h.dim * 4: e.offset + (r0 + n) * h.dim * 4].view(np.float32)
+            self.embedding[r0:r0 + n] = torch.from_numpy(a.reshape(n, h.dim).copy()).to(dev)
+        self.layers = []
+        for l in range(h.n_layers):
+            L = {}
+            qkv = torch.zeros(K.q40t_bytes(self.qkv_d, h.dim), dtype=torch.uint8, device=dev)
+            dpad = _round_up(self.qkv_d, 128)
+            K.q40_repack(rows("wq", l, r * self.q_loc, self.q_loc), self.q_loc, h.dim, qkv, dpad, 0, 1)
+            K.q40_repack(rows("wk", l, r * self.kv_loc, self.kv_loc), self.kv_loc, h.dim, qkv, dpad, self.q_loc, 1)
+            K.q40_repack(rows("wv", l, r * self.kv_loc, self.kv_loc), self.kv_loc, h.dim, qkv, dpad,
+                         self.q_loc + self.kv_loc, 1)
+            L["qkv"] = qkv
+            wo = torch.zeros(K.q40t_bytes(h.dim, self.q_loc), dtype=torch.uint8, device=dev)
+            K.q40_repack(cols("wo", l, r * self.q_loc, self.q_loc), h.dim, self.q_loc, wo, _round_up(h.dim, 128))
+            L["wo"] = wo
+            w13 = torch.zeros(K.q40t_bytes(2 * self.hid_loc, h.dim), dtype=torch.uint8, device=dev)
+            dpad13 = _round_up(2 * self.hid_loc, 128)
+            K.q40_repack(rows("w1", l, r * self.hid_loc, self.hid_loc), self.hid_loc, h.dim, w13, dpad13, 0, 2)
+            K.q40_repack(rows("w3", l, r * self.hid_loc, self.hid_loc), self.hid_loc, h.dim, w13, dpad13, 1, 2)
+            L["w13"] = w13
+            w2 = torch.zeros(K.q40t_bytes(h.dim, self.hid_loc), dtype=torch.uint8, device=dev)
+            K.q40_repack(cols("w2", l, r * self.hid_loc, self.hid_loc), h.dim, self.hid_loc, w2, _round_up(h.dim, 128))
+            L["w2"] = w2
+            L["rms_att"], L["rms_ffn"] = f32("rms_att", l), f32("rms_ffn", l)
+            self.layers.append(L)
+            torch.cuda.synchronize()
+            if verbose and rank_zero(self):
+                print(f"🕒 layer {l + 1}/{h.n_layers} loaded", flush=True)
+        self.rms_final = f32("rms_final")
+        wcls = torch.zeros(K.q40t_bytes(self.vocab_loc, h.dim), dtype=torch.uint8, device=dev)
+        K.q40_repack(rows("wcls", -1, r * self.vocab_loc, self.vocab_loc), self.vocab_loc, h.dim, wcls,
+                     _round_up(self.vocab_loc, 128))
+        self.wcls = wcls
+        torch.cuda.synchronize()
+
+    def weight_bytes(self) -> int:
+        """Q40T bytes streamed per forward on this rank (roofline numerator)."""
+        n = sum(t.numel() for L in self.layers for k, t in L.items() if t.dtype == torch.uint8)
+        return n + self.wcls.numel()
+
+    # ------------------------------------------------------------------------------------------------
+    # slots / pages
+    # ------------------------------------------------------------------------------------------------
+    def alloc_slot(self) -> int:
+        return self.pages.alloc_slot()
+
+    def free_slot(self, slot: int):
+        self.pages.free_slot(slot)
+
+    def ensure_capacity(self, slot: int, n_tokens: int):
+        self.pages.ensure(slot, n_tokens)
+
+    def _sync_block_table(self):
+        if self.pages.dirty:
+            self.h_block_table.numpy()[:] = self.pages.table
+            self.block_table.copy_(self.h_block_table, non_blocking=True)
+            self.pages.dirty = False
+
+    # ------------------------------------------------------------------------------------------------
+    # the forward pass (launch sequence)
+    # ------------------------------------------------------------------------------------------------
+    def _matmul(self, w, d, n, M, xq, xh, epi, kind):
+        if M <= GEMV_MAX_M:
+            R, S = K.choose_splits(d, n, kind, self.n_sms, M)
+            K.gemv_q40(w, d, n, xq, GEMV_MAX_M, M, epi, R, S, pdl=self.use_pdl)
+        else:
+            row_tiles = (d + 127) // 128
+            S = 1
+            if M <= 32:
+                while row_tiles * S < self.n_sms and S < 8 and S * 2 <= n // 128:
+                    S *= 2
+            K.gemm_q40_tc(w, d, n, xh, self.ncap, M, epi, S, pdl=self.use_pdl)
+
+    def _launch_forward(self, M: int, row0: int, greedy: bool, device_loop: bool):
+        """Enqueue one forward over rows 0..M-1 of the descriptor; logits for rows row0..M-1."""
+        h, N, pdl = self.h, self.world, self.use_pdl
+        gemv = M <= GEMV_MAX_M
+        xq = lambda t: t if gemv else None
+        xh = lambda t: None if gemv else t
+        mcap = GEMV_MAX_M if gemv else self.ncap
+        L = h.n_layers
+        R = self.max_rows
+        src_stride = R * h.dim
+        multi = N > 1
+        sc = self.step_counter
+        K.embedding(self.embedding, self.tokens, self.x[0], M, h.dim, _IntPtr(sc))
+        cur = 0
+        n_splits = self._attention_splits(M)
+        for l, W in enumerate(self.layers):
+            # --- attention block ---
+            if l == 0:
+                K.reduce_norm_quant(self.x[0], None, None, 0, 0, None, None, 0, 0, W["rms_att"], h.norm_epsilon,
+                                    h.dim, M, mcap, xq(self.xq_dim), xh(self.xh_dim), pdl=pdl)
+            else:
+                K.reduce_norm_quant(self.x[cur], self.x[cur ^ 1], self.part_ffn[self.rank], N, src_stride,
+                                    self.flags_ffn_local if multi else None, sc, L, l, W["rms_att"], h.norm_epsilon,
+                                    h.dim, M, mcap, xq(self.xq_dim), xh(self.xh_dim), pdl=pdl)
+                cur ^= 1
+            epi = K.epi_qkv_rope(self.q, self.q_loc, self.kv_loc, self.hs, self.rope_freqs, self.pos, self.slot,
+                                 self.block_table, self.max_pages, self.n_kv_loc, self.k_cache[l], self.v_cache[l])
+            self._matmul(W["qkv"], self.qkv_d, h.dim, M, self.xq_dim, self.xh_dim, epi, EPI_QKV_ROPE)
+            K.attention(self.q, M, self.n_heads_loc, self.n_kv_loc, self.hs, self.k_cache[l], self.v_cache[l], self.pos,
+                        self.slot, self.block_table, self.max_pages, n_splits, self.att_scratch, xq(self.xq_att),
+                        xh(self.xh_att), mcap, pdl=pdl)
+            epi = K.epi_store(self.part_att, h.dim, self.rank * src_stride, self.sync_q80,
+                              self.flags_att_peer if multi else None, sc, L, l + 1, self.cta_counters[0])
+            self._matmul(W["wo"], h.dim, self.q_loc, M, self.xq_att, self.xh_att, epi, EPI_STORE)
+            # --- feed-forward block ---
+            K.reduce_norm_quant(self.x[cur], self.x[cur ^ 1], self.part_att[self.rank], N, src_stride,
+                                self.flags_att_local if multi else None, sc, L, l + 1, W["rms_ffn"], h.norm_epsilon,
+                                h.dim, M, mcap, xq(self.xq_dim), xh(self.xh_dim), pdl=pdl)
+            cur ^= 1
+            epi = K.epi_silu_mul(xq(self.xq_hid), xh(self.xh_hid), mcap, gelu=(h.hidden_act != HIDDEN_ACT_SILU))
+            self._matmul(W["w13"], 2 * self.hid_loc, h.dim, M, self.xq_dim, self.xh_dim, epi, EPI_SILU_MUL)
+            epi = K.epi_store(self.part_ffn, h.dim, self.rank * src_stride, self.sync_q80,
+                              self.flags_ffn_peer if multi else None, sc, L, l + 1, self.cta_counters[1])
+            self._matmul(W["w2"], h.dim, self.hid_loc, M, self.xq_hid, self.xh_hid, epi, EPI_STORE)
+        # --- final norm + logits for rows row0.. ---
+        Ml = M - row0
+        gemv_l = Ml <= GEMV_MAX_M
+        mcap_l = GEMV_MAX_M if gemv_l else self.ncap
+        off = row0 * h.dim * 4
+        K.reduce_norm_quant(_Off(self.x[cur], off), _Off(self.x[cur ^ 1], off), self.part_ffn[self.rank] + off, N,
+                            src_stride, self.flags_ffn_local if multi else None, sc, L, L, self.rms_final,
+                            h.norm_epsilon, h.dim, Ml, mcap_l, self.xq_dim if gemv_l else None,
+                            None if gemv_l else self.xh_dim, pdl=pdl)
+        epi = K.epi_store(self.logits_ptrs, h.vocab_size, self.rank * self.vocab_loc, False,
+                          self.flags_log_peer if multi else None, sc, 1, 0, self.cta_counters[2])
+        self._matmul(self.wcls, self.vocab_loc, h.dim, Ml, self.xq_dim, self.xh_dim, epi, EPI_STORE)
+        if greedy:
+            K.argmax(self.logits, Ml, h.vocab_size, h.vocab_size,
+                     self.tokens if device_loop else self.out_tokens,
+                     self.flags_log_local if multi else None, N, sc, 1, 0,
+                     pos_inc=self.pos if device_loop else None,
+                     history=self.history if device_loop else None, history_cap=self.history_cap, pdl=pdl)
+        elif multi:
+            K.wait_flags(self.flags_log_local, N, sc, 1, 0)
+
+    def _attention_splits(self, M: int) -> int:
+        ctas = M * self.n_kv_loc
+        want = max(1, self.n_sms // max(1, ctas))
+        max_by_ctx = max(1, self.max_pages // 4)           # at least 4 pages (128 tokens) per split
+        return int(min(want, max_by_ctx, self.max_splits))
+
+    def _run(self, M: int, row0: int, greedy: bool, device_loop: bool = False):
+        key = (M, row0, greedy, device_loop)
+        if not self.use_graphs:
+            self._launch_forward(M, row0, greedy, device_loop)
+            return
+        g = self._graphs.get(key)
+        if g is None:
+            # warm up once eagerly (sets func attributes, loads modules), then capture
+            self._launch_forward(M, row0, greedy and not device_loop, False)
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            n0 = K.lib.launch_count
+            with torch.cuda.graph(g, stream=self._graph_stream):
+                self._launch_forward(M, row0, greedy, device_loop)
+            self._graph_launches[key] = K.lib.launch_count - n0
+            K.lib.launch_count = n0          # capture enqueued nothing
+            self._graphs[key] = g
+        g.replay()
+        K.lib.count_launch(self._graph_launches[key])
+
+    # ------------------------------------------------------------------------------------------------
+    # public API
+    # ------------------------------------------------------------------------------------------------
+    def set_batch(self, tokens: Sequence[int], positions: Sequence[int], slots: Sequence[int]):
+        """Stage the batch descriptor: pinned host -> device (the reference's control packet +
+        token/position pipes, src/app.cpp:169-209)."""
+        M = len(tokens)
+        assert 1 <= M <= self.max_rows
+        hd = self.h_desc.numpy()
+        hd[0, :M] = tokens
+        hd[1, :M] = positions
+        hd[2, :M] = slots
+        for s, p in zip(slots, positions):
+            self.pages.ensure(int(s), int(p) + 1)
+        self._sync_block_table()
+        self.desc.copy_(self.h_desc, non_blocking=True)
+        return M
+
+    def forward(self, tokens, positions, slots, logits_from: int = 0, greedy: bool = False) -> torch.Tensor:
+        """One forward over a batch of rows (any mix of decode rows and prefill-chunk rows; rows of
+        the same sequence must be in increasing position order).  Returns the device logits view
+        [M - logits_from][vocab] (valid until the next forward)."""
+        M = self.set_batch(tokens, positions, slots)
+        self._run(M, logits_from, greedy)
+        return self.logits[:M - logits_from]
+
+    def prefill(self, slot: int, tokens: Sequence[int], start_pos: int = 0, chunk: Optional[int] = None):
+        """Evaluate a prompt in chunks of <= max_rows rows; returns logits of the last token."""
+        chunk = chunk or self.max_rows
+        out = None
+        for i in range(0, len(tokens), chunk):
+            part = list(tokens[i:i + chunk])
+            pos = list(range(start_pos + i, start_pos + i + len(part)))
+            out = self.forward(part, pos, [slot] * len(part), logits_from=len(part) - 1)
+        return out
+
+    def decode_greedy_host(self, tokens: List[int], positions: List[int], slots: List[int]) -> List[int]:
+        """One greedy decode step end to end: H2D descriptor, forward, device argmax, D2H tokens."""
+        M = self.set_batch(tokens, positions, slots)
+        self._run(M, 0, True)
+        self.h_out_tokens.copy_(self.out_tokens, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return self.h_out_tokens[:M].tolist()
+
+    def decode_greedy_device(self, n_steps: int, M: int):
+        """Device-resident greedy loop: each step's argmax feeds the next step's embedding and
+        advances the positions without a host round trip.  Requires set_batch() first and enough
+        KV pages for n_steps more tokens (ensure_capacity)."""
+        for _ in range(n_steps):
+            self._run(M, 0, True, device_loop=True)
+
+    def read_history(self, n_steps: int, M: int, first_step: int) -> np.ndarray:
+        """Tokens produced by the last device-loop steps: [n_steps][M]."""
+        raw = self.history.cpu().numpy()
+        out = np.zeros((n_steps, M), dtype=np.int32)
+        for i in range(n_steps):
+            idx = (first_step + i) % self.history_cap
+            out[i] = raw[idx * M: idx * M + M]
+        return out
+
+    def current_step(self) -> int:
+        t = self.symm.tensor(self._off_flags + 96, (1,), torch.int32)
+        return int(t.item())
+
+    def close(self):
+        self._graphs.clear()
+        torch.cuda.synchronize()
+        self.symm.close()
+        self.mf.close()
+
+
+def rank_zero(engine) -> bool:
+    return engine.rank == 0
+
+
+class _IntPtr:
+    """Lets a raw device address travel through wrappers that call .data_ptr()."""
+
+    def __init__(self, ptr: int):
+        self._ptr = ptr
+
+    def data_ptr(self) -> int:
+        return self._ptr
+
+
+def _Off(t: torch.Tensor, byte_off: int) -> _IntPtr:
+    return _IntPtr(t.data_ptr() + byte_off)

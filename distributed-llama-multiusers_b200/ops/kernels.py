@@ -1,0 +1,201 @@
+"""Thin torch-tensor wrappers over the C ABI (one function per kernel launch).
+
+Every wrapper launches on ``torch.cuda.current_stream()`` so the calls compose with CUDA graph
+capture; nothing here allocates except where stated.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional, Sequence
+
+import torch
+
+from . import lib
+from .lib import DlEpilogue, EPI_QKV_ROPE, EPI_SILU_MUL, EPI_STORE, check, cuda_lib
+
+Q40T_TILE_BYTES = 9216
+XQ_ROW_BYTES = 160
+PAGE_SIZE = 32
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _p(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+# ---- buffer-size helpers ------------------------------------------------------------------------
+def q40t_bytes(d: int, n: int) -> int:
+    return int(cuda_lib().dl_q40t_bytes(d, n))
+
+
+def xq_bytes(K: int, mcap: int) -> int:
+    return (K // 128) * mcap * XQ_ROW_BYTES
+
+
+def xh_bytes(K: int, ncap: int) -> int:
+    assert ncap % 8 == 0
+    return (K // 128) * (ncap // 8) * 2048
+
+
+def alloc_xq(K: int, mcap: int, device) -> torch.Tensor:
+    return torch.zeros(xq_bytes(K, mcap), dtype=torch.uint8, device=device)
+
+
+def alloc_xh(K: int, ncap: int, device) -> torch.Tensor:
+    return torch.zeros(xh_bytes(K, ncap), dtype=torch.uint8, device=device)
+
+
+# ---- weights ----------------------------------------------------------------------------------------
+def q40_repack(raw: torch.Tensor, rows: int, n: int, q40t: torch.Tensor, d_pad: int, dst_row0: int = 0,
+               dst_row_step: int = 1):
+    check(cuda_lib().dl_q40_repack(raw.data_ptr(), rows, n, q40t.data_ptr(), d_pad, dst_row0, dst_row_step,
+                                   _stream()), "dl_q40_repack")
+    lib.count_launch()
+
+
+def q40t_dequant(q40t: torch.Tensor, d: int, n: int) -> torch.Tensor:
+    out = torch.empty(d, n, dtype=torch.float32, device=q40t.device)
+    check(cuda_lib().dl_q40t_dequant(q40t.data_ptr(), d, n, out.data_ptr(), _stream()), "dl_q40t_dequant")
+    lib.count_launch()
+    return out
+
+
+def make_q40t(raw_q40: torch.Tensor, d: int, n: int) -> torch.Tensor:
+    """raw Q40 file bytes of a [d][n] matrix (uint8 cuda tensor) -> Q40T image (allocates)."""
+    d_pad = (d + 127) // 128 * 128
+    out = torch.zeros(q40t_bytes(d, n), dtype=torch.uint8, device=raw_q40.device)
+    q40_repack(raw_q40, d, n, out, d_pad)
+    return out
+
+
+# ---- epilogue builders ---------------------------------------------------------------------------
+def epi_store(dst: Sequence[int], ld: int, dst_off: int = 0, q80_roundtrip: bool = False,
+              flags: Optional[Sequence[int]] = None, step_counter: Optional[int] = None, flag_mul: int = 0,
+              flag_add: int = 0, cta_counter: Optional[int] = None) -> DlEpilogue:
+    e = DlEpilogue()
+    e.kind = EPI_STORE
+    e.n_dst = len(dst)
+    for i, p in enumerate(dst):
+        e.dst[i] = p
+    e.ld = ld
+    e.dst_off = dst_off
+    e.q80_roundtrip = 1 if q80_roundtrip else 0
+    if flags is not None:
+        assert len(flags) == len(dst) and step_counter is not None and cta_counter is not None
+        for i, p in enumerate(flags):
+            e.flag[i] = p
+        e.step_counter = step_counter
+        e.flag_mul = flag_mul
+        e.flag_add = flag_add
+        e.cta_counter = cta_counter
+    return e
+
+
+def epi_qkv_rope(q_out: torch.Tensor, q_dim: int, kv_dim: int, head_size: int, rope_freqs: torch.Tensor,
+                 pos: torch.Tensor, slot: torch.Tensor, block_table: torch.Tensor, max_pages: int,
+                 n_kv_heads: int, k_cache: torch.Tensor, v_cache: torch.Tensor) -> DlEpilogue:
+    e = DlEpilogue()
+    e.kind = EPI_QKV_ROPE
+    e.q_out = q_out.data_ptr()
+    e.q_dim, e.kv_dim, e.head_size = q_dim, kv_dim, head_size
+    e.rope_freqs = rope_freqs.data_ptr()
+    e.pos, e.slot, e.block_table = pos.data_ptr(), slot.data_ptr(), block_table.data_ptr()
+    e.max_pages, e.page_size, e.n_kv_heads = max_pages, PAGE_SIZE, n_kv_heads
+    e.k_cache, e.v_cache = k_cache.data_ptr(), v_cache.data_ptr()
+    e.kv_f32 = 1 if k_cache.dtype == torch.float32 else 0
+    return e
+
+
+def epi_silu_mul(xq_out: Optional[torch.Tensor], xh_out: Optional[torch.Tensor], out_mcap: int,
+                 gelu: bool = False) -> DlEpilogue:
+    e = DlEpilogue()
+    e.kind = EPI_SILU_MUL
+    e.xq_out = _p(xq_out)
+    e.xh_out = _p(xh_out)
+    e.out_mcap = out_mcap
+    e.act_gelu = 1 if gelu else 0
+    return e
+
+
+# ---- launches ------------------------------------------------------------------------------------
+def reduce_norm_quant(x_in, x_out, partials, n_src, src_stride, flags, step_counter, flag_mul, flag_add, norm_w,
+                      eps, dim, M, mcap, xq_out, xh_out, y_out=None, pdl=False):
+    check(cuda_lib().dl_reduce_norm_quant(_p(x_in), _p(x_out), partials, n_src, src_stride, flags, step_counter,
+                                          flag_mul, flag_add, _p(norm_w), eps, dim, M, mcap, _p(xq_out),
+                                          _p(xh_out), _p(y_out), 1 if pdl else 0, _stream()),
+          "dl_reduce_norm_quant")
+    lib.count_launch()
+
+
+def quant_q80(x: torch.Tensor, M: int, K: int, mcap: int, xq_out=None, xh_out=None):
+    check(cuda_lib().dl_quant_q80(x.data_ptr(), M, K, mcap, _p(xq_out), _p(xh_out), _stream()), "dl_quant_q80")
+    lib.count_launch()
+
+
+def embedding(table: torch.Tensor, tokens: torch.Tensor, x: torch.Tensor, M: int, dim: int, step_counter=None):
+    check(cuda_lib().dl_embedding(table.data_ptr(), tokens.data_ptr(), x.data_ptr(), M, dim, _p(step_counter),
+                                  _stream()), "dl_embedding")
+    lib.count_launch()
+
+
+def gemv_q40(w: torch.Tensor, d: int, n: int, xq: torch.Tensor, mcap: int, M: int, epi: DlEpilogue,
+             row_split: int = 1, k_split: int = 1, pdl: bool = False):
+    check(cuda_lib().dl_gemv_q40(w.data_ptr(), d, n, xq.data_ptr(), mcap, M, row_split, k_split, C.byref(epi),
+                                 1 if pdl else 0, _stream()), "dl_gemv_q40")
+    lib.count_launch()
+
+
+def gemm_q40_tc(w: torch.Tensor, d: int, n: int, xh: torch.Tensor, ncap: int, M: int, epi: DlEpilogue,
+                k_split: int = 1, pdl: bool = False):
+    check(cuda_lib().dl_gemm_q40_tc(w.data_ptr(), d, n, xh.data_ptr(), ncap, M, k_split, C.byref(epi),
+                                    1 if pdl else 0, _stream()), "dl_gemm_q40_tc")
+    lib.count_launch()
+
+
+def attention_scratch_bytes(M: int, n_heads: int, head_size: int, max_splits: int) -> int:
+    return int(cuda_lib().dl_attention_scratch_bytes(M, n_heads, head_size, max_splits))
+
+
+def attention(q, M, n_heads, n_kv_heads, head_size, k_cache, v_cache, pos, slot, block_table, max_pages,
+              n_splits, scratch, xq_out, xh_out, out_mcap, y_out=None, pdl=False):
+    check(cuda_lib().dl_attention(q.data_ptr(), M, n_heads, n_kv_heads, head_size, k_cache.data_ptr(),
+                                  v_cache.data_ptr(), 1 if k_cache.dtype == torch.float32 else 0,
+                                  pos.data_ptr(), slot.data_ptr(), block_table.data_ptr(), max_pages, PAGE_SIZE,
+                                  n_splits, _p(scratch), _p(xq_out), _p(xh_out), out_mcap, _p(y_out),
+                                  1 if pdl else 0, _stream()), "dl_attention")
+    lib.count_launch()
+
+
+def argmax(logits, M: int, vocab: int, ld: int, out: torch.Tensor, flags=None, n_flags=0, step_counter=None,
+           flag_mul=0, flag_add=0, pos_inc=None, history=None, history_cap=0, pdl=False):
+    lp = logits.data_ptr() if isinstance(logits, torch.Tensor) else logits
+    check(cuda_lib().dl_argmax(lp, M, vocab, ld, out.data_ptr(), flags, n_flags, step_counter, flag_mul, flag_add,
+                               _p(pos_inc), _p(history), history_cap, 1 if pdl else 0, _stream()), "dl_argmax")
+    lib.count_launch()
+
+
+def wait_flags(flags: int, n: int, step_counter: int, flag_mul: int, flag_add: int):
+    check(cuda_lib().dl_wait_flags(flags, n, step_counter, flag_mul, flag_add, _stream()), "dl_wait_flags")
+    lib.count_launch()
+
+
+def choose_splits(d: int, n: int, epi_kind: int, n_sms: int = 148, M: int = 1):
+    """Pick (row_split R, k_split S) so the GEMV grid covers the chip.
+
+    Each 128-row tile can be split into R row parts (R<=2 when the epilogue needs 64-row groups)
+    and its K range over a cluster of S CTAs (reduced through DSMEM)."""
+    row_tiles = (d + 127) // 128
+    kt = n // 128
+    max_r = 2 if epi_kind == EPI_SILU_MUL else 4
+    R, S = 1, 1
+    while row_tiles * R * S < n_sms:
+        if R < max_r:
+            R *= 2
+        elif S < 8 and S * 2 <= kt:
+            S *= 2
+        else:
+            break
+    return R, S

@@ -105,7 +105,15 @@ int dl_attention(const float* q, int M, int n_heads, int n_kv_heads, int head_si
 /* ---- sampling helpers --------------------------------------------------------------------- */
 /* argmax over logits[m][0..vocab) -> tokens[m]  (reference: Sampler::sample temperature==0,
  * src/tokenizer.cpp:472-502) */
-int dl_argmax(const float* logits, int M, int vocab, int ld, int* tokens_out, void* stream);
+int dl_argmax(const float* logits, int M, int vocab, int ld, int* tokens_out,
+              const uint32_t* flags /*NULL: no wait*/, int n_flags, const uint32_t* step_counter,
+              uint32_t flag_mul, uint32_t flag_add, int* pos_inc /*NULL or pos[m] += 1*/,
+              int* history /*NULL or [cap][M] ring indexed by *step_counter-1*/, int history_cap, int pdl,
+              void* stream);
+/* block the stream until flags[i] >= *step_counter*flag_mul+flag_add for i<n (logits gather to the
+ * sampling rank; reference: SYNC_NODE_SLICES_EXCEPT_ROOT, src/llm.cpp:432) */
+int dl_wait_flags(const uint32_t* flags, int n, const uint32_t* step_counter, uint32_t flag_mul,
+                  uint32_t flag_add, void* stream);
 
 /* ---- peer memory (symmetric buffers over NVLink) ------------------------------------------ */
 int dl_ipc_alloc(void** dev_ptr, long long bytes, uint8_t* handle_out /*64 B host*/);

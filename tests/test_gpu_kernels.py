@@ -1,0 +1,352 @@
+"""Numerics of every CUDA kernel against plain PyTorch/NumPy f32 references of the same op.
+
+Tolerances follow the reference's own tests (src/nn/nn-cpu-ops-test.cpp:240,289;
+src/nn/nn-vulkan-test.cpp:581) but are much tighter where the arithmetic is exact.
+"""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+from dllama_b200.ops import quant
+
+pytestmark = pytest.mark.gpu
+
+
+def K():
+    from dllama_b200.ops import kernels
+    return kernels
+
+
+def _rand_q40(d, n, seed=0, scale=0.05):
+    rng = np.random.default_rng(seed)
+    w = (rng.standard_normal((d, n), dtype=np.float32) * scale).astype(np.float32)
+    raw = quant.quantize_q40(w)                       # [d*n/32, 18]
+    wdq = quant.dequantize_q40(raw).reshape(d, n)
+    return raw.reshape(-1), wdq
+
+
+def _decode_xq(xq_bytes, K_, mcap, M):
+    a = xq_bytes.cpu().numpy().reshape(K_ // 128, mcap, 160)
+    q = a[:, :M, :128].copy().view(np.int8).astype(np.float32)                  # [kt, M, 128]
+    d = a[:, :M, 128:144].copy().view(np.float32)                               # [kt, M, 4]
+    s = a[:, :M, 144:160].copy().view(np.int32)
+    x = (q.reshape(K_ // 128, M, 4, 32) * d[..., None]).transpose(1, 0, 2, 3).reshape(M, K_)
+    return x, q, d, s
+
+
+def _decode_xh(xh_bytes, K_, ncap, M):
+    """XH slabs -> f32 [M][K] in natural element order."""
+    a = xh_bytes.cpu().numpy().view(np.float16).reshape(K_ // 128, ncap // 8, 16, 8, 8).astype(np.float32)
+    out = np.zeros((M, K_), dtype=np.float32)
+    perm = [0, 2, 1, 3]
+    for e in range(32):
+        hi, e2 = e >> 4, e & 15
+        w, r = e2 >> 2, e2 & 3
+        s = hi * 4 + perm[r]
+        for kb in range(4):
+            # [kt, group, chunk, row, slot]
+            v = a[:, :, kb * 4 + w, :, s]                         # [kt, groups, 8]
+            v = v.reshape(K_ // 128, ncap)[:, :M]                 # [kt, M]
+            out[:, np.arange(K_ // 128) * 128 + kb * 32 + e] = v.T
+    return out
+
+
+def test_repack_dequant_roundtrip():
+    k = K()
+    for d, n in ((128, 128), (200, 256), (384, 1024)):
+        raw, wdq = _rand_q40(d, n, seed=d)
+        t = k.make_q40t(torch.from_numpy(raw).cuda(), d, n)
+        out = k.q40t_dequant(t, d, n).cpu().numpy()
+        np.testing.assert_array_equal(out, wdq)
+
+
+def test_repack_interleave_and_offsets():
+    k = K()
+    d, n = 64, 256
+    raw1, w1 = _rand_q40(d, n, 1)
+    raw3, w3 = _rand_q40(d, n, 2)
+    t = torch.zeros(k.q40t_bytes(2 * d, n), dtype=torch.uint8, device="cuda")
+    k.q40_repack(torch.from_numpy(raw1).cuda(), d, n, t, 128, 0, 2)
+    k.q40_repack(torch.from_numpy(raw3).cuda(), d, n, t, 128, 1, 2)
+    out = k.q40t_dequant(t, 2 * d, n).cpu().numpy()
+    np.testing.assert_array_equal(out[0::2], w1)
+    np.testing.assert_array_equal(out[1::2], w3)
+
+
+@pytest.mark.parametrize("M,Kdim", [(1, 256), (3, 1024), (8, 4096)])
+def test_quant_q80_matches_numpy(M, Kdim):
+    k = K()
+    rng = np.random.default_rng(5)
+    x = (rng.standard_normal((M, Kdim), dtype=np.float32) * 3).astype(np.float32)
+    x[0, :32] = 0.0                                   # an all-zero block (d == 0)
+    xq = k.alloc_xq(Kdim, 8, "cuda")
+    xh = k.alloc_xh(Kdim, 16, "cuda")
+    k.quant_q80(torch.from_numpy(x).cuda(), M, Kdim, 8, xq, None)
+    k.quant_q80(torch.from_numpy(x).cuda(), M, Kdim, 16, None, xh)
+    torch.cuda.synchronize()
+    blocks = quant.quantize_q80(x)                    # numpy oracle, half-even
+    ref = quant.dequantize_q80(blocks).reshape(M, Kdim)
+    got, q, d, s = _decode_xq(xq, Kdim, 8, M)
+    np.testing.assert_array_equal(got, ref)
+    qref = blocks[:, 2:].copy().view(np.int8).reshape(M, Kdim // 32, 32).astype(np.int32)
+    sums = s.transpose(1, 0, 2).reshape(M, Kdim // 32)
+    np.testing.assert_array_equal(sums, 8 * qref.sum(-1))
+    got_h = _decode_xh(xh, Kdim, 16, M)
+    np.testing.assert_allclose(got_h, ref, rtol=1e-3, atol=1e-6)    # fp16 rounding of q*d
+
+
+def _gemv_case(d, n, M, R, S, q80rt=False, seed=0):
+    k = K()
+    raw, wdq = _rand_q40(d, n, seed)
+    w = k.make_q40t(torch.from_numpy(raw).cuda(), d, n)
+    rng = np.random.default_rng(seed + 1)
+    x = rng.standard_normal((M, n), dtype=np.float32)
+    xq = k.alloc_xq(n, 8, "cuda")
+    k.quant_q80(torch.from_numpy(x).cuda(), M, n, 8, xq, None)
+    xdq = quant.q80_roundtrip(x)
+    ref = xdq.astype(np.float64) @ wdq.astype(np.float64).T
+    y = torch.full((M, d), float("nan"), device="cuda")
+    epi = k.epi_store([y.data_ptr()], d, 0, q80rt)
+    k.gemv_q40(w, d, n, xq, 8, M, epi, R, S)
+    torch.cuda.synchronize()
+    return y.cpu().numpy(), ref
+
+
+@pytest.mark.parametrize("d,n,M,R,S", [
+    (128, 128, 1, 1, 1), (256, 512, 1, 2, 1), (256, 1024, 2, 4, 2), (384, 2048, 4, 1, 4),
+    (200, 1024, 8, 2, 8), (1024, 4096, 1, 1, 1), (512, 14336, 3, 4, 8), (128, 2304, 5, 1, 2),
+])
+def test_gemv_q40_matches_reference(d, n, M, R, S):
+    got, ref = _gemv_case(d, n, M, R, S, seed=d + n)
+    assert not np.isnan(got).any()
+    scale = np.abs(ref).max()
+    np.testing.assert_allclose(got, ref, rtol=2e-4, atol=2e-5 * scale)
+
+
+def test_gemv_q80_roundtrip_epilogue():
+    got, ref = _gemv_case(256, 512, 2, 1, 1, q80rt=True)
+    ref_rt = quant.q80_roundtrip(ref.astype(np.float32))
+    scale = np.abs(ref).max()
+    np.testing.assert_allclose(got, ref_rt, rtol=0, atol=scale / 127.0 * 1.01)
+
+
+def _gemm_case(d, n, M, S, seed=0):
+    k = K()
+    raw, wdq = _rand_q40(d, n, seed)
+    w = k.make_q40t(torch.from_numpy(raw).cuda(), d, n)
+    rng = np.random.default_rng(seed + 1)
+    x = rng.standard_normal((M, n), dtype=np.float32)
+    ncap = 16 if M <= 16 else 32 if M <= 32 else 64 if M <= 64 else (M + 127) // 128 * 128
+    xh = k.alloc_xh(n, ncap, "cuda")
+    k.quant_q80(torch.from_numpy(x).cuda(), M, n, ncap, None, xh)
+    ref = quant.q80_roundtrip(x).astype(np.float64) @ wdq.astype(np.float64).T
+    y = torch.full((M, d), float("nan"), device="cuda")
+    epi = k.epi_store([y.data_ptr()], d, 0, False)
+    k.gemm_q40_tc(w, d, n, xh, ncap, M, epi, S)
+    torch.cuda.synchronize()
+    return y.cpu().numpy(), ref
+
+
+@pytest.mark.parametrize("d,n,M,S", [
+    (128, 128, 16, 1), (128, 256, 9, 1), (256, 1024, 32, 1), (256, 1024, 32, 2), (384, 2048, 20, 4),
+    (128, 4096, 64, 1), (512, 1024, 128, 1), (256, 512, 200, 1), (200, 1024, 40, 1),
+])
+def test_gemm_q40_tc_matches_reference(d, n, M, S):
+    got, ref = _gemm_case(d, n, M, S, seed=d + n + M)
+    assert not np.isnan(got).any()
+    scale = np.abs(ref).max()
+    # fp16 rounding of (nibble-8)*d and q*d: ~2^-11 relative per operand, random over K
+    np.testing.assert_allclose(got, ref, rtol=2e-3, atol=2e-3 * scale)
+
+
+def _attention_ref(q, kc, vc, pos, n_heads, n_kv, hs):
+    M = q.shape[0]
+    out = np.zeros((M, n_heads * hs), dtype=np.float64)
+    G = n_heads // n_kv
+    for m in range(M):
+        T = pos[m] + 1
+        for h_ in range(n_heads):
+            kk = kc[m][:T, h_ // G].astype(np.float64)
+            vv = vc[m][:T, h_ // G].astype(np.float64)
+            s = kk @ q[m, h_ * hs:(h_ + 1) * hs].astype(np.float64) / math.sqrt(hs)
+            s = np.exp(s - s.max())
+            out[m, h_ * hs:(h_ + 1) * hs] = (s / s.sum()) @ vv
+    return out
+
+
+@pytest.mark.parametrize("n_heads,n_kv,hs,positions,n_splits,kv_dtype", [
+    (8, 4, 32, [0, 5, 31, 32, 100], 1, torch.float16),
+    (4, 1, 128, [200, 17], 4, torch.float16),
+    (8, 8, 64, [63, 64, 65], 2, torch.float32),
+    (16, 2, 128, [300], 8, torch.float16),
+    (16, 1, 128, [129, 1000], 32, torch.float16),
+])
+def test_attention_matches_reference(n_heads, n_kv, hs, positions, n_splits, kv_dtype):
+    k = K()
+    M = len(positions)
+    max_pages = (max(positions) + 32) // 32 + 1
+    n_pages = M * max_pages
+    rng = np.random.default_rng(7)
+    q = rng.standard_normal((M, n_heads * hs), dtype=np.float32)
+    kc = [rng.standard_normal((max_pages * 32, n_kv, hs), dtype=np.float32) for _ in range(M)]
+    vc = [rng.standard_normal((max_pages * 32, n_kv, hs), dtype=np.float32) for _ in range(M)]
+    perm = rng.permutation(n_pages).astype(np.int32)            # scattered physical pages
+    bt = perm.reshape(M, max_pages)
+    Kc = torch.zeros(n_pages, n_kv, 32, hs, dtype=kv_dtype)
+    Vc = torch.zeros(n_pages, n_kv, 32, hs, dtype=kv_dtype)
+    for m in range(M):
+        for p in range(max_pages):
+            Kc[bt[m, p]] = torch.from_numpy(kc[m][p * 32:(p + 1) * 32].transpose(1, 0, 2).copy()).to(kv_dtype)
+            Vc[bt[m, p]] = torch.from_numpy(vc[m][p * 32:(p + 1) * 32].transpose(1, 0, 2).copy()).to(kv_dtype)
+    # poison the tokens after pos (they must be masked, not multiplied by zero)
+    kc_r = [Kc[torch.from_numpy(bt[m].astype(np.int64))].float().numpy().transpose(0, 2, 1, 3).reshape(-1, n_kv, hs)
+            for m in range(M)]
+    vc_r = [Vc[torch.from_numpy(bt[m].astype(np.int64))].float().numpy().transpose(0, 2, 1, 3).reshape(-1, n_kv, hs)
+            for m in range(M)]
+    for m in range(M):
+        pg, off = divmod(positions[m] + 1, 32)
+        if off:
+            Kc[bt[m, pg], :, off:] = float("nan")
+            Vc[bt[m, pg], :, off:] = float("inf")
+    Kc, Vc = Kc.cuda(), Vc.cuda()
+    y = torch.full((M, n_heads * hs), float("nan"), device="cuda")
+    scratch = torch.zeros(k.attention_scratch_bytes(M, n_heads, hs, max(n_splits, 1)), dtype=torch.uint8,
+                          device="cuda")
+    pos_t = torch.tensor(positions, dtype=torch.int32, device="cuda")
+    slot_t = torch.arange(M, dtype=torch.int32, device="cuda")
+    bt_t = torch.from_numpy(bt).cuda()
+    xq = k.alloc_xq(n_heads * hs, 8, "cuda") if (n_heads * hs) % 128 == 0 and M <= 8 else None
+    for _ in range(2):      # twice: the split counters must self-reset
+        k.attention(torch.from_numpy(q).cuda(), M, n_heads, n_kv, hs, Kc, Vc, pos_t, slot_t, bt_t, max_pages,
+                    n_splits, scratch, xq, None, 8, y)
+    torch.cuda.synchronize()
+    ref = _attention_ref(q, kc_r, vc_r, positions, n_heads, n_kv, hs)
+    got = y.cpu().numpy()
+    assert not np.isnan(got).any()
+    np.testing.assert_allclose(got, ref, rtol=2e-3, atol=2e-3)
+    if xq is not None:
+        dq, _, _, _ = _decode_xq(xq, n_heads * hs, 8, M)
+        np.testing.assert_allclose(dq, quant.q80_roundtrip(got), rtol=0, atol=np.abs(got).max() / 127 * 1.01)
+
+
+def test_qkv_rope_epilogue_and_kv_write():
+    k = K()
+    from dllama_b200.formats.mfile import LlmHeader
+    from dllama_b200.models.oracle import apply_rope, rope_frequencies
+    hs, n_heads, n_kv, dim, M = 64, 4, 2, 256, 3
+    q_dim, kv_dim = n_heads * hs, n_kv * hs
+    d = q_dim + 2 * kv_dim
+    h = LlmHeader(dim=q_dim, n_heads=n_heads, n_kv_heads=n_kv, rope_theta=500000.0, rope_type=2,
+                  rope_scaling_factor=32.0, rope_scaling_low_freq_factor=1.0, rope_scaling_high_freq_factor=4.0,
+                  rope_scaling_orig_max_seq_len=8192)
+    freqs = rope_frequencies(h)
+    raw, wdq = _rand_q40(d, dim, 11)
+    w = k.make_q40t(torch.from_numpy(raw).cuda(), d, dim)
+    rng = np.random.default_rng(12)
+    x = rng.standard_normal((M, dim), dtype=np.float32)
+    xq = k.alloc_xq(dim, 8, "cuda")
+    k.quant_q80(torch.from_numpy(x).cuda(), M, dim, 8, xq, None)
+    y = torch.from_numpy(quant.q80_roundtrip(x) @ wdq.T)
+    positions = [0, 37, 70]
+    pos = torch.tensor(positions, dtype=torch.int32)
+    q_ref = apply_rope(y[:, :q_dim], pos, freqs, hs)
+    k_ref = apply_rope(y[:, q_dim:q_dim + kv_dim], pos, freqs, hs)
+    v_ref = y[:, q_dim + kv_dim:]
+    max_pages, n_pages = 4, 12
+    bt = torch.tensor([[3, 7, 1, 0], [2, 5, 9, 4], [11, 10, 8, 6]], dtype=torch.int32)
+    for kv_dtype in (torch.float16, torch.float32):
+        Kc = torch.zeros(n_pages, n_kv, 32, hs, dtype=kv_dtype, device="cuda")
+        Vc = torch.zeros_like(Kc)
+        q_out = torch.zeros(M, q_dim, device="cuda")
+        epi = k.epi_qkv_rope(q_out, q_dim, kv_dim, hs, freqs.cuda(), pos.cuda(),
+                             torch.arange(M, dtype=torch.int32, device="cuda"), bt.cuda(), max_pages, n_kv, Kc, Vc)
+        k.gemv_q40(w, d, dim, xq, 8, M, epi, 2, 2)
+        torch.cuda.synchronize()
+        np.testing.assert_allclose(q_out.cpu().numpy(), q_ref.numpy(), rtol=1e-3, atol=2e-4)
+        tol = 2e-3 if kv_dtype == torch.float16 else 2e-4
+        for m, p in enumerate(positions):
+            page = int(bt[m, p // 32])
+            got_k = Kc[page, :, p % 32, :].float().cpu().numpy().reshape(-1)
+            got_v = Vc[page, :, p % 32, :].float().cpu().numpy().reshape(-1)
+            np.testing.assert_allclose(got_k, k_ref[m].numpy(), rtol=tol, atol=tol)
+            np.testing.assert_allclose(got_v, v_ref[m].numpy(), rtol=tol, atol=tol)
+        assert float(Kc.abs().sum()) > 0 and int((Kc != 0).any(dim=-1).sum()) == M * n_kv
+
+
+@pytest.mark.parametrize("M,use_tc", [(2, False), (24, True)])
+def test_silu_mul_epilogue(M, use_tc):
+    k = K()
+    hid, dim = 256, 256
+    raw1, w1 = _rand_q40(hid, dim, 21)
+    raw3, w3 = _rand_q40(hid, dim, 22)
+    w = torch.zeros(k.q40t_bytes(2 * hid, dim), dtype=torch.uint8, device="cuda")
+    k.q40_repack(torch.from_numpy(raw1).cuda(), hid, dim, w, 2 * hid, 0, 2)
+    k.q40_repack(torch.from_numpy(raw3).cuda(), hid, dim, w, 2 * hid, 1, 2)
+    rng = np.random.default_rng(23)
+    x = rng.standard_normal((M, dim), dtype=np.float32) * 4
+    xdq = quant.q80_roundtrip(x)
+    g, u = xdq @ w1.T, xdq @ w3.T
+    ref = quant.q80_roundtrip((g / (1 + np.exp(-g)) * u).astype(np.float32))
+    if use_tc:
+        xh = k.alloc_xh(dim, 32, "cuda")
+        k.quant_q80(torch.from_numpy(x).cuda(), M, dim, 32, None, xh)
+        out = k.alloc_xh(hid, 32, "cuda")
+        k.gemm_q40_tc(w, 2 * hid, dim, xh, 32, M, k.epi_silu_mul(None, out, 32), 1)
+        torch.cuda.synchronize()
+        got = _decode_xh(out, hid, 32, M)
+        tol = 5e-3
+    else:
+        xq = k.alloc_xq(dim, 8, "cuda")
+        k.quant_q80(torch.from_numpy(x).cuda(), M, dim, 8, xq, None)
+        out = k.alloc_xq(hid, 8, "cuda")
+        k.gemv_q40(w, 2 * hid, dim, xq, 8, M, k.epi_silu_mul(out, None, 8), 2, 2)
+        torch.cuda.synchronize()
+        got, _, _, _ = _decode_xq(out, hid, 8, M)
+        tol = 1e-4
+    amax = np.abs(ref).max()
+    np.testing.assert_allclose(got, ref, rtol=0, atol=amax / 127 * 1.01 + tol * amax)
+
+
+def test_reduce_norm_quant_with_partials():
+    k = K()
+    M, dim, n_src = 3, 512, 4
+    rng = np.random.default_rng(31)
+    x = rng.standard_normal((M, dim), dtype=np.float32)
+    parts = rng.standard_normal((n_src, 8, dim), dtype=np.float32)
+    wn = rng.standard_normal(dim).astype(np.float32)
+    xin = torch.from_numpy(x).cuda()
+    xout = torch.zeros_like(xin)
+    pt = torch.from_numpy(parts).cuda()
+    yout = torch.zeros(M, dim, device="cuda")
+    xq = k.alloc_xq(dim, 8, "cuda")
+    k.reduce_norm_quant(xin, xout, pt.data_ptr(), n_src, 8 * dim, None, None, 0, 0, torch.from_numpy(wn).cuda(),
+                        1e-5, dim, M, 8, xq, None, yout)
+    torch.cuda.synchronize()
+    xs = x + parts[:, :M].sum(0)
+    np.testing.assert_allclose(xout.cpu().numpy(), xs, rtol=1e-6, atol=1e-6)
+    yref = wn * (xs / np.sqrt((xs * xs).mean(-1, keepdims=True) + 1e-5))
+    np.testing.assert_allclose(yout.cpu().numpy(), yref, rtol=1e-5, atol=1e-5)
+    got, _, _, _ = _decode_xq(xq, dim, 8, M)
+    np.testing.assert_allclose(got, quant.q80_roundtrip(yout.cpu().numpy()), rtol=0, atol=1e-6)
+
+
+def test_argmax_and_embedding():
+    k = K()
+    logits = torch.randn(5, 1000, device="cuda")
+    logits[2, 17] = 100.0
+    logits[3, :] = 0.0                 # ties -> lowest index
+    out = torch.zeros(5, dtype=torch.int32, device="cuda")
+    k.argmax(logits, 5, 1000, 1000, out)
+    torch.cuda.synchronize()
+    ref = logits.argmax(dim=-1).cpu().numpy()
+    got = out.cpu().numpy()
+    assert got[2] == 17 and got[3] == 0
+    np.testing.assert_array_equal(got[[0, 1, 4]], ref[[0, 1, 4]])
+    table = torch.randn(50, 256, device="cuda")
+    toks = torch.tensor([3, 49, 0], dtype=torch.int32, device="cuda")
+    x = torch.zeros(3, 256, device="cuda")
+    k.embedding(table, toks, x, 3, 256, None)
+    torch.cuda.synchronize()
+    torch.testing.assert_close(x, table[[3, 49, 0]])
