@@ -63,6 +63,7 @@ DL_DEVINL void epilogue_rows(const DlEpilogue& e, const float* out_s, int out_ld
                 float v = out_s[m * out_ld + tid];
                 if (e.q80_roundtrip) v = q80_roundtrip_warp(v);
                 if (grow < d_real) {
+                    if (e.residual != nullptr) v += e.residual[(size_t)(m0 + m) * e.residual_ld + grow];
                     const size_t off = (size_t)e.dst_off + (size_t)(m0 + m) * e.ld + grow;
                     for (int p = 0; p < e.n_dst; p++) e.dst[p][off] = v;
                 }

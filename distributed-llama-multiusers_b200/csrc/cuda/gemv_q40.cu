@@ -1,15 +1,21 @@
 // Q40 x Q80 -> f32 matmul for small activation batches (M <= 8): the decode hot path.
 //
 // Design (B200-first, not a port of matmul_Q80_Q40_F32, src/nn/nn-cpu-ops.cpp:222-440):
-//  * weights live in HBM as Q40T tiles (common.cuh): each pipeline stage is ONE contiguous
-//    bulk async copy (cp.async.bulk -> SASS UBLKCP) of a 128x128 tile part into shared memory,
-//    completion tracked by mbarriers; an 8-stage ring keeps ~80 KB per SM in flight, which is
-//    what it takes to cover HBM3e latency at 6.5 TB/s over 148 SMs.
+//  * weights live in HBM as Q40T tiles (common.cuh): each pipeline stage is a contiguous bulk
+//    async copy (cp.async.bulk -> SASS UBLKCP) of a 128x128 tile into shared memory, completion
+//    tracked by mbarriers; an 8-stage ring keeps ~74 KB per SM in flight, which is what it takes
+//    to cover HBM3e latency at 6.5 TB/s over 148 SMs.
 //  * exact reference arithmetic: int8 dot products (dp4a) per 32-block, one f32 multiply by
 //    d_w*d_x, f32 accumulation.
+//  * the Q80 activations of this CTA's K range are resident in shared memory.  They either arrive
+//    with one bulk copy (XQ slabs written by the previous kernel's epilogue), or -- fused prologue
+//    -- the kernel builds them itself: wait for the peers' release flags, merge-add the partial
+//    sums of all ranks into the residual stream, RMSNorm, Q80 cast (DlNormProlog).  The weight
+//    prefetch is already in flight while this runs, so the all-gather / merge-add / norm / cast
+//    of the reference (4 ops + a socket sync) costs no extra kernel and no global round trip.
 //  * grid = row_tiles * R (row split) * S (K split); the S CTAs of a tile form a thread-block
-//    cluster and reduce their partial sums through distributed shared memory -- deterministic,
-//    no atomics, no global scratch.
+//    cluster: they share the row's sum of squares and reduce their partial dot products through
+//    distributed shared memory -- deterministic, no atomics, no global scratch.
 //  * weight prefetch is issued before griddepcontrol.wait, so under programmatic dependent
 //    launch the first stages stream while the previous kernel (or a peer GPU) still runs.
 //  * the epilogue (epilogue.cuh) fuses RoPE + KV-cache write, SiLU*mul + Q80 cast, or the
@@ -19,77 +25,172 @@
 #define GEMV_NS 8                       // pipeline stages
 #define GEMV_CONSUMERS 256              // 2 groups x 128 threads
 #define GEMV_THREADS (GEMV_CONSUMERS + 32)
+#define GEMV_WARPS (GEMV_THREADS / 32)
 #define GEMV_MAX_M 8
-#define GEMV_STAGE_BYTES (Q40T_TILE_BYTES + GEMV_MAX_M * XQ_ROW_BYTES)   // 10496
+#define GEMV_MAX_ACT_BYTES (96 * 1024)
 
 struct GemvArgs {
     const uint8_t* w;
     const uint8_t* xq;
-    int d_real, d_pad, KT, mcap, M, R, S;
+    int d_real, d_pad, KT, M, R, S, n;
     int n_epi_ctas;
+    int fused;
+    DlNormProlog norm;
     DlEpilogue epi;
 };
 
 template <int MT>
 __global__ void __launch_bounds__(GEMV_THREADS, 1) gemv_q40_kernel(const __grid_constant__ GemvArgs a) {
     extern __shared__ __align__(128) uint8_t smem[];
-    uint8_t* stages = smem;
-    float* red = reinterpret_cast<float*>(smem + GEMV_NS * GEMV_STAGE_BYTES);     // [2*R][MT][rows]  (<= 2*MT*128)
-    float* out_s = red + 2 * MT * 128;                                            // [MT][128]
-    uint64_t* full = reinterpret_cast<uint64_t*>(out_s + MT * 128);
+    const int S = a.S, R = a.R, M = a.M;
+    const int nk_max = (a.KT + S - 1) / S;
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem);                               // barriers first (8-byte aligned)
     uint64_t* empty = full + GEMV_NS;
-    int* sflag = reinterpret_cast<int*>(empty + GEMV_NS);
+    uint64_t* act_full = empty + GEMV_NS;
+    int* sflag = reinterpret_cast<int*>(act_full + 1);
+    uint8_t* stages = smem + 256;                                                    // [NS][9216]
+    uint8_t* act_s = stages + GEMV_NS * Q40T_TILE_BYTES;                             // [nk][M][160]
+    float* red = reinterpret_cast<float*>(act_s + (size_t)nk_max * M * XQ_ROW_BYTES);   // [2*R][MT][rows] (<= 2*MT*128)
+    float* out_s = red + 2 * MT * 128;                                               // [MT][128]
+    float* ssq_w = out_s + MT * 128;                                                 // [GEMV_WARPS][MT]
+    float* ssq_c = ssq_w + GEMV_WARPS * MT;                                          // [MT]  (read by cluster peers)
 
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
-    const int S = a.S, R = a.R;
     const int crank = (S > 1) ? (int)cg::this_cluster().block_rank() : 0;
     const int tile_idx = blockIdx.x / S;
     const int rt = tile_idx / R, rs = tile_idx % R;
     const int rows = Q40T_TILE_ROWS / R;
     const int kt0 = (a.KT * crank) / S, kt1 = (a.KT * (crank + 1)) / S;
     const int nk = kt1 - kt0;
+    const bool is_producer = (tid == GEMV_CONSUMERS);
+    const uint32_t nib_bytes = rows * 64, sc_bytes = rows * 8;
+    const uint8_t* wt = a.w + ((size_t)rt * a.KT + kt0) * Q40T_TILE_BYTES;
+    const int pre = nk < GEMV_NS ? nk : GEMV_NS;
+    uint64_t pol = 0;
 
     if (tid == 0) {
         for (int s = 0; s < GEMV_NS; s++) {
             mbar_init(&full[s], 1);
             mbar_init(&empty[s], 4);
         }
+        mbar_init(act_full, 1);
         mbar_fence_init();
     }
     __syncthreads();
     pdl_launch_dependents();
 
-    const uint32_t nib_bytes = rows * 64, sc_bytes = rows * 8, act_bytes = a.M * XQ_ROW_BYTES;
+    if (is_producer) {
+        // weights do not depend on the previous kernel: stream the first ring-full before the PDL wait
+        pol = l2_policy_evict_first();
+        for (int i = 0; i < pre; i++) {
+            uint8_t* st = stages + i * Q40T_TILE_BYTES;
+            const uint8_t* t = wt + (size_t)i * Q40T_TILE_BYTES;
+            mbar_arrive_expect_tx(&full[i], nib_bytes + sc_bytes);
+            bulk_g2s_hint(st, t + rs * nib_bytes, nib_bytes, &full[i], pol);
+            bulk_g2s_hint(st + Q40T_NIB_BYTES, t + Q40T_SCALE_OFF + rs * sc_bytes, sc_bytes, &full[i], pol);
+        }
+    }
+
+    if (a.fused) {
+        // ---------------- fused prologue: flags wait + merge-add + RMSNorm + Q80 -> act_s ----------------
+        const DlNormProlog& nm = a.norm;
+        pdl_wait();
+        if (nm.flags != nullptr) {
+            if (tid < nm.n_src) {
+                const uint32_t epoch = ld_volatile_u32(nm.step_counter) * nm.flag_mul + nm.flag_add;
+                wait_flag_ge(nm.flags + tid, epoch);
+            }
+            __syncthreads();
+        }
+        const int dim = a.n;
+        const int e0 = kt0 * 128, e1 = kt1 * 128;                 // this CTA's K range (cluster ranks tile the row)
+        const bool writer = (nm.x_out != nullptr) && (tile_idx == 0);
+        float ss[MT];
+#pragma unroll
+        for (int m = 0; m < MT; m++) ss[m] = 0.0f;
+        // pass 1: sum of squares of (x + partials) over the K range; row tile 0 publishes x_out
+#pragma unroll
+        for (int m = 0; m < MT; m++) {
+            if (m < M) {
+                const float4* xi = reinterpret_cast<const float4*>(nm.x_in + (size_t)m * dim);
+                for (int i4 = e0 / 4 + tid; i4 < e1 / 4; i4 += GEMV_THREADS) {
+                    float4 v = xi[i4];
+                    for (int s = 0; s < nm.n_src; s++) {
+                        const float4 p = reinterpret_cast<const float4*>(nm.partials + (size_t)s * nm.src_stride + (size_t)m * dim)[i4];
+                        v.x += p.x; v.y += p.y; v.z += p.z; v.w += p.w;
+                    }
+                    if (writer) reinterpret_cast<float4*>(nm.x_out + (size_t)m * dim)[i4] = v;
+                    ss[m] += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+                }
+            }
+        }
+#pragma unroll
+        for (int m = 0; m < MT; m++) {
+            const float t = warp_sum(ss[m]);
+            if (lane == 0) ssq_w[warp * MT + m] = t;
+        }
+        __syncthreads();
+        if (tid < MT) {
+            float t = 0.0f;
+            for (int w = 0; w < GEMV_WARPS; w++) t += ssq_w[w * MT + tid];
+            ssq_c[tid] = t;
+        }
+        if (S > 1) cg::this_cluster().sync(); else __syncthreads();
+        float inv[MT];
+#pragma unroll
+        for (int m = 0; m < MT; m++) {
+            float t = 0.0f;
+            if (S > 1) {
+                for (int c = 0; c < S; c++) t += cg::this_cluster().map_shared_rank(ssq_c, c)[m];
+            } else {
+                t = ssq_c[m];
+            }
+            inv[m] = 1.0f / sqrtf(t / (float)dim + nm.eps);
+        }
+        // pass 2: y = w * (inv * x) -> Q80 -> resident activation slabs (one warp per 32-block)
+        const int nkb = nk * 4;
+        for (int item = warp; item < M * nkb; item += GEMV_WARPS) {
+            const int m = item / nkb, b = item % nkb;
+            const int e = e0 + b * 32 + lane;
+            float v = nm.x_in[(size_t)m * dim + e];
+            for (int s = 0; s < nm.n_src; s++) v += nm.partials[(size_t)s * nm.src_stride + (size_t)m * dim + e];
+            float im = inv[0];
+#pragma unroll
+            for (int q = 1; q < MT; q++) im = (m == q) ? inv[q] : im;
+            const float y = nm.norm_w[e] * (im * v);
+            const float amax = warp_max(fabsf(y));
+            const float d = amax / 127.0f;
+            const float id = (d != 0.0f) ? (1.0f / d) : 0.0f;
+            const int qv = __float2int_rn(y * id);
+            const int sumq = warp_sum_i(qv);
+            uint8_t* rowp = act_s + ((size_t)(b >> 2) * M + m) * XQ_ROW_BYTES;
+            reinterpret_cast<int8_t*>(rowp)[(b & 3) * 32 + lane] = (int8_t)qv;
+            if (lane == 0) {
+                reinterpret_cast<float*>(rowp + 128)[b & 3] = __half2float(__float2half_rn(d));
+                reinterpret_cast<int*>(rowp + 144)[b & 3] = 8 * sumq;
+            }
+        }
+        __syncthreads();
+    }
 
     if (warp == GEMV_CONSUMERS / 32) {
         // ------------------------------ producer warp ------------------------------
-        if (lane == 0) {
-            const uint64_t pol = l2_policy_evict_first();
-            const uint8_t* wt = a.w + ((size_t)rt * a.KT + kt0) * Q40T_TILE_BYTES;
-            const int pre = nk < GEMV_NS ? nk : GEMV_NS;
-            // weights do not depend on the previous kernel: stream them before the PDL wait
-            for (int i = 0; i < pre; i++) {
-                uint8_t* st = stages + i * GEMV_STAGE_BYTES;
-                const uint8_t* t = wt + (size_t)i * Q40T_TILE_BYTES;
-                mbar_arrive_expect_tx(&full[i], nib_bytes + sc_bytes + act_bytes);
-                bulk_g2s_hint(st, t + rs * nib_bytes, nib_bytes, &full[i], pol);
-                bulk_g2s_hint(st + Q40T_NIB_BYTES, t + Q40T_SCALE_OFF + rs * sc_bytes, sc_bytes, &full[i], pol);
-            }
-            pdl_wait();
-            for (int i = 0; i < pre; i++) {
-                uint8_t* st = stages + i * GEMV_STAGE_BYTES;
-                bulk_g2s(st + Q40T_TILE_BYTES, a.xq + (size_t)(kt0 + i) * a.mcap * XQ_ROW_BYTES, act_bytes, &full[i]);
+        if (is_producer) {
+            if (!a.fused) {
+                pdl_wait();
+                const uint32_t act_bytes = (uint32_t)nk * M * XQ_ROW_BYTES;
+                mbar_arrive_expect_tx(act_full, act_bytes);
+                bulk_g2s(act_s, a.xq + (size_t)kt0 * M * XQ_ROW_BYTES, act_bytes, act_full);
             }
             for (int i = pre; i < nk; i++) {
                 const int s = i % GEMV_NS;
                 mbar_wait(&empty[s], ((i / GEMV_NS) & 1) ^ 1);
-                uint8_t* st = stages + s * GEMV_STAGE_BYTES;
+                uint8_t* st = stages + s * Q40T_TILE_BYTES;
                 const uint8_t* t = wt + (size_t)i * Q40T_TILE_BYTES;
-                mbar_arrive_expect_tx(&full[s], nib_bytes + sc_bytes + act_bytes);
+                mbar_arrive_expect_tx(&full[s], nib_bytes + sc_bytes);
                 bulk_g2s_hint(st, t + rs * nib_bytes, nib_bytes, &full[s], pol);
                 bulk_g2s_hint(st + Q40T_NIB_BYTES, t + Q40T_SCALE_OFF + rs * sc_bytes, sc_bytes, &full[s], pol);
-                bulk_g2s(st + Q40T_TILE_BYTES, a.xq + (size_t)(kt0 + i) * a.mcap * XQ_ROW_BYTES, act_bytes, &full[s]);
             }
         }
     } else {
@@ -102,12 +203,13 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) gemv_q40_kernel(const __grid_
         float acc[MT];
 #pragma unroll
         for (int m = 0; m < MT; m++) acc[m] = 0.0f;
+        if (!a.fused) mbar_wait(act_full, 0);
 
         for (int i = g; i < nk; i += 2) {
             const int s = i % GEMV_NS;
             mbar_wait(&full[s], (i / GEMV_NS) & 1);
-            const uint8_t* st = stages + s * GEMV_STAGE_BYTES;
-            const uint8_t* act = st + Q40T_TILE_BYTES;
+            const uint8_t* st = stages + s * Q40T_TILE_BYTES;
+            const uint8_t* act = act_s + (size_t)i * M * XQ_ROW_BYTES;
             for (int kb = kq; kb < 4; kb += R) {
                 const uint4 nb = *reinterpret_cast<const uint4*>(st + row * 64 + (((kb + (rtile >> 1)) & 3) << 4));
                 const float dw = __half2float(*reinterpret_cast<const __half*>(st + Q40T_NIB_BYTES + row * 8 + kb * 2));
@@ -117,21 +219,18 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) gemv_q40_kernel(const __grid_
                 const int lo3 = nb.w & 0x0F0F0F0F, hi3 = (nb.w >> 4) & 0x0F0F0F0F;
 #pragma unroll
                 for (int m = 0; m < MT; m++) {
-                    if (m < a.M) {
+                    if (m < M) {
                         const uint8_t* xr = act + m * XQ_ROW_BYTES;
                         const int4 xl = *reinterpret_cast<const int4*>(xr + kb * 32);
                         const int4 xh = *reinterpret_cast<const int4*>(xr + kb * 32 + 16);
-                        int isum = __dp4a(lo0, xl.x, 0);
-                        isum = __dp4a(lo1, xl.y, isum);
-                        isum = __dp4a(lo2, xl.z, isum);
-                        isum = __dp4a(lo3, xl.w, isum);
-                        isum = __dp4a(hi0, xh.x, isum);
-                        isum = __dp4a(hi1, xh.y, isum);
-                        isum = __dp4a(hi2, xh.z, isum);
-                        isum = __dp4a(hi3, xh.w, isum);
+                        // two independent dp4a chains (low / high nibbles) for ILP
+                        int is0 = __dp4a(lo0, xl.x, 0), is1 = __dp4a(hi0, xh.x, 0);
+                        is0 = __dp4a(lo1, xl.y, is0); is1 = __dp4a(hi1, xh.y, is1);
+                        is0 = __dp4a(lo2, xl.z, is0); is1 = __dp4a(hi2, xh.z, is1);
+                        is0 = __dp4a(lo3, xl.w, is0); is1 = __dp4a(hi3, xh.w, is1);
                         const float dx = reinterpret_cast<const float*>(xr + 128)[kb];
                         const int s8 = reinterpret_cast<const int*>(xr + 144)[kb];
-                        acc[m] += (float)(isum - s8) * (dw * dx);
+                        acc[m] += (float)(is0 + is1 - s8) * (dw * dx);
                     }
                 }
             }
@@ -165,24 +264,34 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) gemv_q40_kernel(const __grid_
     }
     __syncthreads();
     pdl_wait();
-    epilogue_rows(a.epi, out_s, 128, rows, rt * Q40T_TILE_ROWS + rs * rows, a.d_real, a.M, 0, tid);
+    epilogue_rows(a.epi, out_s, 128, rows, rt * Q40T_TILE_ROWS + rs * rows, a.d_real, M, 0, tid);
     epilogue_complete(a.epi, tid, a.n_epi_ctas, sflag);
 }
 
-static size_t gemv_smem_bytes(int MT) {
-    return (size_t)GEMV_NS * GEMV_STAGE_BYTES + (size_t)(2 * MT * 128 + MT * 128) * 4 + 2 * GEMV_NS * 8 + 16;
+static size_t gemv_smem_bytes(int MT, int nk_max, int M) {
+    return 256 + (size_t)GEMV_NS * Q40T_TILE_BYTES + (size_t)nk_max * M * XQ_ROW_BYTES +
+           (size_t)(2 * MT * 128 + MT * 128) * 4 + (size_t)(GEMV_WARPS * MT + 8) * 4 + 16;
+}
+
+static int mt_of(int M) { return M == 1 ? 1 : (M == 2 ? 2 : (M <= 4 ? 4 : 8)); }
+
+extern "C" long long dl_gemv_q40_smem_bytes(int n, int M, int k_split) {
+    const int KT = n / Q40T_TILE_K;
+    if (k_split > KT) k_split = 1;
+    return (long long)gemv_smem_bytes(mt_of(M), (KT + k_split - 1) / k_split, M);
 }
 
 extern void dl_set_error(const char* fmt, ...);
 
 template <int MT>
 static int launch_gemv(const GemvArgs& a, int pdl, cudaStream_t stream) {
-    static bool attr_set = false;
-    const size_t smem = gemv_smem_bytes(MT);
-    if (!attr_set) {
+    static size_t attr_max = 0;
+    const size_t smem = gemv_smem_bytes(MT, (a.KT + a.S - 1) / a.S, a.M);
+    if (smem > 227 * 1024) { dl_set_error("dl_gemv_q40: %zu B of shared memory needed (n=%d, M=%d, k_split=%d): raise k_split", smem, a.n, a.M, a.S); return -1; }
+    if (smem > attr_max) {
         cudaError_t e = cudaFuncSetAttribute(gemv_q40_kernel<MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) { dl_set_error("gemv smem attr: %s", cudaGetErrorString(e)); return -(int)e; }
-        attr_set = true;
+        attr_max = smem;
     }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)((a.d_pad / Q40T_TILE_ROWS) * a.R * a.S));
@@ -210,29 +319,35 @@ static int launch_gemv(const GemvArgs& a, int pdl, cudaStream_t stream) {
     return 0;
 }
 
-extern "C" int dl_gemv_q40(const uint8_t* w_q40t, int d, int n, const uint8_t* xq, int mcap, int M, int row_split,
-                           int k_split, const DlEpilogue* epi, int pdl, void* stream) {
+extern "C" int dl_gemv_q40(const uint8_t* w_q40t, int d, int n, const uint8_t* xq, int M, int row_split, int k_split,
+                           const DlNormProlog* norm, const DlEpilogue* epi, int pdl, void* stream) {
     if (M < 1 || M > GEMV_MAX_M) { dl_set_error("dl_gemv_q40: M=%d out of range 1..8", M); return -1; }
     if (n % Q40T_TILE_K != 0) { dl_set_error("dl_gemv_q40: n=%d not a multiple of 128", n); return -1; }
     if (row_split != 1 && row_split != 2 && row_split != 4) { dl_set_error("dl_gemv_q40: row_split must be 1,2,4"); return -1; }
     if (k_split != 1 && k_split != 2 && k_split != 4 && k_split != 8) { dl_set_error("dl_gemv_q40: k_split must be 1,2,4,8"); return -1; }
     if (epi->kind == DL_EPI_SILU_MUL && (row_split > 2 || d % 64 != 0)) { dl_set_error("dl_gemv_q40: silu epilogue needs row_split<=2, d%%64==0"); return -1; }
+    if (norm == nullptr && xq == nullptr) { dl_set_error("dl_gemv_q40: need xq or a norm prologue"); return -1; }
+    if (norm != nullptr && norm->n_src > DL_MAX_PEERS) { dl_set_error("dl_gemv_q40: n_src > 8"); return -1; }
     GemvArgs a;
     a.w = w_q40t;
     a.xq = xq;
     a.d_real = d;
     a.d_pad = (d + Q40T_TILE_ROWS - 1) / Q40T_TILE_ROWS * Q40T_TILE_ROWS;
     a.KT = n / Q40T_TILE_K;
+    a.n = n;
     if (k_split > a.KT) k_split = 1;
-    a.mcap = mcap;
     a.M = M;
     a.R = row_split;
     a.S = k_split;
     a.n_epi_ctas = (a.d_pad / Q40T_TILE_ROWS) * a.R;
+    a.fused = norm != nullptr ? 1 : 0;
+    if (norm != nullptr) a.norm = *norm; else memset(&a.norm, 0, sizeof(a.norm));
     a.epi = *epi;
     cudaStream_t st = (cudaStream_t)stream;
-    if (M == 1) return launch_gemv<1>(a, pdl, st);
-    if (M == 2) return launch_gemv<2>(a, pdl, st);
-    if (M <= 4) return launch_gemv<4>(a, pdl, st);
-    return launch_gemv<8>(a, pdl, st);
+    switch (mt_of(M)) {
+        case 1: return launch_gemv<1>(a, pdl, st);
+        case 2: return launch_gemv<2>(a, pdl, st);
+        case 4: return launch_gemv<4>(a, pdl, st);
+        default: return launch_gemv<8>(a, pdl, st);
+    }
 }

@@ -244,11 +244,22 @@ struct ArgmaxArgs {
     int* pos_inc;
     int* history;
     int history_cap;
+    uint8_t* scratch;
 };
 
-__global__ void argmax_kernel(const __grid_constant__ ArgmaxArgs a) {
-    __shared__ float s_v[32];
-    __shared__ int s_i[32];
+#define ARGMAX_CHUNKS 32
+#define ARGMAX_THREADS 256
+
+DL_DEVINL void argmax_combine(float& best, int& bi, float ov, int oi) {
+    if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
+}
+
+// grid (ARGMAX_CHUNKS, M): every CTA reduces one vocabulary chunk; the last CTA of a row (self-
+// resetting counter in scratch) reduces the chunk winners and publishes the token.
+__global__ void __launch_bounds__(ARGMAX_THREADS) argmax_kernel(const __grid_constant__ ArgmaxArgs a) {
+    __shared__ float s_v[ARGMAX_THREADS / 32];
+    __shared__ int s_i[ARGMAX_THREADS / 32];
+    __shared__ int s_last;
     pdl_launch_dependents();
     pdl_wait();
     if (a.flags != nullptr) {
@@ -258,53 +269,65 @@ __global__ void argmax_kernel(const __grid_constant__ ArgmaxArgs a) {
         }
         __syncthreads();
     }
-    const int m = blockIdx.x;
+    const int m = blockIdx.y, ch = blockIdx.x, M = gridDim.y;
+    unsigned* counters = reinterpret_cast<unsigned*>(a.scratch);                       // [M]
+    float* part_v = reinterpret_cast<float*>(a.scratch + 1024);                        // [M][CHUNKS]
+    int* part_i = reinterpret_cast<int*>(a.scratch + 1024 + (size_t)M * ARGMAX_CHUNKS * 4);
+    const int per = ((a.vocab + ARGMAX_CHUNKS - 1) / ARGMAX_CHUNKS + 3) & ~3;
+    const int i0 = ch * per, i1 = min(a.vocab, i0 + per);
     const float* row = a.logits + (size_t)m * a.ld;
     float best = -INFINITY;
     int bi = 0x7fffffff;
-    for (int i = threadIdx.x; i < a.vocab; i += blockDim.x) {
-        float v = row[i];
-        if (v > best || (v == best && i < bi)) { best = v; bi = i; }
-    }
-    for (int o = 16; o > 0; o >>= 1) {
-        float ov = __shfl_xor_sync(0xffffffffu, best, o);
-        int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-        if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
-    }
+    for (int i = i0 + threadIdx.x; i < i1; i += ARGMAX_THREADS) argmax_combine(best, bi, row[i], i);
+    for (int o = 16; o > 0; o >>= 1)
+        argmax_combine(best, bi, __shfl_xor_sync(0xffffffffu, best, o), __shfl_xor_sync(0xffffffffu, bi, o));
     if ((threadIdx.x & 31) == 0) { s_v[threadIdx.x >> 5] = best; s_i[threadIdx.x >> 5] = bi; }
     __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < ARGMAX_THREADS / 32; w++) argmax_combine(best, bi, s_v[w], s_i[w]);
+        part_v[m * ARGMAX_CHUNKS + ch] = best;
+        part_i[m * ARGMAX_CHUNKS + ch] = bi;
+        __threadfence();
+        const unsigned prev = atomicAdd(&counters[m], 1u);
+        s_last = (prev == ARGMAX_CHUNKS - 1) ? 1 : 0;
+        if (s_last) counters[m] = 0u;
+    }
+    __syncthreads();
+    if (!s_last) return;
     if (threadIdx.x < 32) {
-        const int nw = blockDim.x >> 5;
-        best = ((int)threadIdx.x < nw) ? s_v[threadIdx.x] : -INFINITY;
-        bi = ((int)threadIdx.x < nw) ? s_i[threadIdx.x] : 0x7fffffff;
-        for (int o = 16; o > 0; o >>= 1) {
-            float ov = __shfl_xor_sync(0xffffffffu, best, o);
-            int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-            if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
-        }
+        __threadfence();
+        best = __ldcg(&part_v[m * ARGMAX_CHUNKS + threadIdx.x]);
+        bi = __ldcg(&part_i[m * ARGMAX_CHUNKS + threadIdx.x]);
+        for (int o = 16; o > 0; o >>= 1)
+            argmax_combine(best, bi, __shfl_xor_sync(0xffffffffu, best, o), __shfl_xor_sync(0xffffffffu, bi, o));
         if (threadIdx.x == 0) {
             if (bi == 0x7fffffff) bi = 0;      // all-NaN row: stay in range
             a.tokens_out[m] = bi;
             if (a.pos_inc != nullptr) a.pos_inc[m] += 1;
             if (a.history != nullptr) {
                 const uint32_t c = ld_volatile_u32(a.step_counter);
-                a.history[(size_t)((c - 1u) % (uint32_t)a.history_cap) * gridDim.x + m] = bi;
+                a.history[(size_t)((c - 1u) % (uint32_t)a.history_cap) * M + m] = bi;
             }
         }
     }
 }
 
+extern "C" long long dl_argmax_scratch_bytes(int M) { return 1024 + (long long)M * ARGMAX_CHUNKS * 8; }
+
 extern "C" int dl_argmax(const float* logits, int M, int vocab, int ld, int* tokens_out, const uint32_t* flags,
                          int n_flags, const uint32_t* step_counter, uint32_t flag_mul, uint32_t flag_add, int* pos_inc,
-                         int* history, int history_cap, int pdl, void* stream) {
+                         int* history, int history_cap, void* scratch, int pdl, void* stream) {
+    static_assert(ARGMAX_CHUNKS == 32, "final reduce assumes one warp of chunk winners");
     ArgmaxArgs a;
     a.logits = logits; a.vocab = vocab; a.ld = ld; a.tokens_out = tokens_out;
     a.flags = flags; a.n_flags = n_flags; a.step_counter = step_counter; a.flag_mul = flag_mul; a.flag_add = flag_add;
     a.pos_inc = pos_inc; a.history = history; a.history_cap = history_cap;
+    a.scratch = reinterpret_cast<uint8_t*>(scratch);
     if (history != nullptr && step_counter == nullptr) { dl_set_error("dl_argmax: history needs step_counter"); return -1; }
+    if (scratch == nullptr || M > 256) { dl_set_error("dl_argmax: needs zero-initialised scratch (dl_argmax_scratch_bytes) and M <= 256"); return -1; }
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(M);
-    cfg.blockDim = dim3(1024);
+    cfg.gridDim = dim3(ARGMAX_CHUNKS, M);
+    cfg.blockDim = dim3(ARGMAX_THREADS);
     cfg.stream = (cudaStream_t)stream;
     cudaLaunchAttribute attr[1];
     if (pdl) {

@@ -162,6 +162,8 @@ class LlamaEngine:
         self.max_splits = 32
         self.att_scratch = torch.zeros(K.attention_scratch_bytes(R, self.n_heads_loc, self.hs, self.max_splits),
                                        dtype=torch.uint8, device=dev)
+        self.argmax_scratch = torch.zeros(int(K.cuda_lib().dl_argmax_scratch_bytes(256)), dtype=torch.uint8,
+                                          device=dev)
         self._graphs: Dict[Tuple, torch.cuda.CUDAGraph] = {}
         self._graph_launches: Dict[Tuple, int] = {}
         self._graph_stream = torch.cuda.Stream(device=dev)
@@ -255,11 +257,12 @@ class LlamaEngine:
     # ------------------------------------------------------------------------------------------------
     # the forward pass (launch sequence)
     # ------------------------------------------------------------------------------------------------
-    def _matmul(self, w, d, n, M, xq, xh, epi, kind):
+    def _matmul(self, w, d, n, M, xq, xh, epi, kind, norm=None):
         if M <= GEMV_MAX_M:
             R, S = K.choose_splits(d, n, kind, self.n_sms, M)
-            K.gemv_q40(w, d, n, xq, GEMV_MAX_M, M, epi, R, S, pdl=self.use_pdl)
+            K.gemv_q40(w, d, n, None if norm is not None else xq, M, epi, R, S, norm=norm, pdl=self.use_pdl)
         else:
+            assert norm is None
             row_tiles = (d + 127) // 128
             S = 1
             if M <= 32:
@@ -273,62 +276,76 @@ class LlamaEngine:
         gemv = M <= GEMV_MAX_M
         xq = lambda t: t if gemv else None
         xh = lambda t: None if gemv else t
-        mcap = GEMV_MAX_M if gemv else self.ncap
+        mcap = M if gemv else self.ncap               # XQ slabs are written with row capacity == M
         L = h.n_layers
-        R = self.max_rows
-        src_stride = R * h.dim
+        src_stride = self.max_rows * h.dim
         multi = N > 1
         sc = self.step_counter
+        eps = h.norm_epsilon
+        # Residual bookkeeping.  TP>1 (and the tensor-core path): matmul epilogues push Q80-cast partial
+        # sums to every rank's exchange buffer; the next norm merges them (x ping-pongs between two
+        # buffers).  TP=1 GEMV path: the wo/w2 epilogues add the Q80-cast product into x in place.
+        inplace = gemv and not multi
         K.embedding(self.embedding, self.tokens, self.x[0], M, h.dim, _IntPtr(sc))
         cur = 0
         n_splits = self._attention_splits(M)
+
+        def norm_then(w_norm, pending, flag_add, weight, d, kind, epi, x_off=0, rows=M):
+            """RMSNorm(+merge of `pending` partials) feeding a dim->d matmul."""
+            nonlocal cur
+            merge = pending is not None and not inplace
+            x_in = _Off(self.x[cur], x_off)
+            x_out = _Off(self.x[cur ^ 1], x_off) if merge else None
+            parts = (pending[0][self.rank] + x_off) if merge else None
+            flags = pending[1] if (merge and multi) else None
+            if rows <= GEMV_MAX_M:
+                nm = K.norm_prolog(x_in, x_out, parts, N, src_stride, flags, sc, L, flag_add, w_norm, eps)
+                self._matmul(weight, d, h.dim, rows, None, None, epi, kind, norm=nm)
+            else:
+                K.reduce_norm_quant(x_in, x_out, parts, N if merge else 0, src_stride, flags, sc, L, flag_add, w_norm,
+                                    eps, h.dim, rows, self.ncap, None, self.xh_dim, pdl=pdl)
+                self._matmul(weight, d, h.dim, rows, None, self.xh_dim, epi, kind)
+            if merge:
+                cur ^= 1
+
+        def push(buf_ptrs, flags_peer, flag_add, counter):
+            if inplace:
+                xp = self.x[cur].data_ptr()
+                return K.epi_store([xp], h.dim, 0, self.sync_q80, residual=xp, residual_ld=h.dim)
+            return K.epi_store(buf_ptrs, h.dim, self.rank * src_stride, self.sync_q80,
+                               flags_peer if multi else None, sc, L, flag_add, counter)
+
+        pending = None
         for l, W in enumerate(self.layers):
             # --- attention block ---
-            if l == 0:
-                K.reduce_norm_quant(self.x[0], None, None, 0, 0, None, None, 0, 0, W["rms_att"], h.norm_epsilon,
-                                    h.dim, M, mcap, xq(self.xq_dim), xh(self.xh_dim), pdl=pdl)
-            else:
-                K.reduce_norm_quant(self.x[cur], self.x[cur ^ 1], self.part_ffn[self.rank], N, src_stride,
-                                    self.flags_ffn_local if multi else None, sc, L, l, W["rms_att"], h.norm_epsilon,
-                                    h.dim, M, mcap, xq(self.xq_dim), xh(self.xh_dim), pdl=pdl)
-                cur ^= 1
             epi = K.epi_qkv_rope(self.q, self.q_loc, self.kv_loc, self.hs, self.rope_freqs, self.pos, self.slot,
                                  self.block_table, self.max_pages, self.n_kv_loc, self.k_cache[l], self.v_cache[l])
-            self._matmul(W["qkv"], self.qkv_d, h.dim, M, self.xq_dim, self.xh_dim, epi, EPI_QKV_ROPE)
+            norm_then(W["rms_att"], pending, l, W["qkv"], self.qkv_d, EPI_QKV_ROPE, epi)
             K.attention(self.q, M, self.n_heads_loc, self.n_kv_loc, self.hs, self.k_cache[l], self.v_cache[l], self.pos,
                         self.slot, self.block_table, self.max_pages, n_splits, self.att_scratch, xq(self.xq_att),
                         xh(self.xh_att), mcap, pdl=pdl)
-            epi = K.epi_store(self.part_att, h.dim, self.rank * src_stride, self.sync_q80,
-                              self.flags_att_peer if multi else None, sc, L, l + 1, self.cta_counters[0])
-            self._matmul(W["wo"], h.dim, self.q_loc, M, self.xq_att, self.xh_att, epi, EPI_STORE)
+            self._matmul(W["wo"], h.dim, self.q_loc, M, self.xq_att, self.xh_att,
+                         push(self.part_att, self.flags_att_peer, l + 1, self.cta_counters[0]), EPI_STORE)
+            pending = (self.part_att, self.flags_att_local)
             # --- feed-forward block ---
-            K.reduce_norm_quant(self.x[cur], self.x[cur ^ 1], self.part_att[self.rank], N, src_stride,
-                                self.flags_att_local if multi else None, sc, L, l + 1, W["rms_ffn"], h.norm_epsilon,
-                                h.dim, M, mcap, xq(self.xq_dim), xh(self.xh_dim), pdl=pdl)
-            cur ^= 1
             epi = K.epi_silu_mul(xq(self.xq_hid), xh(self.xh_hid), mcap, gelu=(h.hidden_act != HIDDEN_ACT_SILU))
-            self._matmul(W["w13"], 2 * self.hid_loc, h.dim, M, self.xq_dim, self.xh_dim, epi, EPI_SILU_MUL)
-            epi = K.epi_store(self.part_ffn, h.dim, self.rank * src_stride, self.sync_q80,
-                              self.flags_ffn_peer if multi else None, sc, L, l + 1, self.cta_counters[1])
-            self._matmul(W["w2"], h.dim, self.hid_loc, M, self.xq_hid, self.xh_hid, epi, EPI_STORE)
+            norm_then(W["rms_ffn"], pending, l + 1, W["w13"], 2 * self.hid_loc, EPI_SILU_MUL, epi)
+            self._matmul(W["w2"], h.dim, self.hid_loc, M, self.xq_hid, self.xh_hid,
+                         push(self.part_ffn, self.flags_ffn_peer, l + 1, self.cta_counters[1]), EPI_STORE)
+            pending = (self.part_ffn, self.flags_ffn_local)
         # --- final norm + logits for rows row0.. ---
         Ml = M - row0
-        gemv_l = Ml <= GEMV_MAX_M
-        mcap_l = GEMV_MAX_M if gemv_l else self.ncap
-        off = row0 * h.dim * 4
-        K.reduce_norm_quant(_Off(self.x[cur], off), _Off(self.x[cur ^ 1], off), self.part_ffn[self.rank] + off, N,
-                            src_stride, self.flags_ffn_local if multi else None, sc, L, L, self.rms_final,
-                            h.norm_epsilon, h.dim, Ml, mcap_l, self.xq_dim if gemv_l else None,
-                            None if gemv_l else self.xh_dim, pdl=pdl)
         epi = K.epi_store(self.logits_ptrs, h.vocab_size, self.rank * self.vocab_loc, False,
                           self.flags_log_peer if multi else None, sc, 1, 0, self.cta_counters[2])
-        self._matmul(self.wcls, self.vocab_loc, h.dim, Ml, self.xq_dim, self.xh_dim, epi, EPI_STORE)
+        norm_then(self.rms_final, pending, L, self.wcls, self.vocab_loc, EPI_STORE, epi, x_off=row0 * h.dim * 4,
+                  rows=Ml)
         if greedy:
             K.argmax(self.logits, Ml, h.vocab_size, h.vocab_size,
                      self.tokens if device_loop else self.out_tokens,
                      self.flags_log_local if multi else None, N, sc, 1, 0,
                      pos_inc=self.pos if device_loop else None,
-                     history=self.history if device_loop else None, history_cap=self.history_cap, pdl=pdl)
+                     history=self.history if device_loop else None, history_cap=self.history_cap,
+                     scratch=self.argmax_scratch, pdl=pdl)
         elif multi:
             K.wait_flags(self.flags_log_local, N, sc, 1, 0)
 

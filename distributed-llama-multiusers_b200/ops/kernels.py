@@ -11,7 +11,7 @@ from typing import List, Optional, Sequence
 import torch
 
 from . import lib
-from .lib import DlEpilogue, EPI_QKV_ROPE, EPI_SILU_MUL, EPI_STORE, check, cuda_lib
+from .lib import DlEpilogue, DlNormProlog, EPI_QKV_ROPE, EPI_SILU_MUL, EPI_STORE, check, cuda_lib
 
 Q40T_TILE_BYTES = 9216
 XQ_ROW_BYTES = 160
@@ -74,9 +74,12 @@ def make_q40t(raw_q40: torch.Tensor, d: int, n: int) -> torch.Tensor:
 # ---- epilogue builders ---------------------------------------------------------------------------
 def epi_store(dst: Sequence[int], ld: int, dst_off: int = 0, q80_roundtrip: bool = False,
               flags: Optional[Sequence[int]] = None, step_counter: Optional[int] = None, flag_mul: int = 0,
-              flag_add: int = 0, cta_counter: Optional[int] = None) -> DlEpilogue:
+              flag_add: int = 0, cta_counter: Optional[int] = None, residual: Optional[int] = None,
+              residual_ld: int = 0) -> DlEpilogue:
     e = DlEpilogue()
     e.kind = EPI_STORE
+    e.residual = residual
+    e.residual_ld = residual_ld
     e.n_dst = len(dst)
     for i, p in enumerate(dst):
         e.dst[i] = p
@@ -141,9 +144,29 @@ def embedding(table: torch.Tensor, tokens: torch.Tensor, x: torch.Tensor, M: int
     lib.count_launch()
 
 
-def gemv_q40(w: torch.Tensor, d: int, n: int, xq: torch.Tensor, mcap: int, M: int, epi: DlEpilogue,
-             row_split: int = 1, k_split: int = 1, pdl: bool = False):
-    check(cuda_lib().dl_gemv_q40(w.data_ptr(), d, n, xq.data_ptr(), mcap, M, row_split, k_split, C.byref(epi),
+def norm_prolog(x_in, x_out, partials: Optional[int], n_src: int, src_stride: int, flags: Optional[int],
+                step_counter: Optional[int], flag_mul: int, flag_add: int, norm_w: torch.Tensor,
+                eps: float) -> DlNormProlog:
+    """Fused merge-add + RMSNorm + Q80 prologue of the GEMV (x_in/x_out: tensors or objects with data_ptr)."""
+    p = DlNormProlog()
+    p.x_in = _p(x_in)
+    p.x_out = _p(x_out)
+    p.partials = partials
+    p.n_src = n_src if partials else 0
+    p.src_stride = src_stride
+    p.flags = flags
+    p.step_counter = step_counter
+    p.flag_mul, p.flag_add = flag_mul, flag_add
+    p.norm_w = norm_w.data_ptr()
+    p.eps = eps
+    return p
+
+
+def gemv_q40(w: torch.Tensor, d: int, n: int, xq: Optional[torch.Tensor], M: int, epi: DlEpilogue,
+             row_split: int = 1, k_split: int = 1, norm: Optional[DlNormProlog] = None, pdl: bool = False):
+    """M<=8 rows.  Activations: XQ slabs with row capacity == M (xq), or the fused norm prologue."""
+    check(cuda_lib().dl_gemv_q40(w.data_ptr(), d, n, _p(xq), M, row_split, k_split,
+                                 C.byref(norm) if norm is not None else None, C.byref(epi),
                                  1 if pdl else 0, _stream()), "dl_gemv_q40")
     lib.count_launch()
 
@@ -170,11 +193,28 @@ def attention(q, M, n_heads, n_kv_heads, head_size, k_cache, v_cache, pos, slot,
 
 
 def argmax(logits, M: int, vocab: int, ld: int, out: torch.Tensor, flags=None, n_flags=0, step_counter=None,
-           flag_mul=0, flag_add=0, pos_inc=None, history=None, history_cap=0, pdl=False):
+           flag_mul=0, flag_add=0, pos_inc=None, history=None, history_cap=0, scratch=None, pdl=False):
     lp = logits.data_ptr() if isinstance(logits, torch.Tensor) else logits
+    if scratch is None:
+        scratch = _argmax_scratch(M, out.device)
     check(cuda_lib().dl_argmax(lp, M, vocab, ld, out.data_ptr(), flags, n_flags, step_counter, flag_mul, flag_add,
-                               _p(pos_inc), _p(history), history_cap, 1 if pdl else 0, _stream()), "dl_argmax")
+                               _p(pos_inc), _p(history), history_cap, scratch.data_ptr(), 1 if pdl else 0,
+                               _stream()), "dl_argmax")
     lib.count_launch()
+
+
+_ARGMAX_SCRATCH = {}
+
+
+def _argmax_scratch(M: int, device) -> torch.Tensor:
+    """Shared default scratch (zeroed once; the kernel leaves its counters at zero)."""
+    key = str(device)
+    t = _ARGMAX_SCRATCH.get(key)
+    need = int(cuda_lib().dl_argmax_scratch_bytes(256))
+    if t is None:
+        t = torch.zeros(need, dtype=torch.uint8, device=device)
+        _ARGMAX_SCRATCH[key] = t
+    return t
 
 
 def wait_flags(flags: int, n: int, step_counter: int, flag_mul: int, flag_add: int):
@@ -183,19 +223,23 @@ def wait_flags(flags: int, n: int, step_counter: int, flag_mul: int, flag_add: i
 
 
 def choose_splits(d: int, n: int, epi_kind: int, n_sms: int = 148, M: int = 1):
-    """Pick (row_split R, k_split S) so the GEMV grid covers the chip.
+    """Pick (row_split R, k_split S) so the GEMV grid covers the chip and its resident
+    activations fit in shared memory.
 
-    Each 128-row tile can be split into R row parts (R<=2 when the epilogue needs 64-row groups)
-    and its K range over a cluster of S CTAs (reduced through DSMEM)."""
+    K is split first (cluster of S CTAs, reduced through DSMEM): it keeps every pipeline stage a
+    full 9 KB tile.  Row splitting (R) shrinks the stages, so it is the last resort (R<=2 when the
+    epilogue needs 64-row groups)."""
     row_tiles = (d + 127) // 128
     kt = n // 128
     max_r = 2 if epi_kind == EPI_SILU_MUL else 4
     R, S = 1, 1
+    while S < 8 and S * 2 <= kt and int(cuda_lib().dl_gemv_q40_smem_bytes(n, M, S)) > 200 * 1024:
+        S *= 2
     while row_tiles * R * S < n_sms:
-        if R < max_r:
-            R *= 2
-        elif S < 8 and S * 2 <= kt:
+        if S < 8 and S * 2 <= kt and kt // (S * 2) >= 2:
             S *= 2
+        elif R < max_r:
+            R *= 2
         else:
             break
     return R, S

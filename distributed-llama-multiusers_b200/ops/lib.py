@@ -29,6 +29,8 @@ class DlEpilogue(C.Structure):
         ("ld", C.c_int),
         ("dst_off", C.c_longlong),
         ("q80_roundtrip", C.c_int),
+        ("residual", C.c_void_p),
+        ("residual_ld", C.c_int),
         ("flag", C.c_void_p * DL_MAX_PEERS),
         ("step_counter", C.c_void_p),
         ("flag_mul", C.c_uint32),
@@ -55,6 +57,23 @@ class DlEpilogue(C.Structure):
     ]
 
 
+class DlNormProlog(C.Structure):
+    """Mirror of ``DlNormProlog`` in include/dllama_b200.h."""
+    _fields_ = [
+        ("x_in", C.c_void_p),
+        ("x_out", C.c_void_p),
+        ("partials", C.c_void_p),
+        ("n_src", C.c_int),
+        ("src_stride", C.c_longlong),
+        ("flags", C.c_void_p),
+        ("step_counter", C.c_void_p),
+        ("flag_mul", C.c_uint32),
+        ("flag_add", C.c_uint32),
+        ("norm_w", C.c_void_p),
+        ("eps", C.c_float),
+    ]
+
+
 _cuda = None
 
 
@@ -78,13 +97,17 @@ def cuda_lib():
                                        vp, vp, vp, i32, vp]
     L.dl_quant_q80.argtypes = [vp, i32, i32, i32, vp, vp, vp]
     L.dl_embedding.argtypes = [vp, vp, vp, i32, i32, vp, vp]
-    L.dl_gemv_q40.argtypes = [vp, i32, i32, vp, i32, i32, i32, i32, C.POINTER(DlEpilogue), i32, vp]
+    L.dl_gemv_q40.argtypes = [vp, i32, i32, vp, i32, i32, i32, C.POINTER(DlNormProlog), C.POINTER(DlEpilogue), i32, vp]
+    L.dl_gemv_q40_smem_bytes.restype = i64
+    L.dl_gemv_q40_smem_bytes.argtypes = [i32, i32, i32]
     L.dl_gemm_q40_tc.argtypes = [vp, i32, i32, vp, i32, i32, i32, C.POINTER(DlEpilogue), i32, vp]
     L.dl_attention_scratch_bytes.restype = i64
     L.dl_attention_scratch_bytes.argtypes = [i32, i32, i32, i32]
     L.dl_attention.argtypes = [vp, i32, i32, i32, i32, vp, vp, i32, vp, vp, vp, i32, i32, i32, vp, vp, vp,
                                i32, vp, i32, vp]
-    L.dl_argmax.argtypes = [vp, i32, i32, i32, vp, vp, i32, vp, u32, u32, vp, vp, i32, i32, vp]
+    L.dl_argmax.argtypes = [vp, i32, i32, i32, vp, vp, i32, vp, u32, u32, vp, vp, i32, vp, i32, vp]
+    L.dl_argmax_scratch_bytes.restype = i64
+    L.dl_argmax_scratch_bytes.argtypes = [i32]
     L.dl_wait_flags.argtypes = [vp, i32, vp, u32, u32, vp]
     L.dl_ipc_alloc.argtypes = [C.POINTER(vp), i64, vp]
     L.dl_ipc_open.argtypes = [vp, C.POINTER(vp)]

@@ -32,6 +32,8 @@ typedef struct {
     int ld;
     long long dst_off;
     int q80_roundtrip;
+    const float* residual;            /* NULL, or value += residual[m*residual_ld + row] (TP=1 residual add) */
+    int residual_ld;
     uint32_t* flag[DL_MAX_PEERS];     /* flag word to release on each destination (NULL: none) */
     const uint32_t* step_counter;     /* epoch = *step_counter * flag_mul + flag_add           */
     uint32_t flag_mul, flag_add;
@@ -53,6 +55,24 @@ typedef struct {
     int out_mcap;                     /* row capacity of the XQ/XH slabs */
     int act_gelu;                     /* 0 = SiLU, 1 = tanh-GELU */
 } DlEpilogue;
+
+/* Fused activation producer for dl_gemv_q40: the kernel itself computes
+ *   x = x_in + sum_src partial[src];  y = rmsnorm(x) * norm_w;  Q80(y)
+ * for its own K range straight into shared memory (no global round trip, no separate kernel), after
+ * waiting on the peers' release flags.  The CTAs of row tile 0 also write x to x_out.
+ * (reference: OP_MERGE_ADD + OP_INV_RMS + OP_RMS_NORM + OP_CAST, src/llm.cpp:204-239,317-342) */
+typedef struct {
+    const float* x_in;                /* [M][dim] residual stream */
+    float* x_out;                     /* [M][dim] or NULL */
+    const float* partials;            /* [n_src][..] partial sums, src_stride floats apart; may be NULL */
+    int n_src;
+    long long src_stride;
+    const uint32_t* flags;            /* [n_src] release flags to wait on, or NULL */
+    const uint32_t* step_counter;
+    uint32_t flag_mul, flag_add;
+    const float* norm_w;              /* [dim] */
+    float eps;
+} DlNormProlog;
 
 const char* dl_last_error(void);
 int dl_device_sm_count(void);
@@ -85,8 +105,11 @@ int dl_embedding(const float* table, const int* tokens, float* x, int M, int dim
 /* ---- Q40 x Q80 matmuls ------------------------------------------------------------------- */
 /* dp4a GEMV, M <= 8 rows: bulk-copy fed, cluster split-K (reference: matmul_Q80_Q40_F32,
  * src/nn/nn-cpu-ops.cpp:222-440) */
-int dl_gemv_q40(const uint8_t* w_q40t, int d, int n, const uint8_t* xq, int mcap, int M, int row_split,
-                int k_split, const DlEpilogue* epi /*host*/, int pdl, void* stream);
+int dl_gemv_q40(const uint8_t* w_q40t, int d, int n, const uint8_t* xq /*XQ slabs with mcap == M; unused when norm != NULL*/,
+                int M, int row_split, int k_split, const DlNormProlog* norm /*host, NULL = read xq*/,
+                const DlEpilogue* epi /*host*/, int pdl, void* stream);
+/* shared-memory bytes the GEMV needs for (n, M, k_split); callers pick k_split so that it fits */
+long long dl_gemv_q40_smem_bytes(int n, int M, int k_split);
 /* tcgen05 GEMM, M up to 256 per tile: Q40 dequantised to fp16 in the smem pipeline, UMMA with
  * TMEM accumulators (reference: llamafile_sgemm Q40xQ80, src/nn/llamafile/sgemm.cpp:593-783) */
 int dl_gemm_q40_tc(const uint8_t* w_q40t, int d, int n, const uint8_t* xh, int ncap, int M, int k_split,
@@ -108,8 +131,9 @@ int dl_attention(const float* q, int M, int n_heads, int n_kv_heads, int head_si
 int dl_argmax(const float* logits, int M, int vocab, int ld, int* tokens_out,
               const uint32_t* flags /*NULL: no wait*/, int n_flags, const uint32_t* step_counter,
               uint32_t flag_mul, uint32_t flag_add, int* pos_inc /*NULL or pos[m] += 1*/,
-              int* history /*NULL or [cap][M] ring indexed by *step_counter-1*/, int history_cap, int pdl,
-              void* stream);
+              int* history /*NULL or [cap][M] ring indexed by *step_counter-1*/, int history_cap,
+              void* scratch /*zero-initialised, dl_argmax_scratch_bytes(M)*/, int pdl, void* stream);
+long long dl_argmax_scratch_bytes(int M);
 /* block the stream until flags[i] >= *step_counter*flag_mul+flag_add for i<n (logits gather to the
  * sampling rank; reference: SYNC_NODE_SLICES_EXCEPT_ROOT, src/llm.cpp:432) */
 int dl_wait_flags(const uint32_t* flags, int n, const uint32_t* step_counter, uint32_t flag_mul,
