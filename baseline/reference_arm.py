@@ -1,0 +1,155 @@
+"""Reference arm of bench.py: runs the UNMODIFIED reference (`dllama inference`, CPU, root + workers
+over loopback TCP) on the same model shape / metric and reports the same JSON line.
+
+The reference is a Makefile C++ project, not a Python package, so the prescribed
+`pip install --target baseline/_ref /root/reference` cannot work ("Neither 'setup.py' nor
+'pyproject.toml' found" -- recorded in DESIGN.md).  Instead its sources are staged, byte for byte,
+under baseline/_ref/reference/ (git-ignored, shipped with the gpurun snapshot) and built here with
+its own Makefile (`make dllama`, g++ -O3 -march=native) in a scratch directory at run time, so the
+binary matches the CPU of the box it runs on.  None of this repo's models, kernels or engine is on
+that path: only the random `.m` / `.t` files (written in the reference's own formats) are shared.
+
+Launch shape: N = --gpus nodes = 1 root + (N-1) `dllama worker` processes on 127.0.0.1, exactly
+like examples/n-workers.sh; the driver starts this arm under torchrun for N>1, so only RANK 0
+acts and the other ranks exit immediately.
+"""
+from __future__ import annotations
+
+import json
+import os
+import re
+import shutil
+import signal
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF_SRC = os.path.join(ROOT, "baseline", "_ref", "reference")
+
+
+def _stage_sources():
+    if os.path.isdir(os.path.join(REF_SRC, "src")):
+        return
+    if os.path.isdir("/root/reference/src"):
+        os.makedirs(REF_SRC, exist_ok=True)
+        for item in ("src", "Makefile", "LICENSE"):
+            src = os.path.join("/root/reference", item)
+            dst = os.path.join(REF_SRC, item)
+            if os.path.isdir(src):
+                shutil.copytree(src, dst, dirs_exist_ok=True)
+            else:
+                shutil.copy(src, dst)
+        return
+    raise RuntimeError("reference sources are not staged under baseline/_ref/reference")
+
+
+def build_reference() -> str:
+    """make dllama in a scratch copy; returns the binary path."""
+    _stage_sources()
+    out_dir = os.path.join(tempfile.gettempdir(), "dllama_ref_build")
+    binary = os.path.join(out_dir, "dllama")
+    if os.path.exists(binary):
+        return binary
+    if os.path.isdir(out_dir):
+        shutil.rmtree(out_dir)
+    shutil.copytree(REF_SRC, out_dir)
+    p = subprocess.run(["make", "dllama"], cwd=out_dir, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if p.returncode != 0 or not os.path.exists(binary):
+        raise RuntimeError("reference build failed: " + p.stdout[-400:])
+    return binary
+
+
+def _prompt_and_count(tok_path: str, n_target: int):
+    """A text prompt and the number of tokens the reference's encoder (BOS + merges) gives it."""
+    sys.path.insert(0, ROOT)
+    from dllama_b200.text.native import Tokenizer
+    tok = Tokenizer(tok_path)
+    words = ["hello", "world", "the", "of", "and", "you", "is", "it", "to", "a"]
+    text, i = "", 0
+    while True:
+        cand = text + (" " if text else "") + words[i % len(words)]
+        n = len(tok.encode(cand, add_bos=True, add_special_tokens=False))
+        if n > n_target:
+            break
+        text, i = cand, i + 1
+    return text, len(tok.encode(text, add_bos=True, add_special_tokens=False))
+
+
+def run_reference_arm(args, metric: str) -> dict:
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        sys.exit(0)
+    sys.path.insert(0, ROOT)
+    from dllama_b200.formats import mfile, tfile
+    from dllama_b200.ops import quant
+    binary = build_reference()
+    name = args.model + (f"-l{args.layers}" if args.layers else "")
+    mpath = os.path.join(args.model_dir, f"dllama_b200_{name}_q40.m")
+    tpath = os.path.join(args.model_dir, f"dllama_b200_{args.model}.t")
+    if not os.path.exists(mpath):
+        mfile.write_random_model(mpath, args.model, quant.Q40, seed=1, n_layers=args.layers or None)
+    if not os.path.exists(tpath):
+        tfile.write_synthetic_tokenizer(tpath, mfile.MODEL_SHAPES[args.model]["vocab_size"])
+    N, K_, W = args.gpus, args.steps, args.warmup
+    prompt, n_prompt = _prompt_and_count(tpath, min(args.prompt_len, 32))
+    steps = n_prompt - 1 + W + K_
+    ncpu = os.cpu_count() or 8
+    # the reference's executor spin-waits on every thread: never oversubscribe the box
+    nthreads = args.nthreads or max(1, min(32, ncpu // N - (1 if ncpu // N > 2 else 0)))
+    workers, procs = [], []
+    try:
+        for i in range(1, N):
+            port = 9990 + i
+            procs.append(subprocess.Popen([binary, "worker", "--port", str(port), "--nthreads", str(nthreads)],
+                                          stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL,
+                                          preexec_fn=os.setsid))
+            workers.append(f"127.0.0.1:{port}")
+        if workers:
+            time.sleep(1.0)
+        cmd = [binary, "inference", "--model", mpath, "--tokenizer", tpath, "--buffer-float-type", "q80",
+               "--prompt", prompt, "--steps", str(steps), "--nthreads", str(nthreads), "--max-seq-len", "2048",
+               "--temperature", "0", "--seed", "1"]
+        if workers:
+            cmd += ["--workers"] + workers
+        root = subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True,
+                                preexec_fn=os.setsid)
+        procs.append(root)
+        pred_ms, lines = [], []
+        t_deadline = time.time() + 3000
+        # the fork never exits after the summary (src/app.cpp:299-309): read until the summary, then kill
+        for line in root.stdout:
+            lines.append(line)
+            m = re.search(r"Pred\s*(\d+) ms Sync\s*(\d+) ms", line)
+            if m:
+                pred_ms.append(int(m.group(1)) + int(m.group(2)))
+            if line.strip().startswith("tokens/s:") and any(l.strip().startswith("Prediction") for l in lines[-4:]):
+                break
+            if time.time() > t_deadline:
+                break
+        summary = "".join(lines[-10:])
+    finally:
+        for p in procs:
+            try:
+                os.killpg(os.getpgid(p.pid), signal.SIGKILL)
+            except Exception:
+                pass
+    m = re.search(r"Prediction\s+nTokens:\s*(\d+)\s+tokens/s:\s*([\d.]+)\s*\(([\d.]+) ms/tok\)", summary)
+    if not m:
+        raise RuntimeError("could not parse the reference's summary: " + summary[-200:].replace("\n", " | "))
+    timed = pred_ms[W:W + K_] if len(pred_ms) >= W + K_ else pred_ms
+    # per-step times are printed in whole milliseconds; the summary block has the exact total
+    ms_per_step = float(m.group(3)) if not timed or min(timed) < 20 else sum(timed) / len(timed)
+    return {
+        "metric": metric, "value": round(1000.0 / ms_per_step, 3), "unit": "tokens/s", "n_gpus": N, "steps": K_,
+        "warmup": W, "ms_per_step": round(ms_per_step, 3), "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "q40 weights x q80 activations (reference CPU kernels)",
+        "data": "synthetic (same random-init .m; text prompt of %d tokens)" % n_prompt,
+        "config": {"model": args.model + (f"-{args.layers}layers-DEBUG" if args.layers else ""), "global_batch": 1,
+                   "seq_len": steps, "parallelism": f"tp{N} (root + {N - 1} workers, loopback TCP)",
+                   "nthreads_per_node": nthreads, "host_cpus": ncpu,
+                   "timing": "reference's own executor timers (Pred+Sync per token)"},
+        "impl": "reference", "gpu_launches": 0,
+        "reference_summary_tokens_per_s": float(m.group(2)),
+    }

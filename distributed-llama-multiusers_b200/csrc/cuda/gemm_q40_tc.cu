@@ -256,9 +256,9 @@ extern "C" int dl_gemm_q40_tc(const uint8_t* w_q40t, int d, int n, const uint8_t
     if (k_split > a.KT) k_split = 1;
     a.S = k_split;
     // stage counts by tile width: A(raw) 9 KB, B NT*256 B, H 32 KB, out 16 KB  (<= ~200 KB)
-    if (a.NT <= 32) { a.NSA = 4; a.NSB = 4; a.NSH = 3; }
-    else if (a.NT == 64) { a.NSA = 4; a.NSB = 3; a.NSH = 3; }
-    else { a.NSA = 4; a.NSB = 2; a.NSH = 2; }
+    if (a.NT <= 32) { a.NSA = 8; a.NSB = 4; a.NSH = 3; }
+    else if (a.NT == 64) { a.NSA = 6; a.NSB = 3; a.NSH = 3; }
+    else { a.NSA = 8; a.NSB = 2; a.NSH = 2; }
     a.n_epi_ctas = (a.d_pad / 128) * ((M + a.NT - 1) / a.NT);
     a.epi = *epi;
     const size_t smem = (size_t)a.NSH * TC_A_BYTES + (size_t)a.NSB * a.NT * 256 + (size_t)a.NSA * Q40T_TILE_BYTES +

@@ -40,7 +40,7 @@ struct GemvArgs {
 };
 
 template <int MT>
-__global__ void __launch_bounds__(GEMV_THREADS, 1) gemv_q40_kernel(const __grid_constant__ GemvArgs a) {
+__global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_q40_kernel(const __grid_constant__ GemvArgs a) {
     extern __shared__ __align__(128) uint8_t smem[];
     const int S = a.S, R = a.R, M = a.M;
     const int nk_max = (a.KT + S - 1) / S;
@@ -148,28 +148,54 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) gemv_q40_kernel(const __grid_
             }
             inv[m] = 1.0f / sqrtf(t / (float)dim + nm.eps);
         }
-        // pass 2: y = w * (inv * x) -> Q80 -> resident activation slabs (one warp per 32-block)
+        // pass 2: y = w * (inv * x) -> Q80 -> resident activation slabs.  One THREAD per 32-block: its 8
+        // float4 loads per operand are independent (one L2 round trip, lines are hot from pass 1), the
+        // abs-max / rounding / sum need no shuffles, and the block is written with two 16-byte stores.
         const int nkb = nk * 4;
-        for (int item = warp; item < M * nkb; item += GEMV_WARPS) {
+        for (int item = tid; item < M * nkb; item += GEMV_THREADS) {
             const int m = item / nkb, b = item % nkb;
-            const int e = e0 + b * 32 + lane;
-            float v = nm.x_in[(size_t)m * dim + e];
-            for (int s = 0; s < nm.n_src; s++) v += nm.partials[(size_t)s * nm.src_stride + (size_t)m * dim + e];
+            const size_t e = (size_t)m * dim + e0 + b * 32;
+            float4 v[8];
+#pragma unroll
+            for (int j = 0; j < 8; j++) v[j] = reinterpret_cast<const float4*>(nm.x_in + e)[j];
+            for (int s = 0; s < nm.n_src; s++) {
+                const float4* p = reinterpret_cast<const float4*>(nm.partials + (size_t)s * nm.src_stride + e);
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                    const float4 t = p[j];
+                    v[j].x += t.x; v[j].y += t.y; v[j].z += t.z; v[j].w += t.w;
+                }
+            }
             float im = inv[0];
 #pragma unroll
             for (int q = 1; q < MT; q++) im = (m == q) ? inv[q] : im;
-            const float y = nm.norm_w[e] * (im * v);
-            const float amax = warp_max(fabsf(y));
+            const float4* wn = reinterpret_cast<const float4*>(nm.norm_w + e0 + b * 32);
+            float amax = 0.0f;
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                const float4 w4 = wn[j];
+                v[j].x = w4.x * (im * v[j].x); v[j].y = w4.y * (im * v[j].y);
+                v[j].z = w4.z * (im * v[j].z); v[j].w = w4.w * (im * v[j].w);
+                amax = fmaxf(amax, fmaxf(fmaxf(fabsf(v[j].x), fabsf(v[j].y)), fmaxf(fabsf(v[j].z), fabsf(v[j].w))));
+            }
             const float d = amax / 127.0f;
             const float id = (d != 0.0f) ? (1.0f / d) : 0.0f;
-            const int qv = __float2int_rn(y * id);
-            const int sumq = warp_sum_i(qv);
-            uint8_t* rowp = act_s + ((size_t)(b >> 2) * M + m) * XQ_ROW_BYTES;
-            reinterpret_cast<int8_t*>(rowp)[(b & 3) * 32 + lane] = (int8_t)qv;
-            if (lane == 0) {
-                reinterpret_cast<float*>(rowp + 128)[b & 3] = __half2float(__float2half_rn(d));
-                reinterpret_cast<int*>(rowp + 144)[b & 3] = 8 * sumq;
+            int sumq = 0;
+            uint32_t packed[8];
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                const int q0 = __float2int_rn(v[j].x * id), q1 = __float2int_rn(v[j].y * id);
+                const int q2 = __float2int_rn(v[j].z * id), q3 = __float2int_rn(v[j].w * id);
+                sumq += q0 + q1 + q2 + q3;
+                packed[j] = (uint32_t)(q0 & 0xff) | ((uint32_t)(q1 & 0xff) << 8) | ((uint32_t)(q2 & 0xff) << 16) |
+                            ((uint32_t)(q3 & 0xff) << 24);
             }
+            uint8_t* rowp = act_s + ((size_t)(b >> 2) * M + m) * XQ_ROW_BYTES;
+            uint4* qdst = reinterpret_cast<uint4*>(rowp + (b & 3) * 32);
+            qdst[0] = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+            qdst[1] = make_uint4(packed[4], packed[5], packed[6], packed[7]);
+            reinterpret_cast<float*>(rowp + 128)[b & 3] = __half2float(__float2half_rn(d));
+            reinterpret_cast<int*>(rowp + 144)[b & 3] = 8 * sumq;
         }
         __syncthreads();
     }

@@ -155,23 +155,18 @@ __global__ void __launch_bounds__(RNQ_THREADS) reduce_norm_quant_kernel(const __
         }
         __syncthreads();
     }
-    // 32-element blocks are dealt round-robin to warps: block b -> warp b % nwarps (lane = element)
-    const int nblocks = a.dim / 32;
+    // pass 1: merged residual (float4, coalesced) -> x_out, sum of squares
     constexpr int nwarps = RNQ_THREADS / 32;
-    float vals[RNQ_MAX_PER_THREAD];
+    const size_t row = (size_t)m * a.dim;
     float ss = 0.0f;
-#pragma unroll
-    for (int c = 0; c < RNQ_MAX_PER_THREAD; c++) {
-        const int b = warp + c * nwarps;
-        vals[c] = 0.0f;
-        if (b < nblocks) {
-            const int i = b * 32 + lane;
-            float v = (a.x_in != nullptr) ? a.x_in[(size_t)m * a.dim + i] : 0.0f;
-            for (int s = 0; s < a.n_src; s++) v += a.partials[(size_t)s * a.src_stride + (size_t)m * a.dim + i];
-            if (a.x_out != nullptr) a.x_out[(size_t)m * a.dim + i] = v;
-            vals[c] = v;
-            ss += v * v;
+    for (int i4 = tid; i4 < a.dim / 4; i4 += RNQ_THREADS) {
+        float4 v = reinterpret_cast<const float4*>(a.x_in + row)[i4];
+        for (int s = 0; s < a.n_src; s++) {
+            const float4 p = reinterpret_cast<const float4*>(a.partials + (size_t)s * a.src_stride + row)[i4];
+            v.x += p.x; v.y += p.y; v.z += p.z; v.w += p.w;
         }
+        if (a.x_out != nullptr) reinterpret_cast<float4*>(a.x_out + row)[i4] = v;
+        ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
     }
     ss = warp_sum(ss);
     if (lane == 0) s_part[warp] = ss;
@@ -182,16 +177,77 @@ __global__ void __launch_bounds__(RNQ_THREADS) reduce_norm_quant_kernel(const __
         if (lane == 0) s_inv = 1.0f / sqrtf(t / (float)a.dim + a.eps);
     }
     __syncthreads();
-    const float inv = s_inv;
+    const float inv = (a.norm_w != nullptr) ? s_inv : 1.0f;
+    // pass 2: one thread per 32-block (independent 16-byte loads, no shuffles)
+    for (int b = tid; b < a.dim / 32; b += RNQ_THREADS) {
+        const size_t e = row + (size_t)b * 32;
+        float4 v[8];
 #pragma unroll
-    for (int c = 0; c < RNQ_MAX_PER_THREAD; c++) {
-        const int b = warp + c * nwarps;
-        if (b < nblocks) {
-            const int i = b * 32 + lane;
-            float y = vals[c];
-            if (a.norm_w != nullptr) y = a.norm_w[i] * (inv * y);
-            if (a.y_out != nullptr) a.y_out[(size_t)m * a.dim + i] = y;
-            if (a.xq_out != nullptr || a.xh_out != nullptr) q80_block_store(y, lane, m, b, a.mcap, a.xq_out, a.xh_out);
+        for (int j = 0; j < 8; j++) v[j] = reinterpret_cast<const float4*>(a.x_in + e)[j];
+        for (int s = 0; s < a.n_src; s++) {
+            const float4* p = reinterpret_cast<const float4*>(a.partials + (size_t)s * a.src_stride + e);
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                const float4 t = p[j];
+                v[j].x += t.x; v[j].y += t.y; v[j].z += t.z; v[j].w += t.w;
+            }
+        }
+        float amax = 0.0f;
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            if (a.norm_w != nullptr) {
+                const float4 w4 = reinterpret_cast<const float4*>(a.norm_w + (size_t)b * 32)[j];
+                v[j].x = w4.x * (inv * v[j].x); v[j].y = w4.y * (inv * v[j].y);
+                v[j].z = w4.z * (inv * v[j].z); v[j].w = w4.w * (inv * v[j].w);
+            }
+            amax = fmaxf(amax, fmaxf(fmaxf(fabsf(v[j].x), fabsf(v[j].y)), fmaxf(fabsf(v[j].z), fabsf(v[j].w))));
+        }
+        if (a.y_out != nullptr) {
+#pragma unroll
+            for (int j = 0; j < 8; j++) reinterpret_cast<float4*>(a.y_out + e)[j] = v[j];
+        }
+        if (a.xq_out == nullptr && a.xh_out == nullptr) continue;
+        const float d = amax / 127.0f;
+        const float id = (d != 0.0f) ? (1.0f / d) : 0.0f;
+        const float df = __half2float(__float2half_rn(d));
+        int q[32];
+        int sumq = 0;
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            q[4 * j + 0] = __float2int_rn(v[j].x * id); q[4 * j + 1] = __float2int_rn(v[j].y * id);
+            q[4 * j + 2] = __float2int_rn(v[j].z * id); q[4 * j + 3] = __float2int_rn(v[j].w * id);
+            sumq += q[4 * j] + q[4 * j + 1] + q[4 * j + 2] + q[4 * j + 3];
+        }
+        const int kt = b >> 2, kb = b & 3;
+        if (a.xq_out != nullptr) {
+            uint8_t* rowp = a.xq_out + ((size_t)kt * a.mcap + m) * XQ_ROW_BYTES;
+            uint32_t pk[8];
+#pragma unroll
+            for (int j = 0; j < 8; j++)
+                pk[j] = (uint32_t)(q[4 * j] & 0xff) | ((uint32_t)(q[4 * j + 1] & 0xff) << 8) |
+                        ((uint32_t)(q[4 * j + 2] & 0xff) << 16) | ((uint32_t)(q[4 * j + 3] & 0xff) << 24);
+            uint4* qd = reinterpret_cast<uint4*>(rowp + kb * 32);
+            qd[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+            qd[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+            reinterpret_cast<float*>(rowp + 128)[kb] = df;
+            reinterpret_cast<int*>(rowp + 144)[kb] = 8 * sumq;
+        }
+        if (a.xh_out != nullptr) {
+            // chunk w holds elements [4w, 4w+2, 4w+1, 4w+3, 4w+16, 4w+18, 4w+17, 4w+19] (see xh_slot)
+            uint8_t* base = a.xh_out + (size_t)kt * (size_t)(a.mcap >> 3) * XH_ROWGROUP_BYTES +
+                            (size_t)(m >> 3) * XH_ROWGROUP_BYTES + (size_t)(kb * 4) * 128 + (size_t)(m & 7) * 16;
+#pragma unroll
+            for (int w = 0; w < 4; w++) {
+                const int o = 4 * w;
+                __half2 h0 = __floats2half2_rn((float)q[o] * df, (float)q[o + 2] * df);
+                __half2 h1 = __floats2half2_rn((float)q[o + 1] * df, (float)q[o + 3] * df);
+                __half2 h2 = __floats2half2_rn((float)q[o + 16] * df, (float)q[o + 18] * df);
+                __half2 h3 = __floats2half2_rn((float)q[o + 17] * df, (float)q[o + 19] * df);
+                uint4 u;
+                u.x = *reinterpret_cast<uint32_t*>(&h0); u.y = *reinterpret_cast<uint32_t*>(&h1);
+                u.z = *reinterpret_cast<uint32_t*>(&h2); u.w = *reinterpret_cast<uint32_t*>(&h3);
+                *reinterpret_cast<uint4*>(base + w * 128) = u;
+            }
         }
     }
 }

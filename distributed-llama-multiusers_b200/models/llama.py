@@ -298,9 +298,17 @@ class LlamaEngine:
             x_out = _Off(self.x[cur ^ 1], x_off) if merge else None
             parts = (pending[0][self.rank] + x_off) if merge else None
             flags = pending[1] if (merge and multi) else None
+            fuse = False
             if rows <= GEMV_MAX_M:
+                r_, s_ = K.choose_splits(d, h.dim, kind, self.n_sms, rows)
+                fuse = ((d + 127) // 128) * r_ * s_ <= 2 * self.n_sms     # every CTA repeats the prologue
+            if fuse:
                 nm = K.norm_prolog(x_in, x_out, parts, N, src_stride, flags, sc, L, flag_add, w_norm, eps)
                 self._matmul(weight, d, h.dim, rows, None, None, epi, kind, norm=nm)
+            elif rows <= GEMV_MAX_M:
+                K.reduce_norm_quant(x_in, x_out, parts, N if merge else 0, src_stride, flags, sc, L, flag_add, w_norm,
+                                    eps, h.dim, rows, rows, self.xq_dim, None, pdl=pdl)
+                self._matmul(weight, d, h.dim, rows, self.xq_dim, None, epi, kind)
             else:
                 K.reduce_norm_quant(x_in, x_out, parts, N if merge else 0, src_stride, flags, sc, L, flag_add, w_norm,
                                     eps, h.dim, rows, self.ncap, None, self.xh_dim, pdl=pdl)

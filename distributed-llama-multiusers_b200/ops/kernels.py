@@ -235,7 +235,8 @@ def choose_splits(d: int, n: int, epi_kind: int, n_sms: int = 148, M: int = 1):
     R, S = 1, 1
     while S < 8 and S * 2 <= kt and int(cuda_lib().dl_gemv_q40_smem_bytes(n, M, S)) > 200 * 1024:
         S *= 2
-    while row_tiles * R * S < n_sms:
+    # two CTAs fit per SM; stay well inside one wave (cluster placement wastes some slots)
+    while row_tiles * R * S < (n_sms * 4) // 5:
         if S < 8 and S * 2 <= kt and kt // (S * 2) >= 2:
             S *= 2
         elif R < max_r:

@@ -1,0 +1,101 @@
+#!/usr/bin/env python3
+"""Micro-benchmark of the two Q40 matmul kernels on the Llama-3.1-8B layer shapes (1 GPU).
+
+Each shape gets enough distinct weight copies (>= 512 MB total) that consecutive launches never hit
+L2; times are CUDA-event averages after warm-up.  Reports achieved HBM bandwidth against
+MEASURED_PEAKS.json and, for the tensor-core kernel, achieved TFLOP/s.
+"""
+import argparse
+import json
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+import torch  # noqa: E402
+
+from dllama_b200.ops import kernels as K  # noqa: E402
+from dllama_b200.ops.lib import EPI_STORE  # noqa: E402
+
+
+def timed(fn, iters, warm=3):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / iters * 1e3      # us
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--tp", type=int, default=1)
+    ap.add_argument("--iters", type=int, default=24)
+    ap.add_argument("--gemv-m", default="1,2,4,8")
+    ap.add_argument("--tc-m", default="8,16,32,64,128,256")
+    ap.add_argument("--out", default="")
+    ap.add_argument("--shapes", default="qkv,wo,w13,w2,wcls")
+    a = ap.parse_args()
+    peaks = json.load(open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "MEASURED_PEAKS.json")))
+    hbm = peaks["hbm_gbs"]
+    dim, hid, N = 4096, 14336, a.tp
+    shapes = {"qkv": (6144 // N, dim), "wo": (dim, dim // N), "w13": (2 * hid // N, dim), "w2": (dim, hid // N),
+              "wcls": (128256 // N, dim)}
+    n_sms = K.cuda_lib().dl_device_sm_count()
+    rows = []
+    for name, (d, n) in shapes.items():
+        if name not in a.shapes.split(","):
+            continue
+        wbytes = K.q40t_bytes(d, n)
+        copies = max(2, min(64, (512 << 20) // wbytes + 1))
+        ws = [torch.randint(0, 255, (wbytes,), dtype=torch.uint8, device="cuda") for _ in range(copies)]
+        for w in ws:      # sane fp16 scales (avoid inf/nan patterns)
+            v = w.view(-1, 9216)[:, 8192:].view(torch.float16)
+            v.copy_(torch.full_like(v, 0.01))
+        y = torch.zeros(256, d, device="cuda")
+        epi = K.epi_store([y.data_ptr()], d)
+        for M in [int(x) for x in a.gemv_m.split(",") if x]:
+            xq = K.alloc_xq(n, M, "cuda")
+            x = torch.randn(M, n, device="cuda")
+            K.quant_q80(x, M, n, M, xq, None)
+            R, S = K.choose_splits(d, n, EPI_STORE, n_sms, M)
+            it = [0]
+
+            def run():
+                K.gemv_q40(ws[it[0] % copies], d, n, xq, M, epi, R, S)
+                it[0] += 1
+            us = timed(run, a.iters)
+            rows.append(dict(kernel="gemv", shape=name, d=d, n=n, M=M, R=R, S=S, us=round(us, 2),
+                             gbs=round(wbytes / us / 1e3, 1), frac_hbm=round(wbytes / us / 1e3 / hbm, 3)))
+            print(rows[-1], flush=True)
+        for M in [int(x) for x in a.tc_m.split(",") if x]:
+            ncap = 16 if M <= 16 else 32 if M <= 32 else 64 if M <= 64 else (M + 127) // 128 * 128
+            xh = K.alloc_xh(n, ncap, "cuda")
+            x = torch.randn(M, n, device="cuda")
+            K.quant_q80(x, M, n, ncap, None, xh)
+            S = 1
+            if M <= 32:
+                while ((d + 127) // 128) * S < n_sms and S < 8 and S * 2 <= n // 128:
+                    S *= 2
+            it = [0]
+
+            def run_tc():
+                K.gemm_q40_tc(ws[it[0] % copies], d, n, xh, ncap, M, epi, S)
+                it[0] += 1
+            us = timed(run_tc, a.iters)
+            rows.append(dict(kernel="tc", shape=name, d=d, n=n, M=M, S=S, us=round(us, 2),
+                             gbs=round(wbytes / us / 1e3, 1), frac_hbm=round(wbytes / us / 1e3 / hbm, 3),
+                             tflops=round(2.0 * d * n * M / us / 1e6, 1)))
+            print(rows[-1], flush=True)
+        del ws
+        torch.cuda.empty_cache()
+    if a.out:
+        json.dump(rows, open(a.out, "w"), indent=1)
+
+
+if __name__ == "__main__":
+    main()

@@ -300,7 +300,7 @@ def test_silu_mul_epilogue(M, use_tc):
     else:
         xq = k.alloc_xq(dim, 8, "cuda")
         k.quant_q80(torch.from_numpy(x).cuda(), M, dim, M, xq, None)
-        out = k.alloc_xq(hid, 8, "cuda")
+        out = k.alloc_xq(hid, M, "cuda")
         k.gemv_q40(w, 2 * hid, dim, xq, M, k.epi_silu_mul(out, None, M), 2, 2)
         torch.cuda.synchronize()
         got, _, _, _ = _decode_xq(out, hid, M, M)
