@@ -99,6 +99,33 @@ DL_DEVINL void mbar_wait(uint64_t* bar, uint32_t parity) {
     }
 }
 
+// ---- cluster-scope variants (DSMEM hand-off between the CTAs of a thread-block cluster) ----
+DL_DEVINL uint32_t mapa_shared(uint32_t cta_smem_addr, uint32_t cta_rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(cta_smem_addr), "r"(cta_rank));
+    return r;
+}
+// arrive (release, cluster scope) on an mbarrier that lives in another CTA of the cluster
+DL_DEVINL void mbar_arrive_remote(uint32_t cluster_smem_addr) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_smem_addr) : "memory");
+}
+DL_DEVINL void st_shared_cluster_f32(uint32_t cluster_smem_addr, float v) {
+    asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(cluster_smem_addr), "f"(v) : "memory");
+}
+DL_DEVINL void mbar_wait_cluster(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    do {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok)
+            : "r"(smem_u32(bar)), "r"(parity)
+            : "memory");
+    } while (!ok);
+}
+DL_DEVINL void fence_acq_rel_cluster() { asm volatile("fence.acq_rel.cluster;" ::: "memory"); }
+
 // generic-proxy smem writes -> visible to the async proxy (bulk copy engine, tcgen05.mma)
 DL_DEVINL void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 

@@ -29,12 +29,23 @@
 #define GEMV_MAX_M 8
 #define GEMV_MAX_ACT_BYTES (96 * 1024)
 
+DL_DEVINL unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+#define GEMV_TRACE(k)                                                                     \
+    do {                                                                                  \
+        if (a.trace != nullptr && (threadIdx.x == 0)) a.trace[blockIdx.x * 8 + (k)] = globaltimer_ns(); \
+    } while (0)
+
 struct GemvArgs {
     const uint8_t* w;
     const uint8_t* xq;
     int d_real, d_pad, KT, M, R, S, n;
     int n_epi_ctas;
     int fused;
+    unsigned long long* trace;
     DlNormProlog norm;
     DlEpilogue epi;
 };
@@ -47,13 +58,15 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_q40_kernel(const __grid_
     uint64_t* full = reinterpret_cast<uint64_t*>(smem);                               // barriers first (8-byte aligned)
     uint64_t* empty = full + GEMV_NS;
     uint64_t* act_full = empty + GEMV_NS;
-    int* sflag = reinterpret_cast<int*>(act_full + 1);
+    uint64_t* red_bar = act_full + 1;                                                // leader: S-1 remote arrivals
+    int* sflag = reinterpret_cast<int*>(red_bar + 1);
     uint8_t* stages = smem + 256;                                                    // [NS][9216]
     uint8_t* act_s = stages + GEMV_NS * Q40T_TILE_BYTES;                             // [nk][M][160]
     float* red = reinterpret_cast<float*>(act_s + (size_t)nk_max * M * XQ_ROW_BYTES);   // [2*R][MT][rows] (<= 2*MT*128)
     float* out_s = red + 2 * MT * 128;                                               // [MT][128]
     float* ssq_w = out_s + MT * 128;                                                 // [GEMV_WARPS][MT]
-    float* ssq_c = ssq_w + GEMV_WARPS * MT;                                          // [MT]  (read by cluster peers)
+    float* ssq_all = ssq_w + GEMV_WARPS * MT;                                        // [S][MT] filled by all cluster ranks
+    float* recv = ssq_all + 8 * MT;                                                         // leader: [S-1][MT][128]
 
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
@@ -75,10 +88,13 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_q40_kernel(const __grid_
             mbar_init(&empty[s], 4);
         }
         mbar_init(act_full, 1);
+        mbar_init(red_bar, S > 1 ? S - 1 : 1);
         mbar_fence_init();
     }
-    __syncthreads();
+    // cluster-wide: the leader's red_bar must be initialised before any peer can arrive on it
+    if (S > 1) cg::this_cluster().sync(); else __syncthreads();
     pdl_launch_dependents();
+    GEMV_TRACE(0);
 
     if (is_producer) {
         // weights do not depend on the previous kernel: stream the first ring-full before the PDL wait
@@ -134,18 +150,21 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_q40_kernel(const __grid_
         if (tid < MT) {
             float t = 0.0f;
             for (int w = 0; w < GEMV_WARPS; w++) t += ssq_w[w * MT + tid];
-            ssq_c[tid] = t;
+            // publish this CTA's share into every cluster rank's table (DSMEM stores): after the
+            // barrier nobody reads remote shared memory, so ranks may exit independently later on
+            if (S > 1) {
+                for (int c = 0; c < S; c++)
+                    st_shared_cluster_f32(mapa_shared(smem_u32(ssq_all + crank * MT + tid), c), t);
+            } else {
+                ssq_all[tid] = t;
+            }
         }
         if (S > 1) cg::this_cluster().sync(); else __syncthreads();
         float inv[MT];
 #pragma unroll
         for (int m = 0; m < MT; m++) {
             float t = 0.0f;
-            if (S > 1) {
-                for (int c = 0; c < S; c++) t += cg::this_cluster().map_shared_rank(ssq_c, c)[m];
-            } else {
-                t = ssq_c[m];
-            }
+            for (int c = 0; c < S; c++) t += ssq_all[c * MT + m];
             inv[m] = 1.0f / sqrtf(t / (float)dim + nm.eps);
         }
         // pass 2: y = w * (inv * x) -> Q80 -> resident activation slabs.  One THREAD per 32-block: its 8
@@ -230,13 +249,18 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_q40_kernel(const __grid_
 #pragma unroll
         for (int m = 0; m < MT; m++) acc[m] = 0.0f;
         if (!a.fused) mbar_wait(act_full, 0);
+        if (tid == 0) { GEMV_TRACE(1); }
 
         for (int i = g; i < nk; i += 2) {
             const int s = i % GEMV_NS;
             mbar_wait(&full[s], (i / GEMV_NS) & 1);
             const uint8_t* st = stages + s * Q40T_TILE_BYTES;
             const uint8_t* act = act_s + (size_t)i * M * XQ_ROW_BYTES;
-            for (int kb = kq; kb < 4; kb += R) {
+            // fully unrolled over the 4 blocks of the tile row (predicated on ownership when R > 1) so the
+            // loads and dp4a chains of different blocks overlap: the loop is latency-bound otherwise
+#pragma unroll
+            for (int kb = 0; kb < 4; kb++) {
+                if ((kb & (R - 1)) != kq) continue;
                 const uint4 nb = *reinterpret_cast<const uint4*>(st + row * 64 + (((kb + (rtile >> 1)) & 3) << 4));
                 const float dw = __half2float(*reinterpret_cast<const __half*>(st + Q40T_NIB_BYTES + row * 8 + kb * 2));
                 const int lo0 = nb.x & 0x0F0F0F0F, hi0 = (nb.x >> 4) & 0x0F0F0F0F;
@@ -263,6 +287,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_q40_kernel(const __grid_
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty[s]);
         }
+        if (tid == 0) { GEMV_TRACE(2); }
         // partial sums of the 2*R (group, kq) owners of each row
 #pragma unroll
         for (int m = 0; m < MT; m++) red[((g * R + kq) * MT + m) * rows + row] = acc[m];
@@ -274,29 +299,41 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_q40_kernel(const __grid_
         for (int j = 0; j < 2 * R; j++) v += red[(j * MT + m) * rows + r];
         out_s[m * 128 + r] = v;
     }
+    GEMV_TRACE(3);
     if (S > 1) {
-        cg::cluster_group cluster = cg::this_cluster();
-        cluster.sync();
-        if (crank == 0) {
+        // split-K reduction without a second cluster barrier: peers push their partial tile into the
+        // leader's shared memory (DSMEM stores), release-arrive on its mbarrier and exit; the leader
+        // acquires the barrier and sums in rank order (deterministic).
+        __syncthreads();
+        if (crank != 0) {
+            const uint32_t dst = mapa_shared(smem_u32(recv + (size_t)(crank - 1) * MT * 128), 0);
             for (int idx = tid; idx < MT * rows; idx += GEMV_THREADS) {
                 const int m = idx / rows, r = idx % rows;
-                float v = out_s[m * 128 + r];
-                for (int c = 1; c < S; c++) v += cluster.map_shared_rank(out_s, c)[m * 128 + r];
-                out_s[m * 128 + r] = v;
+                st_shared_cluster_f32(dst + (uint32_t)(m * 128 + r) * 4u, out_s[m * 128 + r]);
             }
+            fence_acq_rel_cluster();
+            __syncthreads();
+            if (tid == 0) mbar_arrive_remote(mapa_shared(smem_u32(red_bar), 0));
+            return;
         }
-        cluster.sync();
-        if (crank != 0) return;
+        mbar_wait_cluster(red_bar, 0);
+        for (int idx = tid; idx < MT * rows; idx += GEMV_THREADS) {
+            const int m = idx / rows, r = idx % rows;
+            float v = out_s[m * 128 + r];
+            for (int c = 0; c < S - 1; c++) v += recv[(size_t)c * MT * 128 + m * 128 + r];
+            out_s[m * 128 + r] = v;
+        }
     }
     __syncthreads();
     pdl_wait();
     epilogue_rows(a.epi, out_s, 128, rows, rt * Q40T_TILE_ROWS + rs * rows, a.d_real, M, 0, tid);
     epilogue_complete(a.epi, tid, a.n_epi_ctas, sflag);
+    GEMV_TRACE(5);
 }
 
 static size_t gemv_smem_bytes(int MT, int nk_max, int M) {
     return 256 + (size_t)GEMV_NS * Q40T_TILE_BYTES + (size_t)nk_max * M * XQ_ROW_BYTES +
-           (size_t)(2 * MT * 128 + MT * 128) * 4 + (size_t)(GEMV_WARPS * MT + 8) * 4 + 16;
+           (size_t)(2 * MT * 128 + MT * 128) * 4 + (size_t)(GEMV_WARPS * MT + 8 * MT) * 4 + (size_t)7 * MT * 128 * 4 + 16;
 }
 
 static int mt_of(int M) { return M == 1 ? 1 : (M == 2 ? 2 : (M <= 4 ? 4 : 8)); }
@@ -308,6 +345,9 @@ extern "C" long long dl_gemv_q40_smem_bytes(int n, int M, int k_split) {
 }
 
 extern void dl_set_error(const char* fmt, ...);
+static unsigned long long* g_gemv_trace = nullptr;
+// debug: per-CTA timeline (8 x globaltimer ns) written by thread 0 when non-NULL
+extern "C" void dl_debug_set_gemv_trace(unsigned long long* p) { g_gemv_trace = p; }
 
 template <int MT>
 static int launch_gemv(const GemvArgs& a, int pdl, cudaStream_t stream) {
@@ -369,6 +409,7 @@ extern "C" int dl_gemv_q40(const uint8_t* w_q40t, int d, int n, const uint8_t* x
     a.fused = norm != nullptr ? 1 : 0;
     if (norm != nullptr) a.norm = *norm; else memset(&a.norm, 0, sizeof(a.norm));
     a.epi = *epi;
+    a.trace = g_gemv_trace;
     cudaStream_t st = (cudaStream_t)stream;
     switch (mt_of(M)) {
         case 1: return launch_gemv<1>(a, pdl, st);
