@@ -37,6 +37,7 @@ struct AttArgs {
     uint8_t* xh_out;
     int out_mcap;
     float* y_out;              // [M][n_heads*HS] or NULL
+    unsigned long long* tr;
 };
 
 // 32 values per lane -> lane i ends with the warp-wide sum of value i (31 shuffles)
@@ -64,6 +65,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attention_kernel(const __grid_
     constexpr int PAGE_BYTES = ATT_PAGE * HS * (int)sizeof(KV);
     constexpr int GMAX = NCH * 4;
     extern __shared__ __align__(128) uint8_t smem[];
+    trace_begin(a.tr);
     uint8_t* ring = smem;                                                   // [STAGES][2][PAGE_BYTES]
     float* q_s = reinterpret_cast<float*>(ring + ATT_STAGES * 2 * PAGE_BYTES);    // [GMAX][HS] pre-scaled
     float* w_acc = q_s + GMAX * HS;                                         // [WARPS][GMAX][HS]
@@ -241,7 +243,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attention_kernel(const __grid_
             }
         }
     }
-    if (single) return;
+    if (single) { trace_end(a.tr); return; }
 
     // last CTA of this (row, kv head) merges the splits
     __threadfence();
@@ -252,7 +254,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attention_kernel(const __grid_
         if (*s_last) a.counters[m * a.n_kv_heads + kvh] = 0u;
     }
     __syncthreads();
-    if (!*s_last) return;
+    if (!*s_last) { trace_end(a.tr); return; }
     __threadfence();
     if (tid < HS) {
         for (int h = 0; h < G; h++) {
@@ -273,6 +275,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attention_kernel(const __grid_
                 q80_block_store(y, lane, m, (head * HS + tid) >> 5, a.out_mcap, a.xq_out, a.xh_out);
         }
     }
+    trace_end(a.tr);
 }
 
 extern void dl_set_error(const char* fmt, ...);
@@ -339,6 +342,7 @@ extern "C" int dl_attention(const float* q, int M, int n_heads, int n_kv_heads, 
     a.part_o = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(scratch) + ATT_COUNTER_BYTES);
     a.part_ml = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(scratch) + ATT_COUNTER_BYTES + o);
     a.xq_out = xq_out; a.xh_out = xh_out; a.out_mcap = out_mcap; a.y_out = y_out;
+    a.tr = dl_trace_next(TR_ATT);
     const int G = n_heads / n_kv_heads;
     cudaStream_t st = (cudaStream_t)stream;
     if (kv_f32) {

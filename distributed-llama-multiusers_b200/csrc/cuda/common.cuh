@@ -51,6 +51,24 @@ DL_DEVINL void xh_slot(int e, int& w, int& s) {
 }
 
 // --------------------------------------------------------------------------------------------
+// optional per-launch timeline (debug): slot[0] = min start, slot[1] = max end (globaltimer ns)
+// --------------------------------------------------------------------------------------------
+DL_DEVINL unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+DL_DEVINL void trace_begin(unsigned long long* tr) {
+    if (tr != nullptr && threadIdx.x == 0) atomicMin(tr, globaltimer_ns());
+}
+DL_DEVINL void trace_end(unsigned long long* tr) {
+    if (tr != nullptr && threadIdx.x == 0) atomicMax(tr + 1, globaltimer_ns());
+}
+// host side (prep.cu): next trace slot for a launch of `kind`, or NULL when tracing is off
+unsigned long long* dl_trace_next(int kind);
+enum { TR_EMBED = 0, TR_RNQ = 1, TR_GEMV = 2, TR_ATT = 3, TR_ARGMAX = 4, TR_TC = 5, TR_OTHER = 6 };
+
+// --------------------------------------------------------------------------------------------
 // warp reductions
 // --------------------------------------------------------------------------------------------
 DL_DEVINL float warp_sum(float v) {

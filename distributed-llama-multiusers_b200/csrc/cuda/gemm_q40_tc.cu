@@ -30,11 +30,13 @@ struct TcArgs {
     int d_real, d_pad, KT, ncap, M, NT, S;
     int NSA, NSB, NSH;
     int n_epi_ctas;
+    unsigned long long* tr;
     DlEpilogue epi;
 };
 
 __global__ void __launch_bounds__(TC_THREADS, 1) gemm_q40_tc_kernel(const __grid_constant__ TcArgs a) {
     extern __shared__ __align__(1024) uint8_t smem[];
+    trace_begin(a.tr);
     const int NT = a.NT;
     const int b_bytes = NT * 256;
     uint8_t* ringH = smem;                                          // [NSH][32 KB]
@@ -234,6 +236,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_q40_tc_kernel(const __grid
         tmem_dealloc(tmem_base, tmem_cols);
     }
     if (crank == 0) epilogue_complete(a.epi, tid, a.n_epi_ctas, sflag);
+    trace_end(a.tr);
 }
 
 extern void dl_set_error(const char* fmt, ...);
@@ -261,6 +264,7 @@ extern "C" int dl_gemm_q40_tc(const uint8_t* w_q40t, int d, int n, const uint8_t
     else { a.NSA = 8; a.NSB = 2; a.NSH = 2; }
     a.n_epi_ctas = (a.d_pad / 128) * ((M + a.NT - 1) / a.NT);
     a.epi = *epi;
+    a.tr = dl_trace_next(TR_TC);
     const size_t smem = (size_t)a.NSH * TC_A_BYTES + (size_t)a.NSB * a.NT * 256 + (size_t)a.NSA * Q40T_TILE_BYTES +
                         (size_t)TC_EPI_CHUNK * 128 * 4 + 6 * 8 * 8 + 8 + 16;
     static size_t max_set = 0;

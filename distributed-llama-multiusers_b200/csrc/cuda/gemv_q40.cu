@@ -29,11 +29,6 @@
 #define GEMV_MAX_M 8
 #define GEMV_MAX_ACT_BYTES (96 * 1024)
 
-DL_DEVINL unsigned long long globaltimer_ns() {
-    unsigned long long t;
-    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
-    return t;
-}
 #define GEMV_TRACE(k)                                                                     \
     do {                                                                                  \
         if (a.trace != nullptr && (threadIdx.x == 0)) a.trace[blockIdx.x * 8 + (k)] = globaltimer_ns(); \
@@ -46,6 +41,7 @@ struct GemvArgs {
     int n_epi_ctas;
     int fused;
     unsigned long long* trace;
+    unsigned long long* tr;
     DlNormProlog norm;
     DlEpilogue epi;
 };
@@ -53,6 +49,7 @@ struct GemvArgs {
 template <int MT>
 __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_q40_kernel(const __grid_constant__ GemvArgs a) {
     extern __shared__ __align__(128) uint8_t smem[];
+    trace_begin(a.tr);
     const int S = a.S, R = a.R, M = a.M;
     const int nk_max = (a.KT + S - 1) / S;
     uint64_t* full = reinterpret_cast<uint64_t*>(smem);                               // barriers first (8-byte aligned)
@@ -314,6 +311,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_q40_kernel(const __grid_
             fence_acq_rel_cluster();
             __syncthreads();
             if (tid == 0) mbar_arrive_remote(mapa_shared(smem_u32(red_bar), 0));
+            trace_end(a.tr);
             return;
         }
         mbar_wait_cluster(red_bar, 0);
@@ -329,6 +327,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_q40_kernel(const __grid_
     epilogue_rows(a.epi, out_s, 128, rows, rt * Q40T_TILE_ROWS + rs * rows, a.d_real, M, 0, tid);
     epilogue_complete(a.epi, tid, a.n_epi_ctas, sflag);
     GEMV_TRACE(5);
+    trace_end(a.tr);
 }
 
 static size_t gemv_smem_bytes(int MT, int nk_max, int M) {
@@ -410,6 +409,7 @@ extern "C" int dl_gemv_q40(const uint8_t* w_q40t, int d, int n, const uint8_t* x
     if (norm != nullptr) a.norm = *norm; else memset(&a.norm, 0, sizeof(a.norm));
     a.epi = *epi;
     a.trace = g_gemv_trace;
+    a.tr = dl_trace_next(TR_GEMV);
     cudaStream_t st = (cudaStream_t)stream;
     switch (mt_of(M)) {
         case 1: return launch_gemv<1>(a, pdl, st);

@@ -13,6 +13,20 @@ void dl_set_error(const char* fmt, ...) {
 }
 extern "C" const char* dl_last_error(void) { return g_err; }
 
+// ---- optional launch timeline -----------------------------------------------------------------
+static unsigned long long* g_trace_base = nullptr;
+static int g_trace_cap = 0, g_trace_n = 0;
+static int g_trace_kind[8192];
+unsigned long long* dl_trace_next(int kind) {
+    if (g_trace_base == nullptr || g_trace_n >= g_trace_cap || g_trace_n >= 8192) return nullptr;
+    g_trace_kind[g_trace_n] = kind;
+    return g_trace_base + 2 * (size_t)(g_trace_n++);
+}
+// buf: device array of 2*cap uint64, pre-filled by the caller with {UINT64_MAX, 0} pairs; NULL disables
+extern "C" void dl_trace_set(unsigned long long* buf, int cap) { g_trace_base = buf; g_trace_cap = cap; g_trace_n = 0; }
+extern "C" int dl_trace_count(void) { return g_trace_n; }
+extern "C" int dl_trace_kind(int i) { return (i >= 0 && i < g_trace_n) ? g_trace_kind[i] : -1; }
+
 #define CHECK_LAUNCH(name)                                                              \
     do {                                                                                \
         cudaError_t e__ = cudaGetLastError();                                           \
@@ -101,7 +115,8 @@ extern "C" int dl_q40t_dequant(const uint8_t* q40t, int d, int n, float* out, vo
 // embedding gather (+ per-forward step counter used as the epoch base of all peer flags)
 // ------------------------------------------------------------------------------------------------
 __global__ void embedding_kernel(const float* __restrict__ table, const int* __restrict__ tokens, float* __restrict__ x,
-                                 int dim, uint32_t* step_counter) {
+                                 int dim, uint32_t* step_counter, unsigned long long* tr) {
+    trace_begin(tr);
     pdl_launch_dependents();
     pdl_wait();
     const int m = blockIdx.x;
@@ -109,11 +124,12 @@ __global__ void embedding_kernel(const float* __restrict__ table, const int* __r
     float4* dst = reinterpret_cast<float4*>(x + (size_t)m * dim);
     for (int i = threadIdx.x; i < dim / 4; i += blockDim.x) dst[i] = src[i];
     if (step_counter != nullptr && m == 0 && threadIdx.x == 0) *step_counter = *step_counter + 1u;
+    trace_end(tr);
 }
 
 extern "C" int dl_embedding(const float* table, const int* tokens, float* x, int M, int dim, uint32_t* step_counter,
                             void* stream) {
-    embedding_kernel<<<M, 256, 0, (cudaStream_t)stream>>>(table, tokens, x, dim, step_counter);
+    embedding_kernel<<<M, 256, 0, (cudaStream_t)stream>>>(table, tokens, x, dim, step_counter, dl_trace_next(TR_EMBED));
     CHECK_LAUNCH("dl_embedding");
     return 0;
 }
@@ -140,9 +156,11 @@ struct RnqArgs {
     uint8_t* xq_out;
     uint8_t* xh_out;
     float* y_out;
+    unsigned long long* tr;
 };
 
 __global__ void __launch_bounds__(RNQ_THREADS) reduce_norm_quant_kernel(const __grid_constant__ RnqArgs a) {
+    trace_begin(a.tr);
     __shared__ float s_part[RNQ_THREADS / 32];
     __shared__ float s_inv;
     pdl_launch_dependents();
@@ -250,6 +268,7 @@ __global__ void __launch_bounds__(RNQ_THREADS) reduce_norm_quant_kernel(const __
             }
         }
     }
+    trace_end(a.tr);
 }
 
 extern "C" int dl_reduce_norm_quant(const float* x_in, float* x_out, const float* partials, int n_src, int src_stride,
@@ -263,6 +282,7 @@ extern "C" int dl_reduce_norm_quant(const float* x_in, float* x_out, const float
     a.flags = flags; a.step_counter = step_counter; a.flag_mul = flag_mul; a.flag_add = flag_add;
     a.norm_w = norm_w; a.eps = eps; a.dim = dim; a.M = M; a.mcap = mcap;
     a.xq_out = xq_out; a.xh_out = xh_out; a.y_out = y_out;
+    a.tr = dl_trace_next(TR_RNQ);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(M);
     cfg.blockDim = dim3(RNQ_THREADS);
@@ -301,6 +321,7 @@ struct ArgmaxArgs {
     int* history;
     int history_cap;
     uint8_t* scratch;
+    unsigned long long* tr;
 };
 
 #define ARGMAX_CHUNKS 32
@@ -316,6 +337,7 @@ __global__ void __launch_bounds__(ARGMAX_THREADS) argmax_kernel(const __grid_con
     __shared__ float s_v[ARGMAX_THREADS / 32];
     __shared__ int s_i[ARGMAX_THREADS / 32];
     __shared__ int s_last;
+    trace_begin(a.tr);
     pdl_launch_dependents();
     pdl_wait();
     if (a.flags != nullptr) {
@@ -349,7 +371,7 @@ __global__ void __launch_bounds__(ARGMAX_THREADS) argmax_kernel(const __grid_con
         if (s_last) counters[m] = 0u;
     }
     __syncthreads();
-    if (!s_last) return;
+    if (!s_last) { trace_end(a.tr); return; }
     if (threadIdx.x < 32) {
         __threadfence();
         best = __ldcg(&part_v[m * ARGMAX_CHUNKS + threadIdx.x]);
@@ -366,6 +388,7 @@ __global__ void __launch_bounds__(ARGMAX_THREADS) argmax_kernel(const __grid_con
             }
         }
     }
+    trace_end(a.tr);
 }
 
 extern "C" long long dl_argmax_scratch_bytes(int M) { return 1024 + (long long)M * ARGMAX_CHUNKS * 8; }
@@ -379,6 +402,7 @@ extern "C" int dl_argmax(const float* logits, int M, int vocab, int ld, int* tok
     a.flags = flags; a.n_flags = n_flags; a.step_counter = step_counter; a.flag_mul = flag_mul; a.flag_add = flag_add;
     a.pos_inc = pos_inc; a.history = history; a.history_cap = history_cap;
     a.scratch = reinterpret_cast<uint8_t*>(scratch);
+    a.tr = dl_trace_next(TR_ARGMAX);
     if (history != nullptr && step_counter == nullptr) { dl_set_error("dl_argmax: history needs step_counter"); return -1; }
     if (scratch == nullptr || M > 256) { dl_set_error("dl_argmax: needs zero-initialised scratch (dl_argmax_scratch_bytes) and M <= 256"); return -1; }
     cudaLaunchConfig_t cfg = {};

@@ -142,11 +142,18 @@ int dl_sched_next_batch(void* p, long long* req_ids, int* tokens, int* pos, int*
         else if (r.state == PREFILL && pre == nullptr) pre = &r;
     }
     int n_dec = (int)dec.size();
-    if (n_dec > R) {
+    // a pending prompt always gets a share of the rows (else a full house of decoders starves it)
+    int reserve = 0;
+    if (pre != nullptr) {
+        const int left = (int)pre->prompt.size() - pre->n_prefilled;
+        reserve = std::min(left, std::max(1, R / 4));
+    }
+    const int dec_rows = std::max(0, R - reserve);
+    if (n_dec > dec_rows) {
+        // more decoders than rows: serve a rotating window so everybody advances
         std::rotate(dec.begin(), dec.begin() + (s->rr % dec.size()), dec.end());
-        s->rr += R;
-        n_dec = R;
-        pre = nullptr;
+        s->rr += dec_rows > 0 ? dec_rows : 1;
+        n_dec = dec_rows;
     }
     int n = 0;
     s->batch_sampling.clear();

@@ -61,6 +61,12 @@ class PageAllocator:
         self.n_used[slot] = 0
         self.free_slots.append(slot)
 
+    def release_pages(self, slot: int):
+        """Return a slot's pages to the pool; the slot id itself stays with its owner (the scheduler)."""
+        for i in range(int(self.n_used[slot])):
+            self.free_pages.append(int(self.table[slot, i]))
+        self.n_used[slot] = 0
+
     def ensure(self, slot: int, n_tokens: int):
         need = (n_tokens + PAGE - 1) // PAGE
         if need > self.max_pages:
@@ -419,13 +425,17 @@ class LlamaEngine:
             out = self.forward(part, pos, [slot] * len(part), logits_from=len(part) - 1)
         return out
 
-    def decode_greedy_host(self, tokens: List[int], positions: List[int], slots: List[int]) -> List[int]:
-        """One greedy decode step end to end: H2D descriptor, forward, device argmax, D2H tokens."""
+    def decode_step_greedy(self, tokens, positions, slots, logits_from: int = 0) -> List[int]:
+        """One greedy step end to end for rows logits_from..M-1: H2D descriptor, forward, device
+        argmax, D2H token ids."""
         M = self.set_batch(tokens, positions, slots)
-        self._run(M, 0, True)
+        self._run(M, logits_from, True)
         self.h_out_tokens.copy_(self.out_tokens, non_blocking=True)
         torch.cuda.current_stream().synchronize()
-        return self.h_out_tokens[:M].tolist()
+        return self.h_out_tokens[:M - logits_from].tolist()
+
+    def decode_greedy_host(self, tokens: List[int], positions: List[int], slots: List[int]) -> List[int]:
+        return self.decode_step_greedy(tokens, positions, slots, 0)
 
     def decode_greedy_device(self, n_steps: int, M: int):
         """Device-resident greedy loop: each step's argmax feeds the next step's embedding and

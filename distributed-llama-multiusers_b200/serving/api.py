@@ -1,0 +1,186 @@
+"""`dllama-api`: multi-user OpenAI-style HTTP server on top of the continuous-batching engine.
+
+Surface parity with the reference (src/dllama-api.cpp:338-365): ``POST /v1/chat/completions``,
+``GET /v1/models``, ``OPTIONS *`` -> 204 with CORS headers, anything else 404.  Unlike the
+reference (single-threaded accept loop that blocks on each request's future -- defect D4 -- and
+answers ``{"generated_text": ...}`` -- D6) every connection gets its own thread, all in-flight
+requests decode together in one batch, the chat template is applied, and the reply is an OpenAI
+``chat.completion`` (or an SSE stream of ``chat.completion.chunk`` when ``"stream": true``).
+Extras: ``GET /health``, ``GET /metrics`` (Prometheus text).
+"""
+from __future__ import annotations
+
+import json
+import os
+import threading
+import time
+from http.server import BaseHTTPRequestHandler, ThreadingHTTPServer
+from typing import Optional
+
+from ..text import native as T
+from . import api_types as A
+from .batch_engine import BatchEngine, GenerationRequest
+
+
+class ApiState:
+    def __init__(self, batch: BatchEngine, tokenizer: T.Tokenizer, model_name: str, defaults: A.InferenceParams,
+                 chat_template_type: int = T.CHAT_UNKNOWN, max_default_tokens: int = 128):
+        self.batch = batch
+        self.tok = tokenizer
+        self.model_name = model_name
+        self.defaults = defaults
+        self.max_default_tokens = max_default_tokens
+        eos_piece = tokenizer.piece(tokenizer.eos_token_ids[-1]).decode("utf-8", "replace") \
+            if tokenizer.eos_token_ids else ""
+        self.template = T.ChatTemplateGenerator(chat_template_type, tokenizer.chat_template, eos_piece)
+        self.n_requests = 0
+        self.n_errors = 0
+        self.lock = threading.Lock()
+        self.ttft = []
+
+    def build_request(self, p: A.InferenceParams) -> GenerationRequest:
+        content, _public = self.template.generate([(m["role"], m["content"]) for m in p.messages], True)
+        tokens = self.tok.encode(content, add_bos=True, add_special_tokens=True)
+        max_tokens = p.max_tokens if p.max_tokens and p.max_tokens > 0 else self.max_default_tokens
+        return GenerationRequest(prompt_tokens=tokens, max_tokens=max_tokens, temperature=p.temperature,
+                                 top_p=p.top_p, seed=p.seed, stop=p.stop)
+
+
+def make_handler(state: ApiState):
+    class Handler(BaseHTTPRequestHandler):
+        protocol_version = "HTTP/1.1"
+        server_version = "dllama-api-b200"
+
+        def log_message(self, fmt, *args):      # quiet: one line per request is printed below
+            pass
+
+        # ---- helpers ----
+        def _cors(self):
+            self.send_header("Access-Control-Allow-Origin", "*")
+
+        def _json(self, code: int, obj):
+            data = json.dumps(obj, ensure_ascii=False).encode("utf-8")
+            self.send_response(code)
+            self._cors()
+            self.send_header("Content-Type", "application/json; charset=utf-8")
+            self.send_header("Content-Length", str(len(data)))
+            self.send_header("Connection", "close")
+            self.end_headers()
+            self.wfile.write(data)
+
+        def _not_found(self):
+            self.send_response(404)
+            self.send_header("Connection", "close")
+            self.send_header("Content-Length", "9")
+            self.end_headers()
+            self.wfile.write(b"Not Found")
+
+        # ---- methods ----
+        def do_OPTIONS(self):
+            self.send_response(204)
+            self._cors()
+            self.send_header("Access-Control-Allow-Methods", "GET, POST, PUT, DELETE")
+            self.send_header("Access-Control-Allow-Headers", "Content-Type, Authorization")
+            self.send_header("Connection", "close")
+            self.end_headers()
+
+        def do_GET(self):
+            path = self.path.split("?")[0]
+            if path == "/v1/models":
+                self._json(200, A.model_list(state.model_name))
+            elif path == "/health":
+                self._json(200, {"status": "ok", **state.batch.sched.stats()})
+            elif path == "/metrics":
+                st = state.batch.sched.stats()
+                body = ("# TYPE dllama_requests_total counter\ndllama_requests_total %d\n"
+                        "# TYPE dllama_errors_total counter\ndllama_errors_total %d\n"
+                        "# TYPE dllama_steps_total counter\ndllama_steps_total %d\n"
+                        "# TYPE dllama_generated_tokens_total counter\ndllama_generated_tokens_total %d\n"
+                        "# TYPE dllama_running gauge\ndllama_running %d\n"
+                        "# TYPE dllama_waiting gauge\ndllama_waiting %d\n" % (
+                            state.n_requests, state.n_errors, state.batch.n_steps, state.batch.n_generated,
+                            st["running"], st["waiting"])).encode()
+                self.send_response(200)
+                self.send_header("Content-Type", "text/plain; version=0.0.4")
+                self.send_header("Content-Length", str(len(body)))
+                self.send_header("Connection", "close")
+                self.end_headers()
+                self.wfile.write(body)
+            else:
+                self._not_found()
+
+        def do_POST(self):
+            path = self.path.split("?")[0]
+            if path != "/v1/chat/completions":
+                return self._not_found()
+            try:
+                n = int(self.headers.get("Content-Length", "0"))
+                body = json.loads(self.rfile.read(n).decode("utf-8")) if n > 0 else {}
+                params = A.parse_inference_params(body, state.defaults)
+                if not params.messages:
+                    return self._json(400, {"error": {"message": "Prompt is empty.", "type": "invalid_request_error"}})
+                req = state.build_request(params)
+                state.batch.submit(req)
+            except (ValueError, KeyError, TypeError, json.JSONDecodeError) as e:
+                with state.lock:
+                    state.n_errors += 1
+                return self._json(400, {"error": {"message": str(e), "type": "invalid_request_error"}})
+            with state.lock:
+                state.n_requests += 1
+            cid = A.new_completion_id()
+            print(f"🔷 {self.command} {path} id={req.id} prompt_tokens={len(req.prompt_tokens)}", flush=True)
+            try:
+                if params.stream:
+                    self._stream(cid, req)
+                else:
+                    text = req.result()
+                    usage = A.chat_usage(len(req.prompt_tokens), len(req.tokens))
+                    self._json(200, A.chat_completion(cid, state.model_name, text, req.finish_reason or "stop", usage))
+            except (BrokenPipeError, ConnectionResetError):
+                state.batch.cancel(req)         # client went away: free its slot
+            print(f"🔶 id={req.id} tokens={len(req.tokens)} finish={req.finish_reason}", flush=True)
+
+        def _stream(self, cid: str, req: GenerationRequest):
+            self.send_response(200)
+            self._cors()
+            self.send_header("Content-Type", "text/event-stream; charset=utf-8")
+            self.send_header("Cache-Control", "no-cache")
+            self.send_header("Connection", "close")
+            self.end_headers()
+
+            def send(obj):
+                self.wfile.write(b"data: " + json.dumps(obj, ensure_ascii=False).encode("utf-8") + b"\r\n\r\n")
+                self.wfile.flush()
+
+            send(A.chat_completion_chunk(cid, state.model_name, {"role": "assistant", "content": ""}, None))
+            while True:
+                delta = req.out.get()
+                if delta is None:
+                    break
+                send(A.chat_completion_chunk(cid, state.model_name, {"content": delta}, None))
+            send(A.chat_completion_chunk(cid, state.model_name, {}, req.finish_reason or "stop"))
+            self.wfile.write(b"data: [DONE]\r\n\r\n")
+            self.wfile.flush()
+
+    return Handler
+
+
+class ApiServer:
+    def __init__(self, state: ApiState, host: str = "0.0.0.0", port: int = 9990):
+        self.state = state
+        self.httpd = ThreadingHTTPServer((host, port), make_handler(state))
+        self.httpd.daemon_threads = True
+        self.port = self.httpd.server_address[1]
+        self._thread: Optional[threading.Thread] = None
+
+    def serve_forever(self):
+        print(f"Server URL: http://127.0.0.1:{self.port}/v1/", flush=True)
+        self.httpd.serve_forever()
+
+    def start(self):
+        self._thread = threading.Thread(target=self.httpd.serve_forever, daemon=True, name="dllama-api-http")
+        self._thread.start()
+
+    def shutdown(self):
+        self.httpd.shutdown()
+        self.httpd.server_close()

@@ -70,7 +70,9 @@ class BatchEngine:
         eos_pieces = [tokenizer.piece(t).decode("utf-8", "replace") for t in tokenizer.eos_token_ids]
         self._eos_pieces = eos_pieces
         self._max_stop = max([len(p) for p in eos_pieces] + [1])
-        self._logits_host = torch.empty(self.max_rows, engine.h.vocab_size, dtype=torch.float32).pin_memory()
+        self._logits_host = torch.empty(self.max_rows, engine.h.vocab_size, dtype=torch.float32)
+        if torch.cuda.is_available():
+            self._logits_host = self._logits_host.pin_memory()
 
     # ---- client side (any thread) ------------------------------------------------------------------
     def submit(self, req: GenerationRequest) -> GenerationRequest:
@@ -108,7 +110,8 @@ class BatchEngine:
             self.control.send(OP_STOP)
 
     def run(self):
-        torch.cuda.set_device(self.engine.device)
+        if self.engine.device.type == "cuda":
+            torch.cuda.set_device(self.engine.device)
         while not self._stop.is_set():
             if not self.sched.wait(20):
                 continue
@@ -135,15 +138,12 @@ class BatchEngine:
             self.n_steps += 1
             return len(ids)
         if greedy:
-            M = eng.set_batch(toks, pos, slots)
-            eng._run(M, lf, True)
-            eng.h_out_tokens.copy_(eng.out_tokens, non_blocking=True)
-            torch.cuda.current_stream().synchronize()
-            sampled = eng.h_out_tokens[:n_s].tolist()
+            sampled = eng.decode_step_greedy(toks, pos, slots, lf)[:n_s]
         else:
             logits = eng.forward(toks, pos, slots, logits_from=lf)
             self._logits_host[:n_s].copy_(logits[:n_s], non_blocking=True)
-            torch.cuda.current_stream().synchronize()
+            if logits.is_cuda:
+                torch.cuda.current_stream().synchronize()
             lh = self._logits_host.numpy()
             sampled = [r._sampler.sample(lh[i]) if r is not None else 0 for i, r in enumerate(rows)]
         now = time.time()

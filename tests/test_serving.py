@@ -1,0 +1,185 @@
+"""Scheduler, continuous batching and the HTTP API on the CPU engine (no GPU needed)."""
+import json
+import threading
+import urllib.request
+
+import pytest
+
+from dllama_b200.formats import mfile, tfile
+from dllama_b200.models.cpu_engine import CpuEngine
+from dllama_b200.models.oracle import OracleLlama
+from dllama_b200.serving import api_types as A
+from dllama_b200.serving.api import ApiServer, ApiState
+from dllama_b200.serving.batch_engine import BatchEngine, GenerationRequest
+from dllama_b200.text import native as T
+
+
+@pytest.fixture(scope="module")
+def tok(tmp_path_factory):
+    p = str(tmp_path_factory.mktemp("tok") / "tiny.t")
+    tfile.write_synthetic_tokenizer(p, 1024)
+    return T.Tokenizer(p)
+
+
+def test_scheduler_batches_prefill_first_and_decodes_together():
+    s = T.Scheduler(max_rows=8, n_slots=2, prefill_chunk=4, max_seq_len=64)
+    assert s.submit(1, [10, 11, 12, 13, 14, 15], 3) == 0
+    assert s.submit(2, [20, 21], 2) == 0
+    assert s.submit(3, [30], 2) == 0                      # waits: only 2 slots
+    assert s.submit(4, [], 2) == -3 and s.submit(5, list(range(64)), 2) == -1 and s.submit(1, [1], 1) == -2
+    ids, toks, pos, slots, lf, samp = s.next_batch()      # first chunk of request 1 (4 of 6 tokens)
+    assert ids == [1, 1, 1, 1] and toks == [10, 11, 12, 13] and pos == [0, 1, 2, 3] and lf == 4 and samp == []
+    ids, toks, pos, slots, lf, samp = s.next_batch()      # rest of request 1 -> its last row samples
+    assert toks == [14, 15] and pos == [4, 5] and lf == 1 and samp == [1]
+    assert s.commit([100], [False]) == [False]
+    ids, toks, pos, slots, lf, samp = s.next_batch()      # request 2 prefill first, then request 1 decoding
+    assert ids == [2, 2, 1] and toks == [20, 21, 100] and pos == [0, 1, 6] and lf == 1 and samp == [2, 1]
+    assert slots[0] == slots[1] != slots[2]
+    assert s.commit([200, 101], [False, False]) == [False, False]
+    ids, toks, pos, slots, lf, samp = s.next_batch()      # both decode; request 3 still waiting for a slot
+    assert ids == [1, 2] and toks == [101, 200] and pos == [7, 2] and lf == 0
+    fin = s.commit([102, 201], [False, False])
+    assert fin == [True, True]                            # budgets (3 and 2 new tokens) exhausted
+    assert sorted(s.pop_released()) == sorted(set(slots))
+    ids, toks, pos, slots, lf, samp = s.next_batch()      # request 3 admitted into a freed slot
+    assert ids == [3] and toks == [30] and samp == [3]
+    assert s.commit([7], [True]) == [True]                # stop flag ends it at once
+    assert s.next_batch()[0] == []
+    assert s.stats()["free_slots"] == 2
+
+
+def test_scheduler_cancel_and_round_robin():
+    s = T.Scheduler(max_rows=2, n_slots=3, prefill_chunk=2, max_seq_len=64)
+    for i in (1, 2, 3):
+        s.submit(i, [i], 10)
+    for _ in range(3):                                    # prefill one request per step (one prefill seq per batch)
+        ids, toks, pos, slots, lf, samp = s.next_batch()
+        s.commit([50 + x for x in samp], [False] * len(samp))
+    seen = []
+    for _ in range(3):                                    # 3 decoders, 2 rows: round-robin must serve all
+        ids, *_rest, samp = s.next_batch()
+        seen += ids
+        s.commit([60] * len(samp), [False] * len(samp))
+    assert set(seen) == {1, 2, 3}
+    s.cancel(2)
+    ids = s.next_batch()[0]
+    assert 2 not in ids
+    assert s.pop_released() != []
+
+
+def _greedy_reference(path, prompt, n_new):
+    o = OracleLlama(mfile.ModelFile(path), max_seq_len=256)
+    return o.generate_greedy(prompt, n_new)
+
+
+def test_continuous_batching_matches_single_user_runs(tiny_model_path, tok):
+    eng = CpuEngine(tiny_model_path, max_rows=8, n_slots=3, max_seq_len=256)
+    be = BatchEngine(eng, tok, prefill_chunk=4)
+    prompts = [[5, 6, 7, 8, 9, 10], [100, 200, 300], [9, 8, 7, 6, 5, 4, 3, 2, 1], [42]]
+    reqs = [be.submit(GenerationRequest(prompt_tokens=p, max_tokens=5, temperature=0.0)) for p in prompts]
+    be.start()
+    for r in reqs:
+        r.result(timeout=120)
+    be.stop()
+    for r, p in zip(reqs, prompts):
+        want = _greedy_reference(tiny_model_path, p, 5)
+        eos = [i for i, t in enumerate(want) if tok.is_eos(t)]
+        if eos:
+            want = want[:eos[0] + 1]
+        assert r.tokens == want, (p, r.tokens, want)
+        assert r.finish_reason in ("length", "stop") and r.t_first_token is not None
+    assert be.sched.stats() == {"waiting": 0, "running": 0, "free_slots": 3}
+
+
+def test_sampling_is_per_request_and_seeded(tiny_model_path, tok):
+    eng = CpuEngine(tiny_model_path, max_rows=8, n_slots=4, max_seq_len=256)
+    be = BatchEngine(eng, tok)
+    mk = lambda seed: GenerationRequest(prompt_tokens=[3, 4, 5], max_tokens=6, temperature=1.0, top_p=0.95, seed=seed)
+    a, b, c = be.submit(mk(11)), be.submit(mk(11)), be.submit(mk(12))
+    be.start()
+    for r in (a, b, c):
+        r.result(timeout=120)
+    be.stop()
+    assert a.tokens == b.tokens                 # same seed, same prompt -> same sample path, even when batched
+    assert a.tokens != c.tokens
+
+
+def test_stop_string_truncates_output(tiny_model_path, tok):
+    eng = CpuEngine(tiny_model_path, max_rows=4, n_slots=2, max_seq_len=256)
+    be = BatchEngine(eng, tok)
+    free = be.submit(GenerationRequest(prompt_tokens=[5, 6, 7], max_tokens=12, temperature=0.0))
+    be.start()
+    full = free.result(timeout=120)
+    assert len(full) >= 4
+    stop = full[2:4]
+    r = be.submit(GenerationRequest(prompt_tokens=[5, 6, 7], max_tokens=12, temperature=0.0, stop=[stop]))
+    got = r.result(timeout=120)
+    be.stop()
+    assert got == full[:full.index(stop)] and r.finish_reason == "stop"
+
+
+def _post(port, body, timeout=120):
+    req = urllib.request.Request(f"http://127.0.0.1:{port}/v1/chat/completions", data=json.dumps(body).encode(),
+                                 headers={"Content-Type": "application/json"}, method="POST")
+    return urllib.request.urlopen(req, timeout=timeout)
+
+
+def test_http_api_concurrent_users_openai_shape_and_sse(tiny_model_path, tok):
+    eng = CpuEngine(tiny_model_path, max_rows=8, n_slots=4, max_seq_len=256)
+    be = BatchEngine(eng, tok)
+    be.start()
+    state = ApiState(be, tok, "tiny.m", A.InferenceParams(messages=[], temperature=0.0, top_p=0.9, seed=1))
+    srv = ApiServer(state, "127.0.0.1", 0)
+    srv.start()
+    port = srv.port
+    try:
+        with urllib.request.urlopen(f"http://127.0.0.1:{port}/v1/models") as r:
+            models = json.load(r)
+        assert models["object"] == "list" and models["data"][0]["id"] == "tiny.m"
+        opt = urllib.request.Request(f"http://127.0.0.1:{port}/v1/chat/completions", method="OPTIONS")
+        with urllib.request.urlopen(opt) as r:
+            assert r.status == 204 and r.headers["Access-Control-Allow-Origin"] == "*"
+        with pytest.raises(urllib.error.HTTPError) as ei:
+            urllib.request.urlopen(f"http://127.0.0.1:{port}/nope")
+        assert ei.value.code == 404
+        # three users at once; different prompts must give different, self-consistent answers
+        results = {}
+
+        def user(i, text):
+            with _post(port, {"messages": [{"role": "user", "content": text}], "max_tokens": 6}) as r:
+                results[i] = json.load(r)
+
+        threads = [threading.Thread(target=user, args=(i, t)) for i, t in
+                   enumerate(["hello world", "the of and", "hello world"])]
+        [t.start() for t in threads]
+        [t.join(timeout=180) for t in threads]
+        assert len(results) == 3
+        for d in results.values():
+            assert d["object"] == "chat.completion" and d["choices"][0]["message"]["role"] == "assistant"
+            assert d["usage"]["completion_tokens"] <= 6
+            assert d["usage"]["total_tokens"] == d["usage"]["prompt_tokens"] + d["usage"]["completion_tokens"]
+            assert d["generated_text"] == d["choices"][0]["message"]["content"]
+        assert results[0]["choices"][0]["message"]["content"] == results[2]["choices"][0]["message"]["content"]
+        assert results[0]["usage"]["prompt_tokens"] != results[1]["usage"]["prompt_tokens"] or \
+            results[0]["choices"][0]["message"]["content"] != results[1]["choices"][0]["message"]["content"]
+        # streaming: SSE chunks concatenate to the non-streamed answer
+        with _post(port, {"messages": [{"role": "user", "content": "hello world"}], "max_tokens": 6,
+                          "stream": True}) as r:
+            assert r.headers["Content-Type"].startswith("text/event-stream")
+            raw = r.read().decode("utf-8")
+        events = [e[len("data: "):] for e in raw.split("\r\n\r\n") if e.startswith("data: ")]
+        assert events[-1] == "[DONE]"
+        chunks = [json.loads(e) for e in events[:-1]]
+        assert all(c["object"] == "chat.completion.chunk" for c in chunks)
+        text = "".join(c["choices"][0]["delta"].get("content", "") for c in chunks)
+        assert text == results[0]["choices"][0]["message"]["content"]
+        assert chunks[-1]["choices"][0]["finish_reason"] in ("stop", "length")
+        # bad request
+        with pytest.raises(urllib.error.HTTPError) as ei:
+            _post(port, {"messages": "nope"})
+        assert ei.value.code == 400
+        with urllib.request.urlopen(f"http://127.0.0.1:{port}/metrics") as r:
+            assert b"dllama_requests_total 4" in r.read()
+    finally:
+        srv.shutdown()
+        be.stop()
