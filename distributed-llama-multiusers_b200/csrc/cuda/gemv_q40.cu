@@ -3,8 +3,10 @@
 // Design (B200-first, not a port of matmul_Q80_Q40_F32, src/nn/nn-cpu-ops.cpp:222-440):
 //  * weights live in HBM as Q40T tiles (common.cuh): each pipeline stage is a contiguous bulk
 //    async copy (cp.async.bulk -> SASS UBLKCP) of a 128x128 tile into shared memory, completion
-//    tracked by mbarriers; an 8-stage ring keeps ~74 KB per SM in flight, which is what it takes
-//    to cover HBM3e latency at 6.5 TB/s over 148 SMs.
+//    tracked by mbarriers; a 12-stage ring keeps ~110 KB per SM in flight (16 MB chip-wide), which
+//    covers HBM3e latency at 6.5 TB/s.
+//  * one CTA per SM, 16 consumer warps in 4 groups (k-tiles are dealt round-robin to the groups)
+//    plus a producer warp: the dp4a loop is latency-bound per warp, 4 warps per scheduler hide it.
 //  * exact reference arithmetic: int8 dot products (dp4a) per 32-block, one f32 multiply by
 //    d_w*d_x, f32 accumulation.
 //  * the Q80 activations of this CTA's K range are resident in shared memory.  They either arrive
@@ -13,31 +15,35 @@
 //    sums of all ranks into the residual stream, RMSNorm, Q80 cast (DlNormProlog).  The weight
 //    prefetch is already in flight while this runs, so the all-gather / merge-add / norm / cast
 //    of the reference (4 ops + a socket sync) costs no extra kernel and no global round trip.
-//  * grid = row_tiles * R (row split) * S (K split); the S CTAs of a tile form a thread-block
-//    cluster: they share the row's sum of squares and reduce their partial dot products through
-//    distributed shared memory -- deterministic, no atomics, no global scratch.
+//  * work split: a CTA owns 1..T row tiles (T > 1 for matrices with more row tiles than SMs: the
+//    pipeline streams straight through tile boundaries) or, for small matrices, 1/S of the K range
+//    of one row tile; the S CTAs of a tile form a thread-block cluster that shares the row's sum
+//    of squares and pushes partial dot products into the leader through distributed shared
+//    memory (remote stores + a remote mbarrier arrive) -- deterministic, no atomics, no global
+//    scratch, no second cluster barrier.
 //  * weight prefetch is issued before griddepcontrol.wait, so under programmatic dependent
 //    launch the first stages stream while the previous kernel (or a peer GPU) still runs.
 //  * the epilogue (epilogue.cuh) fuses RoPE + KV-cache write, SiLU*mul + Q80 cast, or the
 //    Q80-cast partial-sum push to every peer GPU with release flags.
 #include "epilogue.cuh"
 
-#define GEMV_NS 8                       // pipeline stages
-#define GEMV_CONSUMERS 256              // 2 groups x 128 threads
+#define GEMV_NS 12                      // pipeline stages
+#define GEMV_NG 4                       // consumer groups of 128 threads
+#define GEMV_CONSUMERS (GEMV_NG * 128)
 #define GEMV_THREADS (GEMV_CONSUMERS + 32)
 #define GEMV_WARPS (GEMV_THREADS / 32)
 #define GEMV_MAX_M 8
-#define GEMV_MAX_ACT_BYTES (96 * 1024)
 
-#define GEMV_TRACE(k)                                                                     \
-    do {                                                                                  \
-        if (a.trace != nullptr && (threadIdx.x == 0)) a.trace[blockIdx.x * 8 + (k)] = globaltimer_ns(); \
+#define GEMV_TRACE(k)                                                                                      \
+    do {                                                                                                   \
+        if (a.trace != nullptr && (threadIdx.x == 0)) a.trace[blockIdx.x * 8 + (k)] = globaltimer_ns();    \
     } while (0)
 
 struct GemvArgs {
     const uint8_t* w;
     const uint8_t* xq;
-    int d_real, d_pad, KT, M, R, S, n;
+    int d_real, d_pad, KT, M, R, S, T, n;
+    int n_units;              // row_tiles * R
     int n_epi_ctas;
     int fused;
     unsigned long long* trace;
@@ -46,8 +52,37 @@ struct GemvArgs {
     DlEpilogue epi;
 };
 
+DL_DEVINL void consumer_bar() { asm volatile("bar.sync 1, %0;" ::"n"(GEMV_CONSUMERS) : "memory"); }
+
+// Q80-quantise one 32-element block held in v[8] (already normalised) and store it into the
+// resident activation slab of k-block b, row m.
+DL_DEVINL void store_q80_block_smem(const float4 (&v)[8], uint8_t* act_s, int M, int m, int b) {
+    float amax = 0.0f;
+#pragma unroll
+    for (int j = 0; j < 8; j++)
+        amax = fmaxf(amax, fmaxf(fmaxf(fabsf(v[j].x), fabsf(v[j].y)), fmaxf(fabsf(v[j].z), fabsf(v[j].w))));
+    const float d = amax / 127.0f;
+    const float id = (d != 0.0f) ? (1.0f / d) : 0.0f;
+    int sumq = 0;
+    uint32_t packed[8];
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+        const int q0 = __float2int_rn(v[j].x * id), q1 = __float2int_rn(v[j].y * id);
+        const int q2 = __float2int_rn(v[j].z * id), q3 = __float2int_rn(v[j].w * id);
+        sumq += q0 + q1 + q2 + q3;
+        packed[j] = (uint32_t)(q0 & 0xff) | ((uint32_t)(q1 & 0xff) << 8) | ((uint32_t)(q2 & 0xff) << 16) |
+                    ((uint32_t)(q3 & 0xff) << 24);
+    }
+    uint8_t* rowp = act_s + ((size_t)(b >> 2) * M + m) * XQ_ROW_BYTES;
+    uint4* qdst = reinterpret_cast<uint4*>(rowp + (b & 3) * 32);
+    qdst[0] = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+    qdst[1] = make_uint4(packed[4], packed[5], packed[6], packed[7]);
+    reinterpret_cast<float*>(rowp + 128)[b & 3] = __half2float(__float2half_rn(d));
+    reinterpret_cast<int*>(rowp + 144)[b & 3] = 8 * sumq;
+}
+
 template <int MT>
-__global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_q40_kernel(const __grid_constant__ GemvArgs a) {
+__global__ void __launch_bounds__(GEMV_THREADS, 1) gemv_q40_kernel(const __grid_constant__ GemvArgs a) {
     extern __shared__ __align__(128) uint8_t smem[];
     trace_begin(a.tr);
     const int S = a.S, R = a.R, M = a.M;
@@ -59,25 +94,37 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_q40_kernel(const __grid_
     int* sflag = reinterpret_cast<int*>(red_bar + 1);
     uint8_t* stages = smem + 256;                                                    // [NS][9216]
     uint8_t* act_s = stages + GEMV_NS * Q40T_TILE_BYTES;                             // [nk][M][160]
-    float* red = reinterpret_cast<float*>(act_s + (size_t)nk_max * M * XQ_ROW_BYTES);   // [2*R][MT][rows] (<= 2*MT*128)
-    float* out_s = red + 2 * MT * 128;                                               // [MT][128]
+    float* red = reinterpret_cast<float*>(act_s + (size_t)nk_max * M * XQ_ROW_BYTES);   // [NG*R][MT][rows] (<= NG*MT*128)
+    float* out_s = red + GEMV_NG * MT * 128;                                         // [MT][128]
     float* ssq_w = out_s + MT * 128;                                                 // [GEMV_WARPS][MT]
     float* ssq_all = ssq_w + GEMV_WARPS * MT;                                        // [S][MT] filled by all cluster ranks
-    float* recv = ssq_all + 8 * MT;                                                         // leader: [S-1][MT][128]
+    float* recv = ssq_all + 8 * MT;                                                  // leader: [S-1][MT][128]
 
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
     const int crank = (S > 1) ? (int)cg::this_cluster().block_rank() : 0;
-    const int tile_idx = blockIdx.x / S;
-    const int rt = tile_idx / R, rs = tile_idx % R;
+    const int cl = blockIdx.x / S;                  // cluster (work unit owner) index
+    const int n_owners = gridDim.x / S;
     const int rows = Q40T_TILE_ROWS / R;
     const int kt0 = (a.KT * crank) / S, kt1 = (a.KT * (crank + 1)) / S;
     const int nk = kt1 - kt0;
+    // units (row tile, row part) handled by this cluster: cl, cl + n_owners, ...
+    const int n_my = (a.n_units - cl + n_owners - 1) / n_owners;
+    const int n_it = n_my * nk;
     const bool is_producer = (tid == GEMV_CONSUMERS);
     const uint32_t nib_bytes = rows * 64, sc_bytes = rows * 8;
-    const uint8_t* wt = a.w + ((size_t)rt * a.KT + kt0) * Q40T_TILE_BYTES;
-    const int pre = nk < GEMV_NS ? nk : GEMV_NS;
+    const int pre = n_it < GEMV_NS ? n_it : GEMV_NS;
     uint64_t pol = 0;
+
+    auto issue = [&](int it, int s) {
+        const int unit = cl + (it / nk) * n_owners;
+        const int rt = unit / R, rs = unit % R;
+        const uint8_t* t = a.w + ((size_t)rt * a.KT + kt0 + (it % nk)) * Q40T_TILE_BYTES;
+        uint8_t* st = stages + s * Q40T_TILE_BYTES;
+        mbar_arrive_expect_tx(&full[s], nib_bytes + sc_bytes);
+        bulk_g2s_hint(st, t + rs * nib_bytes, nib_bytes, &full[s], pol);
+        bulk_g2s_hint(st + Q40T_NIB_BYTES, t + Q40T_SCALE_OFF + rs * sc_bytes, sc_bytes, &full[s], pol);
+    };
 
     if (tid == 0) {
         for (int s = 0; s < GEMV_NS; s++) {
@@ -96,13 +143,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_q40_kernel(const __grid_
     if (is_producer) {
         // weights do not depend on the previous kernel: stream the first ring-full before the PDL wait
         pol = l2_policy_evict_first();
-        for (int i = 0; i < pre; i++) {
-            uint8_t* st = stages + i * Q40T_TILE_BYTES;
-            const uint8_t* t = wt + (size_t)i * Q40T_TILE_BYTES;
-            mbar_arrive_expect_tx(&full[i], nib_bytes + sc_bytes);
-            bulk_g2s_hint(st, t + rs * nib_bytes, nib_bytes, &full[i], pol);
-            bulk_g2s_hint(st + Q40T_NIB_BYTES, t + Q40T_SCALE_OFF + rs * sc_bytes, sc_bytes, &full[i], pol);
-        }
+        for (int it = 0; it < pre; it++) issue(it, it);
     }
 
     if (a.fused) {
@@ -118,23 +159,54 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_q40_kernel(const __grid_
         }
         const int dim = a.n;
         const int e0 = kt0 * 128, e1 = kt1 * 128;                 // this CTA's K range (cluster ranks tile the row)
-        const bool writer = (nm.x_out != nullptr) && (tile_idx == 0);
+        const bool writer = (nm.x_out != nullptr) && (cl == 0);
+        const int nkb = nk * 4;
+        const int items = M * nkb;
+        const bool one_pass = items <= GEMV_THREADS;              // a whole 32-block per thread, kept in registers
         float ss[MT];
 #pragma unroll
         for (int m = 0; m < MT; m++) ss[m] = 0.0f;
-        // pass 1: sum of squares of (x + partials) over the K range; row tile 0 publishes x_out
+        float4 v[8];
+        int my_m = 0, my_b = 0;
+        if (one_pass) {
+            if (tid < items) {
+                my_m = tid / nkb;
+                my_b = tid % nkb;
+                const size_t e = (size_t)my_m * dim + e0 + my_b * 32;
 #pragma unroll
-        for (int m = 0; m < MT; m++) {
-            if (m < M) {
-                const float4* xi = reinterpret_cast<const float4*>(nm.x_in + (size_t)m * dim);
-                for (int i4 = e0 / 4 + tid; i4 < e1 / 4; i4 += GEMV_THREADS) {
-                    float4 v = xi[i4];
-                    for (int s = 0; s < nm.n_src; s++) {
-                        const float4 p = reinterpret_cast<const float4*>(nm.partials + (size_t)s * nm.src_stride + (size_t)m * dim)[i4];
-                        v.x += p.x; v.y += p.y; v.z += p.z; v.w += p.w;
+                for (int j = 0; j < 8; j++) v[j] = reinterpret_cast<const float4*>(nm.x_in + e)[j];
+                for (int s = 0; s < nm.n_src; s++) {
+                    const float4* p = reinterpret_cast<const float4*>(nm.partials + (size_t)s * nm.src_stride + e);
+#pragma unroll
+                    for (int j = 0; j < 8; j++) {
+                        const float4 t = p[j];
+                        v[j].x += t.x; v[j].y += t.y; v[j].z += t.z; v[j].w += t.w;
                     }
-                    if (writer) reinterpret_cast<float4*>(nm.x_out + (size_t)m * dim)[i4] = v;
-                    ss[m] += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+                }
+                float sq = 0.0f;
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                    if (writer) reinterpret_cast<float4*>(nm.x_out + e)[j] = v[j];
+                    sq += v[j].x * v[j].x + v[j].y * v[j].y + v[j].z * v[j].z + v[j].w * v[j].w;
+                }
+#pragma unroll
+                for (int m = 0; m < MT; m++) ss[m] = (m == my_m) ? sq : 0.0f;
+            }
+        } else {
+            // pass 1 of 2: coalesced float4 sweep for the sum of squares; row tile 0 publishes x_out
+#pragma unroll
+            for (int m = 0; m < MT; m++) {
+                if (m < M) {
+                    const float4* xi = reinterpret_cast<const float4*>(nm.x_in + (size_t)m * dim);
+                    for (int i4 = e0 / 4 + tid; i4 < e1 / 4; i4 += GEMV_THREADS) {
+                        float4 x4 = xi[i4];
+                        for (int s = 0; s < nm.n_src; s++) {
+                            const float4 p = reinterpret_cast<const float4*>(nm.partials + (size_t)s * nm.src_stride + (size_t)m * dim)[i4];
+                            x4.x += p.x; x4.y += p.y; x4.z += p.z; x4.w += p.w;
+                        }
+                        if (writer) reinterpret_cast<float4*>(nm.x_out + (size_t)m * dim)[i4] = x4;
+                        ss[m] += x4.x * x4.x + x4.y * x4.y + x4.z * x4.z + x4.w * x4.w;
+                    }
                 }
             }
         }
@@ -157,6 +229,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_q40_kernel(const __grid_
             }
         }
         if (S > 1) cg::this_cluster().sync(); else __syncthreads();
+        GEMV_TRACE(4);
         float inv[MT];
 #pragma unroll
         for (int m = 0; m < MT; m++) {
@@ -164,56 +237,36 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_q40_kernel(const __grid_
             for (int c = 0; c < S; c++) t += ssq_all[c * MT + m];
             inv[m] = 1.0f / sqrtf(t / (float)dim + nm.eps);
         }
-        // pass 2: y = w * (inv * x) -> Q80 -> resident activation slabs.  One THREAD per 32-block: its 8
-        // float4 loads per operand are independent (one L2 round trip, lines are hot from pass 1), the
-        // abs-max / rounding / sum need no shuffles, and the block is written with two 16-byte stores.
-        const int nkb = nk * 4;
-        for (int item = tid; item < M * nkb; item += GEMV_THREADS) {
-            const int m = item / nkb, b = item % nkb;
-            const size_t e = (size_t)m * dim + e0 + b * 32;
-            float4 v[8];
+        // y = w * (inv * x) -> Q80 -> resident activation slabs, one THREAD per 32-block (no shuffles)
+        for (int item = tid; item < items; item += GEMV_THREADS) {
+            const int m = one_pass ? my_m : item / nkb, b = one_pass ? my_b : item % nkb;
+            if (!one_pass) {
+                const size_t e = (size_t)m * dim + e0 + b * 32;
 #pragma unroll
-            for (int j = 0; j < 8; j++) v[j] = reinterpret_cast<const float4*>(nm.x_in + e)[j];
-            for (int s = 0; s < nm.n_src; s++) {
-                const float4* p = reinterpret_cast<const float4*>(nm.partials + (size_t)s * nm.src_stride + e);
+                for (int j = 0; j < 8; j++) v[j] = reinterpret_cast<const float4*>(nm.x_in + e)[j];
+                for (int s = 0; s < nm.n_src; s++) {
+                    const float4* p = reinterpret_cast<const float4*>(nm.partials + (size_t)s * nm.src_stride + e);
 #pragma unroll
-                for (int j = 0; j < 8; j++) {
-                    const float4 t = p[j];
-                    v[j].x += t.x; v[j].y += t.y; v[j].z += t.z; v[j].w += t.w;
+                    for (int j = 0; j < 8; j++) {
+                        const float4 t = p[j];
+                        v[j].x += t.x; v[j].y += t.y; v[j].z += t.z; v[j].w += t.w;
+                    }
                 }
             }
             float im = inv[0];
 #pragma unroll
             for (int q = 1; q < MT; q++) im = (m == q) ? inv[q] : im;
             const float4* wn = reinterpret_cast<const float4*>(nm.norm_w + e0 + b * 32);
-            float amax = 0.0f;
 #pragma unroll
             for (int j = 0; j < 8; j++) {
                 const float4 w4 = wn[j];
                 v[j].x = w4.x * (im * v[j].x); v[j].y = w4.y * (im * v[j].y);
                 v[j].z = w4.z * (im * v[j].z); v[j].w = w4.w * (im * v[j].w);
-                amax = fmaxf(amax, fmaxf(fmaxf(fabsf(v[j].x), fabsf(v[j].y)), fmaxf(fabsf(v[j].z), fabsf(v[j].w))));
             }
-            const float d = amax / 127.0f;
-            const float id = (d != 0.0f) ? (1.0f / d) : 0.0f;
-            int sumq = 0;
-            uint32_t packed[8];
-#pragma unroll
-            for (int j = 0; j < 8; j++) {
-                const int q0 = __float2int_rn(v[j].x * id), q1 = __float2int_rn(v[j].y * id);
-                const int q2 = __float2int_rn(v[j].z * id), q3 = __float2int_rn(v[j].w * id);
-                sumq += q0 + q1 + q2 + q3;
-                packed[j] = (uint32_t)(q0 & 0xff) | ((uint32_t)(q1 & 0xff) << 8) | ((uint32_t)(q2 & 0xff) << 16) |
-                            ((uint32_t)(q3 & 0xff) << 24);
-            }
-            uint8_t* rowp = act_s + ((size_t)(b >> 2) * M + m) * XQ_ROW_BYTES;
-            uint4* qdst = reinterpret_cast<uint4*>(rowp + (b & 3) * 32);
-            qdst[0] = make_uint4(packed[0], packed[1], packed[2], packed[3]);
-            qdst[1] = make_uint4(packed[4], packed[5], packed[6], packed[7]);
-            reinterpret_cast<float*>(rowp + 128)[b & 3] = __half2float(__float2half_rn(d));
-            reinterpret_cast<int*>(rowp + 144)[b & 3] = 8 * sumq;
+            store_q80_block_smem(v, act_s, M, m, b);
         }
         __syncthreads();
+        GEMV_TRACE(6);
     }
 
     if (warp == GEMV_CONSUMERS / 32) {
@@ -225,76 +278,82 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_q40_kernel(const __grid_
                 mbar_arrive_expect_tx(act_full, act_bytes);
                 bulk_g2s(act_s, a.xq + (size_t)kt0 * M * XQ_ROW_BYTES, act_bytes, act_full);
             }
-            for (int i = pre; i < nk; i++) {
-                const int s = i % GEMV_NS;
-                mbar_wait(&empty[s], ((i / GEMV_NS) & 1) ^ 1);
-                uint8_t* st = stages + s * Q40T_TILE_BYTES;
-                const uint8_t* t = wt + (size_t)i * Q40T_TILE_BYTES;
-                mbar_arrive_expect_tx(&full[s], nib_bytes + sc_bytes);
-                bulk_g2s_hint(st, t + rs * nib_bytes, nib_bytes, &full[s], pol);
-                bulk_g2s_hint(st + Q40T_NIB_BYTES, t + Q40T_SCALE_OFF + rs * sc_bytes, sc_bytes, &full[s], pol);
+            for (int it = pre; it < n_it; it++) {
+                const int s = it % GEMV_NS;
+                mbar_wait(&empty[s], ((it / GEMV_NS) & 1) ^ 1);
+                issue(it, s);
             }
         }
     } else {
         // ------------------------------ consumers ------------------------------
-        const int g = tid >> 7;              // consumer group: k-iterations i with i%2 == g
+        const int g = tid >> 7;              // consumer group: k-tile i of a unit goes to group i % NG
         const int t = tid & 127;
         const int row = t % rows;            // local row
-        const int kq = t / rows;             // handles blocks kb = kq, kq+R, ...
-        const int rtile = rs * rows + row;   // row inside the 128-row tile (for the rotation)
-        float acc[MT];
-#pragma unroll
-        for (int m = 0; m < MT; m++) acc[m] = 0.0f;
+        const int kq = t / rows;             // handles blocks kb with (kb % R) == kq
         if (!a.fused) mbar_wait(act_full, 0);
+        pdl_wait();                          // already satisfied (producer / prologue waited); orders the epilogue's reads
         if (tid == 0) { GEMV_TRACE(1); }
 
-        for (int i = g; i < nk; i += 2) {
-            const int s = i % GEMV_NS;
-            mbar_wait(&full[s], (i / GEMV_NS) & 1);
-            const uint8_t* st = stages + s * Q40T_TILE_BYTES;
-            const uint8_t* act = act_s + (size_t)i * M * XQ_ROW_BYTES;
-            // fully unrolled over the 4 blocks of the tile row (predicated on ownership when R > 1) so the
-            // loads and dp4a chains of different blocks overlap: the loop is latency-bound otherwise
+        for (int u = 0; u < n_my; u++) {
+            const int unit = cl + u * n_owners;
+            const int rt = unit / R, rs = unit % R;
+            const int rtile = rs * rows + row;   // row inside the 128-row tile (for the rotation)
+            float acc[MT];
 #pragma unroll
-            for (int kb = 0; kb < 4; kb++) {
-                if ((kb & (R - 1)) != kq) continue;
-                const uint4 nb = *reinterpret_cast<const uint4*>(st + row * 64 + (((kb + (rtile >> 1)) & 3) << 4));
-                const float dw = __half2float(*reinterpret_cast<const __half*>(st + Q40T_NIB_BYTES + row * 8 + kb * 2));
-                const int lo0 = nb.x & 0x0F0F0F0F, hi0 = (nb.x >> 4) & 0x0F0F0F0F;
-                const int lo1 = nb.y & 0x0F0F0F0F, hi1 = (nb.y >> 4) & 0x0F0F0F0F;
-                const int lo2 = nb.z & 0x0F0F0F0F, hi2 = (nb.z >> 4) & 0x0F0F0F0F;
-                const int lo3 = nb.w & 0x0F0F0F0F, hi3 = (nb.w >> 4) & 0x0F0F0F0F;
+            for (int m = 0; m < MT; m++) acc[m] = 0.0f;
+            for (int i = g; i < nk; i += GEMV_NG) {
+                const int it = u * nk + i;
+                const int s = it % GEMV_NS;
+                mbar_wait(&full[s], (it / GEMV_NS) & 1);
+                const uint8_t* st = stages + s * Q40T_TILE_BYTES;
+                const uint8_t* act = act_s + (size_t)i * M * XQ_ROW_BYTES;
+                // fully unrolled over the 4 blocks of the tile row (predicated on ownership when R > 1)
+                // so the loads and dp4a chains of different blocks overlap
 #pragma unroll
-                for (int m = 0; m < MT; m++) {
-                    if (m < M) {
-                        const uint8_t* xr = act + m * XQ_ROW_BYTES;
-                        const int4 xl = *reinterpret_cast<const int4*>(xr + kb * 32);
-                        const int4 xh = *reinterpret_cast<const int4*>(xr + kb * 32 + 16);
-                        // two independent dp4a chains (low / high nibbles) for ILP
-                        int is0 = __dp4a(lo0, xl.x, 0), is1 = __dp4a(hi0, xh.x, 0);
-                        is0 = __dp4a(lo1, xl.y, is0); is1 = __dp4a(hi1, xh.y, is1);
-                        is0 = __dp4a(lo2, xl.z, is0); is1 = __dp4a(hi2, xh.z, is1);
-                        is0 = __dp4a(lo3, xl.w, is0); is1 = __dp4a(hi3, xh.w, is1);
-                        const float dx = reinterpret_cast<const float*>(xr + 128)[kb];
-                        const int s8 = reinterpret_cast<const int*>(xr + 144)[kb];
-                        acc[m] += (float)(is0 + is1 - s8) * (dw * dx);
+                for (int kb = 0; kb < 4; kb++) {
+                    if ((kb & (R - 1)) != kq) continue;
+                    const uint4 nb = *reinterpret_cast<const uint4*>(st + row * 64 + (((kb + (rtile >> 1)) & 3) << 4));
+                    const float dw = __half2float(*reinterpret_cast<const __half*>(st + Q40T_NIB_BYTES + row * 8 + kb * 2));
+                    const int lo0 = nb.x & 0x0F0F0F0F, hi0 = (nb.x >> 4) & 0x0F0F0F0F;
+                    const int lo1 = nb.y & 0x0F0F0F0F, hi1 = (nb.y >> 4) & 0x0F0F0F0F;
+                    const int lo2 = nb.z & 0x0F0F0F0F, hi2 = (nb.z >> 4) & 0x0F0F0F0F;
+                    const int lo3 = nb.w & 0x0F0F0F0F, hi3 = (nb.w >> 4) & 0x0F0F0F0F;
+#pragma unroll
+                    for (int m = 0; m < MT; m++) {
+                        if (m < M) {
+                            const uint8_t* xr = act + m * XQ_ROW_BYTES;
+                            const int4 xl = *reinterpret_cast<const int4*>(xr + kb * 32);
+                            const int4 xh = *reinterpret_cast<const int4*>(xr + kb * 32 + 16);
+                            // two independent dp4a chains (low / high nibbles) for ILP
+                            int is0 = __dp4a(lo0, xl.x, 0), is1 = __dp4a(hi0, xh.x, 0);
+                            is0 = __dp4a(lo1, xl.y, is0); is1 = __dp4a(hi1, xh.y, is1);
+                            is0 = __dp4a(lo2, xl.z, is0); is1 = __dp4a(hi2, xh.z, is1);
+                            is0 = __dp4a(lo3, xl.w, is0); is1 = __dp4a(hi3, xh.w, is1);
+                            const float dx = reinterpret_cast<const float*>(xr + 128)[kb];
+                            const int s8 = reinterpret_cast<const int*>(xr + 144)[kb];
+                            acc[m] += (float)(is0 + is1 - s8) * (dw * dx);
+                        }
                     }
                 }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&empty[s]);
             }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&empty[s]);
-        }
-        if (tid == 0) { GEMV_TRACE(2); }
-        // partial sums of the 2*R (group, kq) owners of each row
+            if (tid == 0 && u == n_my - 1) { GEMV_TRACE(2); }
+            // partial sums of the NG*R (group, kq) owners of each row -> out_s
 #pragma unroll
-        for (int m = 0; m < MT; m++) red[((g * R + kq) * MT + m) * rows + row] = acc[m];
-    }
-    __syncthreads();
-    for (int idx = tid; idx < MT * rows; idx += GEMV_THREADS) {
-        const int m = idx / rows, r = idx % rows;
-        float v = 0.0f;
-        for (int j = 0; j < 2 * R; j++) v += red[(j * MT + m) * rows + r];
-        out_s[m * 128 + r] = v;
+            for (int m = 0; m < MT; m++) red[((g * R + kq) * MT + m) * rows + row] = acc[m];
+            consumer_bar();
+            for (int idx = tid; idx < MT * rows; idx += GEMV_CONSUMERS) {
+                const int m = idx / rows, r = idx % rows;
+                float vsum = 0.0f;
+                for (int j = 0; j < GEMV_NG * R; j++) vsum += red[(j * MT + m) * rows + r];
+                out_s[m * 128 + r] = vsum;
+            }
+            if (S > 1) break;                // split-K: finish below (exactly one unit per cluster)
+            consumer_bar();
+            epilogue_rows(a.epi, out_s, 128, rows, rt * Q40T_TILE_ROWS + rs * rows, a.d_real, M, 0, tid);
+            if (u + 1 < n_my) consumer_bar();   // out_s / red are reused by the next unit
+        }
     }
     GEMV_TRACE(3);
     if (S > 1) {
@@ -317,14 +376,15 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_q40_kernel(const __grid_
         mbar_wait_cluster(red_bar, 0);
         for (int idx = tid; idx < MT * rows; idx += GEMV_THREADS) {
             const int m = idx / rows, r = idx % rows;
-            float v = out_s[m * 128 + r];
-            for (int c = 0; c < S - 1; c++) v += recv[(size_t)c * MT * 128 + m * 128 + r];
-            out_s[m * 128 + r] = v;
+            float vsum = out_s[m * 128 + r];
+            for (int c = 0; c < S - 1; c++) vsum += recv[(size_t)c * MT * 128 + m * 128 + r];
+            out_s[m * 128 + r] = vsum;
         }
+        __syncthreads();
+        pdl_wait();
+        const int rt = cl / R, rs = cl % R;
+        epilogue_rows(a.epi, out_s, 128, rows, rt * Q40T_TILE_ROWS + rs * rows, a.d_real, M, 0, tid);
     }
-    __syncthreads();
-    pdl_wait();
-    epilogue_rows(a.epi, out_s, 128, rows, rt * Q40T_TILE_ROWS + rs * rows, a.d_real, M, 0, tid);
     epilogue_complete(a.epi, tid, a.n_epi_ctas, sflag);
     GEMV_TRACE(5);
     trace_end(a.tr);
@@ -332,7 +392,8 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_q40_kernel(const __grid_
 
 static size_t gemv_smem_bytes(int MT, int nk_max, int M) {
     return 256 + (size_t)GEMV_NS * Q40T_TILE_BYTES + (size_t)nk_max * M * XQ_ROW_BYTES +
-           (size_t)(2 * MT * 128 + MT * 128) * 4 + (size_t)(GEMV_WARPS * MT + 8 * MT) * 4 + (size_t)7 * MT * 128 * 4 + 16;
+           (size_t)(GEMV_NG * MT * 128 + MT * 128) * 4 + (size_t)(GEMV_WARPS * MT + 8 * MT) * 4 +
+           (size_t)7 * MT * 128 * 4 + 16;
 }
 
 static int mt_of(int M) { return M == 1 ? 1 : (M == 2 ? 2 : (M <= 4 ? 4 : 8)); }
@@ -349,7 +410,7 @@ static unsigned long long* g_gemv_trace = nullptr;
 extern "C" void dl_debug_set_gemv_trace(unsigned long long* p) { g_gemv_trace = p; }
 
 template <int MT>
-static int launch_gemv(const GemvArgs& a, int pdl, cudaStream_t stream) {
+static int launch_gemv(const GemvArgs& a, int grid, int pdl, cudaStream_t stream) {
     static size_t attr_max = 0;
     const size_t smem = gemv_smem_bytes(MT, (a.KT + a.S - 1) / a.S, a.M);
     if (smem > 227 * 1024) { dl_set_error("dl_gemv_q40: %zu B of shared memory needed (n=%d, M=%d, k_split=%d): raise k_split", smem, a.n, a.M, a.S); return -1; }
@@ -359,7 +420,7 @@ static int launch_gemv(const GemvArgs& a, int pdl, cudaStream_t stream) {
         attr_max = smem;
     }
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((unsigned)((a.d_pad / Q40T_TILE_ROWS) * a.R * a.S));
+    cfg.gridDim = dim3((unsigned)grid);
     cfg.blockDim = dim3(GEMV_THREADS);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = stream;
@@ -384,12 +445,16 @@ static int launch_gemv(const GemvArgs& a, int pdl, cudaStream_t stream) {
     return 0;
 }
 
+// row_split R in {1,2,4}: a 128-row tile is cut into R row parts; k_split S in 1..8: the K range of a
+// unit is cut over a cluster of S CTAs; tiles_per_cta T >= 1 (only with S == 1): each CTA streams
+// through T units back to back.
 extern "C" int dl_gemv_q40(const uint8_t* w_q40t, int d, int n, const uint8_t* xq, int M, int row_split, int k_split,
-                           const DlNormProlog* norm, const DlEpilogue* epi, int pdl, void* stream) {
+                           int tiles_per_cta, const DlNormProlog* norm, const DlEpilogue* epi, int pdl, void* stream) {
     if (M < 1 || M > GEMV_MAX_M) { dl_set_error("dl_gemv_q40: M=%d out of range 1..8", M); return -1; }
     if (n % Q40T_TILE_K != 0) { dl_set_error("dl_gemv_q40: n=%d not a multiple of 128", n); return -1; }
     if (row_split != 1 && row_split != 2 && row_split != 4) { dl_set_error("dl_gemv_q40: row_split must be 1,2,4"); return -1; }
-    if (k_split != 1 && k_split != 2 && k_split != 4 && k_split != 8) { dl_set_error("dl_gemv_q40: k_split must be 1,2,4,8"); return -1; }
+    if (k_split < 1 || k_split > 8) { dl_set_error("dl_gemv_q40: k_split must be 1..8"); return -1; }
+    if (tiles_per_cta < 1) tiles_per_cta = 1;
     if (epi->kind == DL_EPI_SILU_MUL && (row_split > 2 || d % 64 != 0)) { dl_set_error("dl_gemv_q40: silu epilogue needs row_split<=2, d%%64==0"); return -1; }
     if (norm == nullptr && xq == nullptr) { dl_set_error("dl_gemv_q40: need xq or a norm prologue"); return -1; }
     if (norm != nullptr && norm->n_src > DL_MAX_PEERS) { dl_set_error("dl_gemv_q40: n_src > 8"); return -1; }
@@ -401,20 +466,25 @@ extern "C" int dl_gemv_q40(const uint8_t* w_q40t, int d, int n, const uint8_t* x
     a.KT = n / Q40T_TILE_K;
     a.n = n;
     if (k_split > a.KT) k_split = 1;
+    if (k_split > 1) tiles_per_cta = 1;
     a.M = M;
     a.R = row_split;
     a.S = k_split;
-    a.n_epi_ctas = (a.d_pad / Q40T_TILE_ROWS) * a.R;
+    a.T = tiles_per_cta;
+    a.n_units = (a.d_pad / Q40T_TILE_ROWS) * a.R;
+    const int owners = (a.n_units + a.T - 1) / a.T;
+    a.n_epi_ctas = owners;
     a.fused = norm != nullptr ? 1 : 0;
     if (norm != nullptr) a.norm = *norm; else memset(&a.norm, 0, sizeof(a.norm));
     a.epi = *epi;
     a.trace = g_gemv_trace;
     a.tr = dl_trace_next(TR_GEMV);
+    const int grid = owners * a.S;
     cudaStream_t st = (cudaStream_t)stream;
     switch (mt_of(M)) {
-        case 1: return launch_gemv<1>(a, pdl, st);
-        case 2: return launch_gemv<2>(a, pdl, st);
-        case 4: return launch_gemv<4>(a, pdl, st);
-        default: return launch_gemv<8>(a, pdl, st);
+        case 1: return launch_gemv<1>(a, grid, pdl, st);
+        case 2: return launch_gemv<2>(a, grid, pdl, st);
+        case 4: return launch_gemv<4>(a, grid, pdl, st);
+        default: return launch_gemv<8>(a, grid, pdl, st);
     }
 }

@@ -265,8 +265,9 @@ class LlamaEngine:
     # ------------------------------------------------------------------------------------------------
     def _matmul(self, w, d, n, M, xq, xh, epi, kind, norm=None):
         if M <= GEMV_MAX_M:
-            R, S = K.choose_splits(d, n, kind, self.n_sms, M)
-            K.gemv_q40(w, d, n, None if norm is not None else xq, M, epi, R, S, norm=norm, pdl=self.use_pdl)
+            R, S, T = K.choose_splits(d, n, kind, self.n_sms, M)
+            K.gemv_q40(w, d, n, None if norm is not None else xq, M, epi, R, S, norm=norm, pdl=self.use_pdl,
+                       tiles_per_cta=T)
         else:
             assert norm is None
             row_tiles = (d + 127) // 128
@@ -306,8 +307,7 @@ class LlamaEngine:
             flags = pending[1] if (merge and multi) else None
             fuse = False
             if rows <= GEMV_MAX_M:
-                r_, s_ = K.choose_splits(d, h.dim, kind, self.n_sms, rows)
-                fuse = ((d + 127) // 128) * r_ * s_ <= 2 * self.n_sms     # every CTA repeats the prologue
+                fuse = True          # the grid never exceeds one CTA per SM: the repeated prologue is cheap
             if fuse:
                 nm = K.norm_prolog(x_in, x_out, parts, N, src_stride, flags, sc, L, flag_add, w_norm, eps)
                 self._matmul(weight, d, h.dim, rows, None, None, epi, kind, norm=nm)

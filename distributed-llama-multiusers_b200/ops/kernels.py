@@ -163,9 +163,10 @@ def norm_prolog(x_in, x_out, partials: Optional[int], n_src: int, src_stride: in
 
 
 def gemv_q40(w: torch.Tensor, d: int, n: int, xq: Optional[torch.Tensor], M: int, epi: DlEpilogue,
-             row_split: int = 1, k_split: int = 1, norm: Optional[DlNormProlog] = None, pdl: bool = False):
+             row_split: int = 1, k_split: int = 1, norm: Optional[DlNormProlog] = None, pdl: bool = False,
+             tiles_per_cta: int = 1):
     """M<=8 rows.  Activations: XQ slabs with row capacity == M (xq), or the fused norm prologue."""
-    check(cuda_lib().dl_gemv_q40(w.data_ptr(), d, n, _p(xq), M, row_split, k_split,
+    check(cuda_lib().dl_gemv_q40(w.data_ptr(), d, n, _p(xq), M, row_split, k_split, tiles_per_cta,
                                  C.byref(norm) if norm is not None else None, C.byref(epi),
                                  1 if pdl else 0, _stream()), "dl_gemv_q40")
     lib.count_launch()
@@ -223,24 +224,22 @@ def wait_flags(flags: int, n: int, step_counter: int, flag_mul: int, flag_add: i
 
 
 def choose_splits(d: int, n: int, epi_kind: int, n_sms: int = 148, M: int = 1):
-    """Pick (row_split R, k_split S) so the GEMV grid covers the chip and its resident
-    activations fit in shared memory.
+    """Work split of the GEMV -> (row_split R, k_split S, tiles_per_cta T); grid = ceil(units/T)*S.
 
-    K is split first (cluster of S CTAs, reduced through DSMEM): it keeps every pipeline stage a
-    full 9 KB tile.  Row splitting (R) shrinks the stages, so it is the last resort (R<=2 when the
-    epilogue needs 64-row groups)."""
+    The kernel runs one CTA per SM, so the grid is kept within one wave:
+      * more row tiles than SMs: every CTA streams T = ceil(row_tiles/SMs) tiles back to back;
+      * fewer: the K range of each tile is cut over a cluster of S CTAs (DSMEM reduction), and only
+        if that still leaves most SMs idle are tiles also cut into R row parts (which shrinks the
+        pipeline stages; R<=2 when the epilogue needs 64-row groups)."""
     row_tiles = (d + 127) // 128
     kt = n // 128
+    if row_tiles >= n_sms:
+        return 1, 1, (row_tiles + n_sms - 1) // n_sms
+    S = max(1, min(8, kt, n_sms // row_tiles))
+    while S < min(8, kt) and int(cuda_lib().dl_gemv_q40_smem_bytes(n, M, S)) > 200 * 1024:
+        S += 1
+    R = 1
     max_r = 2 if epi_kind == EPI_SILU_MUL else 4
-    R, S = 1, 1
-    while S < 8 and S * 2 <= kt and int(cuda_lib().dl_gemv_q40_smem_bytes(n, M, S)) > 200 * 1024:
-        S *= 2
-    # two CTAs fit per SM; stay well inside one wave (cluster placement wastes some slots)
-    while row_tiles * R * S < (n_sms * 4) // 5:
-        if S < 8 and S * 2 <= kt and kt // (S * 2) >= 2:
-            S *= 2
-        elif R < max_r:
-            R *= 2
-        else:
-            break
-    return R, S
+    while R < max_r and row_tiles * S * R * 2 <= n_sms:
+        R *= 2
+    return R, S, 1

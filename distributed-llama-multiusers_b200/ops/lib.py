@@ -97,7 +97,7 @@ def cuda_lib():
                                        vp, vp, vp, i32, vp]
     L.dl_quant_q80.argtypes = [vp, i32, i32, i32, vp, vp, vp]
     L.dl_embedding.argtypes = [vp, vp, vp, i32, i32, vp, vp]
-    L.dl_gemv_q40.argtypes = [vp, i32, i32, vp, i32, i32, i32, C.POINTER(DlNormProlog), C.POINTER(DlEpilogue), i32, vp]
+    L.dl_gemv_q40.argtypes = [vp, i32, i32, vp, i32, i32, i32, i32, C.POINTER(DlNormProlog), C.POINTER(DlEpilogue), i32, vp]
     L.dl_gemv_q40_smem_bytes.restype = i64
     L.dl_gemv_q40_smem_bytes.argtypes = [i32, i32, i32]
     L.dl_gemm_q40_tc.argtypes = [vp, i32, i32, vp, i32, i32, i32, C.POINTER(DlEpilogue), i32, vp]

@@ -106,7 +106,8 @@ int dl_embedding(const float* table, const int* tokens, float* x, int M, int dim
 /* dp4a GEMV, M <= 8 rows: bulk-copy fed, cluster split-K (reference: matmul_Q80_Q40_F32,
  * src/nn/nn-cpu-ops.cpp:222-440) */
 int dl_gemv_q40(const uint8_t* w_q40t, int d, int n, const uint8_t* xq /*XQ slabs with mcap == M; unused when norm != NULL*/,
-                int M, int row_split, int k_split, const DlNormProlog* norm /*host, NULL = read xq*/,
+                int M, int row_split /*1,2,4*/, int k_split /*1..8, cluster size*/, int tiles_per_cta /*>=1, only with k_split==1*/,
+                const DlNormProlog* norm /*host, NULL = read xq*/,
                 const DlEpilogue* epi /*host*/, int pdl, void* stream);
 /* shared-memory bytes the GEMV needs for (n, M, k_split); callers pick k_split so that it fits */
 long long dl_gemv_q40_smem_bytes(int n, int M, int k_split);

@@ -62,14 +62,14 @@ def main():
             xq = K.alloc_xq(n, M, "cuda")
             x = torch.randn(M, n, device="cuda")
             K.quant_q80(x, M, n, M, xq, None)
-            R, S = K.choose_splits(d, n, EPI_STORE, n_sms, M)
+            R, S, T = K.choose_splits(d, n, EPI_STORE, n_sms, M)
             it = [0]
 
             def run():
-                K.gemv_q40(ws[it[0] % copies], d, n, xq, M, epi, R, S)
+                K.gemv_q40(ws[it[0] % copies], d, n, xq, M, epi, R, S, tiles_per_cta=T)
                 it[0] += 1
             us = timed(run, a.iters)
-            rows.append(dict(kernel="gemv", shape=name, d=d, n=n, M=M, R=R, S=S, us=round(us, 2),
+            rows.append(dict(kernel="gemv", shape=name, d=d, n=n, M=M, R=R, S=S, T=T, us=round(us, 2),
                              gbs=round(wbytes / us / 1e3, 1), frac_hbm=round(wbytes / us / 1e3 / hbm, 3)))
             print(rows[-1], flush=True)
         for M in [int(x) for x in a.tc_m.split(",") if x]:

@@ -22,6 +22,7 @@ def main():
     ap.add_argument("--n", type=int, default=4096)
     ap.add_argument("--M", type=int, default=1)
     ap.add_argument("--configs", default="auto,1x1,1x2,1x4,1x8,2x1,4x1")
+    ap.add_argument("--fused", type=int, default=0)
     a = ap.parse_args()
     L = K.cuda_lib()
     L.dl_debug_set_gemv_trace.argtypes = [C.c_void_p]
@@ -37,29 +38,36 @@ def main():
     y = torch.zeros(M, d, device="cuda")
     epi = K.epi_store([y.data_ptr()], d)
     trace = torch.zeros(4096 * 8, dtype=torch.int64, device="cuda")
+    nm = None
+    if a.fused:
+        xin = torch.randn(8, n, device="cuda")
+        wn = torch.ones(n, device="cuda")
+        nm = K.norm_prolog(xin, None, None, 0, 0, None, None, 0, 0, wn, 1e-5)
+    xq_arg = None if a.fused else xq
     for cfg in a.configs.split(","):
         if cfg == "auto":
-            R, S = K.choose_splits(d, n, EPI_STORE, L.dl_device_sm_count(), M)
+            R, S, T = K.choose_splits(d, n, EPI_STORE, L.dl_device_sm_count(), M)
         else:
-            R, S = [int(x) for x in cfg.split("x")]
-        nct = ((d + 127) // 128) * R * S
+            R, S = [int(x) for x in cfg.split("x")][:2]
+            T = int(cfg.split("x")[2]) if cfg.count("x") == 2 else 1
+        nct = ((((d + 127) // 128) * R + T - 1) // T) * S
         for i in range(3):
-            K.gemv_q40(ws[i % copies], d, n, xq, M, epi, R, S)
+            K.gemv_q40(ws[i % copies], d, n, xq_arg, M, epi, R, S, norm=nm, tiles_per_cta=T)
         torch.cuda.synchronize()
         trace.zero_()
         L.dl_debug_set_gemv_trace(trace.data_ptr())
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        K.gemv_q40(ws[3 % copies], d, n, xq, M, epi, R, S)
+        K.gemv_q40(ws[3 % copies], d, n, xq_arg, M, epi, R, S, norm=nm, tiles_per_cta=T)
         e1.record()
         torch.cuda.synchronize()
         L.dl_debug_set_gemv_trace(None)
         t = trace.cpu().numpy().reshape(-1, 8)[:nct].astype(np.float64)
         t0 = t[:, 0].min()
-        print(f"--- d={d} n={n} M={M} R={R} S={S} ctas={nct}  event time {e0.elapsed_time(e1) * 1e3:.1f} us "
+        print(f"--- d={d} n={n} M={M} R={R} S={S} T={T} ctas={nct}  event time {e0.elapsed_time(e1) * 1e3:.1f} us "
               f"({wbytes / (e0.elapsed_time(e1) * 1e-3) / 1e9:.0f} GB/s)")
-        names = ["start", "act ready", "loop done", "local reduce done", "-", "epilogue done"]
-        for k in (0, 1, 2, 3, 5):
+        names = ["start", "act ready", "loop done", "local reduce done", "ssq exchanged", "epilogue done", "prologue done"]
+        for k in (0, 4, 6, 1, 2, 3, 5):
             col = t[:, k]
             col = col[col > 0] - t0
             if col.size:

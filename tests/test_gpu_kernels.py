@@ -399,3 +399,41 @@ def test_gemv_residual_epilogue_in_place():
     prod = quant.q80_roundtrip(x) @ wdq.T
     ref = res + quant.q80_roundtrip(prod.astype(np.float32))
     np.testing.assert_allclose(r.cpu().numpy(), ref, rtol=0, atol=np.abs(prod).max() / 127 * 1.01)
+
+
+@pytest.mark.parametrize("d,n,M,R,S,T", [
+    (1024, 512, 2, 1, 1, 3), (2048, 256, 1, 1, 1, 4), (640, 1024, 1, 1, 3, 1), (384, 2048, 3, 1, 5, 1),
+    (896, 1536, 8, 1, 7, 1), (2176, 384, 4, 1, 1, 17), (256, 4096, 1, 2, 6, 1),
+])
+def test_gemv_tiles_per_cta_and_odd_clusters(d, n, M, R, S, T):
+    """T row tiles streamed by one CTA (pipeline crosses tile boundaries); cluster sizes that are not
+    powers of two (uneven K ranges)."""
+    k = K()
+    raw, wdq = _rand_q40(d, n, d + n + T)
+    w = k.make_q40t(torch.from_numpy(raw).cuda(), d, n)
+    rng = np.random.default_rng(T + S)
+    x = rng.standard_normal((M, n), dtype=np.float32)
+    xq = k.alloc_xq(n, M, "cuda")
+    k.quant_q80(torch.from_numpy(x).cuda(), M, n, M, xq, None)
+    ref = quant.q80_roundtrip(x).astype(np.float64) @ wdq.astype(np.float64).T
+    y = torch.full((M, d), float("nan"), device="cuda")
+    for _ in range(2):
+        k.gemv_q40(w, d, n, xq, M, k.epi_store([y.data_ptr()], d), R, S, tiles_per_cta=T)
+    torch.cuda.synchronize()
+    got = y.cpu().numpy()
+    assert not np.isnan(got).any()
+    np.testing.assert_allclose(got, ref, rtol=2e-4, atol=2e-5 * np.abs(ref).max())
+
+
+def test_choose_splits_stays_within_one_wave():
+    k = K()
+    from dllama_b200.ops.lib import EPI_QKV_ROPE, EPI_SILU_MUL, EPI_STORE
+    for d, n, kind in [(6144, 4096, EPI_QKV_ROPE), (4096, 4096, EPI_STORE), (28672, 4096, EPI_SILU_MUL),
+                       (4096, 14336, EPI_STORE), (128256, 4096, EPI_STORE), (768, 4096, EPI_QKV_ROPE),
+                       (4096, 512, EPI_STORE), (3584, 4096, EPI_SILU_MUL), (4096, 1792, EPI_STORE), (16032, 4096, EPI_STORE)]:
+        for M in (1, 8):
+            R, S, T = k.choose_splits(d, n, kind, 148, M)
+            units = ((d + 127) // 128) * R
+            grid = ((units + T - 1) // T) * S
+            assert grid <= 148 and (T == 1 or (R == 1 and S == 1)) and S <= n // 128
+            assert k.cuda_lib().dl_gemv_q40_smem_bytes(n, M, S) <= 227 * 1024
