@@ -1,0 +1,46 @@
+"""`dllama-api`: multi-user OpenAI-style HTTP server (reference: src/dllama-api.cpp:367-410)."""
+from __future__ import annotations
+
+import signal
+import sys
+
+from ..serving import api_types as A
+from ..serving.api import ApiServer, ApiState
+from ..serving.batch_engine import BatchEngine
+from .app import USAGE, AppArgs, InferenceContext, run_inference_app
+
+
+def server(ctx: InferenceContext):
+    a = ctx.args
+    batch = BatchEngine(ctx.engine, ctx.tokenizer, control=ctx.control)
+    batch.start()
+    defaults = A.InferenceParams(messages=[], temperature=a.temperature, top_p=a.topp, seed=a.seed)
+    import os
+    state = ApiState(batch, ctx.tokenizer, os.path.basename(a.model_path), defaults, a.chat_template_type)
+    srv = ApiServer(state, "0.0.0.0", a.port)
+    signal.signal(signal.SIGTERM, lambda *_: srv.httpd.shutdown())
+    try:
+        srv.serve_forever()
+    except KeyboardInterrupt:
+        pass
+    finally:
+        ctx.control = None if ctx.control is None else ctx.control
+        batch.stop()
+
+
+def main(argv=None) -> int:
+    argv = list(sys.argv if argv is None else argv)
+    try:
+        args = AppArgs.parse(argv, False)
+        if args.help:
+            print(USAGE)
+            return 0
+        run_inference_app(args, server)
+    except (ValueError, RuntimeError, FileNotFoundError) as e:
+        print(f"🚨 Critical error: {e}")
+        return 1
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

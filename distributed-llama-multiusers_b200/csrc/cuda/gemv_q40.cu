@@ -29,6 +29,7 @@
 
 #define GEMV_NS 12                      // pipeline stages
 #define GEMV_NG 4                       // consumer groups of 128 threads
+#define GEMV_NPROD 4                    // issuing lanes of the producer warp
 #define GEMV_CONSUMERS (GEMV_NG * 128)
 #define GEMV_THREADS (GEMV_CONSUMERS + 32)
 #define GEMV_WARPS (GEMV_THREADS / 32)
@@ -116,15 +117,27 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) gemv_q40_kernel(const __grid_
     const int pre = n_it < GEMV_NS ? n_it : GEMV_NS;
     uint64_t pol = 0;
 
-    auto issue = [&](int it, int s) {
-        const int unit = cl + (it / nk) * n_owners;
-        const int rt = unit / R, rs = unit % R;
-        const uint8_t* t = a.w + ((size_t)rt * a.KT + kt0 + (it % nk)) * Q40T_TILE_BYTES;
+    // producer lanes: lane p of the producer warp owns iterations it == p (mod GEMV_NPROD); a single
+    // issuing thread caps a CTA at ~34 GB/s (measured), four of them lift the cap above the SM's share
+    const int rshift = (R == 1) ? 0 : ((R == 2) ? 1 : 2);
+    auto issue = [&](int u, int i, int s) {
+        const int unit = cl + u * n_owners;
+        const int rt = unit >> rshift, rs = unit & (R - 1);
+        const uint8_t* t = a.w + ((size_t)rt * a.KT + kt0 + i) * Q40T_TILE_BYTES;
         uint8_t* st = stages + s * Q40T_TILE_BYTES;
-        mbar_arrive_expect_tx(&full[s], nib_bytes + sc_bytes);
-        bulk_g2s_hint(st, t + rs * nib_bytes, nib_bytes, &full[s], pol);
-        bulk_g2s_hint(st + Q40T_NIB_BYTES, t + Q40T_SCALE_OFF + rs * sc_bytes, sc_bytes, &full[s], pol);
+        if (R == 1) {
+            // nibbles and scales of a whole tile are contiguous: one 9216-byte copy
+            mbar_arrive_expect_tx(&full[s], Q40T_TILE_BYTES);
+            bulk_g2s_hint(st, t, Q40T_TILE_BYTES, &full[s], pol);
+        } else {
+            mbar_arrive_expect_tx(&full[s], nib_bytes + sc_bytes);
+            bulk_g2s_hint(st, t + rs * nib_bytes, nib_bytes, &full[s], pol);
+            bulk_g2s_hint(st + Q40T_NIB_BYTES, t + Q40T_SCALE_OFF + rs * sc_bytes, sc_bytes, &full[s], pol);
+        }
     };
+    const bool is_prod_lane = (warp == GEMV_CONSUMERS / 32) && (lane < GEMV_NPROD);
+    int p_it = lane, p_u = 0, p_i = lane;          // this producer lane's next iteration (it, unit index, k-tile)
+    auto p_norm = [&]() { while (p_i >= nk && nk > 0) { p_i -= nk; p_u++; } };
 
     if (tid == 0) {
         for (int s = 0; s < GEMV_NS; s++) {
@@ -140,10 +153,14 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) gemv_q40_kernel(const __grid_
     pdl_launch_dependents();
     GEMV_TRACE(0);
 
-    if (is_producer) {
+    if (is_prod_lane) {
         // weights do not depend on the previous kernel: stream the first ring-full before the PDL wait
         pol = l2_policy_evict_first();
-        for (int it = 0; it < pre; it++) issue(it, it);
+        p_norm();
+        for (; p_it < pre; p_it += GEMV_NPROD, p_i += GEMV_NPROD) {
+            p_norm();
+            issue(p_u, p_i, p_it);
+        }
     }
 
     if (a.fused) {
@@ -278,10 +295,13 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) gemv_q40_kernel(const __grid_
                 mbar_arrive_expect_tx(act_full, act_bytes);
                 bulk_g2s(act_s, a.xq + (size_t)kt0 * M * XQ_ROW_BYTES, act_bytes, act_full);
             }
-            for (int it = pre; it < n_it; it++) {
-                const int s = it % GEMV_NS;
-                mbar_wait(&empty[s], ((it / GEMV_NS) & 1) ^ 1);
-                issue(it, s);
+        }
+        if (is_prod_lane) {
+            for (; p_it < n_it; p_it += GEMV_NPROD, p_i += GEMV_NPROD) {
+                p_norm();
+                const int s = p_it % GEMV_NS;
+                mbar_wait(&empty[s], ((p_it / GEMV_NS) & 1) ^ 1);
+                issue(p_u, p_i, s);
             }
         }
     } else {

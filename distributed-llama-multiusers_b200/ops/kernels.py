@@ -235,11 +235,16 @@ def choose_splits(d: int, n: int, epi_kind: int, n_sms: int = 148, M: int = 1):
     kt = n // 128
     if row_tiles >= n_sms:
         return 1, 1, (row_tiles + n_sms - 1) // n_sms
-    S = max(1, min(8, kt, n_sms // row_tiles))
+    # clusters must be co-scheduled inside one GPC (16-20 SMs): power-of-two sizes pack best, and the
+    # grid is kept at <= ~128 CTAs so that placement never spills into a second wave
+    budget = (n_sms * 7) // 8
+    S = 1
+    while S * 2 <= min(8, kt) and row_tiles * S * 2 <= budget:
+        S *= 2
     while S < min(8, kt) and int(cuda_lib().dl_gemv_q40_smem_bytes(n, M, S)) > 200 * 1024:
-        S += 1
+        S *= 2
     R = 1
     max_r = 2 if epi_kind == EPI_SILU_MUL else 4
-    while R < max_r and row_tiles * S * R * 2 <= n_sms:
+    while R < max_r and row_tiles * S * R * 2 <= budget:
         R *= 2
     return R, S, 1
