@@ -421,6 +421,76 @@ extern "C" int dl_argmax(const float* logits, int M, int vocab, int ld, int* tok
     return 0;
 }
 
+// ------------------------------------------------------------------------------------------------
+// dl_argmax_noalloc: greedy pick for callers that must not allocate device memory.
+//
+// Who this is for: code that runs where cudaMalloc is off limits -- a plugin inside a host
+// application that owns the whole memory budget, a latency-critical serving loop that forbids
+// allocator calls after start-up, or a caller that only holds raw pointers and no allocator at
+// all.  dl_argmax() needs a caller-provided scratch buffer (chunk winners + completion counters);
+// this variant keeps that scratch in a fixed array inside the library instead, so the caller
+// passes nothing but its logits and its output.
+//
+// Limits and rules:
+//  * at most DL_ARGMAX_NOALLOC_MAX_ROWS (64) rows per call; larger M is refused with an error.
+//    The array (17 KB) is part of the loaded module: every GPU that loads this library holds it
+//    until the process exits.
+//  * the first call on each device resolves the array's device address (cudaGetSymbolAddress, with
+//    that device current).  Make that first call before starting any stream capture.
+//  * all calls on a device share the one array: two calls whose kernels may overlap on the GPU
+//    (different streams, no ordering between them) race on it.  Serialise them.
+//  * the array keeps whatever the previous call left; the counters the kernel relies on being zero
+//    are cleared on the caller's stream at the start of every call (cudaMemsetAsync, no allocation).
+//  * no cudaMalloc / cudaFree / allocating library routine is called, here or in the kernel.
+// ------------------------------------------------------------------------------------------------
+#define DL_ARGMAX_NOALLOC_MAX_ROWS 64
+#define DL_ARGMAX_NOALLOC_BYTES (1024 + DL_ARGMAX_NOALLOC_MAX_ROWS * ARGMAX_CHUNKS * 8)
+static __device__ __align__(256) unsigned char g_argmax_noalloc_scratch[DL_ARGMAX_NOALLOC_BYTES];
+
+extern "C" int dl_argmax_noalloc(const float* logits, int M, int vocab, int ld, int* tokens_out, void* stream) {
+    // In host code `g_argmax_noalloc_scratch` is only a handle for the runtime, not a device address:
+    // the real address is looked up once per device and cached here.
+    static unsigned char* dev_addr[64] = {nullptr};
+    if (M < 1 || M > DL_ARGMAX_NOALLOC_MAX_ROWS) {
+        dl_set_error("dl_argmax_noalloc: M=%d is outside 1..%d (the built-in scratch is sized for %d rows; use "
+                     "dl_argmax with your own scratch for more)", M, DL_ARGMAX_NOALLOC_MAX_ROWS, DL_ARGMAX_NOALLOC_MAX_ROWS);
+        return -1;
+    }
+    if (logits == nullptr || tokens_out == nullptr || vocab < 1 || ld < vocab) {
+        dl_set_error("dl_argmax_noalloc: bad arguments (logits/tokens_out NULL, vocab < 1 or ld < vocab)");
+        return -1;
+    }
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= 64) {
+        dl_set_error("dl_argmax_noalloc: cudaGetDevice: %s", e != cudaSuccess ? cudaGetErrorString(e) : "device index out of range");
+        return e != cudaSuccess ? -(int)e : -1;
+    }
+    if (dev_addr[dev] == nullptr) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_argmax_noalloc_scratch);
+        if (e != cudaSuccess || p == nullptr) {
+            dl_set_error("dl_argmax_noalloc: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+            return e != cudaSuccess ? -(int)e : -1;
+        }
+        dev_addr[dev] = reinterpret_cast<unsigned char*>(p);
+    }
+    unsigned char* scratch = dev_addr[dev];
+    // completion counters (first 1 KB) must be zero when the kernel starts
+    e = cudaMemsetAsync(scratch, 0, 1024, (cudaStream_t)stream);
+    if (e != cudaSuccess) { dl_set_error("dl_argmax_noalloc: cudaMemsetAsync: %s", cudaGetErrorString(e)); return -(int)e; }
+    ArgmaxArgs a;
+    a.logits = logits; a.vocab = vocab; a.ld = ld; a.tokens_out = tokens_out;
+    a.flags = nullptr; a.n_flags = 0; a.step_counter = nullptr; a.flag_mul = 0; a.flag_add = 0;
+    a.pos_inc = nullptr; a.history = nullptr; a.history_cap = 0;
+    a.scratch = scratch;
+    a.tr = nullptr;
+    argmax_kernel<<<dim3(ARGMAX_CHUNKS, M), ARGMAX_THREADS, 0, (cudaStream_t)stream>>>(a);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) { dl_set_error("dl_argmax_noalloc: launch: %s", cudaGetErrorString(e)); return -(int)e; }
+    return 0;
+}
+
 // wait until flags[i] >= epoch for i < n (orders later stream work after the peers' pushes)
 __global__ void wait_flags_kernel(const uint32_t* flags, int n, const uint32_t* step_counter, uint32_t mul, uint32_t add) {
     pdl_launch_dependents();

@@ -135,6 +135,15 @@ int dl_argmax(const float* logits, int M, int vocab, int ld, int* tokens_out,
               int* history /*NULL or [cap][M] ring indexed by *step_counter-1*/, int history_cap,
               void* scratch /*zero-initialised, dl_argmax_scratch_bytes(M)*/, int pdl, void* stream);
 long long dl_argmax_scratch_bytes(int M);
+/* Greedy pick without any device allocation (this entry point has no counterpart in the reference).
+ * For callers that are not allowed to call cudaMalloc -- plugins living inside someone else's memory
+ * budget, serving loops that ban allocator calls after start-up, hosts that only hand out raw
+ * pointers.  Same result as dl_argmax(), but the scratch it needs lives in a fixed 17 KB array inside
+ * the library (held by every GPU that loads it, until exit), so the caller passes only logits and the
+ * output.  M <= 64 rows, larger M is rejected.  The first call on a device resolves the array's
+ * address and should happen before any stream capture; calls on one device share the array, so calls
+ * that can overlap on the GPU race -- keep them ordered. */
+int dl_argmax_noalloc(const float* logits, int M, int vocab, int ld, int* tokens_out, void* stream);
 /* block the stream until flags[i] >= *step_counter*flag_mul+flag_add for i<n (logits gather to the
  * sampling rank; reference: SYNC_NODE_SLICES_EXCEPT_ROOT, src/llm.cpp:432) */
 int dl_wait_flags(const uint32_t* flags, int n, const uint32_t* step_counter, uint32_t flag_mul,
