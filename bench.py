@@ -35,7 +35,7 @@ def parse_args():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=64)
     ap.add_argument("--warmup", type=int, default=8)
-    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference", "nccl_cublas"])
     ap.add_argument("--model", default="llama3.1-8b")
     ap.add_argument("--layers", type=int, default=0, help="debug only: override layer count (invalid as a bench)")
     ap.add_argument("--prompt-len", type=int, default=128)
@@ -244,6 +244,51 @@ def bench_users(eng, args, barrier, world, dist):
     return {"users": U, "ms_per_step": round(ms, 4), "aggregate_tokens_per_s": round(U * 1000.0 / ms, 1)}
 
 
+def run_nccl_cublas(args):
+    """B2: NCCL all-reduce + Q40 dequant + cuBLAS (models/baseline_nccl.py), same metric and config."""
+    import torch
+    import torch.distributed as dist
+    from dllama_b200.models.baseline_nccl import NcclCublasEngine
+    from dllama_b200.parallel.symm import init_distributed
+    rank, world, _ = init_distributed()
+    path = ensure_model(args, rank)
+    if world > 1:
+        dist.barrier()
+    K_, W = args.steps, args.warmup
+    eng = NcclCublasEngine(path, rank=rank, world=world, max_seq_len=max(512, args.prompt_len + K_ + W + 64))
+    rng = __import__("numpy").random.default_rng(0)
+    prompt = rng.integers(1, eng.h.vocab_size, args.prompt_len).tolist()
+    lg = eng.forward(prompt, 0)
+    tok, pos = int(lg[-1].argmax()), len(prompt)
+    for _ in range(W):
+        tok = int(eng.forward([tok], pos)[0].argmax())
+        pos += 1
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(K_):
+        tok = int(eng.forward([tok], pos)[0].argmax())
+        pos += 1
+    ev1.record()
+    torch.cuda.synchronize()
+    t = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t[0]) / K_
+    if rank == 0:
+        print(json.dumps({"metric": METRIC, "value": round(1000.0 / ms, 2), "unit": "tokens/s", "n_gpus": world,
+                          "steps": K_, "warmup": W, "ms_per_step": round(ms, 4), "higher_is_better": True,
+                          "scaling": "strong", "vs_baseline": None, "dtype": "bf16 cuBLAS on dequantised Q40, NCCL all-reduce",
+                          "data": "synthetic", "impl": "nccl_cublas",
+                          "config": {"model": args.model, "global_batch": 1, "parallelism": f"tp{world}"}}), flush=True)
+    eng.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
 def run_reference(args):
     from baseline.reference_arm import run_reference_arm
     print(json.dumps(run_reference_arm(args, METRIC)), flush=True)
@@ -258,4 +303,7 @@ if __name__ == "__main__":
             if int(os.environ.get("RANK", "0")) == 0:
                 print(json.dumps({"impl": "reference", "unavailable": f"{type(e).__name__}: {e}"[:300]}), flush=True)
         sys.exit(0)
-    run_b200(a)
+    if a.impl == "nccl_cublas":
+        run_nccl_cublas(a)
+    else:
+        run_b200(a)

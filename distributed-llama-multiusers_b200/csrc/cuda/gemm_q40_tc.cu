@@ -148,7 +148,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_q40_tc_kernel(const __grid
 #pragma unroll
             for (int half_i = 0; half_i < 2; half_i++) {
                 const int it = t + half_i * 256;
-                const int r = it >> 2, kb = it & 3;
+                // a quarter-warp (8 lanes = one STS.128 / LDS.128 phase) covers 8 rows of ONE k-block: its
+                // stores fill one contiguous 128-byte core matrix and its rotated raw loads hit 8 distinct
+                // 16-byte slots -- both conflict-free (ncu: the (row%8,kb) lane order cost 4x the wavefronts)
+                const int r = ((it >> 5) << 3) | (it & 7), kb = (it >> 3) & 3;
                 const uint4 nb = *reinterpret_cast<const uint4*>(raw + r * 64 + (((kb + (r >> 1)) & 3) << 4));
                 const __half dh = *reinterpret_cast<const __half*>(raw + Q40T_SCALE_OFF + r * 8 + kb * 2);
                 const __half2 d2 = __half2half2(dh);

@@ -102,3 +102,18 @@ def test_greedy_device_loop_matches_host_loop(tiny_model_path):
     dev = e.read_history(8, 1, first)[:, 0].tolist()
     assert dev == host
     e.close()
+
+
+def test_nccl_cublas_baseline_engine_matches_oracle(tiny_model_path):
+    """The B2 baseline (dequant + cuBLAS + PyTorch ops) computes the same function."""
+    from dllama_b200.models.baseline_nccl import NcclCublasEngine
+    o = _oracle(tiny_model_path)
+    b = NcclCublasEngine(tiny_model_path, max_seq_len=512)
+    prompt = [1, 17, 300, 42, 7]
+    ref = o.forward(prompt, 0).numpy()
+    got = b.forward(prompt, 0).float().cpu().numpy()
+    assert _rel_err(got[-1], ref[-1]) < 5e-2          # bf16 operands
+    ref1 = o.forward([11], 5).numpy()
+    got1 = b.forward([11], 5).float().cpu().numpy()
+    assert _rel_err(got1[0], ref1[0]) < 5e-2
+    b.close()
