@@ -52,20 +52,44 @@ DL_DEVINL float act_gelu(float x) {
 // ---- the epilogue --------------------------------------------------------------------------------
 // epilogue_rows: called by (at least) the first `rows` threads (tid = local output row; rows is a
 // multiple of 32 so every warp is either fully in or fully out).  out_s[m*out_ld + r] holds
-// activation rows m0..m0+M-1; grow0 = global row of local row 0, d_real = real (unpadded) rows.
+// activation rows m0..m0+M-1 (M <= 32); grow0 = global row of local row 0, d_real = real (unpadded)
+// rows.  A caller with several thread groups per tile passes (m_first, m_step) so group k handles
+// rows k, k+step, ...; everything a row needs from global memory (position, KV page) is fetched
+// once per warp by lane m and broadcast with shuffles, so the per-row loop has no dependent loads.
 DL_DEVINL void epilogue_rows(const DlEpilogue& e, const float* out_s, int out_ld, int rows, int grow0, int d_real,
-                             int M, int m0, int tid) {
+                             int M, int m0, int tid, int m_first = 0, int m_step = 1) {
     const int lane = tid & 31;
     if (e.kind == DL_EPI_STORE) {
         if (tid < rows) {
             const int grow = grow0 + tid;
-            for (int m = 0; m < M; m++) {
-                float v = out_s[m * out_ld + tid];
-                if (e.q80_roundtrip) v = q80_roundtrip_warp(v);
-                if (grow < d_real) {
-                    if (e.residual != nullptr) v += e.residual[(size_t)(m0 + m) * e.residual_ld + grow];
-                    const size_t off = (size_t)e.dst_off + (size_t)(m0 + m) * e.ld + grow;
-                    for (int p = 0; p < e.n_dst; p++) e.dst[p][off] = v;
+            const bool live = grow < d_real;
+            const bool rt = e.q80_roundtrip != 0;
+            const int nd = e.n_dst;
+            const size_t ld = (size_t)e.ld;
+            const size_t res_ld = (size_t)e.residual_ld;
+            const float* res = (e.residual != nullptr && live) ? e.residual + (size_t)m0 * res_ld + grow : nullptr;
+            const size_t off0 = (size_t)e.dst_off + (size_t)m0 * ld + grow;
+            if (nd == 1) {
+                float* d0 = e.dst[0] + off0;
+#pragma unroll 4
+                for (int m = m_first; m < M; m += m_step) {
+                    float v = out_s[m * out_ld + tid];
+                    if (rt) v = q80_roundtrip_warp(v);
+                    if (live) {
+                        if (res != nullptr) v += res[m * res_ld];
+                        d0[m * ld] = v;
+                    }
+                }
+            } else {
+                for (int m = m_first; m < M; m += m_step) {
+                    float v = out_s[m * out_ld + tid];
+                    if (rt) v = q80_roundtrip_warp(v);
+                    if (live) {
+                        if (res != nullptr) v += res[m * res_ld];
+                        const size_t off = off0 + m * ld;
+#pragma unroll 1
+                        for (int p = 0; p < nd; p++) e.dst[p][off] = v;
+                    }
                 }
             }
         }
@@ -76,10 +100,24 @@ DL_DEVINL void epilogue_rows(const DlEpilogue& e, const float* out_s, int out_ld
             const int region = (grow < e.q_dim) ? 0 : ((grow < e.q_dim + e.kv_dim) ? 1 : 2);   // warp-uniform
             const int rrow = (region == 0) ? grow : ((region == 1) ? grow - e.q_dim : grow - e.q_dim - e.kv_dim);
             const int hd = rrow % hs;
-            const float freq = (region < 2 && grow < d_real) ? e.rope_freqs[hd >> 1] : 0.0f;
-            for (int m = 0; m < M; m++) {
+            const int kvh = rrow / hs;
+            const bool live = grow < d_real;
+            const float freq = (region < 2 && live) ? e.rope_freqs[hd >> 1] : 0.0f;
+            // lane m fetches row m's position and (for k/v rows) its KV page; shuffled to the warp below
+            int my_pos = 0, my_page = 0;
+            if (lane < M) {
+                my_pos = e.pos[m0 + lane];
+                if (region != 0) my_page = e.block_table[(size_t)e.slot[m0 + lane] * e.max_pages + my_pos / e.page_size];
+            }
+            const int page_size = e.page_size, n_kv = e.n_kv_heads, q_dim = e.q_dim;
+            float* q_out = e.q_out + (size_t)m0 * q_dim + rrow;
+            void* base = (region == 1) ? e.k_cache : e.v_cache;
+            const bool kv_f32 = e.kv_f32 != 0;
+#pragma unroll 2
+            for (int m = m_first; m < M; m += m_step) {
                 float v = out_s[m * out_ld + tid];
-                const int p = e.pos[m0 + m];
+                const int p = __shfl_sync(0xffffffffu, my_pos, m);
+                const int page = __shfl_sync(0xffffffffu, my_page, m);
                 if (region < 2) {
                     float other = __shfl_xor_sync(0xffffffffu, v, 1);
                     float sn, cs;
@@ -87,17 +125,13 @@ DL_DEVINL void epilogue_rows(const DlEpilogue& e, const float* out_s, int out_ld
                     // even lane holds x0, odd lane holds x1
                     v = (lane & 1) ? (other * sn + v * cs) : (v * cs - other * sn);
                 }
-                if (grow >= d_real) {
+                if (!live) {
                     // padded row: nothing to store
                 } else if (region == 0) {
-                    e.q_out[(size_t)(m0 + m) * e.q_dim + rrow] = v;
+                    q_out[(size_t)m * q_dim] = v;
                 } else {
-                    const int page = e.block_table[(size_t)e.slot[m0 + m] * e.max_pages + p / e.page_size];
-                    const int kvh = rrow / hs;
-                    const size_t off =
-                        (((size_t)page * e.n_kv_heads + kvh) * e.page_size + (p % e.page_size)) * hs + hd;
-                    void* base = (region == 1) ? e.k_cache : e.v_cache;
-                    if (e.kv_f32) reinterpret_cast<float*>(base)[off] = v;
+                    const size_t off = (((size_t)page * n_kv + kvh) * page_size + (p % page_size)) * hs + hd;
+                    if (kv_f32) reinterpret_cast<float*>(base)[off] = v;
                     else reinterpret_cast<__half*>(base)[off] = __float2half_rn(v);
                 }
             }
@@ -108,11 +142,15 @@ DL_DEVINL void epilogue_rows(const DlEpilogue& e, const float* out_s, int out_ld
         const int hrow0 = grow0 >> 1;
         // d_real % 64 == 0 is required, so validity is uniform per 32-value block (= per warp)
         if (tid < nh && 2 * (hrow0 + (tid & ~31)) < d_real) {
-            for (int m = 0; m < M; m++) {
-                float g = out_s[m * out_ld + 2 * tid];
-                float u = out_s[m * out_ld + 2 * tid + 1];
-                float h = (e.act_gelu ? act_gelu(g) : act_silu(g)) * u;
-                q80_block_store(h, lane, m0 + m, (hrow0 + tid) >> 5, e.out_mcap, e.xq_out, e.xh_out);
+            const bool gelu = e.act_gelu != 0;
+            const int mcap = e.out_mcap;
+            uint8_t* xq = e.xq_out;
+            uint8_t* xh = e.xh_out;
+#pragma unroll 2
+            for (int m = m_first; m < M; m += m_step) {
+                const float2 gu = *reinterpret_cast<const float2*>(out_s + m * out_ld + 2 * tid);
+                float h = (gelu ? act_gelu(gu.x) : act_silu(gu.x)) * gu.y;
+                q80_block_store(h, lane, m0 + m, (hrow0 + tid) >> 5, mcap, xq, xh);
             }
         }
     }
@@ -122,19 +160,23 @@ DL_DEVINL void epilogue_rows(const DlEpilogue& e, const float* out_s, int out_ld
 // DL_EPI_STORE with flags: every CTA fences its (peer) stores, the last one releases the flags.
 DL_DEVINL void epilogue_complete(const DlEpilogue& e, int tid, int n_epi_ctas, int* smem_flag) {
     if (e.kind != DL_EPI_STORE || e.flag[0] == nullptr) return;
-    __threadfence_system();
+    // Ordering chain (PTX memory model, cumulativity): every thread's peer stores -> bar.sync ->
+    // thread 0: fence.sys + counter atomic -> (observed by the last CTA's thread 0) atomic + fence.sys
+    // -> bar.sync -> st.release.sys of the flags.  One thread fences per CTA instead of all of them.
     __syncthreads();
     if (tid == 0) {
+        __threadfence_system();
         unsigned prev = atomicAdd(e.cta_counter, 1u);
-        *smem_flag = (prev == (unsigned)n_epi_ctas - 1u) ? 1 : 0;
+        const int last = (prev == (unsigned)n_epi_ctas - 1u) ? 1 : 0;
+        if (last) {
+            __threadfence_system();
+            *e.cta_counter = 0u;
+        }
+        *smem_flag = last;
     }
     __syncthreads();
-    if (*smem_flag) {
-        __threadfence_system();
-        if (tid < e.n_dst) {
-            uint32_t epoch = ld_volatile_u32(e.step_counter) * e.flag_mul + e.flag_add;
-            st_release_sys(e.flag[tid], epoch);
-        }
-        if (tid == 0) *e.cta_counter = 0u;
+    if (*smem_flag && tid < e.n_dst) {
+        uint32_t epoch = ld_volatile_u32(e.step_counter) * e.flag_mul + e.flag_add;
+        st_release_sys(e.flag[tid], epoch);
     }
 }

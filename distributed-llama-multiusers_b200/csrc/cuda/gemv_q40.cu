@@ -166,6 +166,18 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) gemv_q40_kernel(const __grid_
     if (a.fused) {
         // ---------------- fused prologue: flags wait + merge-add + RMSNorm + Q80 -> act_s ----------------
         const DlNormProlog& nm = a.norm;
+        const int dim = a.n;
+        const int e0 = kt0 * 128, e1 = kt1 * 128;                 // this CTA's K range (cluster ranks tile the row)
+        const int nkb = nk * 4;
+        const int items = M * nkb;
+        const bool one_pass = items <= GEMV_THREADS;              // a whole 32-block per thread, kept in registers
+        // the norm weights are model weights: fetch them before waiting on the previous kernel
+        float4 wreg[8];
+        if (one_pass && tid < items) {
+            const float4* wn = reinterpret_cast<const float4*>(nm.norm_w + e0 + (tid % nkb) * 32);
+#pragma unroll
+            for (int j = 0; j < 8; j++) wreg[j] = wn[j];
+        }
         pdl_wait();
         if (nm.flags != nullptr) {
             if (tid < nm.n_src) {
@@ -174,12 +186,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) gemv_q40_kernel(const __grid_
             }
             __syncthreads();
         }
-        const int dim = a.n;
-        const int e0 = kt0 * 128, e1 = kt1 * 128;                 // this CTA's K range (cluster ranks tile the row)
         const bool writer = (nm.x_out != nullptr) && (cl == 0);
-        const int nkb = nk * 4;
-        const int items = M * nkb;
-        const bool one_pass = items <= GEMV_THREADS;              // a whole 32-block per thread, kept in registers
         float ss[MT];
 #pragma unroll
         for (int m = 0; m < MT; m++) ss[m] = 0.0f;
@@ -233,16 +240,19 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) gemv_q40_kernel(const __grid_
             if (lane == 0) ssq_w[warp * MT + m] = t;
         }
         __syncthreads();
-        if (tid < MT) {
-            float t = 0.0f;
-            for (int w = 0; w < GEMV_WARPS; w++) t += ssq_w[w * MT + tid];
+        if (warp < MT) {                                  // warp m reduces row m's per-warp partials
+            float t = (lane < GEMV_WARPS) ? ssq_w[lane * MT + warp] : 0.0f;
+            t = warp_sum(t);
+            const int tidm = warp;
+            if (lane == 0) {
             // publish this CTA's share into every cluster rank's table (DSMEM stores): after the
             // barrier nobody reads remote shared memory, so ranks may exit independently later on
             if (S > 1) {
                 for (int c = 0; c < S; c++)
-                    st_shared_cluster_f32(mapa_shared(smem_u32(ssq_all + crank * MT + tid), c), t);
+                    st_shared_cluster_f32(mapa_shared(smem_u32(ssq_all + crank * MT + tidm), c), t);
             } else {
-                ssq_all[tid] = t;
+                ssq_all[tidm] = t;
+            }
             }
         }
         if (S > 1) cg::this_cluster().sync(); else __syncthreads();
@@ -276,7 +286,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) gemv_q40_kernel(const __grid_
             const float4* wn = reinterpret_cast<const float4*>(nm.norm_w + e0 + b * 32);
 #pragma unroll
             for (int j = 0; j < 8; j++) {
-                const float4 w4 = wn[j];
+                const float4 w4 = one_pass ? wreg[j] : wn[j];
                 v[j].x = w4.x * (im * v[j].x); v[j].y = w4.y * (im * v[j].y);
                 v[j].z = w4.z * (im * v[j].z); v[j].w = w4.w * (im * v[j].w);
             }

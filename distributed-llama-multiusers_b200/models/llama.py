@@ -270,11 +270,7 @@ class LlamaEngine:
                        tiles_per_cta=T)
         else:
             assert norm is None
-            row_tiles = (d + 127) // 128
-            S = 1
-            if M <= 32:
-                while row_tiles * S < self.n_sms and S < 8 and S * 2 <= n // 128:
-                    S *= 2
+            S = K.choose_tc_split(d, n, M, self.n_sms)
             K.gemm_q40_tc(w, d, n, xh, self.ncap, M, epi, S, pdl=self.use_pdl)
 
     def _launch_forward(self, M: int, row0: int, greedy: bool, device_loop: bool):

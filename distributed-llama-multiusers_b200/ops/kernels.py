@@ -223,6 +223,18 @@ def wait_flags(flags: int, n: int, step_counter: int, flag_mul: int, flag_add: i
     lib.count_launch()
 
 
+def choose_tc_split(d: int, n: int, M: int, n_sms: int) -> int:
+    """Cluster split-K factor of the tcgen05 GEMM: only for narrow activation tiles (M <= 32, one
+    epilogue chunk), a power of two, and never more CTAs than SMs (one CTA per SM: a second wave of
+    half-empty CTAs costs more than the extra parallelism buys)."""
+    row_tiles = (d + 127) // 128
+    S = 1
+    if M <= 32:
+        while row_tiles * S * 2 <= n_sms and S < 8 and S * 2 <= n // 128:
+            S *= 2
+    return S
+
+
 def choose_splits(d: int, n: int, epi_kind: int, n_sms: int = 148, M: int = 1):
     """Work split of the GEMV -> (row_split R, k_split S, tiles_per_cta T); grid = ceil(units/T)*S.
 

@@ -77,10 +77,7 @@ def main():
             xh = K.alloc_xh(n, ncap, "cuda")
             x = torch.randn(M, n, device="cuda")
             K.quant_q80(x, M, n, ncap, None, xh)
-            S = 1
-            if M <= 32:
-                while ((d + 127) // 128) * S < n_sms and S < 8 and S * 2 <= n // 128:
-                    S *= 2
+            S = K.choose_tc_split(d, n, M, n_sms)
             it = [0]
 
             def run_tc():
