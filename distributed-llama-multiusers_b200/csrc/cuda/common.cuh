@@ -112,8 +112,29 @@ DL_DEVINL bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
         : "memory");
     return ok != 0;
 }
+// non-blocking probe (test_wait never suspends the thread): lets several lanes of ONE warp poll different
+// barriers without the first unready one stalling the rest
+DL_DEVINL bool mbar_test_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
 DL_DEVINL void mbar_wait(uint64_t* bar, uint32_t parity) {
     while (!mbar_try_wait(bar, parity)) {
+    }
+}
+
+// wait with a sleep between probes: for roles that share an SM sub-partition with busy math warps, so
+// their polling does not eat the issue slots (costs up to `ns` of wake-up latency)
+DL_DEVINL void mbar_wait_sleep(uint64_t* bar, uint32_t parity, uint32_t ns) {
+    while (!mbar_try_wait(bar, parity)) {
+        if (ns) __nanosleep(ns);
     }
 }
 

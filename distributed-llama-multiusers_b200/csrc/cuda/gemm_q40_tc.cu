@@ -14,8 +14,8 @@
 // tiles in smem: 32 KB written + 32 KB read per 9 KB of weights saturated the 128 B/clk crossbar
 // (per-tile timeline in profiles/: 1450 clk per k-tile, all of it in the MMA queue).
 //
-// Warp roles (704 threads):
-//   warp 0, 21   producers: bulk async copies (UBLKCP) of raw 9 KB Q40T tiles (warp 0) and XH slabs (warp 21)
+// Warp roles (672 threads):
+//   warp 0       producer: bulk async copies (UBLKCP) of raw 9 KB Q40T tiles (lanes 0-3) and XH slabs (lanes 4-7)
 //   warps 1,18-20 MMA issuers (one elected lane each; tcgen05.mma / tcgen05.commit), k-tiles round-robin,
 //                one accumulator each; warp 1 also allocates TMEM
 //   warps 2-17   dequantisers, 4 groups x 4 warps: group = k-tile % 4 = A stage, warp % 4 = TMEM lane
@@ -30,9 +30,7 @@
 #include "epilogue.cuh"
 
 #define TC_DEQ_WARPS 16
-#define TC_THREADS (64 + TC_DEQ_WARPS * 32 + 128)     // weight producer, MMA warp 0, dequantisers, MMA warps 1-3, activation producer
-#define TC_BPROD_WARP (2 + TC_DEQ_WARPS + 3)
-#define TC_NSA 8                  // raw weight-tile ring stages
+#define TC_THREADS (64 + TC_DEQ_WARPS * 32 + 96)      // producer, MMA warp 0, dequantisers, MMA warps 1-3
 #define TC_EPI_CHUNK 32           // activation rows per epilogue pass
 #define TC_TMEM_COLS 512
 #define TC_A_STAGE_COLS 64        // 128 K x fp16 = 64 32-bit columns per lane
@@ -65,9 +63,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_q40_tc_kernel(const __grid
     uint8_t* ringA = ringB + a.NSB * b_bytes;                       // [NSA][9216]
     float* out_s = reinterpret_cast<float*>(ringA + a.NSA * Q40T_TILE_BYTES);   // [32][128]
     uint64_t* bars = reinterpret_cast<uint64_t*>(out_s + TC_EPI_CHUNK * 128);
-    uint64_t* fullA = bars;
-    uint64_t* emptyA = fullA + 8;
-    uint64_t* fullB = emptyA + 8;
+    uint64_t* fullA = bars;                     // [16]
+    uint64_t* emptyA = fullA + 16;              // [16]
+    uint64_t* fullB = emptyA + 16;              // [8] each from here
     uint64_t* emptyB = fullB + 8;
     uint64_t* fullH = emptyB + 8;
     uint64_t* emptyH = fullH + 8;
@@ -86,9 +84,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_q40_tc_kernel(const __grid
     const int nacc = (a.nacc <= nk) ? a.nacc : (nk >= 2 ? 2 : 1);      // accumulators in use = MMA-issuing warps (power of two)
 
     if (tid == 0) {
-        for (int s = 0; s < 8; s++) {
+        for (int s = 0; s < 16; s++) {
             mbar_init(&fullA[s], 1);
             mbar_init(&emptyA[s], 4);
+        }
+        for (int s = 0; s < 8; s++) {
             mbar_init(&fullB[s], 1);
             mbar_init(&emptyB[s], 1);
             mbar_init(&fullH[s], 4);
@@ -106,36 +106,55 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_q40_tc_kernel(const __grid
     pdl_launch_dependents();
 
     if (warp == 0) {
-        // ------------------------------------ weight producer ------------------------------------
-        // lanes 0..LA-1 stream the raw weight tiles: one issuing thread caps a CTA at ~34 GB/s (measured on
-        // the GEMV).  A stage has exactly one owner lane (LA | NSA): a stage shared by two lanes could be
-        // lapped by two phases, which a parity wait cannot see.  The activation slabs are streamed by a
-        // different WARP: two spin-waiting roles in one warp starve each other (divergent paths).
+        // ------------------------------------ producer ------------------------------------
+        // lanes 0..LA-1 stream the raw weight tiles, lanes 4..4+LB-1 the activation slabs: one issuing thread
+        // caps a CTA at ~34 GB/s (measured on the GEMV).  A stage has exactly one owner lane (LA | NSA,
+        // LB | NSB): a stage shared by two lanes could be lapped by two phases, which a parity wait cannot see.
+        // Every lane polls ITS next stage with a non-blocking test_wait inside one converged loop, so a lane
+        // whose stage is still busy never holds back a lane whose stage is free (blocking waits serialise the
+        // divergent lanes of a warp and let one role starve the other).
+        const bool role_a = lane < a.LA, role_b = lane >= 4 && lane < 4 + a.LB;
         const uint8_t* wt = a.w + ((size_t)rt * a.KT + kt0) * Q40T_TILE_BYTES;
-        if (lane < a.LA) {
-            const uint64_t pol = l2_policy_evict_first();
-            for (int i = lane; i < nk; i += a.LA) {      // weights do not depend on the previous kernel: no PDL wait
-                const int sa = i % a.NSA;
-                if (i >= a.NSA) mbar_wait(&emptyA[sa], ((i / a.NSA) & 1) ^ 1);
+        const uint8_t* xb = a.xh + (size_t)kt0 * (a.ncap >> 3) * XH_ROWGROUP_BYTES + (size_t)(m0 >> 3) * XH_ROWGROUP_BYTES;
+        const size_t x_kt_stride = (size_t)(a.ncap >> 3) * XH_ROWGROUP_BYTES;
+        const uint64_t pol = l2_policy_evict_first();
+        int i = role_a ? lane : (role_b ? lane - 4 : nk);
+        const int step = role_a ? a.LA : a.LB;
+        if (role_a) {
+            // weights do not depend on the previous kernel: fill the whole ring before the PDL wait
+            for (; i < nk && i < a.NSA; i += step) {
                 if (!(a.dbg_mode & 4)) TC_DBG(0, i);
-                mbar_arrive_expect_tx(&fullA[sa], Q40T_TILE_BYTES);
-                bulk_g2s_hint(ringA + sa * Q40T_TILE_BYTES, wt + (size_t)i * Q40T_TILE_BYTES, Q40T_TILE_BYTES, &fullA[sa], pol);
+                mbar_arrive_expect_tx(&fullA[i], Q40T_TILE_BYTES);
+                bulk_g2s_hint(ringA + i * Q40T_TILE_BYTES, wt + (size_t)i * Q40T_TILE_BYTES, Q40T_TILE_BYTES, &fullA[i], pol);
             }
         }
-    } else if (warp == TC_BPROD_WARP) {
-        // ------------------------------------ activation producer ------------------------------------
-        if (lane < a.LB) {
-            const uint8_t* xb = a.xh + (size_t)kt0 * (a.ncap >> 3) * XH_ROWGROUP_BYTES + (size_t)(m0 >> 3) * XH_ROWGROUP_BYTES;
-            const size_t x_kt_stride = (size_t)(a.ncap >> 3) * XH_ROWGROUP_BYTES;
-            pdl_wait();
-            for (int i = lane; i < nk; i += a.LB) {
-                const int sb = i % a.NSB;
-                if (i >= a.NSB) mbar_wait(&emptyB[sb], ((i / a.NSB) & 1) ^ 1);
-                mbar_arrive_expect_tx(&fullB[sb], b_bytes);
-                bulk_g2s(ringB + sb * b_bytes, xb + (size_t)i * x_kt_stride, b_bytes, &fullB[sb]);
+        __syncwarp();
+        pdl_wait();
+        while (__any_sync(0xffffffffu, i < nk)) {
+            bool issued = false;
+            if (i < nk) {
+                if (role_a) {
+                    const int sa = i % a.NSA;
+                    if (mbar_test_wait(&emptyA[sa], ((i / a.NSA) & 1) ^ 1)) {      // i >= NSA here
+                        if (!(a.dbg_mode & 4)) TC_DBG(0, i);
+                        mbar_arrive_expect_tx(&fullA[sa], Q40T_TILE_BYTES);
+                        bulk_g2s_hint(ringA + sa * Q40T_TILE_BYTES, wt + (size_t)i * Q40T_TILE_BYTES, Q40T_TILE_BYTES, &fullA[sa], pol);
+                        i += step;
+                        issued = true;
+                    }
+                } else {
+                    const int sb = i % a.NSB;
+                    if (i < a.NSB || mbar_test_wait(&emptyB[sb], ((i / a.NSB) & 1) ^ 1)) {
+                        mbar_arrive_expect_tx(&fullB[sb], b_bytes);
+                        bulk_g2s(ringB + sb * b_bytes, xb + (size_t)i * x_kt_stride, b_bytes, &fullB[sb]);
+                        i += step;
+                        issued = true;
+                    }
+                }
             }
+            if (!__any_sync(0xffffffffu, issued)) __nanosleep(40);      // leave the issue slots to the dequantisers
         }
-    } else if (warp == 1 || (warp >= 2 + TC_DEQ_WARPS && warp < TC_BPROD_WARP)) {
+    } else if (warp == 1 || warp >= 2 + TC_DEQ_WARPS) {
         // ------------------------------------ MMA issuers ------------------------------------
         // One k-tile costs its issuing thread ~900 clk of mostly fixed latency (two barrier waits, fence,
         // 8 x ~45 clk UTCHMMA issue, two commits; per-tile timeline in profiles/), far more than the MMAs
@@ -150,8 +169,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_q40_tc_kernel(const __grid
         const uint32_t desc_lo0 = ((smem_u32(ringB) & 0x3FFFFu) >> 4) | ((128u >> 4) << 16);
         const uint32_t acc = tmem_base + (uint32_t)(mw * NT);
         const bool det = (a.dbg_mode & 4) != 0;      // detail stamps of warp 1 only (slots 0..7)
-        const bool stamp = (lane == 0 && mw == 0);
+        const bool stamp = (lane == 0 && mw == 0 && !(a.dbg_mode & 8));
         const int nsb_mask = a.NSB - 1, nsb_log = a.nsb_log;
+        // narrow tiles are dequant-bound: the issuers sleep between probes and leave their sub-partition's issue
+        // slots to the math warps; wide tiles are MMA-bound: the issuers are the critical path and spin
+        const uint32_t mma_sleep = (NT <= 32) ? 64u : 0u;
         const int nstg = a.nstg;
         const uint32_t a_col0 = TC_TMEM_COLS - nstg * TC_A_STAGE_COLS;
         if (mw < nacc) {
@@ -159,9 +181,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_q40_tc_kernel(const __grid
             for (int i = mw; i < nk; i += nacc) {
                 const int sb = i & nsb_mask, pb = (i >> nsb_log) & 1;
                 if (det && stamp) TC_DBG(0, i);
-                mbar_wait(&fullH[sh], ph);
+                mbar_wait_sleep(&fullH[sh], ph, mma_sleep);
                 if (stamp) TC_DBG(det ? 1 : 5, i);
-                mbar_wait(&fullB[sb], pb);
+                mbar_wait_sleep(&fullB[sb], pb, mma_sleep);
                 if (stamp) TC_DBG(det ? 2 : 6, i);
                 tc_fence_after();
                 if (det && stamp) TC_DBG(3, i);
@@ -204,18 +226,26 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_q40_tc_kernel(const __grid
         const __half2 c1032 = __float2half2_rn(1032.0f);
         const __half2 c1152 = __float2half2_rn(1152.0f);
         const __half2 sixteenth = __float2half2_rn(0.0625f);
-        const bool stamp = (tid == 64 && !(a.dbg_mode & 4));
+        const bool stamp = (tid == 64 && !(a.dbg_mode & 12));
+        const bool qstamp = (lane == 0 && (a.dbg_mode & 8));      // mode 8: slots 1..4 = arrival time of lane quarter 0..3
+        const int nsa = a.NSA;
         int sh = g, ph = 0;      // A stage of k-tile i = i % nstg (g < 4 <= nstg), phase parity = (i / nstg) & 1
+        int sa = g, pa = 0;      // raw ring stage i % NSA and its phase parity
         for (int i = g; i < nk; i += TC_GROUPS) {
-            const int sa = i & (TC_NSA - 1), pa = (i / TC_NSA) & 1;
-            mbar_wait(&fullA[sa], pa);
+            mbar_wait_sleep(&fullA[sa], pa, 32);
             if (stamp) TC_DBG(1, i);
             const uint8_t* raw = ringA + sa * Q40T_TILE_BYTES;
             uint4 nb[4];
 #pragma unroll
             for (int kb = 0; kb < 4; kb++) nb[kb] = *reinterpret_cast<const uint4*>(raw + row_off + (((kb + rot) & 3) << 4));
             const uint2 sc = *reinterpret_cast<const uint2*>(raw + sc_off);      // 4 fp16 scales of this row
-            if (i >= nstg) mbar_wait(&emptyH[sh], ph ^ 1);      // the MMAs that read this A stage have retired
+            // the tile now lives in registers: hand the raw stage back BEFORE the unpack (the ring has to cover
+            // DRAM latency + queueing; holding a stage through the ~1300 clk unpack halved its effective depth).
+            // The loads above were issued by this warp before the arrive and shared-memory operations of a warp
+            // complete in order; the refill is >500 ns away (barrier -> producer poll -> HBM fetch).
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&emptyA[sa]);
+            if (i >= nstg) mbar_wait_sleep(&emptyH[sh], ph ^ 1, 32);      // the MMAs that read this A stage have retired
             if (stamp) TC_DBG(2, i);
             tc_fence_after();
 #pragma unroll
@@ -251,13 +281,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_q40_tc_kernel(const __grid
             if (stamp) TC_DBG(3, i);
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) {
-                mbar_arrive(&fullH[sh]);
-                mbar_arrive(&emptyA[sa]);
-            }
+            if (lane == 0) mbar_arrive(&fullH[sh]);
             if (stamp) TC_DBG(4, i);
+            if (qstamp) TC_DBG(1 + q, i);
             sh += TC_GROUPS;
             if (sh >= nstg) { sh -= nstg; ph ^= 1; }
+            sa += TC_GROUPS;
+            if (sa >= nsa) { sa -= nsa; pa ^= 1; }
         }
     }
 
@@ -297,7 +327,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_q40_tc_kernel(const __grid
             }
         }
         if (S > 1) {
-            // split-K: only used with a single chunk (NT <= 32); all threads of the cluster sync
+            // split-K: every rank publishes its partial chunk, the leader sums them over DSMEM and runs the
+            // epilogue; all threads of the cluster take part in both syncs
             cg::cluster_group cluster = cg::this_cluster();
             tc_fence_before();
             cluster.sync();
@@ -312,6 +343,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_q40_tc_kernel(const __grid
             if (crank == 0 && is_epi) {
                 pdl_wait();
                 epilogue_rows(a.epi, out_s, 128, 128, rt * 128, a.d_real, mc, m0 + ch * TC_EPI_CHUNK, etid, eg, TC_GROUPS);
+                if (ch + 1 < n_chunks) asm volatile("bar.sync 1, 512;");      // out_s is rewritten by the next chunk
             }
         } else if (is_epi) {
             if (tid == 64 && ch == 0) TC_DBG(4, 63);
@@ -355,14 +387,15 @@ extern "C" int dl_gemm_q40_tc(const uint8_t* w_q40t, int d, int n, const uint8_t
     a.ncap = ncap; a.M = M;
     a.NT = (M <= 16) ? 16 : (M <= 32) ? 32 : (M <= 64) ? 64 : (M <= 128 || ncap % 256 != 0) ? 128 : 256;
     if (ncap < (M + a.NT - 1) / a.NT * a.NT) { dl_set_error("dl_gemm_q40_tc: ncap=%d too small for M=%d (tile %d)", ncap, M, a.NT); return -1; }
-    if (a.NT > 32) k_split = 1;
     if (k_split != 1 && k_split != 2 && k_split != 4 && k_split != 8) { dl_set_error("dl_gemm_q40_tc: k_split must be 1,2,4,8"); return -1; }
     if (k_split > a.KT) k_split = 1;
     a.S = k_split;
     // stage counts by tile width: raw 9 KB, B NT*256 B, out 16 KB  (<= ~216 KB)
-    if (a.NT <= 64) { a.NSA = 8; a.NSB = 8; }
+    if (a.NT <= 64) { a.NSA = 12; a.NSB = 4; }
     else if (a.NT == 128) { a.NSA = 8; a.NSB = 4; }
     else { a.NSA = 8; a.NSB = 2; }
+    if (const char* e = getenv("DL_TC_NSA")) a.NSA = atoi(e);      // tuning override (debug); 4 <= NSA <= 16
+    if (a.NSA < TC_GROUPS || a.NSA > 16) { dl_set_error("dl_gemm_q40_tc: bad NSA=%d", a.NSA); return -1; }
     // nacc must divide nstg: then successive phases of an A stage are consumed by the SAME issuing warp (and
     // written after a retire that is ordered behind the previous one), so a parity wait can never be lapped
     a.nacc = (a.NT <= 128) ? 2 : 1;
@@ -382,7 +415,7 @@ extern "C" int dl_gemm_q40_tc(const uint8_t* w_q40t, int d, int n, const uint8_t
     a.dbg = g_tc_dbg;
     a.dbg_mode = g_tc_dbg_mode;
     const size_t smem = (size_t)a.NSB * a.NT * 256 + (size_t)a.NSA * Q40T_TILE_BYTES +
-                        (size_t)TC_EPI_CHUNK * 128 * 4 + 6 * 8 * 8 + 8 + 16;
+                        (size_t)TC_EPI_CHUNK * 128 * 4 + (2 * 16 + 4 * 8) * 8 + 8 + 16;
     static size_t max_set = 0;
     if (smem > max_set) {
         cudaError_t e = cudaFuncSetAttribute(gemm_q40_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

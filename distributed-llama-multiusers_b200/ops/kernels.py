@@ -224,14 +224,19 @@ def wait_flags(flags: int, n: int, step_counter: int, flag_mul: int, flag_add: i
 
 
 def choose_tc_split(d: int, n: int, M: int, n_sms: int) -> int:
-    """Cluster split-K factor of the tcgen05 GEMM: only for narrow activation tiles (M <= 32, one
-    epilogue chunk), a power of two, and never more CTAs than SMs (one CTA per SM: a second wave of
-    half-empty CTAs costs more than the extra parallelism buys)."""
+    """Cluster split-K factor of the tcgen05 GEMM: a power of two (<= 8) that fills the chip without
+    ever launching more CTAs than SMs (one CTA per SM: a second wave of half-empty CTAs costs more
+    than the extra parallelism buys).  The activation tile is 16/32/64/128 rows (256 with a 256-row
+    capacity), so wide batches already bring ceil(M / tile) CTAs per row tile."""
     row_tiles = (d + 127) // 128
+    nt = 16 if M <= 16 else 32 if M <= 32 else 64 if M <= 64 else 128
+    m_tiles = (M + nt - 1) // nt
+    # wide tiles reduce one 32-row chunk at a time over DSMEM (two cluster syncs per chunk): only worth it when
+    # every CTA still keeps a long k-loop (measured: w2 with 112 k-tiles gains 1.5x at S=4, qkv/wo with 32 lose)
+    min_kt = 1 if M <= 32 else 24
     S = 1
-    if M <= 32:
-        while row_tiles * S * 2 <= n_sms and S < 8 and S * 2 <= n // 128:
-            S *= 2
+    while row_tiles * m_tiles * S * 2 <= n_sms and S < 8 and (n // 128) // (S * 2) >= min_kt:
+        S *= 2
     return S
 
 

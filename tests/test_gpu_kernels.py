@@ -152,6 +152,7 @@ def _gemm_case(d, n, M, S, seed=0):
 @pytest.mark.parametrize("d,n,M,S", [
     (128, 128, 16, 1), (128, 256, 9, 1), (256, 1024, 32, 1), (256, 1024, 32, 2), (384, 2048, 20, 4),
     (128, 4096, 64, 1), (512, 1024, 128, 1), (256, 512, 200, 1), (200, 1024, 40, 1),
+    (256, 2048, 64, 2), (128, 2048, 128, 4), (256, 1024, 100, 8), (128, 1024, 256, 2), (128, 384, 300, 2),
 ])
 def test_gemm_q40_tc_matches_reference(d, n, M, S):
     got, ref = _gemm_case(d, n, M, S, seed=d + n + M)
