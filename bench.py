@@ -325,8 +325,18 @@ def run_reference(args):
     print(json.dumps(run_reference_arm(args, METRIC)), flush=True)
 
 
+def _claim_stdout():
+    """The contract is ONE JSON line on stdout.  Libraries (NCCL's version banner, torchrun notices) also
+    write to fd 1, so fd 1 is pointed at stderr for the whole run and the JSON line goes to the saved fd."""
+    sys.stdout.flush()
+    saved = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(saved, "w", buffering=1)
+
+
 if __name__ == "__main__":
     a = parse_args()
+    _claim_stdout()
     if a.impl == "reference":
         try:
             run_reference(a)

@@ -209,6 +209,13 @@ def build_engine(model_path: str, rank: int, world: int, max_batch: int, n_slots
             torch.cuda.set_device(gpu_index)
         return LlamaEngine(model_path, rank=rank, world=world, max_rows=max_batch, n_slots=slots,
                            max_seq_len=seq_len, sync_q80=True)
+    if use_cuda:
+        # f32 / f16 weights with an f32 buffer: the library path (cuBLAS + NCCL), same engine surface
+        from ..models.f32_engine import F32Engine
+        if gpu_index >= 0:
+            torch.cuda.set_device(gpu_index)
+        return F32Engine(model_path, rank=rank, world=world, max_rows=max_batch, n_slots=slots,
+                         max_seq_len=min(seq_len, 8192))
     if world > 1:
         raise ValueError("multi-node runs need the CUDA engine")
     from ..models.cpu_engine import CpuEngine

@@ -1,0 +1,203 @@
+"""GPU engine for models whose weights are F32 / F16 in the `.m` file, run with an f32 sync buffer
+(`--buffer-float-type f32`): the reference's "f32 / f32" path (matmul_F32_F32_F32, nn-cpu-ops.cpp:
+182-220; merge-add of f32 slices :835-852; no Q80 cast anywhere).
+
+The hand-written kernels of this repo are Q40 x Q80 (that is what the published models use), so this
+path is deliberately the *library* one: weights stay f32 in HBM, matmuls are plain cuBLAS SGEMMs
+(`torch.matmul`, TF32 disabled), the wo / w2 partial sums are combined with an NCCL all-reduce, and
+RMSNorm / RoPE / attention / SiLU*mul are PyTorch ops.  What it shares with ``LlamaEngine`` is the
+public surface -- slots, batched rows with per-row positions, tensor-parallel slicing by rank -- so
+the scheduler, the HTTP API and the CLI run f32 models on GPUs unchanged.
+
+Slicing follows the reference (llm.cpp:131-142): q/k/v/w1/w3/wcls by output rows, wo/w2 by input
+columns, KV cache by kv head, residual stream replicated.
+"""
+from __future__ import annotations
+
+import math
+from typing import List, Optional, Sequence
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from ..formats.mfile import HIDDEN_ACT_SILU, ModelFile
+from ..parallel.symm import validate_tp
+from .oracle import rope_frequencies
+
+
+class _Slots:
+    def __init__(self, n_slots: int):
+        self.free_slots = list(range(n_slots - 1, -1, -1))
+
+    def alloc_slot(self) -> int:
+        if not self.free_slots:
+            raise RuntimeError("no free sequence slot")
+        return self.free_slots.pop()
+
+    def free_slot(self, slot: int):
+        self.free_slots.append(slot)
+
+    def release_pages(self, slot: int):
+        pass
+
+    def ensure(self, slot: int, n_tokens: int):
+        pass
+
+
+class F32Engine:
+    def __init__(self, model_path: str, rank: int = 0, world: int = 1, group=None, max_rows: int = 32,
+                 n_slots: int = 4, max_seq_len: int = 2048, device: Optional[str] = None, **_unused):
+        self.mf = ModelFile(model_path, max_seq_len=max_seq_len)
+        h = self.h = self.mf.header
+        validate_tp(world, h.n_kv_heads, h.dim, h.hidden_dim, h.n_heads, h.n_heads, q40=False)      # vocab may be replicated
+        self.rank, self.world, self.group = rank, world, group
+        self.max_rows, self.n_slots = max_rows, n_slots
+        self.seq_len = min(h.seq_len, max_seq_len)
+        self.device = torch.device(device or (f"cuda:{torch.cuda.current_device()}" if torch.cuda.is_available() else "cpu"))
+        if self.device.type == "cuda":
+            torch.backends.cuda.matmul.allow_tf32 = False          # the reference accumulates in f32
+        N, hs = world, h.head_size
+        self.hs = hs
+        self.n_heads_loc, self.n_kv_loc = h.n_heads // N, h.n_kv_heads // N
+        self.q_loc, self.kv_loc, self.hid_loc = h.dim // N, h.kv_dim // N, h.hidden_dim // N
+        self.vocab_loc = h.vocab_size // N if h.vocab_size % N == 0 else None
+
+        def up(a: np.ndarray) -> torch.Tensor:
+            return torch.from_numpy(np.ascontiguousarray(a, dtype=np.float32)).to(self.device)
+
+        def rows(name, l, r0, n):
+            return up(self.mf.f32(name, l)[r0:r0 + n])
+
+        def cols(name, l, c0, n):
+            return up(self.mf.f32(name, l)[:, c0:c0 + n])
+
+        r = rank
+        self.embedding = up(self.mf.f32("embedding"))
+        self.layers = []
+        for l in range(h.n_layers):
+            self.layers.append({
+                "qkv": torch.cat([rows("wq", l, r * self.q_loc, self.q_loc), rows("wk", l, r * self.kv_loc, self.kv_loc),
+                                  rows("wv", l, r * self.kv_loc, self.kv_loc)], dim=0),
+                "wo": cols("wo", l, r * self.q_loc, self.q_loc),
+                "w1": rows("w1", l, r * self.hid_loc, self.hid_loc),
+                "w3": rows("w3", l, r * self.hid_loc, self.hid_loc),
+                "w2": cols("w2", l, r * self.hid_loc, self.hid_loc),
+                "rms_att": up(self.mf.f32("rms_att", l)).reshape(-1),
+                "rms_ffn": up(self.mf.f32("rms_ffn", l)).reshape(-1),
+            })
+        self.rms_final = up(self.mf.f32("rms_final")).reshape(-1)
+        if self.vocab_loc is not None:
+            self.wcls = rows("wcls", -1, r * self.vocab_loc, self.vocab_loc)
+        else:                                                     # vocab not divisible: replicate the classifier
+            self.wcls = up(self.mf.f32("wcls"))
+        self.freqs = rope_frequencies(h).to(self.device)
+        L = h.n_layers
+        self.k_cache = torch.zeros(n_slots, L, self.seq_len, self.n_kv_loc, hs, device=self.device)
+        self.v_cache = torch.zeros(n_slots, L, self.seq_len, self.n_kv_loc, hs, device=self.device)
+        self.pages = _Slots(n_slots)
+        self.logits = torch.zeros(max_rows, h.vocab_size, device=self.device)
+        self.act_gelu = h.hidden_act != HIDDEN_ACT_SILU
+
+    # ---- LlamaEngine surface ---------------------------------------------------------------------
+    def alloc_slot(self) -> int:
+        return self.pages.alloc_slot()
+
+    def free_slot(self, slot: int):
+        self.pages.free_slot(slot)
+
+    def ensure_capacity(self, slot: int, n_tokens: int):
+        if n_tokens > self.seq_len:
+            raise RuntimeError(f"sequence of {n_tokens} tokens exceeds max_seq_len")
+
+    def weight_bytes(self) -> int:
+        n = sum(t.numel() for L in self.layers for t in L.values()) + self.wcls.numel() + self.rms_final.numel()
+        return 4 * n
+
+    def _all_reduce(self, t: torch.Tensor) -> torch.Tensor:
+        if self.world > 1:
+            dist.all_reduce(t, group=self.group)
+        return t
+
+    def _rms(self, x, w):
+        return w * (x * torch.rsqrt((x * x).mean(-1, keepdim=True) + self.h.norm_epsilon))
+
+    def _rope(self, x, pos):
+        M = x.shape[0]
+        xr = x.reshape(M, -1, self.hs // 2, 2)
+        ang = pos.float()[:, None] * self.freqs[None, :]
+        c, s = torch.cos(ang)[:, None, :], torch.sin(ang)[:, None, :]
+        x0, x1 = xr[..., 0], xr[..., 1]
+        return torch.stack([x0 * c - x1 * s, x0 * s + x1 * c], dim=-1).reshape(x.shape)
+
+    @torch.no_grad()
+    def forward(self, tokens: Sequence[int], positions: Sequence[int], slots: Sequence[int], logits_from: int = 0,
+                greedy: bool = False) -> torch.Tensor:
+        """Rows may mix sequences; rows of one sequence must be in increasing position order."""
+        h, M = self.h, len(tokens)
+        assert 1 <= M <= self.max_rows
+        dev = self.device
+        pos = torch.tensor(list(positions), device=dev, dtype=torch.long)
+        slot_t = torch.tensor(list(slots), device=dev, dtype=torch.long)
+        x = self.embedding[torch.tensor(list(tokens), device=dev, dtype=torch.long)]
+        G = self.n_heads_loc // self.n_kv_loc
+        # chunks = maximal runs of consecutive positions of one slot (a prompt chunk or one decode row)
+        chunks, i = [], 0
+        while i < M:
+            j = i + 1
+            while j < M and slots[j] == slots[i] and positions[j] == positions[j - 1] + 1:
+                j += 1
+            chunks.append((i, j))
+            i = j
+        scale = 1.0 / math.sqrt(self.hs)
+        for l, W in enumerate(self.layers):
+            y = self._rms(x, W["rms_att"])
+            qkv = y @ W["qkv"].t()
+            q = self._rope(qkv[:, :self.q_loc], pos).reshape(M, self.n_heads_loc, self.hs)
+            k = self._rope(qkv[:, self.q_loc:self.q_loc + self.kv_loc], pos).reshape(M, self.n_kv_loc, self.hs)
+            v = qkv[:, self.q_loc + self.kv_loc:].reshape(M, self.n_kv_loc, self.hs)
+            self.k_cache[slot_t, l, pos] = k
+            self.v_cache[slot_t, l, pos] = v
+            att = torch.empty(M, self.n_heads_loc, self.hs, device=dev)
+            for (a, b) in chunks:
+                s, p0, p1 = int(slots[a]), int(positions[a]), int(positions[b - 1]) + 1
+                kk = self.k_cache[s, l, :p1].repeat_interleave(G, dim=1)              # [S, heads, hs]
+                vv = self.v_cache[s, l, :p1].repeat_interleave(G, dim=1)
+                sc = torch.einsum("thd,shd->hts", q[a:b], kk) * scale
+                mask = torch.arange(p1, device=dev)[None, :] > pos[a:b, None]         # causal inside the chunk
+                sc = sc.masked_fill(mask[None], float("-inf"))
+                att[a:b] = torch.einsum("hts,shd->thd", torch.softmax(sc, dim=-1), vv)
+            x = x + self._all_reduce(att.reshape(M, self.q_loc) @ W["wo"].t())
+            y = self._rms(x, W["rms_ffn"])
+            g = y @ W["w1"].t()
+            u = y @ W["w3"].t()
+            act = torch.nn.functional.gelu(g, approximate="tanh") if self.act_gelu else torch.nn.functional.silu(g)
+            x = x + self._all_reduce((act * u) @ W["w2"].t())
+        y = self._rms(x[logits_from:], self.rms_final)
+        lg = y @ self.wcls.t()
+        if self.world > 1 and self.vocab_loc is not None:
+            parts = [torch.empty_like(lg) for _ in range(self.world)]
+            dist.all_gather(parts, lg, group=self.group)
+            lg = torch.cat(parts, dim=-1)
+        n_out = M - logits_from
+        self.logits[:n_out] = lg
+        return self.logits[:n_out]
+
+    def prefill(self, slot: int, tokens: Sequence[int], start_pos: int = 0, chunk: Optional[int] = None):
+        chunk = chunk or self.max_rows
+        out = None
+        for i in range(0, len(tokens), chunk):
+            part = list(tokens[i:i + chunk])
+            pos = list(range(start_pos + i, start_pos + i + len(part)))
+            out = self.forward(part, pos, [slot] * len(part), logits_from=len(part) - 1)
+        return out
+
+    def decode_step_greedy(self, tokens, positions, slots, logits_from: int = 0) -> List[int]:
+        lg = self.forward(tokens, positions, slots, logits_from)
+        return [int(t) for t in torch.argmax(lg, dim=-1).cpu()]
+
+    def decode_greedy_host(self, tokens, positions, slots) -> List[int]:
+        return self.decode_step_greedy(tokens, positions, slots, 0)
+
+    def close(self):
+        self.mf.close()
