@@ -40,6 +40,7 @@ def parse_args():
     ap.add_argument("--layers", type=int, default=0, help="debug only: override layer count (invalid as a bench)")
     ap.add_argument("--prompt-len", type=int, default=128)
     ap.add_argument("--prefill-chunk", type=int, default=128, help="rows per prefill forward (engine max_rows)")
+    ap.add_argument("--b2-cache", type=int, default=0, help="nccl_cublas arm: keep bf16 copies of the weights (1) or dequantise per call (0)")
     ap.add_argument("--no-pdl", action="store_true")
     ap.add_argument("--no-graphs", action="store_true")
     ap.add_argument("--users", type=int, default=0, help="also measure an N-user batched decode (extra key)")
@@ -286,7 +287,8 @@ def run_nccl_cublas(args):
     if world > 1:
         dist.barrier()
     K_, W = args.steps, args.warmup
-    eng = NcclCublasEngine(path, rank=rank, world=world, max_seq_len=max(512, args.prompt_len + K_ + W + 64))
+    eng = NcclCublasEngine(path, rank=rank, world=world, max_seq_len=max(512, args.prompt_len + K_ + W + 64),
+                           cache_weights=bool(args.b2_cache))
     rng = __import__("numpy").random.default_rng(0)
     prompt = rng.integers(1, eng.h.vocab_size, args.prompt_len).tolist()
     lg = eng.forward(prompt, 0)
@@ -311,7 +313,7 @@ def run_nccl_cublas(args):
     if rank == 0:
         print(json.dumps({"metric": METRIC, "value": round(1000.0 / ms, 2), "unit": "tokens/s", "n_gpus": world,
                           "steps": K_, "warmup": W, "ms_per_step": round(ms, 4), "higher_is_better": True,
-                          "scaling": "strong", "vs_baseline": None, "dtype": "bf16 cuBLAS on dequantised Q40, NCCL all-reduce",
+                          "scaling": "strong", "vs_baseline": None, "dtype": "bf16 cuBLAS on dequantised Q40 (%s), NCCL all-reduce" % ("bf16 copies cached in HBM" if args.b2_cache else "dequantised on every call"),
                           "data": "synthetic", "impl": "nccl_cublas",
                           "config": {"model": args.model, "global_batch": 1, "parallelism": f"tp{world}"}}), flush=True)
     eng.close()
