@@ -2,10 +2,11 @@
 (`--buffer-float-type f32`): the reference's "f32 / f32" path (matmul_F32_F32_F32, nn-cpu-ops.cpp:
 182-220; merge-add of f32 slices :835-852; no Q80 cast anywhere).
 
-The hand-written kernels of this repo are Q40 x Q80 (that is what the published models use), so this
-path is deliberately the *library* one: weights stay f32 in HBM, matmuls are plain cuBLAS SGEMMs
-(`torch.matmul`, TF32 disabled), the wo / w2 partial sums are combined with an NCCL all-reduce, and
-RMSNorm / RoPE / attention / SiLU*mul are PyTorch ops.  What it shares with ``LlamaEngine`` is the
+Weights stay f32 in HBM.  On a GPU the matmuls are this repo's `gemm_f32_kernel` (csrc/cuda/gemm_f32.cu:
+plain f32 FMAs, weights streamed once per <= 8 activation rows); chunks wider than 64 rows (prefill) fall
+back to a cuBLAS SGEMM with TF32 disabled.  The wo / w2 partial sums are combined with an NCCL
+all-reduce, and RMSNorm / RoPE / attention / SiLU*mul are PyTorch ops -- the tuned, fused kernels of
+this repo are Q40 x Q80 (what the published models use); this path is about running f32 models at all.  What it shares with ``LlamaEngine`` is the
 public surface -- slots, batched rows with per-row positions, tensor-parallel slicing by rank -- so
 the scheduler, the HTTP API and the CLI run f32 models on GPUs unchanged.
 
@@ -98,6 +99,11 @@ class F32Engine:
         self.pages = _Slots(n_slots)
         self.logits = torch.zeros(max_rows, h.vocab_size, device=self.device)
         self.act_gelu = h.hidden_act != HIDDEN_ACT_SILU
+        self.native = self.device.type == "cuda"
+        if self.native:
+            from ..ops import kernels as _K          # fails loudly if the CUDA library is missing on a GPU box
+            _K.cuda_lib()
+            self._K = _K
 
     # ---- LlamaEngine surface ---------------------------------------------------------------------
     def alloc_slot(self) -> int:
@@ -118,6 +124,12 @@ class F32Engine:
         if self.world > 1:
             dist.all_reduce(t, group=self.group)
         return t
+
+    def _mm(self, x: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
+        """x[M][n] @ w[d][n]^T in f32."""
+        if self.native and x.shape[0] <= 64:
+            return self._K.gemm_f32(w, x.contiguous())
+        return x @ w.t()
 
     def _rms(self, x, w):
         return w * (x * torch.rsqrt((x * x).mean(-1, keepdim=True) + self.h.norm_epsilon))
@@ -152,7 +164,7 @@ class F32Engine:
         scale = 1.0 / math.sqrt(self.hs)
         for l, W in enumerate(self.layers):
             y = self._rms(x, W["rms_att"])
-            qkv = y @ W["qkv"].t()
+            qkv = self._mm(y, W["qkv"])
             q = self._rope(qkv[:, :self.q_loc], pos).reshape(M, self.n_heads_loc, self.hs)
             k = self._rope(qkv[:, self.q_loc:self.q_loc + self.kv_loc], pos).reshape(M, self.n_kv_loc, self.hs)
             v = qkv[:, self.q_loc + self.kv_loc:].reshape(M, self.n_kv_loc, self.hs)
@@ -167,14 +179,14 @@ class F32Engine:
                 mask = torch.arange(p1, device=dev)[None, :] > pos[a:b, None]         # causal inside the chunk
                 sc = sc.masked_fill(mask[None], float("-inf"))
                 att[a:b] = torch.einsum("hts,shd->thd", torch.softmax(sc, dim=-1), vv)
-            x = x + self._all_reduce(att.reshape(M, self.q_loc) @ W["wo"].t())
+            x = x + self._all_reduce(self._mm(att.reshape(M, self.q_loc), W["wo"]))
             y = self._rms(x, W["rms_ffn"])
-            g = y @ W["w1"].t()
-            u = y @ W["w3"].t()
+            g = self._mm(y, W["w1"])
+            u = self._mm(y, W["w3"])
             act = torch.nn.functional.gelu(g, approximate="tanh") if self.act_gelu else torch.nn.functional.silu(g)
-            x = x + self._all_reduce((act * u) @ W["w2"].t())
+            x = x + self._all_reduce(self._mm(act * u, W["w2"]))
         y = self._rms(x[logits_from:], self.rms_final)
-        lg = y @ self.wcls.t()
+        lg = self._mm(y, self.wcls)
         if self.world > 1 and self.vocab_loc is not None:
             parts = [torch.empty_like(lg) for _ in range(self.world)]
             dist.all_gather(parts, lg, group=self.group)

@@ -223,6 +223,21 @@ def wait_flags(flags: int, n: int, step_counter: int, flag_mul: int, flag_add: i
     lib.count_launch()
 
 
+def gemm_f32(w: torch.Tensor, x: torch.Tensor, out: Optional[torch.Tensor] = None, accumulate: bool = False) -> torch.Tensor:
+    """out[M][d] (+)= x[M][n] @ w[d][n]^T with plain f32 FMAs (the f32-weights path).  w may be a column
+    slice of a wider matrix (row stride w.stride(0)); x and out are row-major."""
+    d, n = w.shape
+    M = x.shape[0]
+    assert w.dtype == torch.float32 and x.dtype == torch.float32 and w.stride(1) == 1 and x.stride(1) == 1
+    if out is None:
+        out = torch.empty(M, d, device=x.device, dtype=torch.float32)
+        accumulate = False
+    check(cuda_lib().dl_gemm_f32(w.data_ptr(), d, n, w.stride(0), x.data_ptr(), M, x.stride(0), out.data_ptr(),
+                                 out.stride(0), 1 if accumulate else 0, _stream()), "dl_gemm_f32")
+    lib.count_launch((M + 7) // 8)
+    return out
+
+
 def choose_tc_split(d: int, n: int, M: int, n_sms: int) -> int:
     """Cluster split-K factor of the tcgen05 GEMM: a power of two (<= 8) that fills the chip without
     ever launching more CTAs than SMs (one CTA per SM: a second wave of half-empty CTAs costs more

@@ -102,6 +102,11 @@ int dl_quant_q80(const float* x, int M, int K, int mcap, uint8_t* xq_out, uint8_
 int dl_embedding(const float* table, const int* tokens, float* x, int M, int dim, uint32_t* step_counter,
                  void* stream);
 
+/* F32 x F32 -> F32 matmul (f32-weights / f32-buffer path; reference: matmul_F32_F32_F32, nn-cpu-ops.cpp:182-220):
+ * y[m][r] (+)= sum_k w[r*ldw + k] * x[m*ldx + k], plain f32 FMAs; n, ldw, ldx multiples of 4, w and x 16-byte aligned */
+int dl_gemm_f32(const float* w, int d, int n, long long ldw, const float* x, int M, int ldx, float* y, int ldy,
+                int accumulate, void* stream);
+
 /* ---- Q40 x Q80 matmuls ------------------------------------------------------------------- */
 /* dp4a GEMV, M <= 8 rows: bulk-copy fed, cluster split-K (reference: matmul_Q80_Q40_F32,
  * src/nn/nn-cpu-ops.cpp:222-440) */

@@ -7,7 +7,7 @@ mkdir -p gpurun_out
 OUT=gpurun_out/gpu_check.log
 : > $OUT
 nvidia-smi --query-gpu=name,memory.total,clocks.max.sm --format=csv >> $OUT 2>&1
-FILES="${@:-tests/test_gpu_kernels.py tests/test_gpu_model.py}"
+FILES="${@:-tests/test_gpu_kernels.py tests/test_gpu_model.py tests/test_f32_engine.py tests/test_zz_no_alloc.py}"
 for f in $FILES; do
   for t in $(python -m pytest $f --collect-only -q -m gpu 2>/dev/null | grep "::" | sed 's/\[.*//' | sort -u); do
     echo "=== $t" >> $OUT

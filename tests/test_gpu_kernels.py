@@ -162,6 +162,23 @@ def test_gemm_q40_tc_matches_reference(d, n, M, S):
     np.testing.assert_allclose(got, ref, rtol=2e-3, atol=2e-3 * scale)
 
 
+@pytest.mark.parametrize("d,n,M,acc", [(64, 256, 1, False), (100, 512, 3, False), (37, 1024, 8, True), (256, 4096, 20, False),
+                                       (128, 128, 5, True)])
+def test_gemm_f32_matches_reference(d, n, M, acc):
+    """f32-weights path: plain f32 FMA matmul, incl. a column slice of a wider matrix (row stride > n)."""
+    k = K()
+    rng = np.random.default_rng(d + n + M)
+    w_full = torch.from_numpy(rng.standard_normal((d, 2 * n), dtype=np.float32)).cuda()
+    w = w_full[:, n:]                                   # column slice, like the wo / w2 slices of a TP rank
+    x = torch.from_numpy(rng.standard_normal((M, n), dtype=np.float32)).cuda()
+    y0 = torch.from_numpy(rng.standard_normal((M, d), dtype=np.float32)).cuda()
+    y = y0.clone()
+    out = k.gemm_f32(w, x, y, accumulate=acc)
+    torch.cuda.synchronize()
+    ref = x.double().cpu().numpy() @ w.double().cpu().numpy().T + (y0.double().cpu().numpy() if acc else 0.0)
+    np.testing.assert_allclose(out.cpu().numpy(), ref, rtol=2e-5, atol=2e-5 * np.abs(ref).max())
+
+
 def _attention_ref(q, kc, vc, pos, n_heads, n_kv, hs):
     M = q.shape[0]
     out = np.zeros((M, n_heads * hs), dtype=np.float64)
