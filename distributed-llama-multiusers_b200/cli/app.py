@@ -207,8 +207,10 @@ def build_engine(model_path: str, rank: int, world: int, max_batch: int, n_slots
         from ..models.llama import LlamaEngine
         if gpu_index >= 0:
             torch.cuda.set_device(gpu_index)
+        # bucket_rows: the CLI and the API server run arbitrary batch shapes (prompt chunks, changing user
+        # counts); padding them to powers of two bounds the number of CUDA graphs (same flag on every rank)
         return LlamaEngine(model_path, rank=rank, world=world, max_rows=max_batch, n_slots=slots,
-                           max_seq_len=seq_len, sync_q80=True)
+                           max_seq_len=seq_len, sync_q80=True, bucket_rows=True)
     if use_cuda:
         # f32 / f16 weights with an f32 buffer: the library path (cuBLAS + NCCL), same engine surface
         from ..models.f32_engine import F32Engine

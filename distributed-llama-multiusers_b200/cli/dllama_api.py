@@ -13,6 +13,7 @@ from .app import USAGE, AppArgs, InferenceContext, run_inference_app
 def server(ctx: InferenceContext):
     a = ctx.args
     batch = BatchEngine(ctx.engine, ctx.tokenizer, control=ctx.control)
+    batch.warmup()                       # capture the CUDA graphs of every batch shape before taking traffic
     batch.start()
     defaults = A.InferenceParams(messages=[], temperature=a.temperature, top_p=a.topp, seed=a.seed)
     import os

@@ -134,20 +134,19 @@ int dl_sched_next_batch(void* p, long long* req_ids, int* tokens, int* pos, int*
         s->running.push_back(r.id);
     }
     // decode rows (round-robin window if there are more decoders than rows)
-    std::vector<Req*> dec;
-    Req* pre = nullptr;
+    std::vector<Req*> dec, pres;
+    int prompt_left = 0;
     for (long long id : s->running) {
         Req& r = s->reqs[id];
         if (r.state == DECODE) dec.push_back(&r);
-        else if (r.state == PREFILL && pre == nullptr) pre = &r;
+        else if (r.state == PREFILL) {
+            pres.push_back(&r);
+            prompt_left += (int)r.prompt.size() - r.n_prefilled;
+        }
     }
     int n_dec = (int)dec.size();
-    // a pending prompt always gets a share of the rows (else a full house of decoders starves it)
-    int reserve = 0;
-    if (pre != nullptr) {
-        const int left = (int)pre->prompt.size() - pre->n_prefilled;
-        reserve = std::min(left, std::max(1, R / 4));
-    }
+    // pending prompts always get a share of the rows (else a full house of decoders starves them)
+    const int reserve = pres.empty() ? 0 : std::min(prompt_left, std::max(1, R / 4));
     const int dec_rows = std::max(0, R - reserve);
     if (n_dec > dec_rows) {
         // more decoders than rows: serve a rotating window so everybody advances
@@ -157,25 +156,40 @@ int dl_sched_next_batch(void* p, long long* req_ids, int* tokens, int* pos, int*
     }
     int n = 0;
     s->batch_sampling.clear();
-    *logits_from = 0;
-    if (pre != nullptr && R - n_dec > 0) {
+    // Prompt rows of as many pending requests as fit (admission order, at most prefill_chunk rows per
+    // request and step).  Rows that need no logits go first; the LAST row of every prompt that completes
+    // in this step is moved to the tail, in front of the decode rows, so that the rows needing logits stay
+    // one contiguous range [logits_from, n).  (Rows of a sequence only have to be in increasing position
+    // order, not adjacent: the KV rows of the whole batch are written before attention runs.)
+    struct TailRow { Req* r; int token, pos; };
+    std::vector<TailRow> tail;
+    int budget = R - n_dec;
+    for (Req* pre : pres) {
+        if (budget <= 0) break;
         const int left = (int)pre->prompt.size() - pre->n_prefilled;
-        const int take = std::min({left, s->prefill_chunk, R - n_dec});
-        for (int i = 0; i < take; i++) {
+        const int take = std::min({left, s->prefill_chunk, budget});
+        const bool completes = take == left;
+        const int head = completes ? take - 1 : take;
+        for (int i = 0; i < head; i++) {
             req_ids[n] = pre->id;
             tokens[n] = pre->prompt[pre->n_prefilled + i];
             pos[n] = pre->pos + i;
             slots[n] = pre->slot;
             n++;
         }
+        if (completes) tail.push_back({pre, pre->prompt[pre->n_prefilled + take - 1], pre->pos + take - 1});
         pre->n_prefilled += take;
         pre->pos += take;
-        if (pre->n_prefilled == (int)pre->prompt.size()) {
-            *logits_from = n - 1;                       // last prompt row samples the first new token
-            s->batch_sampling.push_back(pre->id);
-        } else {
-            *logits_from = n;
-        }
+        budget -= take;
+    }
+    *logits_from = n;
+    for (const TailRow& t : tail) {                     // last prompt row samples the first new token
+        req_ids[n] = t.r->id;
+        tokens[n] = t.token;
+        pos[n] = t.pos;
+        slots[n] = t.r->slot;
+        n++;
+        s->batch_sampling.push_back(t.r->id);
     }
     for (int i = 0; i < n_dec; i++) {
         Req* r = dec[i];

@@ -423,6 +423,8 @@ void dl_sampler_set_temp(void* s, float t) { ((Sampler*)s)->temperature = t; }
 void dl_sampler_set_topp(void* s, float p) { ((Sampler*)s)->topp = p; }
 void dl_sampler_set_seed(void* s, unsigned long long seed) { ((Sampler*)s)->rng = seed; }
 int dl_sampler_sample(void* s, float* logits) { return sample((Sampler*)s, logits); }
+// next uniform [0,1) draw of this sampler's stream (for the device sampler: one coin per generated token)
+float dl_sampler_coin(void* s) { return rng_f32(&((Sampler*)s)->rng); }
 unsigned int dl_rng_u32(unsigned long long* state) { return rng_u32((uint64_t*)state); }
 float dl_rng_f32(unsigned long long* state) { return rng_f32((uint64_t*)state); }
 void dl_softmax(float* x, int n) { softmax_inplace(x, n); }

@@ -83,7 +83,7 @@ class LlamaEngine:
     def __init__(self, model_path: str, rank: int = 0, world: int = 1, group=None, max_rows: int = 32,
                  n_slots: int = 4, max_seq_len: int = 2048, kv_dtype: torch.dtype = torch.float16,
                  sync_q80: bool = True, use_pdl: bool = True, use_graphs: bool = True, n_pages: Optional[int] = None,
-                 device: Optional[torch.device] = None, verbose: bool = False):
+                 device: Optional[torch.device] = None, verbose: bool = False, bucket_rows: bool = False):
         self.mf = ModelFile(model_path, max_seq_len=max_seq_len)
         h = self.h = self.mf.header
         if h.weight_type != quant.Q40:
@@ -157,14 +157,24 @@ class LlamaEngine:
 
         # ---- KV cache ----------------------------------------------------------------------------
         self.max_pages = (self.seq_len + PAGE - 1) // PAGE
+        # bucket_rows (serving): every batch is padded to a power-of-two row count with rows of a hidden
+        # scratch sequence, so continuous batching replays a handful of CUDA graphs instead of capturing
+        # a new one for every (rows, first-logit-row) combination it produces
+        self.bucket_rows = bucket_rows
         self.n_slots = n_slots
-        self.n_pages = n_pages or n_slots * self.max_pages
+        n_slots = n_slots + (1 if bucket_rows else 0)
+        self.n_pages = (n_pages or self.n_slots * self.max_pages) + (1 if bucket_rows else 0)
         self.pages = PageAllocator(self.n_pages, n_slots, self.max_pages)
         self.block_table = torch.zeros(n_slots, self.max_pages, dtype=torch.int32, device=dev)
         self.h_block_table = torch.zeros(n_slots, self.max_pages, dtype=torch.int32).pin_memory()
         kv_shape = (self.n_pages, self.n_kv_loc, PAGE, self.hs)
         self.k_cache = [torch.zeros(kv_shape, dtype=kv_dtype, device=dev) for _ in range(h.n_layers)]
         self.v_cache = [torch.zeros(kv_shape, dtype=kv_dtype, device=dev) for _ in range(h.n_layers)]
+        self._pad_slot, self._Mp = -1, 0
+        if bucket_rows:
+            self._pad_slot = n_slots - 1
+            self.pages.free_slots.remove(self._pad_slot)
+            self.pages.ensure(self._pad_slot, 1)
         self.max_splits = 32
         self.att_scratch = torch.zeros(K.attention_scratch_bytes(R, self.n_heads_loc, self.hs, self.max_splits),
                                        dtype=torch.uint8, device=dev)
@@ -385,6 +395,40 @@ class LlamaEngine:
         g.replay()
         K.lib.count_launch(self._graph_launches[key])
 
+    def _run_batch(self, M: int, logits_from: int, greedy: bool) -> int:
+        """Run the batch staged by set_batch(); returns the index of the first wanted row in
+        self.logits / self.out_tokens.  With bucket_rows the graph key is (padded rows, 0 or last row)."""
+        if not self.bucket_rows:
+            self._run(M, logits_from, greedy)
+            return 0
+        Mp = self._Mp
+        if logits_from == M - 1:              # prompt chunk or single decode row: only the last row's logits
+            self._run(Mp, Mp - 1, greedy)
+            return 0
+        self._run(Mp, 0, greedy)              # logits of every row; the caller's rows are the tail
+        return (Mp - M) + logits_from
+
+    def warmup_graphs(self):
+        """Capture every CUDA graph a bucket_rows engine can ask for (power-of-two row counts x {all-row
+        logits, last-row logits} x {argmax, logits}) on rows of the scratch sequence, so that no request
+        ever waits for a capture.  Every rank must call it at the same point (it runs real forwards)."""
+        assert self.bucket_rows and self.use_graphs
+        hd = self.h_desc.numpy()
+        Mp = 1
+        while True:
+            Mp = min(Mp, self.max_rows)
+            hd[0, :Mp] = 0
+            hd[1, :Mp] = 0
+            hd[2, :Mp] = self._pad_slot
+            self.desc.copy_(self.h_desc, non_blocking=True)
+            for row0 in sorted({0, Mp - 1}):
+                for greedy in (False, True):
+                    self._run(Mp, row0, greedy)
+            if Mp >= self.max_rows:
+                break
+            Mp *= 2
+        torch.cuda.synchronize()
+
     # ------------------------------------------------------------------------------------------------
     # public API
     # ------------------------------------------------------------------------------------------------
@@ -394,9 +438,20 @@ class LlamaEngine:
         M = len(tokens)
         assert 1 <= M <= self.max_rows
         hd = self.h_desc.numpy()
-        hd[0, :M] = tokens
-        hd[1, :M] = positions
-        hd[2, :M] = slots
+        off = 0
+        if self.bucket_rows:
+            Mp = 1
+            while Mp < M:
+                Mp *= 2
+            Mp = min(Mp, self.max_rows)
+            off = Mp - M                      # padding rows first, real rows last (the last row stays last)
+            hd[0, :off] = 0
+            hd[1, :off] = 0
+            hd[2, :off] = self._pad_slot
+            self._Mp = Mp
+        hd[0, off:off + M] = tokens
+        hd[1, off:off + M] = positions
+        hd[2, off:off + M] = slots
         for s, p in zip(slots, positions):
             self.pages.ensure(int(s), int(p) + 1)
         self._sync_block_table()
@@ -408,8 +463,8 @@ class LlamaEngine:
         the same sequence must be in increasing position order).  Returns the device logits view
         [M - logits_from][vocab] (valid until the next forward)."""
         M = self.set_batch(tokens, positions, slots)
-        self._run(M, logits_from, greedy)
-        return self.logits[:M - logits_from]
+        o = self._run_batch(M, logits_from, greedy)
+        return self.logits[o:o + M - logits_from]
 
     def prefill(self, slot: int, tokens: Sequence[int], start_pos: int = 0, chunk: Optional[int] = None):
         """Evaluate a prompt in chunks of <= max_rows rows; returns logits of the last token."""
@@ -425,10 +480,10 @@ class LlamaEngine:
         """One greedy step end to end for rows logits_from..M-1: H2D descriptor, forward, device
         argmax, D2H token ids."""
         M = self.set_batch(tokens, positions, slots)
-        self._run(M, logits_from, True)
+        o = self._run_batch(M, logits_from, True)
         self.h_out_tokens.copy_(self.out_tokens, non_blocking=True)
         torch.cuda.current_stream().synchronize()
-        return self.h_out_tokens[:M - logits_from].tolist()
+        return self.h_out_tokens[o:o + M - logits_from].tolist()
 
     def decode_greedy_host(self, tokens: List[int], positions: List[int], slots: List[int]) -> List[int]:
         return self.decode_step_greedy(tokens, positions, slots, 0)
@@ -437,6 +492,7 @@ class LlamaEngine:
         """Device-resident greedy loop: each step's argmax feeds the next step's embedding and
         advances the positions without a host round trip.  Requires set_batch() first and enough
         KV pages for n_steps more tokens (ensure_capacity)."""
+        assert not self.bucket_rows, "the device-resident loop runs exact batch shapes"
         for _ in range(n_steps):
             self._run(M, 0, True, device_loop=True)
 

@@ -223,6 +223,15 @@ def wait_flags(flags: int, n: int, step_counter: int, flag_mul: int, flag_add: i
     lib.count_launch()
 
 
+def sample_rows(logits: torch.Tensor, temperature: torch.Tensor, topp: torch.Tensor, coin: torch.Tensor,
+                tokens_out: torch.Tensor):
+    """tokens_out[m] = sample(logits[m]) on the device; temperature / topp / coin are f32 device tensors [M]."""
+    M, vocab = logits.shape
+    check(cuda_lib().dl_sample_rows(logits.data_ptr(), M, vocab, logits.stride(0), temperature.data_ptr(), topp.data_ptr(),
+                                    coin.data_ptr(), tokens_out.data_ptr(), _stream()), "dl_sample_rows")
+    lib.count_launch()
+
+
 def gemm_f32(w: torch.Tensor, x: torch.Tensor, out: Optional[torch.Tensor] = None, accumulate: bool = False) -> torch.Tensor:
     """out[M][d] (+)= x[M][n] @ w[d][n]^T with plain f32 FMAs (the f32-weights path).  w may be a column
     slice of a wider matrix (row stride w.stride(0)); x and out are row-major."""

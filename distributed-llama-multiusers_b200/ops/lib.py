@@ -97,6 +97,7 @@ def cuda_lib():
                                        vp, vp, vp, i32, vp]
     L.dl_quant_q80.argtypes = [vp, i32, i32, i32, vp, vp, vp]
     L.dl_embedding.argtypes = [vp, vp, vp, i32, i32, vp, vp]
+    L.dl_sample_rows.argtypes = [vp, i32, i32, i32, vp, vp, vp, vp, vp]
     L.dl_gemm_f32.argtypes = [vp, i32, i32, i64, vp, i32, i32, vp, i32, i32, vp]
     L.dl_gemv_q40.argtypes = [vp, i32, i32, vp, i32, i32, i32, i32, C.POINTER(DlNormProlog), C.POINTER(DlEpilogue), i32, vp]
     L.dl_gemv_q40_smem_bytes.restype = i64
@@ -116,7 +117,7 @@ def cuda_lib():
     L.dl_ipc_free.argtypes = [vp]
     L.dl_peer_barrier.argtypes = [C.POINTER(vp), vp, i32, i32, u32, vp]
     for name in ("dl_q40_repack", "dl_q40t_dequant", "dl_reduce_norm_quant", "dl_quant_q80", "dl_embedding",
-                 "dl_gemm_f32", "dl_gemv_q40", "dl_gemm_q40_tc", "dl_attention", "dl_argmax", "dl_ipc_alloc", "dl_ipc_open",
+                 "dl_sample_rows", "dl_gemm_f32", "dl_gemv_q40", "dl_gemm_q40_tc", "dl_attention", "dl_argmax", "dl_ipc_alloc", "dl_ipc_open",
                  "dl_ipc_close", "dl_ipc_free", "dl_peer_barrier", "dl_wait_flags"):
         getattr(L, name).restype = i32
     _cuda = L

@@ -20,7 +20,7 @@ from typing import List, Optional, Sequence
 
 import numpy as np
 
-OP_STOP, OP_FORWARD, OP_RESET = 0, 1, 2
+OP_STOP, OP_FORWARD, OP_RESET, OP_WARMUP = 0, 1, 2, 3
 _HDR = 8            # int32 words: op, M, logits_from, greedy, n_released, reserved...
 
 

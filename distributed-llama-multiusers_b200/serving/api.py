@@ -165,10 +165,16 @@ def make_handler(state: ApiState):
     return Handler
 
 
+class _Server(ThreadingHTTPServer):
+    # the default listen backlog (5) drops SYNs when tens of users connect at once; the kernel retries them
+    # a full second later (measured: TTFT p95 of 1.05 s with 32 simultaneous clients)
+    request_queue_size = 1024
+
+
 class ApiServer:
     def __init__(self, state: ApiState, host: str = "0.0.0.0", port: int = 9990):
         self.state = state
-        self.httpd = ThreadingHTTPServer((host, port), make_handler(state))
+        self.httpd = _Server((host, port), make_handler(state))
         self.httpd.daemon_threads = True
         self.port = self.httpd.server_address[1]
         self._thread: Optional[threading.Thread] = None

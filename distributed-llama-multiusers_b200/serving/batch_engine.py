@@ -10,6 +10,7 @@ samples, detokenises and hands text deltas to whoever submitted the request.
 from __future__ import annotations
 
 import itertools
+import os
 import queue
 import threading
 import time
@@ -19,7 +20,7 @@ from typing import Callable, List, Optional, Sequence
 import numpy as np
 import torch
 
-from ..parallel.control import OP_FORWARD, OP_STOP, ControlChannel
+from ..parallel.control import OP_FORWARD, OP_STOP, OP_WARMUP, ControlChannel
 from ..text import native as T
 
 
@@ -67,12 +68,29 @@ class BatchEngine:
         self._thread: Optional[threading.Thread] = None
         self.n_steps = 0
         self.n_generated = 0
+        self.n_rows = 0
+        # seconds spent forming batches / in the engine (incl. sampling) / detokenising + bookkeeping
+        self.t_sched = self.t_engine = self.t_emit = 0.0
         eos_pieces = [tokenizer.piece(t).decode("utf-8", "replace") for t in tokenizer.eos_token_ids]
         self._eos_pieces = eos_pieces
         self._max_stop = max([len(p) for p in eos_pieces] + [1])
-        self._logits_host = torch.empty(self.max_rows, engine.h.vocab_size, dtype=torch.float32)
-        if torch.cuda.is_available():
-            self._logits_host = self._logits_host.pin_memory()
+        # sampling: on a GPU engine the rows are sampled by `sample_kernel` (only token ids cross PCIe);
+        # the host sampler (reference-exact arithmetic) serves CPU engines and DLLAMA_HOST_SAMPLER=1
+        dev = getattr(engine, "device", torch.device("cpu"))
+        self._device_sampler = dev.type == "cuda" and os.environ.get("DLLAMA_HOST_SAMPLER", "0") != "1"
+        if self._device_sampler:
+            from ..ops import kernels as _K
+            self._K = _K
+            R = self.max_rows
+            self._h_params = torch.zeros(3, R, dtype=torch.float32).pin_memory()      # temperature | topp | coin
+            self._d_params = torch.zeros(3, R, dtype=torch.float32, device=dev)
+            self._d_tok = torch.zeros(R, dtype=torch.int32, device=dev)
+            self._h_tok = torch.zeros(R, dtype=torch.int32).pin_memory()
+            self._logits_host = None
+        else:
+            self._logits_host = torch.empty(self.max_rows, engine.h.vocab_size, dtype=torch.float32)
+            if torch.cuda.is_available():
+                self._logits_host = self._logits_host.pin_memory()
 
     # ---- client side (any thread) ------------------------------------------------------------------
     def submit(self, req: GenerationRequest) -> GenerationRequest:
@@ -98,6 +116,14 @@ class BatchEngine:
         self.sched.cancel(req.id)
 
     # ---- engine loop (one thread) --------------------------------------------------------------------
+    def warmup(self):
+        """Pre-capture the engine's CUDA graphs on every rank (call before start(); no-op for engines
+        without bucketed shapes)."""
+        if getattr(self.engine, "bucket_rows", False) and getattr(self.engine, "use_graphs", False):
+            if self.control is not None:
+                self.control.send(OP_WARMUP)
+            self.engine.warmup_graphs()
+
     def start(self):
         self._thread = threading.Thread(target=self.run, name="dllama-batch-engine", daemon=True)
         self._thread.start()
@@ -119,6 +145,7 @@ class BatchEngine:
 
     def step(self) -> int:
         """One scheduler step = one forward pass.  Returns the number of rows run."""
+        t_a = time.perf_counter()
         ids, toks, pos, slots, lf, sampling = self.sched.next_batch()
         released = self.sched.pop_released()
         for s in released:
@@ -133,12 +160,30 @@ class BatchEngine:
             self.control.send(OP_FORWARD, toks, pos, slots, lf, greedy, released)
         eng = self.engine
         n_s = len(sampling)
+        t_b = time.perf_counter()
+        self.t_sched += t_b - t_a
         if n_s == 0:
             eng.forward(toks, pos, slots, logits_from=len(toks) - 1)       # pure prefill chunk
             self.n_steps += 1
+            self.n_rows += len(ids)
+            self.t_engine += time.perf_counter() - t_b
             return len(ids)
         if greedy:
             sampled = eng.decode_step_greedy(toks, pos, slots, lf)[:n_s]
+        elif self._device_sampler:
+            logits = eng.forward(toks, pos, slots, logits_from=lf)
+            hp = self._h_params.numpy()
+            for i, r in enumerate(rows):
+                if r is None:
+                    hp[0, i], hp[1, i], hp[2, i] = 0.0, 0.0, 0.0
+                else:
+                    hp[0, i], hp[1, i] = r.temperature, r.top_p
+                    hp[2, i] = r._sampler.coin() if r.temperature != 0.0 else 0.0
+            self._d_params.copy_(self._h_params, non_blocking=True)
+            self._K.sample_rows(logits[:n_s], self._d_params[0], self._d_params[1], self._d_params[2], self._d_tok)
+            self._h_tok.copy_(self._d_tok, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+            sampled = self._h_tok[:n_s].tolist()
         else:
             logits = eng.forward(toks, pos, slots, logits_from=lf)
             self._logits_host[:n_s].copy_(logits[:n_s], non_blocking=True)
@@ -146,6 +191,8 @@ class BatchEngine:
                 torch.cuda.current_stream().synchronize()
             lh = self._logits_host.numpy()
             sampled = [r._sampler.sample(lh[i]) if r is not None else 0 for i, r in enumerate(rows)]
+        t_c = time.perf_counter()
+        self.t_engine += t_c - t_b
         now = time.time()
         stop_flags = []
         for r, t in zip(rows, sampled):
@@ -155,7 +202,9 @@ class BatchEngine:
             if r is not None and fin:
                 self._finalize(r, "stop" if r.finish_reason == "stop" else "length")
         self.n_steps += 1
+        self.n_rows += len(ids)
         self.n_generated += n_s
+        self.t_emit += time.perf_counter() - t_c
         return len(ids)
 
     # ---- per-token text handling -----------------------------------------------------------------------
@@ -210,6 +259,9 @@ def worker_loop(engine, control: ControlChannel):
             return
         for s in pkt["released"]:
             engine.pages.release_pages(s)
+        if pkt["op"] == OP_WARMUP:
+            engine.warmup_graphs()
+            continue
         if pkt["op"] == OP_FORWARD and pkt["M"] > 0:
             M = engine.set_batch(pkt["tokens"], pkt["positions"], pkt["slots"])
-            engine._run(M, pkt["logits_from"], pkt["greedy"])
+            engine._run_batch(M, pkt["logits_from"], pkt["greedy"])

@@ -32,7 +32,7 @@ def host_lib():
         "dl_dec_push": (i32, [vp, i32, cp, i32]),
         "dl_sampler_new": (vp, [i32, f32, f32, u64]), "dl_sampler_free": (None, [vp]),
         "dl_sampler_set_temp": (None, [vp, f32]), "dl_sampler_set_topp": (None, [vp, f32]),
-        "dl_sampler_set_seed": (None, [vp, u64]), "dl_sampler_sample": (i32, [vp, vp]),
+        "dl_sampler_set_seed": (None, [vp, u64]), "dl_sampler_sample": (i32, [vp, vp]), "dl_sampler_coin": (C.c_float, [vp]),
         "dl_rng_u32": (C.c_uint, [C.POINTER(u64)]), "dl_rng_f32": (f32, [C.POINTER(u64)]),
         "dl_softmax": (None, [vp, i32]),
         "dl_chat_detect": (i32, [cp]),
@@ -173,6 +173,10 @@ class Sampler:
 
     def set_seed(self, seed: int):
         host_lib().dl_sampler_set_seed(self._h, seed & 0xFFFFFFFFFFFFFFFF)
+
+    def coin(self) -> float:
+        """Next uniform [0, 1) draw of this request's RNG stream (fed to the device sampler)."""
+        return float(host_lib().dl_sampler_coin(self._h))
 
     def sample(self, logits: np.ndarray) -> int:
         """``logits``: contiguous float32 [vocab]; mutated in place like the reference."""

@@ -102,6 +102,12 @@ int dl_quant_q80(const float* x, int M, int K, int mcap, uint8_t* xq_out, uint8_
 int dl_embedding(const float* table, const int* tokens, float* x, int M, int dim, uint32_t* step_counter,
                  void* stream);
 
+/* per-row sampling on the device (reference: Sampler::sample, src/tokenizer.cpp:382-510): temperature 0 -> first
+ * argmax; else softmax(logits / temperature) and top-p nucleus (0 < topp < 1) or multinomial, drawn with coin[m] in
+ * [0,1) (the caller's per-request RNG).  All arrays are device pointers with M entries; one CTA per row. */
+int dl_sample_rows(const float* logits, int M, int vocab, int ld, const float* temperature, const float* topp,
+                   const float* coin, int* tokens_out, void* stream);
+
 /* F32 x F32 -> F32 matmul (f32-weights / f32-buffer path; reference: matmul_F32_F32_F32, nn-cpu-ops.cpp:182-220):
  * y[m][r] (+)= sum_k w[r*ldw + k] * x[m*ldx + k], plain f32 FMAs; n, ldw, ldx multiples of 4, w and x 16-byte aligned */
 int dl_gemm_f32(const float* w, int d, int n, long long ldw, const float* x, int M, int ldx, float* y, int ldy,

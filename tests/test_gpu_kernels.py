@@ -179,6 +179,45 @@ def test_gemm_f32_matches_reference(d, n, M, acc):
     np.testing.assert_allclose(out.cpu().numpy(), ref, rtol=2e-5, atol=2e-5 * np.abs(ref).max())
 
 
+def test_device_sampler_distribution_and_determinism():
+    """sample_kernel: argmax at temperature 0; with top-p every draw lies inside the nucleus the host sampler
+    would build (sorted cumulative > topp) and frequencies follow the renormalised probabilities."""
+    k = K()
+    rng = np.random.default_rng(11)
+    V, M = 3000, 4096
+    base = (rng.standard_normal(V) * 2.5).astype(np.float32)
+    logits = torch.from_numpy(np.tile(base, (M, 1))).cuda()
+    coins = torch.from_numpy(((np.arange(M) + 0.5) / M).astype(np.float32)).cuda()       # stratified coins
+    out = torch.zeros(M, dtype=torch.int32, device="cuda")
+    temp, topp = 0.8, 0.9
+    p = np.exp((base.astype(np.float64) - base.max()) / temp)
+    p /= p.sum()
+    order = np.argsort(-p)
+    cut = int(np.searchsorted(np.cumsum(p[order]), topp)) + 1                             # crossing token included
+    nucleus = set(order[:cut].tolist())
+    k.sample_rows(logits, torch.full((M,), temp, device="cuda"), torch.full((M,), topp, device="cuda"), coins, out)
+    torch.cuda.synchronize()
+    got = out.cpu().numpy()
+    assert set(got.tolist()) <= nucleus
+    pn = np.zeros(V)
+    pn[order[:cut]] = p[order[:cut]] / p[order[:cut]].sum()
+    freq = np.bincount(got, minlength=V) / M
+    assert np.abs(freq - pn).max() < 2.0 / M + 1e-3                                       # stratified coins: near-exact CDF inversion
+    out2 = torch.zeros_like(out)
+    k.sample_rows(logits, torch.full((M,), temp, device="cuda"), torch.full((M,), topp, device="cuda"), coins, out2)
+    assert torch.equal(out, out2)                                                         # bit-deterministic
+    # multinomial (top-p off) and greedy rows in one launch
+    temps = torch.full((M,), 1.3, device="cuda")
+    temps[::2] = 0.0
+    k.sample_rows(logits, temps, torch.ones(M, device="cuda"), coins, out)
+    got = out.cpu().numpy()
+    assert (got[::2] == int(np.argmax(base))).all()
+    p2 = np.exp((base.astype(np.float64) - base.max()) / 1.3)
+    p2 /= p2.sum()
+    freq2 = np.bincount(got[1::2], minlength=V) / (M // 2)
+    assert np.abs(freq2 - p2).max() < 4.0 / M + 2e-3
+
+
 def _attention_ref(q, kc, vc, pos, n_heads, n_kv, hs):
     M = q.shape[0]
     out = np.zeros((M, n_heads * hs), dtype=np.float64)

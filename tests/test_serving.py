@@ -27,24 +27,27 @@ def test_scheduler_batches_prefill_first_and_decodes_together():
     assert s.submit(2, [20, 21], 2) == 0
     assert s.submit(3, [30], 2) == 0                      # waits: only 2 slots
     assert s.submit(4, [], 2) == -3 and s.submit(5, list(range(64)), 2) == -1 and s.submit(1, [1], 1) == -2
-    ids, toks, pos, slots, lf, samp = s.next_batch()      # first chunk of request 1 (4 of 6 tokens)
-    assert ids == [1, 1, 1, 1] and toks == [10, 11, 12, 13] and pos == [0, 1, 2, 3] and lf == 4 and samp == []
-    ids, toks, pos, slots, lf, samp = s.next_batch()      # rest of request 1 -> its last row samples
-    assert toks == [14, 15] and pos == [4, 5] and lf == 1 and samp == [1]
-    assert s.commit([100], [False]) == [False]
-    ids, toks, pos, slots, lf, samp = s.next_batch()      # request 2 prefill first, then request 1 decoding
-    assert ids == [2, 2, 1] and toks == [20, 21, 100] and pos == [0, 1, 6] and lf == 1 and samp == [2, 1]
-    assert slots[0] == slots[1] != slots[2]
-    assert s.commit([200, 101], [False, False]) == [False, False]
-    ids, toks, pos, slots, lf, samp = s.next_batch()      # both decode; request 3 still waiting for a slot
-    assert ids == [1, 2] and toks == [101, 200] and pos == [7, 2] and lf == 0
-    fin = s.commit([102, 201], [False, False])
-    assert fin == [True, True]                            # budgets (3 and 2 new tokens) exhausted
-    assert sorted(s.pop_released()) == sorted(set(slots))
-    ids, toks, pos, slots, lf, samp = s.next_batch()      # request 3 admitted into a freed slot
-    assert ids == [3] and toks == [30] and samp == [3]
-    assert s.commit([7], [True]) == [True]                # stop flag ends it at once
+    # step 1: 4 of request 1's 6 prompt tokens (prefill_chunk) + all of request 2's prompt; the row that
+    # completes prompt 2 is moved to the tail so the rows needing logits are one contiguous range
+    ids, toks, pos, slots, lf, samp = s.next_batch()
+    assert ids == [1, 1, 1, 1, 2, 2] and toks == [10, 11, 12, 13, 20, 21] and pos == [0, 1, 2, 3, 0, 1]
+    assert lf == 5 and samp == [2]
+    assert slots[0] == slots[3] != slots[4] == slots[5]
+    assert s.commit([200], [False]) == [False]
+    # step 2: rest of request 1 (its last row samples) + request 2 decoding
+    ids, toks, pos, slots, lf, samp = s.next_batch()
+    assert ids == [1, 1, 2] and toks == [14, 15, 200] and pos == [4, 5, 2] and lf == 1 and samp == [1, 2]
+    assert s.commit([100, 201], [False, False]) == [False, True]      # request 2's budget (2 tokens) is spent
+    assert len(s.pop_released()) == 1
+    # step 3: request 3 admitted into the freed slot, prefilled while request 1 decodes
+    ids, toks, pos, slots, lf, samp = s.next_batch()
+    assert ids == [3, 1] and toks == [30, 100] and pos == [0, 6] and lf == 0 and samp == [3, 1]
+    assert s.commit([7, 101], [True, False]) == [True, False]          # stop flag ends request 3 at once
+    ids, toks, pos, slots, lf, samp = s.next_batch()
+    assert ids == [1] and toks == [101] and pos == [7]
+    assert s.commit([102], [False]) == [True]                           # 3 new tokens: done
     assert s.next_batch()[0] == []
+    s.pop_released()
     assert s.stats()["free_slots"] == 2
 
 
@@ -52,9 +55,11 @@ def test_scheduler_cancel_and_round_robin():
     s = T.Scheduler(max_rows=2, n_slots=3, prefill_chunk=2, max_seq_len=64)
     for i in (1, 2, 3):
         s.submit(i, [i], 10)
-    for _ in range(3):                                    # prefill one request per step (one prefill seq per batch)
+    while True:                                           # prefill (2 rows per step) until all three decode
         ids, toks, pos, slots, lf, samp = s.next_batch()
         s.commit([50 + x for x in samp], [False] * len(samp))
+        if s.stats()["running"] == 3 and lf == 0 and len(samp) == len(ids) and len(ids) == 2:
+            break
     seen = []
     for _ in range(3):                                    # 3 decoders, 2 rows: round-robin must serve all
         ids, *_rest, samp = s.next_batch()
