@@ -39,7 +39,7 @@ def parse_args():
     ap.add_argument("--model", default="llama3.1-8b")
     ap.add_argument("--layers", type=int, default=0, help="debug only: override layer count (invalid as a bench)")
     ap.add_argument("--prompt-len", type=int, default=128)
-    ap.add_argument("--prefill-chunk", type=int, default=128, help="rows per prefill forward (engine max_rows)")
+    ap.add_argument("--prefill-chunk", type=int, default=256, help="rows per prefill forward (engine max_rows)")
     ap.add_argument("--b2-cache", type=int, default=0, help="nccl_cublas arm: keep bf16 copies of the weights (1) or dequantise per call (0)")
     ap.add_argument("--no-pdl", action="store_true")
     ap.add_argument("--no-graphs", action="store_true")
@@ -194,7 +194,7 @@ def run_b200(args):
                    "l2": "inputs larger than L2: every step streams %.0f MB of weights per GPU" % (wbytes / 1e6),
                    "pdl": not args.no_pdl, "cuda_graph": not args.no_graphs},
         "clocks": clocks,
-        "e2e": {"value": round(1000.0 * K_ / e2e_ms, 2), "unit": "tokens/s", "h2d_bytes_per_step": 3 * eng.max_rows * 4,
+        "e2e": {"value": round(1000.0 * K_ / e2e_ms, 2), "unit": "tokens/s", "h2d_bytes_per_step": eng.h_desc.numel() * 4,
                 "d2h_bytes_per_step": eng.max_rows * 4, "ms_per_step": round(e2e_ms / K_, 4)},
         "gpu_launches": launches,
         "roofline": {"weight_bytes_per_gpu_per_step": wbytes, "hbm_gbs_measured": hbm,

@@ -26,7 +26,6 @@
 // Pipelines: raw ring (producer -> dequant), B ring (producer -> MMA), A stages (dequant -> MMA,
 // released by tcgen05.commit), accumulator barrier (MMA -> epilogue).  K can be split over a
 // thread-block cluster (DSMEM reduction) when there are too few row tiles to fill the chip.
-#include <stdlib.h>
 #include "epilogue.cuh"
 
 #define TC_DEQ_WARPS 16
@@ -394,14 +393,11 @@ extern "C" int dl_gemm_q40_tc(const uint8_t* w_q40t, int d, int n, const uint8_t
     if (a.NT <= 64) { a.NSA = 12; a.NSB = 4; }
     else if (a.NT == 128) { a.NSA = 8; a.NSB = 4; }
     else { a.NSA = 8; a.NSB = 2; }
-    if (const char* e = getenv("DL_TC_NSA")) a.NSA = atoi(e);      // tuning override (debug); 4 <= NSA <= 16
     if (a.NSA < TC_GROUPS || a.NSA > 16) { dl_set_error("dl_gemm_q40_tc: bad NSA=%d", a.NSA); return -1; }
     // nacc must divide nstg: then successive phases of an A stage are consumed by the SAME issuing warp (and
     // written after a retire that is ordered behind the previous one), so a parity wait can never be lapped
     a.nacc = (a.NT <= 128) ? 2 : 1;
     a.nstg = (a.NT <= 64) ? 6 : 4;
-    if (const char* e = getenv("DL_TC_NACC")) a.nacc = atoi(e);      // tuning overrides (debug)
-    if (const char* e = getenv("DL_TC_NSTG")) a.nstg = atoi(e);
     if (a.nacc * a.NT + a.nstg * TC_A_STAGE_COLS > TC_TMEM_COLS || a.nstg < TC_GROUPS || a.nstg > 8 || a.nstg % a.nacc != 0 || (a.nacc != 1 && a.nacc != 2 && a.nacc != 4)) {
         dl_set_error("dl_gemm_q40_tc: bad TMEM plan nacc=%d nstg=%d NT=%d", a.nacc, a.nstg, a.NT);
         return -1;

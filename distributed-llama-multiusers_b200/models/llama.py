@@ -116,9 +116,12 @@ class LlamaEngine:
         # ---- activations -----------------------------------------------------------------------
         R = max_rows
         self.ncap = max(16, _round_up(R, 128) if R > 64 else (16 if R <= 16 else 32 if R <= 32 else 64))
-        self.desc = torch.zeros(3, R, dtype=torch.int32, device=dev)      # tokens | pos | slot
-        self.h_desc = torch.zeros(3, R, dtype=torch.int32).pin_memory()
-        self.tokens, self.pos, self.slot = self.desc[0], self.desc[1], self.desc[2]
+        self.desc = torch.zeros(4, R, dtype=torch.int32, device=dev)      # tokens | pos | slot | meta (meta[0] = first chunk row)
+        self.h_desc = torch.zeros(4, R, dtype=torch.int32).pin_memory()
+        self.tokens, self.pos, self.slot, self.meta = self.desc[0], self.desc[1], self.desc[2], self.desc[3]
+        # prompt chunks (>= 16 consecutive positions of one sequence) use the tensor-core prefill attention
+        self.prefill_attention = kv_dtype == torch.float16 and self.hs in (64, 128)
+        self._chunk = False
         self.x = [torch.zeros(R, h.dim, dtype=torch.float32, device=dev) for _ in range(2)]
         self.q = torch.zeros(R, self.q_loc, dtype=torch.float32, device=dev)
         self.xq_dim = K.alloc_xq(h.dim, GEMV_MAX_M, dev)
@@ -283,7 +286,7 @@ class LlamaEngine:
             S = K.choose_tc_split(d, n, M, self.n_sms)
             K.gemm_q40_tc(w, d, n, xh, self.ncap, M, epi, S, pdl=self.use_pdl)
 
-    def _launch_forward(self, M: int, row0: int, greedy: bool, device_loop: bool):
+    def _launch_forward(self, M: int, row0: int, greedy: bool, device_loop: bool, chunk: bool = False):
         """Enqueue one forward over rows 0..M-1 of the descriptor; logits for rows row0..M-1."""
         h, N, pdl = self.h, self.world, self.use_pdl
         gemv = M <= GEMV_MAX_M
@@ -341,9 +344,14 @@ class LlamaEngine:
             epi = K.epi_qkv_rope(self.q, self.q_loc, self.kv_loc, self.hs, self.rope_freqs, self.pos, self.slot,
                                  self.block_table, self.max_pages, self.n_kv_loc, self.k_cache[l], self.v_cache[l])
             norm_then(W["rms_att"], pending, l, W["qkv"], self.qkv_d, EPI_QKV_ROPE, epi)
-            K.attention(self.q, M, self.n_heads_loc, self.n_kv_loc, self.hs, self.k_cache[l], self.v_cache[l], self.pos,
-                        self.slot, self.block_table, self.max_pages, n_splits, self.att_scratch, xq(self.xq_att),
-                        xh(self.xh_att), mcap, pdl=pdl)
+            if chunk:
+                K.attention_prefill(self.q, M, self.n_heads_loc, self.n_kv_loc, self.hs, self.k_cache[l], self.v_cache[l],
+                                    self.pos, self.slot, self.block_table, self.max_pages, self.meta, xq(self.xq_att),
+                                    xh(self.xh_att), mcap, pdl=pdl)
+            else:
+                K.attention(self.q, M, self.n_heads_loc, self.n_kv_loc, self.hs, self.k_cache[l], self.v_cache[l], self.pos,
+                            self.slot, self.block_table, self.max_pages, n_splits, self.att_scratch, xq(self.xq_att),
+                            xh(self.xh_att), mcap, pdl=pdl)
             self._matmul(W["wo"], h.dim, self.q_loc, M, self.xq_att, self.xh_att,
                          push(self.part_att, self.flags_att_peer, l + 1, self.cta_counters[0]), EPI_STORE)
             pending = (self.part_att, self.flags_att_local)
@@ -375,20 +383,21 @@ class LlamaEngine:
         max_by_ctx = max(1, self.max_pages // 4)           # at least 4 pages (128 tokens) per split
         return int(min(want, max_by_ctx, self.max_splits))
 
-    def _run(self, M: int, row0: int, greedy: bool, device_loop: bool = False):
-        key = (M, row0, greedy, device_loop)
+    def _run(self, M: int, row0: int, greedy: bool, device_loop: bool = False, chunk: Optional[bool] = None):
+        chunk = (self._chunk and not device_loop) if chunk is None else chunk
+        key = (M, row0, greedy, device_loop, chunk)
         if not self.use_graphs:
-            self._launch_forward(M, row0, greedy, device_loop)
+            self._launch_forward(M, row0, greedy, device_loop, chunk)
             return
         g = self._graphs.get(key)
         if g is None:
             # warm up once eagerly (sets func attributes, loads modules), then capture
-            self._launch_forward(M, row0, greedy and not device_loop, False)
+            self._launch_forward(M, row0, greedy and not device_loop, False, chunk)
             torch.cuda.synchronize()
             g = torch.cuda.CUDAGraph()
             n0 = K.lib.launch_count
             with torch.cuda.graph(g, stream=self._graph_stream):
-                self._launch_forward(M, row0, greedy, device_loop)
+                self._launch_forward(M, row0, greedy, device_loop, chunk)
             self._graph_launches[key] = K.lib.launch_count - n0
             K.lib.launch_count = n0          # capture enqueued nothing
             self._graphs[key] = g
@@ -423,7 +432,13 @@ class LlamaEngine:
             self.desc.copy_(self.h_desc, non_blocking=True)
             for row0 in sorted({0, Mp - 1}):
                 for greedy in (False, True):
-                    self._run(Mp, row0, greedy)
+                    self._run(Mp, row0, greedy, chunk=False)
+            if self.prefill_attention and Mp >= 16:          # prompt chunks: last-row logits only
+                hd[3, 0] = Mp - 1                            # one real row is enough to run the kernel
+                self.desc.copy_(self.h_desc, non_blocking=True)
+                for greedy in (False, True):
+                    self._run(Mp, Mp - 1, greedy, chunk=True)
+                hd[3, 0] = 0
             if Mp >= self.max_rows:
                 break
             Mp *= 2
@@ -452,6 +467,10 @@ class LlamaEngine:
         hd[0, off:off + M] = tokens
         hd[1, off:off + M] = positions
         hd[2, off:off + M] = slots
+        # one sequence, consecutive positions, enough rows to fill a tensor-core tile -> prefill attention
+        self._chunk = (self.prefill_attention and M >= 16 and all(s == slots[0] for s in slots)
+                       and all(positions[i] == positions[0] + i for i in range(M)))
+        hd[3, 0] = off
         for s, p in zip(slots, positions):
             self.pages.ensure(int(s), int(p) + 1)
         self._sync_block_table()

@@ -193,6 +193,17 @@ def attention(q, M, n_heads, n_kv_heads, head_size, k_cache, v_cache, pos, slot,
     lib.count_launch()
 
 
+def attention_prefill(q, M, n_heads, n_kv_heads, head_size, k_cache, v_cache, pos, slot, block_table, max_pages,
+                      meta, xq_out, xh_out, out_mcap, y_out=None, pdl=False):
+    """Tensor-core causal attention of a prompt chunk: rows [meta[0], M) = consecutive positions of one sequence."""
+    assert k_cache.dtype == torch.float16
+    check(cuda_lib().dl_attention_prefill(q.data_ptr(), M, n_heads, n_kv_heads, head_size, k_cache.data_ptr(),
+                                          v_cache.data_ptr(), pos.data_ptr(), slot.data_ptr(), block_table.data_ptr(),
+                                          max_pages, PAGE_SIZE, meta.data_ptr(), _p(xq_out), _p(xh_out), out_mcap,
+                                          _p(y_out), 1 if pdl else 0, _stream()), "dl_attention_prefill")
+    lib.count_launch()
+
+
 def argmax(logits, M: int, vocab: int, ld: int, out: torch.Tensor, flags=None, n_flags=0, step_counter=None,
            flag_mul=0, flag_add=0, pos_inc=None, history=None, history_cap=0, scratch=None, pdl=False):
     lp = logits.data_ptr() if isinstance(logits, torch.Tensor) else logits

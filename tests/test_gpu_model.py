@@ -59,6 +59,26 @@ def test_tensor_core_path_matches_oracle(tiny_model_path):
     e.close()
 
 
+def test_wide_prefill_chunk_matches_oracle(tiny_model_path):
+    """One 200-row forward: 256-row tcgen05 tiles + the tensor-core prefill attention (3 query tiles, causal
+    inside the chunk), then a second chunk that starts at a non-zero position."""
+    o = _oracle(tiny_model_path)
+    e = _engine(tiny_model_path, max_rows=256, n_slots=2, use_graphs=True, use_pdl=True)
+    rng = np.random.default_rng(5)
+    prompt = rng.integers(1, 1024, 200).tolist()
+    slot = e.alloc_slot()
+    ref = o.forward(prompt, 0).numpy()
+    got = e.forward(prompt, list(range(200)), [slot] * 200, logits_from=0).float().cpu().numpy()
+    for t in (0, 1, 63, 64, 127, 128, 199):
+        assert _rel_err(got[t], ref[t]) < 3e-2, t
+    more = rng.integers(1, 1024, 40).tolist()
+    ref2 = o.forward(more, 200).numpy()
+    got2 = e.forward(more, list(range(200, 240)), [slot] * 40, logits_from=0).float().cpu().numpy()
+    for t in (0, 17, 39):
+        assert _rel_err(got2[t], ref2[t]) < 3e-2, t
+    e.close()
+
+
 def test_multi_user_batch_isolated_kv(tiny_model_path):
     """Three users with different prompts and positions decode in ONE batch; each must equal its
     own single-user run (the reference's shared KV cache / shared position cannot do this)."""
