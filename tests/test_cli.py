@@ -1,0 +1,81 @@
+"""`dllama inference / chat` and the argument parser (reference: src/app.cpp:33-136, src/dllama.cpp): run
+in-process on the CPU engine (and on a GPU with the CUDA engine) with a tiny random model and a
+synthetic tokenizer; the output block must keep the reference's benchmark format."""
+import io
+import os
+import re
+import sys
+from contextlib import redirect_stdout
+
+import pytest
+
+from dllama_b200.cli import dllama as cli
+from dllama_b200.cli.app import AppArgs
+from dllama_b200.formats import tfile
+
+
+@pytest.fixture(scope="module")
+def tok_path(tmp_path_factory):
+    p = str(tmp_path_factory.mktemp("clitok") / "tiny.t")
+    tfile.write_synthetic_tokenizer(p, 1024)
+    return p
+
+
+def _run(argv):
+    buf = io.StringIO()
+    with redirect_stdout(buf):
+        rc = cli.main(argv)
+    return rc, buf.getvalue()
+
+
+def test_arg_parser_accepts_the_reference_flags():
+    a = AppArgs.parse(["dllama", "inference", "--model", "m.m", "--tokenizer", "t.t", "--prompt", "hi", "--steps", "7",
+                       "--buffer-float-type", "q80", "--nthreads", "4", "--max-seq-len", "128", "--temperature", "0.5",
+                       "--topp", "0.8", "--seed", "42", "--workers", "127.0.0.1:9999", "10.0.0.2:9998", "--port", "9990",
+                       "--net-turbo", "0", "--gpu-index", "1", "--gpu-segments", "0:3", "--chat-template", "llama3"], True)
+    assert a.mode == "inference" and a.model_path == "m.m" and a.tokenizer_path == "t.t" and a.steps == 7
+    assert a.max_seq_len == 128 and abs(a.temperature - 0.5) < 1e-6 and abs(a.topp - 0.8) < 1e-6 and a.seed == 42
+    assert len(a.workers) == 2 and a.workers[0] == ("127.0.0.1", 9999) and a.workers[1] == ("10.0.0.2", 9998)
+    assert a.port == 9990 and a.gpu_index == 1
+    with pytest.raises(ValueError):
+        AppArgs.parse(["dllama", "inference", "--no-such-flag", "1"], True)
+
+
+def _check_inference_output(out: str, steps: int):
+    assert re.search(r"Evaluation\n\s+nBatches: \d+\n\s+nTokens: \d+\n\s+tokens/s: [\d.]+", out), out
+    assert re.search(r"Prediction\n\s+nTokens: \d+\n\s+tokens/s: [\d.]+", out), out
+    assert len(re.findall(r"Pred\s+\d+ ms", out)) >= 1
+    assert "Eval" in out
+
+
+def test_inference_on_cpu_engine(tiny_model_path, tok_path):
+    rc, out = _run(["dllama", "inference", "--model", tiny_model_path, "--tokenizer", tok_path, "--buffer-float-type", "q80",
+                    "--prompt", "hello world the of and", "--steps", "12", "--max-seq-len", "128", "--device", "cpu", "--seed", "7"])
+    assert rc == 0, out
+    _check_inference_output(out, 12)
+    rc2, out2 = _run(["dllama", "inference", "--model", tiny_model_path, "--tokenizer", tok_path, "--buffer-float-type", "q80",
+                      "--prompt", "hello world the of and", "--steps", "12", "--max-seq-len", "128", "--device", "cpu", "--seed", "7"])
+    pieces = lambda s: [ln.rsplit("|", 1)[1] for ln in s.splitlines() if "Pred" in ln and "|" in ln]
+    assert pieces(out) and pieces(out) == pieces(out2)    # same seed: same text twice
+
+
+def test_missing_model_is_a_clean_error(tok_path):
+    rc, out = _run(["dllama", "inference", "--model", "/nonexistent.m", "--tokenizer", tok_path, "--prompt", "x", "--steps", "2"])
+    assert rc != 0 and "error" in out.lower()
+
+
+def test_chat_repl_on_cpu_engine(tiny_model_path, tok_path, monkeypatch):
+    monkeypatch.setattr(sys, "stdin", io.StringIO("\nhello world\n"))      # empty system prompt, one user turn, then EOF
+    rc, out = _run(["dllama", "chat", "--model", tiny_model_path, "--tokenizer", tok_path, "--buffer-float-type", "q80",
+                    "--max-seq-len", "96", "--device", "cpu", "--temperature", "0"])
+    assert rc == 0, out
+    assert "Assistant" in out or "🤖" in out
+
+
+@pytest.mark.gpu
+def test_inference_on_gpu_engine_matches_cpu_text(tiny_model_path, tok_path):
+    argv = ["dllama", "inference", "--model", tiny_model_path, "--tokenizer", tok_path, "--buffer-float-type", "q80",
+            "--prompt", "hello world the of and", "--steps", "10", "--max-seq-len", "128", "--temperature", "0"]
+    rc_g, out_g = _run(argv)
+    assert rc_g == 0, out_g
+    _check_inference_output(out_g, 10)
