@@ -29,6 +29,7 @@ struct AttArgs {
     const int* pos;
     const int* slot;
     const int* block_table;
+    const int* row_skip;       // NULL, or row_skip[m] != 0: row m is served by the prefill kernel
     int M, n_heads, n_kv_heads, max_pages, n_splits;
     unsigned* counters;        // scratch: [M][n_kv_heads] at offset 0 (fixed 64 KB region, stays zero)
     float* part_o;             //          [M][n_heads][n_splits][HS]
@@ -89,6 +90,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attention_kernel(const __grid_
     __syncthreads();
     pdl_launch_dependents();
     pdl_wait();     // q, pos, block tables and the KV cache all come from earlier kernels
+    if (a.row_skip != nullptr && a.row_skip[m] != 0) { trace_end(a.tr); return; }      // uniform for the CTA
 
     const int T = a.pos[m] + 1;                                // attend to positions 0..pos
     const int n_pages = (T + ATT_PAGE - 1) / ATT_PAGE;
@@ -328,13 +330,14 @@ extern "C" long long dl_attention_scratch_bytes(int M, int n_heads, int head_siz
 extern "C" int dl_attention(const float* q, int M, int n_heads, int n_kv_heads, int head_size, const void* k_cache,
                             const void* v_cache, int kv_f32, const int* pos, const int* slot, const int* block_table,
                             int max_pages, int page_size, int n_splits, void* scratch, uint8_t* xq_out,
-                            uint8_t* xh_out, int out_mcap, float* y_out, int pdl, void* stream) {
+                            uint8_t* xh_out, int out_mcap, float* y_out, const int* row_skip, int pdl, void* stream) {
     if (page_size != ATT_PAGE) { dl_set_error("dl_attention: page_size must be %d", ATT_PAGE); return -1; }
     if (n_heads % n_kv_heads != 0 || n_heads / n_kv_heads > 16) { dl_set_error("dl_attention: unsupported head grouping %d/%d", n_heads, n_kv_heads); return -1; }
     if (n_splits < 1) n_splits = 1;
     if (n_splits > 1 && scratch == nullptr) { dl_set_error("dl_attention: n_splits>1 needs scratch"); return -1; }
     AttArgs a;
     a.q = q; a.k_cache = k_cache; a.v_cache = v_cache; a.pos = pos; a.slot = slot; a.block_table = block_table;
+    a.row_skip = row_skip;
     a.M = M; a.n_heads = n_heads; a.n_kv_heads = n_kv_heads; a.max_pages = max_pages; a.n_splits = n_splits;
     if ((long long)M * n_kv_heads * 4 > ATT_COUNTER_BYTES) { dl_set_error("dl_attention: M*n_kv_heads too large"); return -1; }
     long long o = ((long long)M * n_heads * n_splits * head_size * 4 + 255) / 256 * 256;

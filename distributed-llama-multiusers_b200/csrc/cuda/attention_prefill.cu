@@ -1,5 +1,6 @@
-// Causal attention for a PROMPT CHUNK: rows [begin, M) of the batch are consecutive positions of ONE
-// sequence (the common prefill case).  The per-row flash-decode kernel (attention.cu) re-reads the
+// Causal attention for PROMPT CHUNKS: segments [begin, end) of batch rows that are consecutive positions
+// of one sequence (up to PF_MAX_SEG segments per batch, listed in device memory; all other rows -- decode
+// rows, short chunks, padding -- are served by the per-row kernel, which skips the segment rows).  The per-row flash-decode kernel (attention.cu) re-reads the
 // whole KV history once per row -- for a 4096-token prompt that is ~1 TB of L2 traffic and 2/3 of the
 // time to first token.  Here a CTA owns a tile of 64 query rows x one query head, streams each KV page
 // of the sequence ONCE per tile through shared memory, and does both products on the tensor cores
@@ -9,8 +10,7 @@
 // Reference semantics: OP_MULTIHEAD_ATT (multiheadAtt_F32, src/nn/nn-cpu-ops.cpp:749-784) over the
 // positions 0..pos of each row, softmax in f32; output cast to Q80 in the XQ / XH slab layout the wo
 // matmul consumes (OP_CAST, src/llm.cpp:296-301).  KV cache: fp16 pages [page][kv_head][32][HS].
-// `meta[0]` (device) holds `begin`: rows below it are padding rows of the serving engine's power-of-two
-// batches; their output is written as zeros.
+// `meta` (device): meta[0] = number of segments, then (begin, end) pairs.
 #include <math.h>
 #include <mma.h>
 #include "epilogue.cuh"
@@ -20,6 +20,7 @@
 #define PF_THREADS (PF_WARPS * 32)
 #define PF_PAGE 32
 #define PF_STAGES 2
+#define PF_MAX_SEG 8
 
 struct PfArgs {
     const float* q;            // [M][n_heads*HS]
@@ -28,7 +29,7 @@ struct PfArgs {
     const int* pos;
     const int* slot;
     const int* block_table;
-    const int* meta;           // meta[0] = first chunk row
+    const int* meta;           // meta[0] = n_seg, meta[1+2i], meta[2+2i] = [begin, end) of segment i
     int M, n_heads, n_kv_heads, max_pages;
     uint8_t* xq_out;
     uint8_t* xh_out;
@@ -78,23 +79,27 @@ __global__ void __launch_bounds__(PF_THREADS) attention_prefill_kernel(const __g
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int g = lane >> 2, tig = lane & 3;
-    const int head = blockIdx.y, tile = blockIdx.x;
+    const int head = blockIdx.y;
     const int G = a.n_heads / a.n_kv_heads;
     const int kvh = head / G;
     pdl_launch_dependents();
     pdl_wait();                                                            // q, the KV rows of this chunk and meta come from earlier kernels
-    const int begin = a.meta[0];
-    const int n_rows = a.M - begin;
-    const int r_first = tile * PF_QTILE;                                   // chunk-relative first row of this tile
-
-    // padding rows of this tile's index range: zero output (keeps the slabs finite)
-    for (int r = tile * PF_QTILE + warp; r < min(begin, (tile + 1) * PF_QTILE); r += PF_WARPS) {
-        for (int b = 0; b < HS / 32; b++) {
-            q80_block_store(0.0f, lane, r, (head * HS) / 32 + b, a.out_mcap, a.xq_out, a.xh_out);
-            if (a.y_out != nullptr) a.y_out[(size_t)r * a.n_heads * HS + head * HS + b * 32 + lane] = 0.0f;
+    // which (segment, 64-row tile) is this CTA?
+    int tile = blockIdx.x, begin = 0, end = 0;
+    {
+        const int n_seg = min(a.meta[0], PF_MAX_SEG);
+        int i = 0;
+        for (; i < n_seg; i++) {
+            begin = a.meta[1 + 2 * i];
+            end = a.meta[2 + 2 * i];
+            const int nt = (end - begin + PF_QTILE - 1) / PF_QTILE;
+            if (tile < nt) break;
+            tile -= nt;
         }
+        if (i == n_seg) { trace_end(a.tr); return; }
     }
-    if (r_first >= n_rows) { trace_end(a.tr); return; }
+    const int n_rows = end - begin;
+    const int r_first = tile * PF_QTILE;                                   // chunk-relative first row of this tile
 
     const int p0 = a.pos[begin];
     const int slot = a.slot[begin];
@@ -268,7 +273,7 @@ static int launch_pf(const PfArgs& a, int pdl, cudaStream_t stream) {
         set = true;
     }
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((unsigned)((a.M + PF_QTILE - 1) / PF_QTILE), (unsigned)a.n_heads);
+    cfg.gridDim = dim3((unsigned)((a.M + PF_QTILE - 1) / PF_QTILE + PF_MAX_SEG), (unsigned)a.n_heads);      // upper bound of the tiles of all segments
     cfg.blockDim = dim3(PF_THREADS);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = stream;

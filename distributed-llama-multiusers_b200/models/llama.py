@@ -31,6 +31,7 @@ from ..parallel.symm import SymmetricBuffer, validate_tp
 from .oracle import rope_frequencies
 
 GEMV_MAX_M = 8
+PREFILL_MAX_SEG = 8          # prompt-chunk segments per batch (attention_prefill.cu: PF_MAX_SEG)
 PAGE = K.PAGE_SIZE
 
 
@@ -116,10 +117,13 @@ class LlamaEngine:
         # ---- activations -----------------------------------------------------------------------
         R = max_rows
         self.ncap = max(16, _round_up(R, 128) if R > 64 else (16 if R <= 16 else 32 if R <= 32 else 64))
-        self.desc = torch.zeros(4, R, dtype=torch.int32, device=dev)      # tokens | pos | slot | meta (meta[0] = first chunk row)
-        self.h_desc = torch.zeros(4, R, dtype=torch.int32).pin_memory()
-        self.tokens, self.pos, self.slot, self.meta = self.desc[0], self.desc[1], self.desc[2], self.desc[3]
-        # prompt chunks (>= 16 consecutive positions of one sequence) use the tensor-core prefill attention
+        # batch descriptor: tokens | pos | slot | row_skip | meta.  Runs of >= 16 consecutive positions of one
+        # sequence (prompt chunks) are listed in meta = [n_seg, begin0, end0, ...] and served by the tensor-core
+        # prefill attention; row_skip marks their rows for the per-row kernel, which serves everything else.
+        DW = max(R, 2 * PREFILL_MAX_SEG + 1)
+        self.desc = torch.zeros(5, DW, dtype=torch.int32, device=dev)
+        self.h_desc = torch.zeros(5, DW, dtype=torch.int32).pin_memory()
+        self.tokens, self.pos, self.slot, self.row_skip, self.meta = (self.desc[i] for i in range(5))
         self.prefill_attention = kv_dtype == torch.float16 and self.hs in (64, 128)
         self._chunk = False
         self.x = [torch.zeros(R, h.dim, dtype=torch.float32, device=dev) for _ in range(2)]
@@ -344,14 +348,13 @@ class LlamaEngine:
             epi = K.epi_qkv_rope(self.q, self.q_loc, self.kv_loc, self.hs, self.rope_freqs, self.pos, self.slot,
                                  self.block_table, self.max_pages, self.n_kv_loc, self.k_cache[l], self.v_cache[l])
             norm_then(W["rms_att"], pending, l, W["qkv"], self.qkv_d, EPI_QKV_ROPE, epi)
-            if chunk:
+            K.attention(self.q, M, self.n_heads_loc, self.n_kv_loc, self.hs, self.k_cache[l], self.v_cache[l], self.pos,
+                        self.slot, self.block_table, self.max_pages, n_splits, self.att_scratch, xq(self.xq_att),
+                        xh(self.xh_att), mcap, pdl=pdl, row_skip=self.row_skip if chunk else None)
+            if chunk:        # prompt-chunk rows (skipped above) on the tensor cores
                 K.attention_prefill(self.q, M, self.n_heads_loc, self.n_kv_loc, self.hs, self.k_cache[l], self.v_cache[l],
                                     self.pos, self.slot, self.block_table, self.max_pages, self.meta, xq(self.xq_att),
                                     xh(self.xh_att), mcap, pdl=pdl)
-            else:
-                K.attention(self.q, M, self.n_heads_loc, self.n_kv_loc, self.hs, self.k_cache[l], self.v_cache[l], self.pos,
-                            self.slot, self.block_table, self.max_pages, n_splits, self.att_scratch, xq(self.xq_att),
-                            xh(self.xh_att), mcap, pdl=pdl)
             self._matmul(W["wo"], h.dim, self.q_loc, M, self.xq_att, self.xh_att,
                          push(self.part_att, self.flags_att_peer, l + 1, self.cta_counters[0]), EPI_STORE)
             pending = (self.part_att, self.flags_att_local)
@@ -433,12 +436,13 @@ class LlamaEngine:
             for row0 in sorted({0, Mp - 1}):
                 for greedy in (False, True):
                     self._run(Mp, row0, greedy, chunk=False)
-            if self.prefill_attention and Mp >= 16:          # prompt chunks: last-row logits only
-                hd[3, 0] = Mp - 1                            # one real row is enough to run the kernel
+            if self.prefill_attention and Mp >= 16:          # batches that contain prompt chunks
+                hd[3, :Mp] = 0
+                hd[4, 0] = 0                                 # no segment: both kernels run, the prefill one exits at once
                 self.desc.copy_(self.h_desc, non_blocking=True)
-                for greedy in (False, True):
-                    self._run(Mp, Mp - 1, greedy, chunk=True)
-                hd[3, 0] = 0
+                for row0 in sorted({0, Mp - 1}):
+                    for greedy in (False, True):
+                        self._run(Mp, row0, greedy, chunk=True)
             if Mp >= self.max_rows:
                 break
             Mp *= 2
@@ -467,10 +471,25 @@ class LlamaEngine:
         hd[0, off:off + M] = tokens
         hd[1, off:off + M] = positions
         hd[2, off:off + M] = slots
-        # one sequence, consecutive positions, enough rows to fill a tensor-core tile -> prefill attention
-        self._chunk = (self.prefill_attention and M >= 16 and all(s == slots[0] for s in slots)
-                       and all(positions[i] == positions[0] + i for i in range(M)))
-        hd[3, 0] = off
+        # prompt chunks: maximal runs of consecutive positions of one sequence, >= 16 rows
+        segs = []
+        if self.prefill_attention and M >= 16:
+            i = 0
+            while i < M:
+                j = i + 1
+                while j < M and slots[j] == slots[i] and positions[j] == positions[j - 1] + 1:
+                    j += 1
+                if j - i >= 16 and len(segs) < PREFILL_MAX_SEG:
+                    segs.append((off + i, off + j))
+                i = j
+        self._chunk = bool(segs)
+        if segs:
+            hd[3, :off + M] = 0
+            hd[4, 0] = len(segs)
+            for k, (b, e) in enumerate(segs):
+                hd[3, b:e] = 1
+                hd[4, 1 + 2 * k] = b
+                hd[4, 2 + 2 * k] = e
         for s, p in zip(slots, positions):
             self.pages.ensure(int(s), int(p) + 1)
         self._sync_block_table()

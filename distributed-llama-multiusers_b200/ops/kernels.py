@@ -184,18 +184,19 @@ def attention_scratch_bytes(M: int, n_heads: int, head_size: int, max_splits: in
 
 
 def attention(q, M, n_heads, n_kv_heads, head_size, k_cache, v_cache, pos, slot, block_table, max_pages,
-              n_splits, scratch, xq_out, xh_out, out_mcap, y_out=None, pdl=False):
+              n_splits, scratch, xq_out, xh_out, out_mcap, y_out=None, pdl=False, row_skip=None):
     check(cuda_lib().dl_attention(q.data_ptr(), M, n_heads, n_kv_heads, head_size, k_cache.data_ptr(),
                                   v_cache.data_ptr(), 1 if k_cache.dtype == torch.float32 else 0,
                                   pos.data_ptr(), slot.data_ptr(), block_table.data_ptr(), max_pages, PAGE_SIZE,
-                                  n_splits, _p(scratch), _p(xq_out), _p(xh_out), out_mcap, _p(y_out),
+                                  n_splits, _p(scratch), _p(xq_out), _p(xh_out), out_mcap, _p(y_out), _p(row_skip),
                                   1 if pdl else 0, _stream()), "dl_attention")
     lib.count_launch()
 
 
 def attention_prefill(q, M, n_heads, n_kv_heads, head_size, k_cache, v_cache, pos, slot, block_table, max_pages,
                       meta, xq_out, xh_out, out_mcap, y_out=None, pdl=False):
-    """Tensor-core causal attention of a prompt chunk: rows [meta[0], M) = consecutive positions of one sequence."""
+    """Tensor-core causal attention of prompt chunks: meta = [n_seg, begin0, end0, ...] (device int32), each
+    range being consecutive positions of one sequence."""
     assert k_cache.dtype == torch.float16
     check(cuda_lib().dl_attention_prefill(q.data_ptr(), M, n_heads, n_kv_heads, head_size, k_cache.data_ptr(),
                                           v_cache.data_ptr(), pos.data_ptr(), slot.data_ptr(), block_table.data_ptr(),

@@ -135,11 +135,13 @@ long long dl_attention_scratch_bytes(int M, int n_heads, int head_size, int max_
 int dl_attention(const float* q, int M, int n_heads, int n_kv_heads, int head_size, const void* k_cache,
                  const void* v_cache, int kv_f32, const int* pos, const int* slot, const int* block_table,
                  int max_pages, int page_size, int n_splits, void* scratch, uint8_t* xq_out, uint8_t* xh_out,
-                 int out_mcap, float* y_out, int pdl, void* stream);
+                 int out_mcap, float* y_out, const int* row_skip /*device, NULL or [M]: non-zero rows are left to
+                 dl_attention_prefill*/, int pdl, void* stream);
 
-/* causal attention of a prompt chunk on the tensor cores (mma.sync fp16, f32 accumulate): rows [meta[0], M) are
- * consecutive positions of ONE sequence (slot[meta[0]], first position pos[meta[0]]); rows below meta[0] are padding
- * and get a zero output.  fp16 KV cache, head_size 64 or 128.  Same outputs as dl_attention. */
+/* causal attention of prompt chunks on the tensor cores (mma.sync fp16, f32 accumulate).  meta (device):
+ * meta[0] = n_seg (<= 8), then [begin, end) row ranges; each range is consecutive positions of ONE sequence
+ * (slot[begin], first position pos[begin]).  Rows outside the ranges are not touched (dl_attention with row_skip
+ * serves them).  fp16 KV cache, head_size 64 or 128.  Same outputs as dl_attention. */
 int dl_attention_prefill(const float* q, int M, int n_heads, int n_kv_heads, int head_size, const void* k_cache,
                          const void* v_cache, const int* pos, const int* slot, const int* block_table, int max_pages,
                          int page_size, const int* meta /*device*/, uint8_t* xq_out, uint8_t* xh_out, int out_mcap,

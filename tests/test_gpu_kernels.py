@@ -288,52 +288,62 @@ def test_attention_matches_reference(n_heads, n_kv, hs, positions, n_splits, kv_
         np.testing.assert_allclose(dq, quant.q80_roundtrip(got), rtol=0, atol=np.abs(got).max() / 127 * 1.01)
 
 
-@pytest.mark.parametrize("n_heads,n_kv,hs,p0,n_rows,begin", [
-    (4, 1, 128, 0, 16, 0), (8, 2, 128, 37, 100, 0), (4, 4, 64, 5, 70, 3), (2, 1, 128, 200, 130, 62), (2, 2, 64, 31, 33, 31),
+@pytest.mark.parametrize("n_heads,n_kv,hs,segs", [
+    (4, 1, 128, [(0, 0, 16)]), (8, 2, 128, [(0, 37, 100)]), (4, 4, 64, [(3, 5, 70)]), (2, 1, 128, [(62, 200, 130)]),
+    (2, 2, 64, [(31, 31, 33)]), (4, 2, 128, [(2, 10, 40), (45, 0, 90)]),
 ])
-def test_attention_prefill_matches_reference(n_heads, n_kv, hs, p0, n_rows, begin):
-    """Tensor-core prompt-chunk attention: rows [begin, M) are positions p0.. of one sequence (slot 1); rows
-    below `begin` are padding (zero output).  Compared with the f64 reference and with the per-row kernel."""
+def test_attention_prefill_matches_reference(n_heads, n_kv, hs, segs):
+    """Tensor-core prompt-chunk attention.  segs = [(first row, first position, rows)]: every segment is a run of
+    consecutive positions of its own sequence; rows outside the segments must not be touched (the per-row kernel
+    serves them).  Compared with the f64 reference."""
     k = K()
-    M = begin + n_rows
-    last = p0 + n_rows - 1
-    max_pages = last // 32 + 2
-    n_slots = 2
-    rng = np.random.default_rng(p0 + n_rows)
+    M = max(b + n for b, _, n in segs) + 2
+    max_pages = max(p0 + n for _, p0, n in segs) // 32 + 2
+    n_slots = len(segs)
+    rng = np.random.default_rng(M)
     q = rng.standard_normal((M, n_heads * hs), dtype=np.float32)
-    kc = rng.standard_normal((max_pages * 32, n_kv, hs), dtype=np.float32)
-    vc = rng.standard_normal((max_pages * 32, n_kv, hs), dtype=np.float32)
     bt = rng.permutation(n_slots * max_pages).astype(np.int32).reshape(n_slots, max_pages)
     Kc = torch.zeros(n_slots * max_pages, n_kv, 32, hs, dtype=torch.float16)
     Vc = torch.zeros_like(Kc)
-    for p in range(max_pages):
-        Kc[bt[1, p]] = torch.from_numpy(kc[p * 32:(p + 1) * 32].transpose(1, 0, 2).copy()).half()
-        Vc[bt[1, p]] = torch.from_numpy(vc[p * 32:(p + 1) * 32].transpose(1, 0, 2).copy()).half()
-    kc_r = Kc[torch.from_numpy(bt[1].astype(np.int64))].float().numpy().transpose(0, 2, 1, 3).reshape(-1, n_kv, hs)
-    vc_r = Vc[torch.from_numpy(bt[1].astype(np.int64))].float().numpy().transpose(0, 2, 1, 3).reshape(-1, n_kv, hs)
-    pg, off = divmod(last + 1, 32)                       # poison what lies after the last position
-    if off:
-        Kc[bt[1, pg], :, off:] = float("nan")
-        Vc[bt[1, pg], :, off:] = float("inf")
+    kc_r, vc_r = [], []
+    for s_i, (b, p0, n) in enumerate(segs):
+        kc = rng.standard_normal((max_pages * 32, n_kv, hs), dtype=np.float32)
+        vc = rng.standard_normal((max_pages * 32, n_kv, hs), dtype=np.float32)
+        for p in range(max_pages):
+            Kc[bt[s_i, p]] = torch.from_numpy(kc[p * 32:(p + 1) * 32].transpose(1, 0, 2).copy()).half()
+            Vc[bt[s_i, p]] = torch.from_numpy(vc[p * 32:(p + 1) * 32].transpose(1, 0, 2).copy()).half()
+        idx = torch.from_numpy(bt[s_i].astype(np.int64))
+        kc_r.append(Kc[idx].float().numpy().transpose(0, 2, 1, 3).reshape(-1, n_kv, hs))
+        vc_r.append(Vc[idx].float().numpy().transpose(0, 2, 1, 3).reshape(-1, n_kv, hs))
+        pg, off = divmod(p0 + n, 32)                     # poison what lies after the last position
+        if off:
+            Kc[bt[s_i, pg], :, off:] = float("nan")
+            Vc[bt[s_i, pg], :, off:] = float("inf")
     Kc, Vc = Kc.cuda(), Vc.cuda()
-    positions = [0] * begin + [p0 + i for i in range(n_rows)]
-    slots = [0] * begin + [1] * n_rows
+    positions, slots, meta = [0] * M, [0] * M, [len(segs)]
+    for s_i, (b, p0, n) in enumerate(segs):
+        for i in range(n):
+            positions[b + i], slots[b + i] = p0 + i, s_i
+        meta += [b, b + n]
     pos_t = torch.tensor(positions, dtype=torch.int32, device="cuda")
     slot_t = torch.tensor(slots, dtype=torch.int32, device="cuda")
-    meta = torch.tensor([begin, 0, 0, 0], dtype=torch.int32, device="cuda")
+    meta_t = torch.tensor(meta + [0] * 8, dtype=torch.int32, device="cuda")
     bt_t = torch.from_numpy(bt).cuda()
     y = torch.full((M, n_heads * hs), float("nan"), device="cuda")
     ncap = (M + 127) // 128 * 128
     xh = k.alloc_xh(n_heads * hs, ncap, "cuda") if (n_heads * hs) % 128 == 0 else None
-    k.attention_prefill(torch.from_numpy(q).cuda(), M, n_heads, n_kv, hs, Kc, Vc, pos_t, slot_t, bt_t, max_pages, meta,
+    k.attention_prefill(torch.from_numpy(q).cuda(), M, n_heads, n_kv, hs, Kc, Vc, pos_t, slot_t, bt_t, max_pages, meta_t,
                         None, xh, ncap, y)
     torch.cuda.synchronize()
     got = y.cpu().numpy()
-    assert not np.isnan(got).any()
-    assert (got[:begin] == 0).all()
-    ref = _attention_ref(q[begin:], [kc_r] * n_rows, [vc_r] * n_rows, positions[begin:], n_heads, n_kv, hs)
-    # fp16 Q / P operands: ~1e-3 relative
-    np.testing.assert_allclose(got[begin:], ref, rtol=0, atol=4e-3 * max(1.0, np.abs(ref).max()))
+    covered = np.zeros(M, dtype=bool)
+    for s_i, (b, p0, n) in enumerate(segs):
+        covered[b:b + n] = True
+        ref = _attention_ref(q[b:b + n], [kc_r[s_i]] * n, [vc_r[s_i]] * n, positions[b:b + n], n_heads, n_kv, hs)
+        assert not np.isnan(got[b:b + n]).any()
+        # fp16 Q / P operands: ~1e-3 relative
+        np.testing.assert_allclose(got[b:b + n], ref, rtol=0, atol=4e-3 * max(1.0, np.abs(ref).max()))
+    assert np.isnan(got[~covered]).all()                 # rows outside the segments are left alone
 
 
 def test_qkv_rope_epilogue_and_kv_write():

@@ -79,6 +79,32 @@ def test_wide_prefill_chunk_matches_oracle(tiny_model_path):
     e.close()
 
 
+def test_prompt_chunk_mixed_with_decode_rows(tiny_model_path):
+    """A batch holding a 40-row prompt chunk of one sequence plus decode rows of two others: the chunk goes
+    through the tensor-core prefill attention, the other rows through the per-row kernel (row_skip)."""
+    e = _engine(tiny_model_path, max_rows=64, n_slots=4, use_graphs=True, use_pdl=True)
+    rng = np.random.default_rng(9)
+    pa, pb = rng.integers(1, 1024, 7).tolist(), rng.integers(1, 1024, 3).tolist()
+    chunk = rng.integers(1, 1024, 40).tolist()
+    sa, sb, sc = e.alloc_slot(), e.alloc_slot(), e.alloc_slot()
+    e.prefill(sa, pa, 0)
+    e.prefill(sb, pb, 0)
+    toks = chunk + [11, 12]
+    pos = list(range(40)) + [7, 3]
+    slots = [sc] * 40 + [sa, sb]
+    got = e.forward(toks, pos, slots, logits_from=39).float().cpu().numpy().copy()      # rows 39 (chunk end), 40, 41
+    oc = _oracle(tiny_model_path)
+    ref_c = oc.forward(chunk, 0).numpy()[-1]
+    oa = _oracle(tiny_model_path)
+    oa.forward(pa, 0)
+    ref_a = oa.forward([11], 7).numpy()[0]
+    ob = _oracle(tiny_model_path)
+    ob.forward(pb, 0)
+    ref_b = ob.forward([12], 3).numpy()[0]
+    assert _rel_err(got[0], ref_c) < 3e-2 and _rel_err(got[1], ref_a) < 3e-2 and _rel_err(got[2], ref_b) < 3e-2
+    e.close()
+
+
 def test_multi_user_batch_isolated_kv(tiny_model_path):
     """Three users with different prompts and positions decode in ONE batch; each must equal its
     own single-user run (the reference's shared KV cache / shared position cannot do this)."""
