@@ -19,7 +19,7 @@
 #define PF_WARPS 4
 #define PF_THREADS (PF_WARPS * 32)
 #define PF_PAGE 32
-#define PF_STAGES 2
+#define PF_STAGES 2            // KV pages in flight (4 measured slower: 255 -> 283 ms on a 4096-token prompt)
 #define PF_MAX_SEG 8
 
 struct PfArgs {
@@ -148,10 +148,15 @@ __global__ void __launch_bounds__(PF_THREADS) attention_prefill_kernel(const __g
         cp_async_commit();
     };
 
-    load_page(0, 0);
+    // PF_STAGES-1 pages ahead; an empty commit keeps one cp.async group per iteration so that
+    // wait_group<PF_STAGES-1> always means "page j has landed"
+    for (int j = 0; j < PF_STAGES - 1; j++) {
+        if (j < n_pages) load_page(j, j); else cp_async_commit();
+    }
     for (int j = 0; j < n_pages; j++) {
-        const int st = j & 1;
-        if (j + 1 < n_pages) { load_page(j + 1, st ^ 1); cp_async_wait<1>(); } else { cp_async_wait<0>(); }
+        const int st = j % PF_STAGES;
+        if (j + PF_STAGES - 1 < n_pages) load_page(j + PF_STAGES - 1, (j + PF_STAGES - 1) % PF_STAGES); else cp_async_commit();
+        cp_async_wait<PF_STAGES - 1>();
         __syncthreads();
         const __half* kp = ks + st * PAGE_H;
         const __half* vp = vs + st * PAGE_H;

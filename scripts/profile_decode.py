@@ -23,6 +23,7 @@ def main():
     ap.add_argument("--users", type=int, default=1)
     ap.add_argument("--ctx", type=int, default=128)
     ap.add_argument("--pdl", type=int, default=0)
+    ap.add_argument("--prefill", type=int, default=0, help="profile one prefill forward of this many rows instead of decode steps")
     ap.add_argument("--model-dir", default="/dev/shm")
     a = ap.parse_args()
     from dllama_b200.formats import mfile
@@ -32,7 +33,7 @@ def main():
     if not os.path.exists(path):
         mfile.write_random_model(path, a.model, quant.Q40, seed=1, n_layers=a.layers)
     U = a.users
-    eng = LlamaEngine(path, max_rows=max(8, U), n_slots=U + 1, max_seq_len=a.ctx + 64, use_graphs=False,
+    eng = LlamaEngine(path, max_rows=max(8, U, a.prefill), n_slots=U + 2, max_seq_len=a.ctx + 64, use_graphs=False,
                       use_pdl=bool(a.pdl))
     slots = [eng.alloc_slot() for _ in range(U)]
     toks = [5 + u for u in range(U)]
@@ -44,6 +45,20 @@ def main():
     for _ in range(2):
         eng.decode_greedy_device(1, U)
     torch.cuda.synchronize()
+    if a.prefill:
+        ps = eng.alloc_slot()
+        prompt = [7 + (i % 1000) for i in range(a.prefill)]
+        eng.prefill(ps, prompt, 0)                   # warm-up (same shapes)
+        eng.free_slot(ps)
+        ps = eng.alloc_slot()
+        torch.cuda.synchronize()
+        torch.cuda.profiler.start()
+        eng.prefill(ps, prompt, 0)
+        torch.cuda.synchronize()
+        torch.cuda.profiler.stop()
+        print("profile target done")
+        eng.close()
+        return
     torch.cuda.profiler.start()
     eng.decode_greedy_device(a.steps, U)
     torch.cuda.synchronize()
