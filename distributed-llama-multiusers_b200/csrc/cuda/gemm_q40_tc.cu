@@ -367,6 +367,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_q40_tc_kernel(const __grid
 }
 
 extern void dl_set_error(const char* fmt, ...);
+extern "C" int dl_device_sm_count();
 
 static long long* g_tc_dbg = nullptr;
 static int g_tc_dbg_mode = 0;
@@ -384,7 +385,10 @@ extern "C" int dl_gemm_q40_tc(const uint8_t* w_q40t, int d, int n, const uint8_t
     a.d_pad = (d + 127) / 128 * 128;
     a.KT = n / Q40T_TILE_K;
     a.ncap = ncap; a.M = M;
-    a.NT = (M <= 16) ? 16 : (M <= 32) ? 32 : (M <= 64) ? 64 : (M <= 128 || ncap % 256 != 0) ? 128 : 256;
+    a.NT = (M <= 16) ? 16 : (M <= 32) ? 32 : (M <= 64) ? 64 : 128;
+    // 256-wide tiles halve the dequant work per activation row, but only pay when they still leave enough CTAs
+    // to fill the chip (w13: 224 row tiles); narrow matrices (qkv / wo / w2: 32-48 row tiles) keep 128
+    if (M > 128 && ncap % 256 == 0 && ((d + 127) / 128) * ((M + 255) / 256) >= dl_device_sm_count() / 2) a.NT = 256;
     if (ncap < (M + a.NT - 1) / a.NT * a.NT) { dl_set_error("dl_gemm_q40_tc: ncap=%d too small for M=%d (tile %d)", ncap, M, a.NT); return -1; }
     if (k_split != 1 && k_split != 2 && k_split != 4 && k_split != 8) { dl_set_error("dl_gemm_q40_tc: k_split must be 1,2,4,8"); return -1; }
     if (k_split > a.KT) k_split = 1;
