@@ -386,9 +386,14 @@ extern "C" int dl_gemm_q40_tc(const uint8_t* w_q40t, int d, int n, const uint8_t
     a.KT = n / Q40T_TILE_K;
     a.ncap = ncap; a.M = M;
     a.NT = (M <= 16) ? 16 : (M <= 32) ? 32 : (M <= 64) ? 64 : 128;
+    const int row_tiles = (d + 127) / 128, n_sms = dl_device_sm_count();
+    const int ks = (k_split == 2 || k_split == 4 || k_split == 8) ? k_split : 1;
     // 256-wide tiles halve the dequant work per activation row, but only pay when they still leave enough CTAs
-    // to fill the chip (w13: 224 row tiles); narrow matrices (qkv / wo / w2: 32-48 row tiles) keep 128
-    if (M > 128 && ncap % 256 == 0 && ((d + 127) / 128) * ((M + 255) / 256) >= dl_device_sm_count() / 2) a.NT = 256;
+    // to fill the chip (w13: 224 row tiles) ...
+    if (M > 128 && ncap % 256 == 0 && row_tiles * ((M + 255) / 256) * ks >= n_sms / 2) a.NT = 256;
+    // ... and narrow matrices (qkv / wo: 32-48 row tiles) are better off with narrower tiles that launch more
+    // CTAs, even though every CTA then unpacks the weight tile again (the unpack overlaps the MMAs)
+    while (a.NT > 32 && row_tiles * ((M + a.NT - 1) / a.NT) * ks < n_sms / 2) a.NT >>= 1;
     if (ncap < (M + a.NT - 1) / a.NT * a.NT) { dl_set_error("dl_gemm_q40_tc: ncap=%d too small for M=%d (tile %d)", ncap, M, a.NT); return -1; }
     if (k_split != 1 && k_split != 2 && k_split != 4 && k_split != 8) { dl_set_error("dl_gemm_q40_tc: k_split must be 1,2,4,8"); return -1; }
     if (k_split > a.KT) k_split = 1;
