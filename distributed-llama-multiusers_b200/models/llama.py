@@ -171,6 +171,19 @@ class LlamaEngine:
         self.n_slots = n_slots
         n_slots = n_slots + (1 if bucket_rows else 0)
         self.n_pages = (n_pages or self.n_slots * self.max_pages) + (1 if bucket_rows else 0)
+        # the page pool is shared by all sequences and grows on demand, so it does not have to cover
+        # n_slots x max_seq_len (Llama-3.1 headers say 131072): cap it at 85 % of the free HBM
+        page_bytes = 2 * h.n_layers * self.n_kv_loc * PAGE * self.hs * torch.empty((), dtype=kv_dtype).element_size()
+        if n_pages is None and dev.type == "cuda":
+            free_b, _ = torch.cuda.mem_get_info(dev)
+            fit = int(0.85 * free_b) // page_bytes
+            if fit < self.n_pages:
+                if fit < self.max_pages + 1:
+                    raise RuntimeError(f"KV cache: not even one full sequence of {self.seq_len} tokens fits in "
+                                       f"{free_b >> 20} MiB of free device memory; lower --max-seq-len")
+                print(f"💡 KV page pool capped at {fit} pages ({fit * page_bytes >> 20} MiB) instead of "
+                      f"{self.n_pages} (n_slots x max_seq_len); sequences share it on demand", flush=True)
+                self.n_pages = fit
         self.pages = PageAllocator(self.n_pages, n_slots, self.max_pages)
         self.block_table = torch.zeros(n_slots, self.max_pages, dtype=torch.int32, device=dev)
         self.h_block_table = torch.zeros(n_slots, self.max_pages, dtype=torch.int32).pin_memory()

@@ -134,8 +134,13 @@ def make_handler(state: ApiState):
                     self._stream(cid, req)
                 else:
                     text = req.result()
-                    usage = A.chat_usage(len(req.prompt_tokens), len(req.tokens))
-                    self._json(200, A.chat_completion(cid, state.model_name, text, req.finish_reason or "stop", usage))
+                    if req.finish_reason == "error":
+                        with state.lock:
+                            state.n_errors += 1
+                        self._json(500, {"error": {"message": req.error or "generation failed", "type": "server_error"}})
+                    else:
+                        usage = A.chat_usage(len(req.prompt_tokens), len(req.tokens))
+                        self._json(200, A.chat_completion(cid, state.model_name, text, req.finish_reason or "stop", usage))
             except (BrokenPipeError, ConnectionResetError):
                 state.batch.cancel(req)         # client went away: free its slot
             print(f"🔶 id={req.id} tokens={len(req.tokens)} finish={req.finish_reason}", flush=True)

@@ -38,6 +38,7 @@ class GenerationRequest:
     text: str = ""
     tokens: List[int] = field(default_factory=list)
     finish_reason: Optional[str] = None
+    error: Optional[str] = None                 # set when finish_reason == "error"
     t_submit: float = 0.0
     t_first_token: Optional[float] = None
     t_done: Optional[float] = None
@@ -69,6 +70,8 @@ class BatchEngine:
         self.n_steps = 0
         self.n_generated = 0
         self.n_rows = 0
+        self.n_errors = 0
+        self._last_ids, self._last_sampling = [], []
         # seconds spent forming batches / in the engine (incl. sampling) / detokenising + bookkeeping
         self.t_sched = self.t_engine = self.t_emit = 0.0
         eos_pieces = [tokenizer.piece(t).decode("utf-8", "replace") for t in tokenizer.eos_token_ids]
@@ -141,7 +144,12 @@ class BatchEngine:
         while not self._stop.is_set():
             if not self.sched.wait(20):
                 continue
-            self.step()
+            try:
+                self.step()
+            except Exception as e:                      # one bad batch must not take the server down
+                self.n_errors += 1
+                print(f"🚨 engine step failed: {type(e).__name__}: {e}", flush=True)
+                self._fail_batch(e)
 
     def step(self) -> int:
         """One scheduler step = one forward pass.  Returns the number of rows run."""
@@ -150,6 +158,7 @@ class BatchEngine:
         released = self.sched.pop_released()
         for s in released:
             self.engine.pages.release_pages(s)
+        self._last_ids, self._last_sampling = ids, sampling
         if not ids:
             self._finish_cancelled()
             return 0
@@ -239,6 +248,28 @@ class BatchEngine:
         with self._lock:
             self.reqs.pop(r.id, None)
         self.sched.forget(r.id)
+
+    def _fail_batch(self, exc: Exception):
+        """A forward raised (e.g. the KV page pool is exhausted): the scheduler has already advanced the
+        requests of that batch, so they cannot be retried -- end them with finish_reason "error", give their
+        slots and pages back, keep serving everybody else (reference: the API loop swallows per-request
+        exceptions, src/dllama-api.cpp:362-364)."""
+        ids = list(dict.fromkeys(self._last_ids))
+        n_s = len(self._last_sampling)
+        if n_s:
+            try:
+                self.sched.commit([0] * n_s, [True] * n_s)          # finishes the sampling rows' requests
+            except Exception:
+                pass
+        for rid in ids:
+            self.sched.cancel(rid)
+            with self._lock:
+                r = self.reqs.get(rid)
+            if r is not None:
+                r.error = f"{type(exc).__name__}: {exc}"
+                self._finalize(r, "error")
+        for s in self.sched.pop_released():
+            self.engine.pages.release_pages(s)
 
     def _finish_cancelled(self):
         with self._lock:

@@ -123,6 +123,36 @@ def test_stop_string_truncates_output(tiny_model_path, tok):
     assert got == full[:full.index(stop)] and r.finish_reason == "stop"
 
 
+def test_engine_failure_ends_the_batch_but_not_the_server(tiny_model_path, tok):
+    """A forward that raises (KV pool exhausted, CUDA error...) ends the requests of that batch with
+    finish_reason "error"; the engine thread survives and serves the next request."""
+    eng = CpuEngine(tiny_model_path, max_rows=8, n_slots=4, max_seq_len=256)
+    real_forward = eng.forward
+    calls = {"n": 0}
+
+    def flaky(*a, **kw):
+        calls["n"] += 1
+        if calls["n"] == 2:
+            raise RuntimeError("KV cache exhausted")
+        return real_forward(*a, **kw)
+
+    eng.forward = flaky
+    be = BatchEngine(eng, tok)
+    be.start()
+    try:
+        r1 = be.submit(GenerationRequest(prompt_tokens=[5, 6, 7], max_tokens=6, temperature=0.0))
+        while r1.out.get(timeout=60) is not None:
+            pass
+        assert r1.finish_reason == "error" and "exhausted" in r1.error
+        r2 = be.submit(GenerationRequest(prompt_tokens=[5, 6, 7], max_tokens=4, temperature=0.0))
+        while r2.out.get(timeout=60) is not None:
+            pass
+        assert r2.finish_reason in ("length", "stop") and len(r2.tokens) >= 1
+        assert be.n_errors == 1 and be.sched.stats()["free_slots"] == 4
+    finally:
+        be.stop()
+
+
 def _post(port, body, timeout=120):
     req = urllib.request.Request(f"http://127.0.0.1:{port}/v1/chat/completions", data=json.dumps(body).encode(),
                                  headers={"Content-Type": "application/json"}, method="POST")
