@@ -299,6 +299,12 @@ class InferenceContext:
             self.control.send(OP_STOP)
             self.control.close(unlink=True)
         self.engine.close()
+        try:
+            import torch.distributed as dist
+            if dist.is_available() and dist.is_initialized():
+                dist.destroy_process_group()
+        except Exception:
+            pass
 
 
 def run_inference_app(args: AppArgs, handler):
