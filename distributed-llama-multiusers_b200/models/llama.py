@@ -17,6 +17,8 @@ stores from the matmul epilogue plus a flag wait in the next kernel's prologue.
 """
 from __future__ import annotations
 
+import os
+
 import math
 from typing import Dict, List, Optional, Sequence, Tuple
 
@@ -30,7 +32,11 @@ from ..ops.lib import EPI_QKV_ROPE, EPI_SILU_MUL, EPI_STORE
 from ..parallel.symm import SymmetricBuffer, validate_tp
 from .oracle import rope_frequencies
 
-GEMV_MAX_M = 8
+GEMV_MAX_M = 8              # rows the dp4a GEMV kernel supports (XQ buffer capacity)
+# rows up to which the GEMV path is USED: its dp4a work grows with every row (w13: 19 us at M=1, 33 us at M=4)
+# while the tcgen05 GEMM costs the same for 1..16 rows (33 us).  Measured decode step of the 8B model: 3 users
+# 2.54 ms (GEMV) vs 2.59 ms (tcgen05), 6 users 4.03 vs 2.72 ms, 8 users 4.68 vs 2.75 ms -> cross over above 3 rows
+GEMV_PATH_MAX_M = int(os.environ.get("DLLAMA_GEMV_MAX_M", "3"))
 PREFILL_MAX_SEG = 8          # prompt-chunk segments per batch (attention_prefill.cu: PF_MAX_SEG)
 PAGE = K.PAGE_SIZE
 
@@ -294,7 +300,7 @@ class LlamaEngine:
     # the forward pass (launch sequence)
     # ------------------------------------------------------------------------------------------------
     def _matmul(self, w, d, n, M, xq, xh, epi, kind, norm=None):
-        if M <= GEMV_MAX_M:
+        if M <= GEMV_PATH_MAX_M:
             R, S, T = K.choose_splits(d, n, kind, self.n_sms, M)
             K.gemv_q40(w, d, n, None if norm is not None else xq, M, epi, R, S, norm=norm, pdl=self.use_pdl,
                        tiles_per_cta=T)
@@ -306,7 +312,7 @@ class LlamaEngine:
     def _launch_forward(self, M: int, row0: int, greedy: bool, device_loop: bool, chunk: bool = False):
         """Enqueue one forward over rows 0..M-1 of the descriptor; logits for rows row0..M-1."""
         h, N, pdl = self.h, self.world, self.use_pdl
-        gemv = M <= GEMV_MAX_M
+        gemv = M <= GEMV_PATH_MAX_M
         xq = lambda t: t if gemv else None
         xh = lambda t: None if gemv else t
         mcap = M if gemv else self.ncap               # XQ slabs are written with row capacity == M
@@ -332,12 +338,12 @@ class LlamaEngine:
             parts = (pending[0][self.rank] + x_off) if merge else None
             flags = pending[1] if (merge and multi) else None
             fuse = False
-            if rows <= GEMV_MAX_M:
+            if rows <= GEMV_PATH_MAX_M:
                 fuse = True          # the grid never exceeds one CTA per SM: the repeated prologue is cheap
             if fuse:
                 nm = K.norm_prolog(x_in, x_out, parts, N, src_stride, flags, sc, L, flag_add, w_norm, eps)
                 self._matmul(weight, d, h.dim, rows, None, None, epi, kind, norm=nm)
-            elif rows <= GEMV_MAX_M:
+            elif rows <= GEMV_PATH_MAX_M:
                 K.reduce_norm_quant(x_in, x_out, parts, N if merge else 0, src_stride, flags, sc, L, flag_add, w_norm,
                                     eps, h.dim, rows, rows, self.xq_dim, None, pdl=pdl)
                 self._matmul(weight, d, h.dim, rows, self.xq_dim, None, epi, kind)
