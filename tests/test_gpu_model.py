@@ -141,13 +141,18 @@ def test_bucketed_rows_match_exact_shapes(tiny_model_path):
         r.append(e.prefill(s2, p2, 0).float().cpu().numpy().copy())                       # 5 rows -> 8 (GEMV path)
         # mixed batch: 3 prompt rows of a third sequence are not needed; two decode rows + all logits
         r.append(e.forward([7, 9, 11], [11, 5, 12], [s1, s2, s1], logits_from=0).float().cpu().numpy().copy())
-        r.append(np.array(e.decode_step_greedy([3, 4], [13, 6], [s1, s2], 0)))
-        r.append(np.array(e.decode_step_greedy([5], [14], [s1], 0)))
+        lg = e.forward([3, 4], [13, 6], [s1, s2], logits_from=0).float().cpu().numpy().copy()
+        r.append(lg)
+        # the greedy pick must agree with the engine's own logits for the real rows (not the padding rows)
+        toks = e.decode_step_greedy([3, 4], [13, 6], [s1, s2], 0)
+        assert toks == [int(t) for t in lg.argmax(axis=1)]
+        r.append(e.forward([5], [14], [s1], logits_from=0).float().cpu().numpy().copy())
         outs.append(r)
         e.close()
     for a, b in zip(*outs):
-        # attention split counts / GEMV row templates depend on the padded row count: summation order may differ
-        np.testing.assert_allclose(a, b, rtol=0, atol=2e-3 * max(1.0, float(np.abs(a).max())))
+        # a padded batch may cross the GEMV (exact int8 dp4a) / tcgen05 (fp16 operands) boundary and changes the
+        # attention split count: same function, different rounding
+        assert _rel_err(b, a) < 2e-2
 
 
 def test_greedy_device_loop_matches_host_loop(tiny_model_path):
