@@ -18,6 +18,7 @@
 
 #define ATT_PAGE 32            // tokens per KV page (fixed)
 #define ATT_STAGES 4
+#define ATT_MIN_SPLIT_PAGES 24    // contexts up to 768 tokens: one CTA per (row, kv head), no split
 #define ATT_WARPS 4
 #define ATT_THREADS (ATT_WARPS * 32 + 32)
 #define ATT_COUNTER_BYTES 65536   // completion counters live at scratch offset 0; caller zeroes scratch once
@@ -94,7 +95,14 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attention_kernel(const __grid_
 
     const int T = a.pos[m] + 1;                                // attend to positions 0..pos
     const int n_pages = (T + ATT_PAGE - 1) / ATT_PAGE;
-    const int pps = (n_pages + a.n_splits - 1) / a.n_splits;   // pages per split
+    // The grid carries a.n_splits CTAs per (row, kv head) -- sized for the longest context the engine allows --
+    // but the split + merge round trip (scratch, counter, last-CTA merge) costs about as much as streaming 12
+    // pages, so a row only uses as many splits as its OWN context justifies; the other CTAs leave at once.
+    // (measured, 8B decode: ~170-token context 574 tok/s with 4 splits, 603 with 1; 4096-token context 434 tok/s
+    // with 18 splits of 7 pages, 454 with 16 of 8)
+    const int n_eff = (n_pages <= ATT_MIN_SPLIT_PAGES) ? 1 : min(a.n_splits, (n_pages + 7) / 8);
+    if (sp >= n_eff) { trace_end(a.tr); return; }
+    const int pps = (n_pages + n_eff - 1) / n_eff;             // pages per split
     const int pg0 = sp * pps;
     const int pg1 = min(n_pages, pg0 + pps);
     const int np = max(0, pg1 - pg0);
@@ -217,7 +225,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attention_kernel(const __grid_
     __syncthreads();
 
     // CTA-level merge of the 4 warps: thread d < HS owns head dim d
-    const bool single = (a.n_splits == 1);
+    const bool single = (n_eff == 1);
     if (tid < HS) {
         for (int h = 0; h < G; h++) {
             float Mx = -INFINITY;
@@ -252,29 +260,48 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attention_kernel(const __grid_
     __syncthreads();
     if (tid == 0) {
         const unsigned prev = atomicAdd(&a.counters[m * a.n_kv_heads + kvh], 1u);
-        *s_last = (prev == (unsigned)a.n_splits - 1u) ? 1 : 0;
+        *s_last = (prev == (unsigned)n_eff - 1u) ? 1 : 0;
         if (*s_last) a.counters[m * a.n_kv_heads + kvh] = 0u;
     }
     __syncthreads();
     if (!*s_last) { trace_end(a.tr); return; }
     __threadfence();
-    if (tid < HS) {
-        for (int h = 0; h < G; h++) {
+    // merge: warp w takes heads w, w+4, ...; lane s holds split s's (max, sum) so the rescale factors come out of
+    // two warp reductions, then every lane sums its head dims over the splits (independent loads, one latency)
+    if (warp < ATT_WARPS) {
+        for (int h = warp; h < G; h += ATT_WARPS) {
             const int head = kvh * G + h;
             const size_t base = ((size_t)m * a.n_heads + head) * a.n_splits;
-            float Mx = -INFINITY;
-            for (int s2 = 0; s2 < a.n_splits; s2++) Mx = fmaxf(Mx, __ldcg(&a.part_ml[(base + s2) * 2]));
-            const float Mu = (Mx == -INFINITY) ? 0.0f : Mx;
-            float L = 0.0f, O = 0.0f;
-            for (int s2 = 0; s2 < a.n_splits; s2++) {
-                const float e = __expf(__ldcg(&a.part_ml[(base + s2) * 2]) - Mu);
-                L += __ldcg(&a.part_ml[(base + s2) * 2 + 1]) * e;
-                O += __ldcg(&a.part_o[(base + s2) * HS + tid]) * e;
+            float ms = -INFINITY, ls = 0.0f;
+            if (lane < n_eff) {
+                ms = __ldcg(&a.part_ml[(base + lane) * 2]);
+                ls = __ldcg(&a.part_ml[(base + lane) * 2 + 1]);
             }
-            const float y = (L > 0.0f) ? O / L : 0.0f;
-            if (a.y_out != nullptr) a.y_out[(size_t)m * a.n_heads * HS + (size_t)head * HS + tid] = y;
-            if (a.xq_out != nullptr || a.xh_out != nullptr)
-                q80_block_store(y, lane, m, (head * HS + tid) >> 5, a.out_mcap, a.xq_out, a.xh_out);
+            const float Mx = warp_max(ms);
+            const float Mu = (Mx == -INFINITY) ? 0.0f : Mx;
+            const float e = (lane < n_eff) ? __expf(ms - Mu) : 0.0f;
+            const float L = warp_sum(ls * e);
+            float O[DPL];
+#pragma unroll
+            for (int d = 0; d < DPL; d++) O[d] = 0.0f;
+            for (int s2 = 0; s2 < n_eff; s2++) {
+                const float es = __shfl_sync(0xffffffffu, e, s2);
+#pragma unroll
+                for (int d = 0; d < DPL; d++) O[d] += __ldcg(&a.part_o[(base + s2) * HS + lane * DPL + d]) * es;
+            }
+            const float inv = (L > 0.0f) ? 1.0f / L : 0.0f;
+#pragma unroll
+            for (int d = 0; d < DPL; d++) w_acc[h * HS + lane * DPL + d] = O[d] * inv;
+        }
+        asm volatile("bar.sync 1, %0;" ::"n"(ATT_WARPS * 32));
+        if (tid < HS) {
+            for (int h = 0; h < G; h++) {
+                const int head = kvh * G + h;
+                const float y = w_acc[h * HS + tid];
+                if (a.y_out != nullptr) a.y_out[(size_t)m * a.n_heads * HS + (size_t)head * HS + tid] = y;
+                if (a.xq_out != nullptr || a.xh_out != nullptr)
+                    q80_block_store(y, lane, m, (head * HS + tid) >> 5, a.out_mcap, a.xq_out, a.xh_out);
+            }
         }
     }
     trace_end(a.tr);

@@ -402,7 +402,7 @@ class LlamaEngine:
     def _attention_splits(self, M: int) -> int:
         ctas = M * self.n_kv_loc
         want = max(1, self.n_sms // max(1, ctas))
-        max_by_ctx = max(1, self.max_pages // 4)           # at least 4 pages (128 tokens) per split
+        max_by_ctx = max(1, self.max_pages // 8)           # >= 8 pages per split; the kernel uses fewer splits for short rows
         return int(min(want, max_by_ctx, self.max_splits))
 
     def _run(self, M: int, row0: int, greedy: bool, device_loop: bool = False, chunk: Optional[bool] = None):

@@ -115,7 +115,7 @@ class Tokenizer:
 
     def decode(self, token: int) -> Optional[str]:
         n = host_lib().dl_dec_push(self._dec, token, self._buf, len(self._buf))
-        return self._buf.raw[:n].decode("utf-8", "replace") if n > 0 else None
+        return C.string_at(self._buf, n)          # (.raw would copy the whole 64 KB buffer per token).decode("utf-8", "replace") if n > 0 else None
 
     def decode_all(self, tokens: Sequence[int]) -> str:
         d = self.new_decoder()
@@ -143,7 +143,7 @@ class StreamDecoder:
 
     def push_bytes(self, token: int) -> bytes:
         n = host_lib().dl_dec_push(self._h, token, self._buf, len(self._buf))
-        return self._buf.raw[:n]
+        return C.string_at(self._buf, n)          # (.raw would copy the whole 64 KB buffer per token)
 
     def push(self, token: int) -> Optional[str]:
         b = self.push_bytes(token)
