@@ -109,14 +109,23 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attention_kernel(const __grid_
     const int* bt = a.block_table + (size_t)a.slot[m] * a.max_pages;
 
     if (warp == ATT_WARPS) {
-        if (lane == 0) {
-            for (int i = 0; i < np; i++) {
-                const int s = i % ATT_STAGES;
-                if (i >= ATT_STAGES) mbar_wait(&empty[s], ((i / ATT_STAGES) & 1) ^ 1);
-                const size_t poff = ((size_t)bt[pg0 + i] * a.n_kv_heads + kvh) * (size_t)PAGE_BYTES;
-                mbar_arrive_expect_tx(&full[s], 2 * PAGE_BYTES);
-                bulk_g2s(ring + (s * 2 + 0) * PAGE_BYTES, reinterpret_cast<const uint8_t*>(a.k_cache) + poff, PAGE_BYTES, &full[s]);
-                bulk_g2s(ring + (s * 2 + 1) * PAGE_BYTES, reinterpret_cast<const uint8_t*>(a.v_cache) + poff, PAGE_BYTES, &full[s]);
+        // producer warp: the 32 lanes fetch 32 block-table entries at once (one load latency instead of one per
+        // page in front of every copy), lane 0 issues the bulk copies
+        for (int i0 = 0; i0 < np; i0 += 32) {
+            const int my_page = (i0 + lane < np) ? bt[pg0 + i0 + lane] : 0;
+            const int cnt = min(32, np - i0);
+            for (int j = 0; j < cnt; j++) {
+                const int page = __shfl_sync(0xffffffffu, my_page, j);
+                if (lane == 0) {
+                    const int i = i0 + j;
+                    const int s = i % ATT_STAGES;
+                    if (i >= ATT_STAGES) mbar_wait(&empty[s], ((i / ATT_STAGES) & 1) ^ 1);
+                    const size_t poff = ((size_t)page * a.n_kv_heads + kvh) * (size_t)PAGE_BYTES;
+                    mbar_arrive_expect_tx(&full[s], 2 * PAGE_BYTES);
+                    bulk_g2s(ring + (s * 2 + 0) * PAGE_BYTES, reinterpret_cast<const uint8_t*>(a.k_cache) + poff, PAGE_BYTES, &full[s]);
+                    bulk_g2s(ring + (s * 2 + 1) * PAGE_BYTES, reinterpret_cast<const uint8_t*>(a.v_cache) + poff, PAGE_BYTES, &full[s]);
+                }
+                __syncwarp();
             }
         }
     } else {
