@@ -194,7 +194,7 @@ def run_b200(args):
                    "l2": "inputs larger than L2: every step streams %.0f MB of weights per GPU" % (wbytes / 1e6),
                    "pdl": not args.no_pdl, "cuda_graph": not args.no_graphs},
         "clocks": clocks,
-        "e2e": {"value": round(1000.0 * K_ / e2e_ms, 2), "unit": "tokens/s", "h2d_bytes_per_step": eng.h_desc.numel() * 4,
+        "e2e": {"value": round(1000.0 * K_ / e2e_ms, 2), "unit": "tokens/s", "h2d_bytes_per_step": eng._h_desc3.numel() * 4,
                 "d2h_bytes_per_step": eng.max_rows * 4, "ms_per_step": round(e2e_ms / K_, 4)},
         "gpu_launches": launches,
         "roofline": {"weight_bytes_per_gpu_per_step": wbytes, "hbm_gbs_measured": hbm,

@@ -130,6 +130,8 @@ class LlamaEngine:
         self.desc = torch.zeros(5, DW, dtype=torch.int32, device=dev)
         self.h_desc = torch.zeros(5, DW, dtype=torch.int32).pin_memory()
         self.tokens, self.pos, self.slot, self.row_skip, self.meta = (self.desc[i] for i in range(5))
+        self._hd = self.h_desc.numpy()                                   # host view, filled by set_batch
+        self._desc3, self._h_desc3 = self.desc[:3], self.h_desc[:3]      # tokens | pos | slot: all a batch without prompt chunks needs
         self.prefill_attention = kv_dtype == torch.float16 and self.hs in (64, 128)
         self._chunk = False
         self.x = [torch.zeros(R, h.dim, dtype=torch.float32, device=dev) for _ in range(2)]
@@ -475,7 +477,15 @@ class LlamaEngine:
         token/position pipes, src/app.cpp:169-209)."""
         M = len(tokens)
         assert 1 <= M <= self.max_rows
-        hd = self.h_desc.numpy()
+        hd = self._hd
+        if M == 1 and not self.bucket_rows:          # single-stream decode: the latency-critical host path
+            hd[0, 0], hd[1, 0], hd[2, 0] = tokens[0], positions[0], slots[0]
+            self._chunk = False
+            self.pages.ensure(int(slots[0]), int(positions[0]) + 1)
+            if self.pages.dirty:
+                self._sync_block_table()
+            self._desc3.copy_(self._h_desc3, non_blocking=True)
+            return 1
         off = 0
         if self.bucket_rows:
             Mp = 1
@@ -512,7 +522,10 @@ class LlamaEngine:
         for s, p in zip(slots, positions):
             self.pages.ensure(int(s), int(p) + 1)
         self._sync_block_table()
-        self.desc.copy_(self.h_desc, non_blocking=True)
+        if segs:
+            self.desc.copy_(self.h_desc, non_blocking=True)
+        else:
+            self._desc3.copy_(self._h_desc3, non_blocking=True)
         return M
 
     def forward(self, tokens, positions, slots, logits_from: int = 0, greedy: bool = False) -> torch.Tensor:
