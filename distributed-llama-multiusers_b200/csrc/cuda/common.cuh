@@ -226,6 +226,35 @@ DL_DEVINL void wait_flag_ge(const uint32_t* p, uint32_t target) {
 }
 
 // --------------------------------------------------------------------------------------------
+// LL ("low latency") exchange words: {f32 value bits, epoch} in one aligned 8-byte store.  Such a store is
+// atomic, so a reader that finds the expected epoch in the upper half also has the value: no fence after
+// the peer stores, no counter, no separate flag -- the cost of a hand-off is one NVLink store latency.
+// (Same idea as NCCL's LL protocol.)  Epochs increase monotonically, so a stale word can never match.
+// --------------------------------------------------------------------------------------------
+DL_DEVINL void ll_store(float* base, size_t elem, float v, uint32_t epoch) {
+    reinterpret_cast<uint2*>(base)[elem] = make_uint2(__float_as_uint(v), epoch);
+}
+DL_DEVINL uint4 ld_volatile_v4(const void* p) {
+    uint4 r;
+    asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
+    return r;
+}
+// four consecutive values starting at element `elem` (multiple of 4); spins until all four carry `epoch`
+DL_DEVINL float4 ll_load4(const float* base, size_t elem, uint32_t epoch) {
+    const uint2* p = reinterpret_cast<const uint2*>(base) + elem;
+    uint4 a, b;
+    do {
+        a = ld_volatile_v4(p);
+        b = ld_volatile_v4(p + 2);
+    } while (a.y != epoch || a.w != epoch || b.y != epoch || b.w != epoch);
+    return make_float4(__uint_as_float(a.x), __uint_as_float(a.z), __uint_as_float(b.x), __uint_as_float(b.z));
+}
+// partial-sum read shared by the consumers: plain f32 or LL words
+DL_DEVINL float4 part_load4(const float* base, size_t elem, int ll, uint32_t epoch) {
+    return ll ? ll_load4(base, elem, epoch) : *reinterpret_cast<const float4*>(base + elem);
+}
+
+// --------------------------------------------------------------------------------------------
 // tcgen05 / TMEM
 // --------------------------------------------------------------------------------------------
 DL_DEVINL void tmem_alloc(uint32_t* smem_holder, uint32_t ncols) {

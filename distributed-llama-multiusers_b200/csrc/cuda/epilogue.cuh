@@ -80,6 +80,19 @@ DL_DEVINL void epilogue_rows(const DlEpilogue& e, const float* out_s, int out_ld
                         d0[m * ld] = v;
                     }
                 }
+            } else if (e.ll) {
+                // tensor-parallel push, LL words: value and epoch travel in one 8-byte store per peer; the consumer
+                // polls the words themselves, so there is nothing to fence and no flag to release afterwards
+                const uint32_t epoch = ld_volatile_u32(e.step_counter) * e.flag_mul + e.flag_add;
+                for (int m = m_first; m < M; m += m_step) {
+                    float v = out_s[m * out_ld + tid];
+                    if (rt) v = q80_roundtrip_warp(v);
+                    if (live) {
+                        const size_t off = off0 + m * ld;
+#pragma unroll 1
+                        for (int p = 0; p < nd; p++) ll_store(e.dst[p], off, v, epoch);
+                    }
+                }
             } else {
                 for (int m = m_first; m < M; m += m_step) {
                     float v = out_s[m * out_ld + tid];

@@ -186,6 +186,8 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) gemv_q40_kernel(const __grid_
             }
             __syncthreads();
         }
+        const int ll = nm.ll;
+        const uint32_t ll_epoch = ll ? ld_volatile_u32(nm.step_counter) * nm.flag_mul + nm.flag_add : 0u;
         const bool writer = (nm.x_out != nullptr) && (cl == 0);
         float ss[MT];
 #pragma unroll
@@ -200,10 +202,10 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) gemv_q40_kernel(const __grid_
 #pragma unroll
                 for (int j = 0; j < 8; j++) v[j] = reinterpret_cast<const float4*>(nm.x_in + e)[j];
                 for (int s = 0; s < nm.n_src; s++) {
-                    const float4* p = reinterpret_cast<const float4*>(nm.partials + (size_t)s * nm.src_stride + e);
+                    const size_t pe = (size_t)s * nm.src_stride + e;
 #pragma unroll
                     for (int j = 0; j < 8; j++) {
-                        const float4 t = p[j];
+                        const float4 t = part_load4(nm.partials, pe + 4 * j, ll, ll_epoch);
                         v[j].x += t.x; v[j].y += t.y; v[j].z += t.z; v[j].w += t.w;
                     }
                 }
@@ -225,7 +227,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) gemv_q40_kernel(const __grid_
                     for (int i4 = e0 / 4 + tid; i4 < e1 / 4; i4 += GEMV_THREADS) {
                         float4 x4 = xi[i4];
                         for (int s = 0; s < nm.n_src; s++) {
-                            const float4 p = reinterpret_cast<const float4*>(nm.partials + (size_t)s * nm.src_stride + (size_t)m * dim)[i4];
+                            const float4 p = part_load4(nm.partials, (size_t)s * nm.src_stride + (size_t)m * dim + 4 * (size_t)i4, ll, ll_epoch);
                             x4.x += p.x; x4.y += p.y; x4.z += p.z; x4.w += p.w;
                         }
                         if (writer) reinterpret_cast<float4*>(nm.x_out + (size_t)m * dim)[i4] = x4;
@@ -272,10 +274,10 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) gemv_q40_kernel(const __grid_
 #pragma unroll
                 for (int j = 0; j < 8; j++) v[j] = reinterpret_cast<const float4*>(nm.x_in + e)[j];
                 for (int s = 0; s < nm.n_src; s++) {
-                    const float4* p = reinterpret_cast<const float4*>(nm.partials + (size_t)s * nm.src_stride + e);
+                    const size_t pe = (size_t)s * nm.src_stride + e;
 #pragma unroll
                     for (int j = 0; j < 8; j++) {
-                        const float4 t = p[j];
+                        const float4 t = part_load4(nm.partials, pe + 4 * j, ll, ll_epoch);
                         v[j].x += t.x; v[j].y += t.y; v[j].z += t.z; v[j].w += t.w;
                     }
                 }

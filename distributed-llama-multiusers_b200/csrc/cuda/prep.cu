@@ -150,6 +150,7 @@ struct RnqArgs {
     const uint32_t* flags;
     const uint32_t* step_counter;
     uint32_t flag_mul, flag_add;
+    int ll;                     // partials are LL words {f32 bits, epoch}: poll the data, no flags
     const float* norm_w;
     float eps;
     int dim, M, mcap;
@@ -173,6 +174,8 @@ __global__ void __launch_bounds__(RNQ_THREADS) reduce_norm_quant_kernel(const __
         }
         __syncthreads();
     }
+    const int ll = a.ll;
+    const uint32_t ll_epoch = ll ? ld_volatile_u32(a.step_counter) * a.flag_mul + a.flag_add : 0u;
     // pass 1: merged residual (float4, coalesced) -> x_out, sum of squares
     constexpr int nwarps = RNQ_THREADS / 32;
     const size_t row = (size_t)m * a.dim;
@@ -180,7 +183,7 @@ __global__ void __launch_bounds__(RNQ_THREADS) reduce_norm_quant_kernel(const __
     for (int i4 = tid; i4 < a.dim / 4; i4 += RNQ_THREADS) {
         float4 v = reinterpret_cast<const float4*>(a.x_in + row)[i4];
         for (int s = 0; s < a.n_src; s++) {
-            const float4 p = reinterpret_cast<const float4*>(a.partials + (size_t)s * a.src_stride + row)[i4];
+            const float4 p = part_load4(a.partials, (size_t)s * a.src_stride + row + 4 * (size_t)i4, ll, ll_epoch);
             v.x += p.x; v.y += p.y; v.z += p.z; v.w += p.w;
         }
         if (a.x_out != nullptr) reinterpret_cast<float4*>(a.x_out + row)[i4] = v;
@@ -203,10 +206,10 @@ __global__ void __launch_bounds__(RNQ_THREADS) reduce_norm_quant_kernel(const __
 #pragma unroll
         for (int j = 0; j < 8; j++) v[j] = reinterpret_cast<const float4*>(a.x_in + e)[j];
         for (int s = 0; s < a.n_src; s++) {
-            const float4* p = reinterpret_cast<const float4*>(a.partials + (size_t)s * a.src_stride + e);
+            const size_t pe = (size_t)s * a.src_stride + e;
 #pragma unroll
             for (int j = 0; j < 8; j++) {
-                const float4 t = p[j];
+                const float4 t = part_load4(a.partials, pe + 4 * j, ll, ll_epoch);
                 v[j].x += t.x; v[j].y += t.y; v[j].z += t.z; v[j].w += t.w;
             }
         }
@@ -273,13 +276,13 @@ __global__ void __launch_bounds__(RNQ_THREADS) reduce_norm_quant_kernel(const __
 
 extern "C" int dl_reduce_norm_quant(const float* x_in, float* x_out, const float* partials, int n_src, int src_stride,
                                     const uint32_t* flags, const uint32_t* step_counter, uint32_t flag_mul,
-                                    uint32_t flag_add, const float* norm_w, float eps, int dim, int M, int mcap,
+                                    uint32_t flag_add, int ll, const float* norm_w, float eps, int dim, int M, int mcap,
                                     uint8_t* xq_out, uint8_t* xh_out, float* y_out, int pdl, void* stream) {
     if (dim % 32 != 0 || dim > RNQ_THREADS * RNQ_MAX_PER_THREAD) { dl_set_error("dl_reduce_norm_quant: bad dim %d", dim); return -1; }
     if (n_src > DL_MAX_PEERS) { dl_set_error("dl_reduce_norm_quant: n_src > 8"); return -1; }
     RnqArgs a;
     a.x_in = x_in; a.x_out = x_out; a.partials = partials; a.n_src = n_src; a.src_stride = src_stride;
-    a.flags = flags; a.step_counter = step_counter; a.flag_mul = flag_mul; a.flag_add = flag_add;
+    a.flags = flags; a.step_counter = step_counter; a.flag_mul = flag_mul; a.flag_add = flag_add; a.ll = ll;
     a.norm_w = norm_w; a.eps = eps; a.dim = dim; a.M = M; a.mcap = mcap;
     a.xq_out = xq_out; a.xh_out = xh_out; a.y_out = y_out;
     a.tr = dl_trace_next(TR_RNQ);
@@ -301,7 +304,7 @@ extern "C" int dl_reduce_norm_quant(const float* x_in, float* x_out, const float
 
 extern "C" int dl_quant_q80(const float* x, int M, int K, int mcap, uint8_t* xq_out, uint8_t* xh_out, void* stream) {
     // the same kernel with no residual/partials/norm: y = x
-    return dl_reduce_norm_quant(x, nullptr, nullptr, 0, 0, nullptr, nullptr, 0, 0, nullptr, 0.0f, K, M, mcap, xq_out,
+    return dl_reduce_norm_quant(x, nullptr, nullptr, 0, 0, nullptr, nullptr, 0, 0, 0, nullptr, 0.0f, K, M, mcap, xq_out,
                                 xh_out, nullptr, 0, stream);
 }
 

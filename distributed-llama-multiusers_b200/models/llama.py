@@ -149,7 +149,11 @@ class LlamaEngine:
         self.history = torch.zeros(self.history_cap * R, dtype=torch.int32, device=dev)
 
         # ---- symmetric exchange area: partial sums, logits, flags, counters ------------------------
-        part_bytes = N * R * h.dim * 4
+        # Tensor-parallel partial sums travel as LL words {f32 bits, epoch} (8 bytes per value, one atomic store):
+        # the consumer polls the data itself, so the hand-off needs no fence, counter or flag (DLLAMA_LL=0 keeps
+        # the plain f32 + release-flag protocol for comparison)
+        self.use_ll = N > 1 and os.environ.get("DLLAMA_LL", "1") != "0"
+        part_bytes = N * R * h.dim * (8 if self.use_ll else 4)
         logit_bytes = R * h.vocab_size * 4
         self._off_att, self._off_ffn = 0, part_bytes
         self._off_logits = 2 * part_bytes
@@ -337,21 +341,22 @@ class LlamaEngine:
             merge = pending is not None and not inplace
             x_in = _Off(self.x[cur], x_off)
             x_out = _Off(self.x[cur ^ 1], x_off) if merge else None
-            parts = (pending[0][self.rank] + x_off) if merge else None
-            flags = pending[1] if (merge and multi) else None
+            ll = self.use_ll and merge
+            parts = (pending[0][self.rank] + x_off * (2 if ll else 1)) if merge else None
+            flags = pending[1] if (merge and multi and not ll) else None
             fuse = False
             if rows <= GEMV_PATH_MAX_M:
                 fuse = True          # the grid never exceeds one CTA per SM: the repeated prologue is cheap
             if fuse:
-                nm = K.norm_prolog(x_in, x_out, parts, N, src_stride, flags, sc, L, flag_add, w_norm, eps)
+                nm = K.norm_prolog(x_in, x_out, parts, N, src_stride, flags, sc, L, flag_add, w_norm, eps, ll=ll)
                 self._matmul(weight, d, h.dim, rows, None, None, epi, kind, norm=nm)
             elif rows <= GEMV_PATH_MAX_M:
                 K.reduce_norm_quant(x_in, x_out, parts, N if merge else 0, src_stride, flags, sc, L, flag_add, w_norm,
-                                    eps, h.dim, rows, rows, self.xq_dim, None, pdl=pdl)
+                                    eps, h.dim, rows, rows, self.xq_dim, None, pdl=pdl, ll=ll)
                 self._matmul(weight, d, h.dim, rows, self.xq_dim, None, epi, kind)
             else:
                 K.reduce_norm_quant(x_in, x_out, parts, N if merge else 0, src_stride, flags, sc, L, flag_add, w_norm,
-                                    eps, h.dim, rows, self.ncap, None, self.xh_dim, pdl=pdl)
+                                    eps, h.dim, rows, self.ncap, None, self.xh_dim, pdl=pdl, ll=ll)
                 self._matmul(weight, d, h.dim, rows, None, self.xh_dim, epi, kind)
             if merge:
                 cur ^= 1
@@ -360,6 +365,9 @@ class LlamaEngine:
             if inplace:
                 xp = self.x[cur].data_ptr()
                 return K.epi_store([xp], h.dim, 0, self.sync_q80, residual=xp, residual_ld=h.dim)
+            if self.use_ll:
+                return K.epi_store(buf_ptrs, h.dim, self.rank * src_stride, self.sync_q80, None, sc, L, flag_add,
+                                   ll=True)
             return K.epi_store(buf_ptrs, h.dim, self.rank * src_stride, self.sync_q80,
                                flags_peer if multi else None, sc, L, flag_add, counter)
 

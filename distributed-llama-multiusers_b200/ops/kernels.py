@@ -75,9 +75,17 @@ def make_q40t(raw_q40: torch.Tensor, d: int, n: int) -> torch.Tensor:
 def epi_store(dst: Sequence[int], ld: int, dst_off: int = 0, q80_roundtrip: bool = False,
               flags: Optional[Sequence[int]] = None, step_counter: Optional[int] = None, flag_mul: int = 0,
               flag_add: int = 0, cta_counter: Optional[int] = None, residual: Optional[int] = None,
-              residual_ld: int = 0) -> DlEpilogue:
+              residual_ld: int = 0, ll: bool = False) -> DlEpilogue:
+    """ll=True: dst[] hold LL words {f32 bits, epoch} (tensor-parallel partial sums); step_counter / flag_mul /
+    flag_add define the epoch and no flags are released."""
     e = DlEpilogue()
     e.kind = EPI_STORE
+    e.ll = 1 if ll else 0
+    if ll:
+        assert flags is None and step_counter is not None
+        e.step_counter = step_counter
+        e.flag_mul = flag_mul
+        e.flag_add = flag_add
     e.residual = residual
     e.residual_ld = residual_ld
     e.n_dst = len(dst)
@@ -125,9 +133,10 @@ def epi_silu_mul(xq_out: Optional[torch.Tensor], xh_out: Optional[torch.Tensor],
 
 # ---- launches ------------------------------------------------------------------------------------
 def reduce_norm_quant(x_in, x_out, partials, n_src, src_stride, flags, step_counter, flag_mul, flag_add, norm_w,
-                      eps, dim, M, mcap, xq_out, xh_out, y_out=None, pdl=False):
+                      eps, dim, M, mcap, xq_out, xh_out, y_out=None, pdl=False, ll=False):
     check(cuda_lib().dl_reduce_norm_quant(_p(x_in), _p(x_out), partials, n_src, src_stride, flags, step_counter,
-                                          flag_mul, flag_add, _p(norm_w), eps, dim, M, mcap, _p(xq_out),
+                                          flag_mul, flag_add, 1 if (ll and partials and n_src) else 0, _p(norm_w), eps,
+                                          dim, M, mcap, _p(xq_out),
                                           _p(xh_out), _p(y_out), 1 if pdl else 0, _stream()),
           "dl_reduce_norm_quant")
     lib.count_launch()
@@ -146,7 +155,7 @@ def embedding(table: torch.Tensor, tokens: torch.Tensor, x: torch.Tensor, M: int
 
 def norm_prolog(x_in, x_out, partials: Optional[int], n_src: int, src_stride: int, flags: Optional[int],
                 step_counter: Optional[int], flag_mul: int, flag_add: int, norm_w: torch.Tensor,
-                eps: float) -> DlNormProlog:
+                eps: float, ll: bool = False) -> DlNormProlog:
     """Fused merge-add + RMSNorm + Q80 prologue of the GEMV (x_in/x_out: tensors or objects with data_ptr)."""
     p = DlNormProlog()
     p.x_in = _p(x_in)
@@ -159,6 +168,7 @@ def norm_prolog(x_in, x_out, partials: Optional[int], n_src: int, src_stride: in
     p.flag_mul, p.flag_add = flag_mul, flag_add
     p.norm_w = norm_w.data_ptr()
     p.eps = eps
+    p.ll = 1 if (ll and partials) else 0
     return p
 
 

@@ -54,6 +54,7 @@ class DlEpilogue(C.Structure):
         ("xh_out", C.c_void_p),
         ("out_mcap", C.c_int),
         ("act_gelu", C.c_int),
+        ("ll", C.c_int),
     ]
 
 
@@ -71,6 +72,7 @@ class DlNormProlog(C.Structure):
         ("flag_add", C.c_uint32),
         ("norm_w", C.c_void_p),
         ("eps", C.c_float),
+        ("ll", C.c_int),
     ]
 
 
@@ -93,7 +95,7 @@ def cuda_lib():
     L.dl_q40t_bytes.argtypes = [i32, i32]
     L.dl_q40_repack.argtypes = [vp, i32, i32, vp, i32, i32, i32, vp]
     L.dl_q40t_dequant.argtypes = [vp, i32, i32, vp, vp]
-    L.dl_reduce_norm_quant.argtypes = [vp, vp, vp, i32, i32, vp, vp, u32, u32, vp, f32, i32, i32, i32,
+    L.dl_reduce_norm_quant.argtypes = [vp, vp, vp, i32, i32, vp, vp, u32, u32, i32, vp, f32, i32, i32, i32,
                                        vp, vp, vp, i32, vp]
     L.dl_quant_q80.argtypes = [vp, i32, i32, i32, vp, vp, vp]
     L.dl_embedding.argtypes = [vp, vp, vp, i32, i32, vp, vp]

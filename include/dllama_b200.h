@@ -54,6 +54,9 @@ typedef struct {
     uint8_t* xh_out;                  /* XH slabs (may be NULL) */
     int out_mcap;                     /* row capacity of the XQ/XH slabs */
     int act_gelu;                     /* 0 = SiLU, 1 = tanh-GELU */
+    /* DL_EPI_STORE, tensor-parallel partial sums: 1 = dst[] are arrays of {f32 bits, epoch} 8-byte words (LL
+     * protocol: no fence, no flags; step_counter / flag_mul / flag_add give the epoch), 0 = plain f32 */
+    int ll;
 } DlEpilogue;
 
 /* Fused activation producer for dl_gemv_q40: the kernel itself computes
@@ -72,6 +75,7 @@ typedef struct {
     uint32_t flag_mul, flag_add;
     const float* norm_w;              /* [dim] */
     float eps;
+    int ll;                           /* 1: partials are LL words {f32 bits, epoch}; wait on the words, not on flags */
 } DlNormProlog;
 
 const char* dl_last_error(void);
@@ -92,9 +96,9 @@ int dl_q40t_dequant(const uint8_t* q40t, int d, int n, float* out, void* stream)
 /* x_out = x_in + sum_src partial[src] ; y = rmsnorm(x_out)*w ; y -> Q80 -> XQ and/or XH slabs.
  * Waits (acquire.sys) on flags[src] >= epoch before reading partials when flags != NULL.
  * (reference: OP_MERGE_ADD + OP_INV_RMS + OP_RMS_NORM + OP_CAST, src/llm.cpp:204-239,317-342) */
-int dl_reduce_norm_quant(const float* x_in, float* x_out, const float* partials, int n_src, int src_stride,
+int dl_reduce_norm_quant(const float* x_in, float* x_out, const float* partials /*f32, or LL words when ll*/, int n_src, int src_stride,
                          const uint32_t* flags, const uint32_t* step_counter, uint32_t flag_mul,
-                         uint32_t flag_add, const float* norm_w, float eps, int dim, int M, int mcap,
+                         uint32_t flag_add, int ll, const float* norm_w, float eps, int dim, int M, int mcap,
                          uint8_t* xq_out, uint8_t* xh_out, float* y_out, int pdl, void* stream);
 /* plain f32 [M][K] -> XQ / XH (no norm); (reference: OP_CAST F32->Q80, nn-cpu-ops.cpp:1221-1235) */
 int dl_quant_q80(const float* x, int M, int K, int mcap, uint8_t* xq_out, uint8_t* xh_out, void* stream);

@@ -447,6 +447,63 @@ def test_reduce_norm_quant_with_partials():
     np.testing.assert_allclose(got, quant.q80_roundtrip(yout.cpu().numpy()), rtol=0, atol=1e-6)
 
 
+def test_ll_exchange_words_producer_to_consumers():
+    """Tensor-parallel hand-off in LL words: a matmul epilogue pushes {value, epoch} pairs into N destination
+    buffers (standing in for the peers), then the fused GEMV prologue and the stand-alone rnq kernel consume
+    them by polling the epoch in the data -- no flags.  A stale epoch in the buffer must not be accepted."""
+    k = K()
+    M, d, n, n_src = 2, 512, 256, 2
+    raw, wdq = _rand_q40(d, n, 61)
+    w = k.make_q40t(torch.from_numpy(raw).cuda(), d, n)
+    rng = np.random.default_rng(62)
+    xa = rng.standard_normal((M, n), dtype=np.float32)
+    xq = k.alloc_xq(n, M, "cuda")
+    k.quant_q80(torch.from_numpy(xa).cuda(), M, n, M, xq, None)
+    step = torch.tensor([7], dtype=torch.int32, device="cuda")
+    flag_mul, flag_add = 33, 5
+    epoch = 7 * flag_mul + flag_add
+    src_stride = 8 * d                                   # elements between sources (row capacity 8)
+    # every "rank" holds [n_src][8][d] LL words; pre-fill with a stale epoch and a poison value
+    bufs = [torch.zeros(n_src * src_stride, 2, dtype=torch.int32, device="cuda") for _ in range(2)]
+    for b in bufs:
+        b[:, 0] = 0x7FC00000                              # NaN bits
+        b[:, 1] = epoch - 1
+    ref_part = quant.q80_roundtrip((quant.q80_roundtrip(xa).astype(np.float64) @ wdq.astype(np.float64).T).astype(np.float32))
+    for src in range(n_src):                              # source `src` writes its slot in both destinations
+        epi = k.epi_store([b.data_ptr() for b in bufs], d, src * src_stride, True, None, step.data_ptr(), flag_mul, flag_add,
+                          ll=True)
+        k.gemv_q40(w, d, n, xq, M, epi, 1, 2)
+    torch.cuda.synchronize()
+    words = bufs[1].cpu().numpy().reshape(n_src, 8, d, 2)
+    assert (words[:, :M, :, 1] == epoch).all() and (words[:, M:, :, 1] == epoch - 1).all()
+    got_part = words[:, :M, :, 0].copy().view(np.float32)
+    np.testing.assert_allclose(got_part[0], ref_part, rtol=0, atol=np.abs(ref_part).max() / 127 * 1.01)
+    np.testing.assert_array_equal(got_part[0], got_part[1])
+    # consumers: x_out = x_in + sum of the sources
+    x = rng.standard_normal((8, d), dtype=np.float32)
+    wn = (1.0 + 0.1 * rng.standard_normal(d)).astype(np.float32)
+    xin = torch.from_numpy(x).cuda()
+    xs = x[:M] + got_part.sum(0)
+    xout = torch.full_like(xin, float("nan"))
+    yout = torch.zeros(M, d, device="cuda")
+    k.reduce_norm_quant(xin, xout, bufs[0].data_ptr(), n_src, src_stride, None, step.data_ptr(), flag_mul, flag_add,
+                        torch.from_numpy(wn).cuda(), 1e-5, d, M, 8, None, None, yout, ll=True)
+    torch.cuda.synchronize()
+    np.testing.assert_allclose(xout.cpu().numpy()[:M], xs, rtol=1e-6, atol=1e-6)
+    raw2, wdq2 = _rand_q40(128, d, 63)
+    w2 = k.make_q40t(torch.from_numpy(raw2).cuda(), 128, d)
+    xout2 = torch.full_like(xin, float("nan"))
+    y = torch.full((M, 128), float("nan"), device="cuda")
+    nm = k.norm_prolog(xin, xout2, bufs[1].data_ptr(), n_src, src_stride, None, step.data_ptr(), flag_mul, flag_add,
+                       torch.from_numpy(wn).cuda(), 1e-5, ll=True)
+    k.gemv_q40(w2, 128, d, None, M, k.epi_store([y.data_ptr()], 128), 1, 2, norm=nm)
+    torch.cuda.synchronize()
+    np.testing.assert_allclose(xout2.cpu().numpy()[:M], xs, rtol=1e-6, atol=1e-6)
+    yn = wn * (xs / np.sqrt((xs * xs).mean(-1, keepdims=True) + 1e-5))
+    ref = quant.q80_roundtrip(yn.astype(np.float32)).astype(np.float64) @ wdq2.astype(np.float64).T
+    np.testing.assert_allclose(y.cpu().numpy(), ref, rtol=2e-3, atol=2e-3 * np.abs(ref).max())
+
+
 def test_argmax_and_embedding():
     k = K()
     logits = torch.randn(5, 1000, device="cuda")
