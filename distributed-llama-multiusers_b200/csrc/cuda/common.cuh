@@ -243,10 +243,12 @@ DL_DEVINL uint4 ld_volatile_v4(const void* p) {
 DL_DEVINL float4 ll_load4(const float* base, size_t elem, uint32_t epoch) {
     const uint2* p = reinterpret_cast<const uint2*>(base) + elem;
     uint4 a, b;
-    do {
+    while (true) {
         a = ld_volatile_v4(p);
         b = ld_volatile_v4(p + 2);
-    } while (a.y != epoch || a.w != epoch || b.y != epoch || b.w != epoch);
+        if (a.y == epoch && a.w == epoch && b.y == epoch && b.w == epoch) break;
+        __nanosleep(100);      // thousands of threads re-reading L2 would slow down the very stores they wait for
+    }
     return make_float4(__uint_as_float(a.x), __uint_as_float(a.z), __uint_as_float(b.x), __uint_as_float(b.z));
 }
 // partial-sum read shared by the consumers: plain f32 or LL words

@@ -37,6 +37,8 @@ GEMV_MAX_M = 8              # rows the dp4a GEMV kernel supports (XQ buffer capa
 # while the tcgen05 GEMM costs the same for 1..16 rows (33 us).  Measured decode step of the 8B model: 3 users
 # 2.54 ms (GEMV) vs 2.59 ms (tcgen05), 6 users 4.03 vs 2.72 ms, 8 users 4.68 vs 2.75 ms -> cross over above 3 rows
 GEMV_PATH_MAX_M = int(os.environ.get("DLLAMA_GEMV_MAX_M", "3"))
+LL_MAX_ROWS = 32             # batches up to this many rows use the LL exchange (see LlamaEngine.__init__)
+LL_MAX_WORLD = 4             # largest tensor-parallel group that exchanges partial sums as LL words
 PREFILL_MAX_SEG = 8          # prompt-chunk segments per batch (attention_prefill.cu: PF_MAX_SEG)
 PAGE = K.PAGE_SIZE
 
@@ -152,17 +154,30 @@ class LlamaEngine:
         # Tensor-parallel partial sums travel as LL words {f32 bits, epoch} (8 bytes per value, one atomic store):
         # the consumer polls the data itself, so the hand-off needs no fence, counter or flag (DLLAMA_LL=0 keeps
         # the plain f32 + release-flag protocol for comparison)
-        self.use_ll = N > 1 and os.environ.get("DLLAMA_LL", "1") != "0"
-        part_bytes = N * R * h.dim * (8 if self.use_ll else 4)
+        # Measured (8B decode): TP=2 518 -> 634 tok/s with LL; at TP=8 the 8 x 2x larger reads and the polling of
+        # every consumer CTA cost more than the fence they save (545 -> 460), so wide groups keep the flag protocol.
+        # DLLAMA_LL=1 / 0 forces it on / off.
+        ll_env = os.environ.get("DLLAMA_LL", "auto")
+        self.use_ll = N > 1 and (ll_env == "1" or (ll_env != "0" and N <= LL_MAX_WORLD))
+        # LL words for latency-bound batches (<= LL_MAX_ROWS rows: decode), plain f32 + flags for prompt-sized
+        # batches (there the 2x bytes cost more than the fence: TTFT 4.8 -> 5.5 ms at TP=4); the two protocols
+        # use disjoint regions so stale data of one can never be read as the other
+        ll_rows = min(R, LL_MAX_ROWS) if self.use_ll else 0
+        part_bytes = N * R * h.dim * 4
+        ll_bytes = N * ll_rows * h.dim * 8
         logit_bytes = R * h.vocab_size * 4
         self._off_att, self._off_ffn = 0, part_bytes
-        self._off_logits = 2 * part_bytes
+        self._off_att_ll, self._off_ffn_ll = 2 * part_bytes, 2 * part_bytes + ll_bytes
+        self._off_logits = 2 * part_bytes + 2 * ll_bytes
         self._off_flags = _round_up(self._off_logits + logit_bytes, 256)
         total = self._off_flags + 4096
         self.symm = SymmetricBuffer(total, rank, world, group)
         sp = self.symm.ptrs
         self.part_att = [p + self._off_att for p in sp]
         self.part_ffn = [p + self._off_ffn for p in sp]
+        self.part_att_ll = [p + self._off_att_ll for p in sp]
+        self.part_ffn_ll = [p + self._off_ffn_ll for p in sp]
+        self._ll_rows = ll_rows
         self.logits_ptrs = [p + self._off_logits for p in sp]
         # flag words: [att: 8][ffn: 8][logits: 8][step counter][cta counters: 8]
         fl = [p + self._off_flags for p in sp]
@@ -323,8 +338,11 @@ class LlamaEngine:
         xh = lambda t: None if gemv else t
         mcap = M if gemv else self.ncap               # XQ slabs are written with row capacity == M
         L = h.n_layers
-        src_stride = self.max_rows * h.dim
         multi = N > 1
+        ll_fwd = self.use_ll and M <= self._ll_rows          # this forward exchanges LL words (same choice on every rank)
+        src_stride = (self._ll_rows if ll_fwd else self.max_rows) * h.dim
+        part_att = self.part_att_ll if ll_fwd else self.part_att
+        part_ffn = self.part_ffn_ll if ll_fwd else self.part_ffn
         sc = self.step_counter
         eps = h.norm_epsilon
         # Residual bookkeeping.  TP>1 (and the tensor-core path): matmul epilogues push Q80-cast partial
@@ -341,7 +359,7 @@ class LlamaEngine:
             merge = pending is not None and not inplace
             x_in = _Off(self.x[cur], x_off)
             x_out = _Off(self.x[cur ^ 1], x_off) if merge else None
-            ll = self.use_ll and merge
+            ll = ll_fwd and merge
             parts = (pending[0][self.rank] + x_off * (2 if ll else 1)) if merge else None
             flags = pending[1] if (merge and multi and not ll) else None
             fuse = False
@@ -365,7 +383,7 @@ class LlamaEngine:
             if inplace:
                 xp = self.x[cur].data_ptr()
                 return K.epi_store([xp], h.dim, 0, self.sync_q80, residual=xp, residual_ld=h.dim)
-            if self.use_ll:
+            if ll_fwd:
                 return K.epi_store(buf_ptrs, h.dim, self.rank * src_stride, self.sync_q80, None, sc, L, flag_add,
                                    ll=True)
             return K.epi_store(buf_ptrs, h.dim, self.rank * src_stride, self.sync_q80,
@@ -385,14 +403,14 @@ class LlamaEngine:
                                     self.pos, self.slot, self.block_table, self.max_pages, self.meta, xq(self.xq_att),
                                     xh(self.xh_att), mcap, pdl=pdl)
             self._matmul(W["wo"], h.dim, self.q_loc, M, self.xq_att, self.xh_att,
-                         push(self.part_att, self.flags_att_peer, l + 1, self.cta_counters[0]), EPI_STORE)
-            pending = (self.part_att, self.flags_att_local)
+                         push(part_att, self.flags_att_peer, l + 1, self.cta_counters[0]), EPI_STORE)
+            pending = (part_att, self.flags_att_local)
             # --- feed-forward block ---
             epi = K.epi_silu_mul(xq(self.xq_hid), xh(self.xh_hid), mcap, gelu=(h.hidden_act != HIDDEN_ACT_SILU))
             norm_then(W["rms_ffn"], pending, l + 1, W["w13"], 2 * self.hid_loc, EPI_SILU_MUL, epi)
             self._matmul(W["w2"], h.dim, self.hid_loc, M, self.xq_hid, self.xh_hid,
-                         push(self.part_ffn, self.flags_ffn_peer, l + 1, self.cta_counters[1]), EPI_STORE)
-            pending = (self.part_ffn, self.flags_ffn_local)
+                         push(part_ffn, self.flags_ffn_peer, l + 1, self.cta_counters[1]), EPI_STORE)
+            pending = (part_ffn, self.flags_ffn_local)
         # --- final norm + logits for rows row0.. ---
         Ml = M - row0
         epi = K.epi_store(self.logits_ptrs, h.vocab_size, self.rank * self.vocab_loc, False,
