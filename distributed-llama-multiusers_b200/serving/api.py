@@ -131,7 +131,7 @@ def make_handler(state: ApiState):
             print(f"🔷 {self.command} {path} id={req.id} prompt_tokens={len(req.prompt_tokens)}", flush=True)
             try:
                 if params.stream:
-                    self._stream(cid, req)
+                    self._stream(cid, req, params.include_usage)
                 else:
                     text = req.result()
                     if req.finish_reason == "error":
@@ -145,7 +145,7 @@ def make_handler(state: ApiState):
                 state.batch.cancel(req)         # client went away: free its slot
             print(f"🔶 id={req.id} tokens={len(req.tokens)} finish={req.finish_reason}", flush=True)
 
-        def _stream(self, cid: str, req: GenerationRequest):
+        def _stream(self, cid: str, req: GenerationRequest, include_usage: bool = False):
             self.send_response(200)
             self._cors()
             self.send_header("Content-Type", "text/event-stream; charset=utf-8")
@@ -163,7 +163,12 @@ def make_handler(state: ApiState):
                 if delta is None:
                     break
                 send(A.chat_completion_chunk(cid, state.model_name, {"content": delta}, None))
-            send(A.chat_completion_chunk(cid, state.model_name, {}, req.finish_reason or "stop"))
+            last = A.chat_completion_chunk(cid, state.model_name, {}, req.finish_reason or "stop")
+            if include_usage:
+                last["usage"] = A.chat_usage(len(req.prompt_tokens), len(req.tokens))
+            if req.finish_reason == "error":
+                last["error"] = {"message": req.error or "generation failed", "type": "server_error"}
+            send(last)
             self.wfile.write(b"data: [DONE]\r\n\r\n")
             self.wfile.flush()
 

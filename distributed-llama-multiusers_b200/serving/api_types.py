@@ -17,6 +17,7 @@ class InferenceParams:
     stop: List[str] = field(default_factory=list)
     stream: bool = False
     seed: int = 0
+    include_usage: bool = False      # stream_options.include_usage: usage in the last SSE chunk (OpenAI)
 
 
 def parse_chat_messages(items) -> List[Dict[str, str]]:
@@ -49,6 +50,9 @@ def parse_inference_params(body: dict, defaults: InferenceParams) -> InferencePa
         p.max_tokens = int(body["max_tokens"])
     elif body.get("max_completion_tokens") is not None:
         p.max_tokens = int(body["max_completion_tokens"])
+    so = body.get("stream_options")
+    if isinstance(so, dict) and so.get("include_usage"):
+        p.include_usage = True
     stop = body.get("stop")
     if isinstance(stop, str):
         p.stop = [stop]

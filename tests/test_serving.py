@@ -208,13 +208,20 @@ def test_http_api_concurrent_users_openai_shape_and_sse(tiny_model_path, tok):
         assert all(c["object"] == "chat.completion.chunk" for c in chunks)
         text = "".join(c["choices"][0]["delta"].get("content", "") for c in chunks)
         assert text == results[0]["choices"][0]["message"]["content"]
+        assert "usage" not in chunks[-1]
+        # stream_options.include_usage: the last chunk carries the token counts
+        with _post(port, {"messages": [{"role": "user", "content": "hello world"}], "max_tokens": 6, "stream": True,
+                          "stream_options": {"include_usage": True}}) as r:
+            raw = r.read().decode("utf-8")
+        last = json.loads([e[len("data: "):] for e in raw.split("\r\n\r\n") if e.startswith("data: ")][-2])
+        assert last["usage"] == results[0]["usage"] and last["choices"][0]["finish_reason"] in ("stop", "length")
         assert chunks[-1]["choices"][0]["finish_reason"] in ("stop", "length")
         # bad request
         with pytest.raises(urllib.error.HTTPError) as ei:
             _post(port, {"messages": "nope"})
         assert ei.value.code == 400
         with urllib.request.urlopen(f"http://127.0.0.1:{port}/metrics") as r:
-            assert b"dllama_requests_total 4" in r.read()
+            assert b"dllama_requests_total 5" in r.read()
     finally:
         srv.shutdown()
         be.stop()
