@@ -96,6 +96,42 @@ def test_continuous_batching_matches_single_user_runs(tiny_model_path, tok):
     assert be.sched.stats() == {"waiting": 0, "running": 0, "free_slots": 3}
 
 
+@pytest.mark.gpu
+def test_gpu_engine_behind_the_batch_engine(tiny_model_path, tok):
+    """The serving path on the CUDA engine: power-of-two batch buckets + pre-captured graphs, several prompts
+    packed per step (one long enough for the prefill attention), device greedy pick and device sampler."""
+    from dllama_b200.models.llama import LlamaEngine
+    eng = LlamaEngine(tiny_model_path, max_rows=32, n_slots=6, max_seq_len=256, bucket_rows=True)
+    be = BatchEngine(eng, tok)
+    be.warmup()
+    n_graphs = len(eng._graphs)
+    assert n_graphs >= 12
+    rng = __import__("numpy").random.default_rng(4)
+    prompts = [[5, 6, 7, 8, 9, 10], [100, 200, 300], rng.integers(1, 1000, 40).tolist(), [42]]
+    reqs = [be.submit(GenerationRequest(prompt_tokens=p, max_tokens=5, temperature=0.0)) for p in prompts]
+    mk = lambda seed: GenerationRequest(prompt_tokens=[3, 4, 5], max_tokens=6, temperature=1.0, top_p=0.95, seed=seed)
+    a, b, c = be.submit(mk(11)), be.submit(mk(11)), be.submit(mk(12))
+    be.start()
+    for r in reqs + [a]:
+        r.result(timeout=120)
+    for r in (b, c):
+        r.result(timeout=120)
+    be.stop()
+    o = OracleLlama(mfile.ModelFile(tiny_model_path), max_seq_len=256)
+    for r, p in zip(reqs, prompts):
+        # greedy tokens: every generated token must be (near-)argmax of the oracle's logits given the same prefix
+        assert 1 <= len(r.tokens) <= 5 and r.finish_reason in ("length", "stop")
+        o.reset()
+        lg = o.forward(p, 0).numpy()[-1]
+        for i, t in enumerate(r.tokens):
+            assert lg[t] >= lg.max() - 2e-2 * max(1.0, float(abs(lg).max())), (p, i, t)
+            lg = o.forward([t], len(p) + i).numpy()[0]
+    assert a.tokens == b.tokens and len(a.tokens) >= 1          # same seed -> same sample path on the device sampler
+    assert len(eng._graphs) == n_graphs                         # no shape outside the warmed-up buckets
+    assert be.sched.stats() == {"waiting": 0, "running": 0, "free_slots": 6}
+    eng.close()
+
+
 def test_sampling_is_per_request_and_seeded(tiny_model_path, tok):
     eng = CpuEngine(tiny_model_path, max_rows=8, n_slots=4, max_seq_len=256)
     be = BatchEngine(eng, tok)
