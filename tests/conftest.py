@@ -10,6 +10,17 @@ if ROOT not in sys.path:
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+    # a fresh checkout has no built artefacts (*.so are git-ignored): build what is missing so the suite is
+    # self-sufficient (host library: g++, seconds; CUDA library: nvcc cross-compiles without a GPU)
+    import build as _build
+    lib_dir = os.path.join(ROOT, "distributed-llama-multiusers_b200", "lib")
+    if not os.path.exists(os.path.join(lib_dir, "libdllama_b200_host.so")):
+        _build.build_host()
+    if not os.path.exists(os.path.join(lib_dir, "libdllama_b200_cuda.so")):
+        try:
+            _build.build_cuda()
+        except Exception as e:          # CPU-only tests do not need it
+            print(f"[conftest] CUDA library not built: {e}")
 
 
 def pytest_collection_modifyitems(config, items):
