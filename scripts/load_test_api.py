@@ -63,7 +63,7 @@ def main():
     be = BatchEngine(eng, tok, control=ctl)
     t0 = time.perf_counter()
     be.warmup()
-    print(f"graph warm-up: {time.perf_counter() - t0:.2f} s ({len(getattr(eng, "_graphs", {}))} graphs)", flush=True)
+    print(f"graph warm-up: {time.perf_counter() - t0:.2f} s ({len(getattr(eng, '_graphs', {}))} graphs)", flush=True)
     be.start()
     state = ApiState(be, tok, os.path.basename(path), A.InferenceParams(messages=[], temperature=a.temperature, top_p=0.9, seed=1),
                      max_default_tokens=a.max_tokens)
