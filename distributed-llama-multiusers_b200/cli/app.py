@@ -11,7 +11,8 @@ Surface parity with the reference (src/app.cpp:33-136 flags; src/dllama.cpp:11-2
 Options: --buffer-float-type {f32,f16,q40,q80}, --workers host:port ..., --port, --nthreads,
 --steps, --temperature, --topp, --seed, --chat-template {llama2,llama3,deepSeek3}, --max-seq-len,
 --gpu-index, --gpu-segments a:b, --net-turbo {0,1}; unknown options raise (src/app.cpp:131-133).
-New here: --max-batch (rows per forward / concurrent users), --n-slots, --device {auto,cuda,cpu}.
+New here: --max-batch (rows per forward / concurrent users), --n-slots, --device {auto,cuda,cpu},
+--api-backend {native,python} (dllama-api front end: the C++ epoll server or the Python one).
 
 Multi-GPU: every node is one process on one GPU of the same NVSwitch box.  Two equivalent ways to
 start them: (a) the reference's way -- ``dllama worker --port P`` per extra GPU, then the root with
@@ -60,6 +61,7 @@ class AppArgs:
     max_batch: int = 32
     n_slots: int = 0
     device: str = "auto"
+    api_backend: str = "native"
     benchmark: bool = False
 
     @staticmethod
@@ -109,6 +111,10 @@ class AppArgs:
             elif name == "--max-batch": a.max_batch = int(value)
             elif name == "--n-slots": a.n_slots = int(value)
             elif name == "--device": a.device = value
+            elif name == "--api-backend":
+                if value not in ("native", "python"):
+                    raise ValueError(f"Invalid API backend: {value}")
+                a.api_backend = value
             else:
                 raise ValueError(f"Unknown option: {name}")
             i += 2
@@ -122,6 +128,7 @@ Options:
   --buffer-float-type {f32,f16,q40,q80}   --max-seq-len <n>   --temperature <f> --topp <f> --seed <n>
   --workers <host:port> ...   --port <n>   --chat-template {llama2,llama3,deepSeek3}
   --max-batch <rows>  --n-slots <sequences>  --gpu-index <i>  --device {auto,cuda,cpu}
+  --api-backend {native,python}   (dllama-api: C++ epoll front end, or the Python one)
   --nthreads / --gpu-segments / --net-turbo are accepted for compatibility (no effect on B200)."""
 
 

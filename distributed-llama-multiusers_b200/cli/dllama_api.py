@@ -12,14 +12,31 @@ from .app import USAGE, AppArgs, InferenceContext, run_inference_app
 
 def server(ctx: InferenceContext):
     a = ctx.args
+    defaults = A.InferenceParams(messages=[], temperature=a.temperature, top_p=a.topp, seed=a.seed)
+    import os
+    if a.api_backend == "native":
+        # C++ front end (csrc/host/server.cpp): sockets, HTTP/JSON/SSE, tokenizer, scheduler, detokeniser in one
+        # I/O thread; this thread only runs the forward passes
+        from ..serving.native_server import NativeApiServer
+        srv = NativeApiServer(ctx.engine, ctx.tokenizer, os.path.basename(a.model_path), defaults, a.chat_template_type,
+                              control=ctx.control, host="0.0.0.0", port=a.port)
+        srv.warmup()                     # capture the CUDA graphs of every batch shape before taking traffic
+        signal.signal(signal.SIGTERM, lambda *_: srv._stop.set())
+        try:
+            srv.serve_forever()
+        except KeyboardInterrupt:
+            pass
+        finally:
+            srv.close()
+        return
     batch = BatchEngine(ctx.engine, ctx.tokenizer, control=ctx.control)
     batch.warmup()                       # capture the CUDA graphs of every batch shape before taking traffic
     batch.start()
-    defaults = A.InferenceParams(messages=[], temperature=a.temperature, top_p=a.topp, seed=a.seed)
-    import os
     state = ApiState(batch, ctx.tokenizer, os.path.basename(a.model_path), defaults, a.chat_template_type)
     srv = ApiServer(state, "0.0.0.0", a.port)
-    signal.signal(signal.SIGTERM, lambda *_: srv.httpd.shutdown())
+    # (shutdown() blocks until serve_forever returns, and the handler runs on the thread that is inside it)
+    import threading
+    signal.signal(signal.SIGTERM, lambda *_: threading.Thread(target=srv.httpd.shutdown, daemon=True).start())
     try:
         srv.serve_forever()
     except KeyboardInterrupt:

@@ -253,6 +253,14 @@ int dl_sched_forget(void* p, long long req_id) {
     return 0;
 }
 
+// -1 = unknown id, else 0 waiting / 1 prefill / 2 decode / 3 done (finished or cancelled, not yet forgotten)
+int dl_sched_state(void* p, long long req_id) {
+    auto* s = (Sched*)p;
+    std::lock_guard<std::mutex> g(s->mu);
+    auto it = s->reqs.find(req_id);
+    return it == s->reqs.end() ? -1 : it->second.state;
+}
+
 void dl_sched_stats(void* p, int* waiting, int* running, int* free_slots) {
     auto* s = (Sched*)p;
     std::lock_guard<std::mutex> g(s->mu);

@@ -47,7 +47,15 @@ def host_lib():
         "dl_sched_sampling_rows": (i32, [vp, C.POINTER(ll), i32]),
         "dl_sched_commit": (i32, [vp, i32, ip, ip, ip]),
         "dl_sched_pop_released": (i32, [vp, ip, i32]), "dl_sched_forget": (i32, [vp, ll]),
-        "dl_sched_stats": (None, [vp, ip, ip, ip]),
+        "dl_sched_stats": (None, [vp, ip, ip, ip]), "dl_sched_state": (i32, [vp, ll]),
+        # native API server (csrc/host/server.cpp)
+        "dl_srv_new": (vp, [vp, cp, i32, cp, i32, i32, i32, i32, i32, f32, f32, u64, i32, i32]),
+        "dl_srv_listen": (i32, [vp, cp, i32]), "dl_srv_shutdown": (None, [vp]), "dl_srv_free": (None, [vp]),
+        "dl_srv_wait": (i32, [vp, i32]),
+        "dl_srv_next_batch": (i32, [vp, vp, vp, vp, i32, ip, ip, vp, vp, vp, i32, ip, vp, i32, ip]),
+        "dl_srv_sample_host": (i32, [vp, vp, ll, vp]), "dl_srv_commit": (i32, [vp, i32, vp]),
+        "dl_srv_fail_batch": (i32, [vp, cp]), "dl_srv_port": (i32, [vp]),
+        "dl_srv_stats": (None, [vp, C.POINTER(ll)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)

@@ -79,3 +79,47 @@ def test_inference_on_gpu_engine_matches_cpu_text(tiny_model_path, tok_path):
     rc_g, out_g = _run(argv)
     assert rc_g == 0, out_g
     _check_inference_output(out_g, 10)
+
+
+@pytest.mark.parametrize("backend", ["native", "python"])
+def test_dllama_api_executable_serves_http(tiny_model_path, tok_path, backend):
+    """`./dllama-api --model .. --tokenizer .. --port P` as a user starts it (reference: src/dllama-api.cpp:367-410),
+    on the CPU engine, with either front end; SIGTERM ends it cleanly."""
+    import json
+    import signal
+    import socket
+    import subprocess
+    import time
+    import urllib.request
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    p = subprocess.Popen([sys.executable, os.path.join(root, "dllama-api"), "--model", tiny_model_path, "--tokenizer", tok_path,
+                          "--buffer-float-type", "q80", "--max-seq-len", "128", "--device", "cpu", "--port", str(port),
+                          "--temperature", "0", "--api-backend", backend, "--max-batch", "8"],
+                         stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    try:
+        t0 = time.time()
+        up = False
+        while time.time() - t0 < 120 and p.poll() is None:
+            try:
+                with urllib.request.urlopen(f"http://127.0.0.1:{port}/v1/models", timeout=2) as r:
+                    up = json.load(r)["data"][0]["id"] == os.path.basename(tiny_model_path)
+                break
+            except OSError:
+                time.sleep(0.2)
+        assert up, p.stdout.read() if p.poll() is not None else "server did not come up"
+        body = json.dumps({"messages": [{"role": "user", "content": "hello world"}], "max_tokens": 5}).encode()
+        req = urllib.request.Request(f"http://127.0.0.1:{port}/v1/chat/completions", data=body, method="POST",
+                                     headers={"Content-Type": "application/json"})
+        with urllib.request.urlopen(req, timeout=120) as r:
+            d = json.load(r)
+        assert d["object"] == "chat.completion" and 1 <= d["usage"]["completion_tokens"] <= 5
+    finally:
+        p.send_signal(signal.SIGTERM)
+        try:
+            p.wait(timeout=30)
+        except subprocess.TimeoutExpired:
+            p.kill()
+            raise

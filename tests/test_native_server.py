@@ -1,0 +1,229 @@
+"""The native front end of `dllama-api` (csrc/host/server.cpp) on the CPU engine: same contract as the Python
+front end (tests/test_serving.py), which also serves as the oracle for the generated text."""
+import json
+import socket
+import threading
+import time
+import urllib.error
+import urllib.request
+
+import pytest
+
+from dllama_b200.formats import tfile
+from dllama_b200.models.cpu_engine import CpuEngine
+from dllama_b200.serving import api_types as A
+from dllama_b200.serving.api import ApiServer, ApiState
+from dllama_b200.serving.batch_engine import BatchEngine
+from dllama_b200.serving.native_server import NativeApiServer
+from dllama_b200.text import native as T
+
+
+@pytest.fixture(scope="module")
+def tok(tmp_path_factory):
+    p = str(tmp_path_factory.mktemp("tok") / "tiny.t")
+    tfile.write_synthetic_tokenizer(p, 1024)
+    return T.Tokenizer(p)
+
+
+def _native(tiny_model_path, tok, engine=None, **kw):
+    eng = engine or CpuEngine(tiny_model_path, max_rows=8, n_slots=4, max_seq_len=256)
+    defaults = A.InferenceParams(messages=[], temperature=0.0, top_p=0.9, seed=1)
+    srv = NativeApiServer(eng, tok, "tiny.m", defaults, host="127.0.0.1", port=0, verbose=False, **kw)
+    srv.start()
+    return srv
+
+
+def _post(port, body, timeout=120):
+    req = urllib.request.Request(f"http://127.0.0.1:{port}/v1/chat/completions", data=json.dumps(body).encode(),
+                                 headers={"Content-Type": "application/json"}, method="POST")
+    return urllib.request.urlopen(req, timeout=timeout)
+
+
+def _sse_events(raw: str):
+    return [e[len("data: "):] for e in raw.split("\r\n\r\n") if e.startswith("data: ")]
+
+
+def test_native_server_openai_shape_sse_and_errors(tiny_model_path, tok):
+    """Routes, CORS, concurrent users in one batch, chat.completion / SSE chunk shapes, usage, 400s, metrics --
+    and text identical to the Python front end's."""
+    srv = _native(tiny_model_path, tok)
+    port = srv.port
+    eng2 = CpuEngine(tiny_model_path, max_rows=8, n_slots=4, max_seq_len=256)
+    be = BatchEngine(eng2, tok)
+    be.start()
+    pstate = ApiState(be, tok, "tiny.m", A.InferenceParams(messages=[], temperature=0.0, top_p=0.9, seed=1))
+    psrv = ApiServer(pstate, "127.0.0.1", 0)
+    psrv.start()
+    try:
+        with urllib.request.urlopen(f"http://127.0.0.1:{port}/v1/models") as r:
+            models = json.load(r)
+        assert models["object"] == "list" and models["data"][0]["id"] == "tiny.m"
+        opt = urllib.request.Request(f"http://127.0.0.1:{port}/v1/chat/completions", method="OPTIONS")
+        with urllib.request.urlopen(opt) as r:
+            assert r.status == 204 and r.headers["Access-Control-Allow-Origin"] == "*"
+        with pytest.raises(urllib.error.HTTPError) as ei:
+            urllib.request.urlopen(f"http://127.0.0.1:{port}/nope")
+        assert ei.value.code == 404
+        with urllib.request.urlopen(f"http://127.0.0.1:{port}/health") as r:
+            assert json.load(r)["status"] == "ok"
+        results = {}
+
+        def user(i, text):
+            with _post(port, {"messages": [{"role": "user", "content": text}], "max_tokens": 6}) as r:
+                results[i] = json.load(r)
+
+        texts = ["hello world", "the of and", "hello world", "a \"quoted\"\n\\ line é世 \U0001F600"]
+        threads = [threading.Thread(target=user, args=(i, t)) for i, t in enumerate(texts)]
+        [t.start() for t in threads]
+        [t.join(timeout=180) for t in threads]
+        assert len(results) == 4
+        for i, d in results.items():
+            assert d["object"] == "chat.completion" and d["choices"][0]["message"]["role"] == "assistant"
+            assert d["id"].startswith("cmpl-") and d["model"] == "tiny.m"
+            assert 1 <= d["usage"]["completion_tokens"] <= 6
+            assert d["usage"]["total_tokens"] == d["usage"]["prompt_tokens"] + d["usage"]["completion_tokens"]
+            assert d["generated_text"] == d["choices"][0]["message"]["content"]
+            assert d["choices"][0]["finish_reason"] in ("stop", "length")
+            with _post(psrv.port, {"messages": [{"role": "user", "content": texts[i]}], "max_tokens": 6}) as r:
+                want = json.load(r)
+            assert d["choices"][0]["message"]["content"] == want["choices"][0]["message"]["content"]
+            assert d["usage"] == want["usage"] and d["choices"][0]["finish_reason"] == want["choices"][0]["finish_reason"]
+        # streaming: SSE chunks concatenate to the non-streamed answer
+        with _post(port, {"messages": [{"role": "user", "content": "hello world"}], "max_tokens": 6,
+                          "stream": True}) as r:
+            assert r.headers["Content-Type"].startswith("text/event-stream")
+            raw = r.read().decode("utf-8")
+        events = _sse_events(raw)
+        assert events[-1] == "[DONE]"
+        chunks = [json.loads(e) for e in events[:-1]]
+        assert all(c["object"] == "chat.completion.chunk" for c in chunks)
+        assert chunks[0]["choices"][0]["delta"] == {"role": "assistant", "content": ""}
+        text = "".join(c["choices"][0]["delta"].get("content", "") for c in chunks)
+        assert text == results[0]["choices"][0]["message"]["content"]
+        assert "usage" not in chunks[-1] and chunks[-1]["choices"][0]["finish_reason"] in ("stop", "length")
+        with _post(port, {"messages": [{"role": "user", "content": "hello world"}], "max_tokens": 6, "stream": True,
+                          "stream_options": {"include_usage": True}}) as r:
+            last = json.loads(_sse_events(r.read().decode("utf-8"))[-2])
+        assert last["usage"] == results[0]["usage"]
+        # OpenAI content parts + system message + max_completion_tokens
+        with _post(port, {"messages": [{"role": "system", "content": "be brief"},
+                                       {"role": "user", "content": [{"type": "text", "text": "hello "},
+                                                                    {"type": "text", "text": "world"}]}],
+                          "max_completion_tokens": 3}) as r:
+            assert json.load(r)["usage"]["completion_tokens"] <= 3
+        # bad requests: wrong type, empty messages, missing content, prompt longer than the context window
+        for body in ({"messages": "nope"}, {"messages": []}, {"messages": [{"role": "user"}]},
+                     {"messages": [{"role": "user", "content": "hello " * 400}]}):
+            with pytest.raises(urllib.error.HTTPError) as ei:
+                _post(port, body)
+            assert ei.value.code == 400 and "error" in json.load(ei.value)
+        req = urllib.request.Request(f"http://127.0.0.1:{port}/v1/chat/completions", data=b"{\"messages\": [",
+                                     method="POST")
+        with pytest.raises(urllib.error.HTTPError) as ei:
+            urllib.request.urlopen(req)
+        assert ei.value.code == 400
+        with urllib.request.urlopen(f"http://127.0.0.1:{port}/metrics") as r:
+            m = r.read()
+        assert b"dllama_requests_total 7" in m and b"dllama_errors_total 5" in m
+        st = srv.stats()
+        assert st["waiting"] == 0 and st["running"] == 0 and st["free_slots"] == 4
+    finally:
+        srv.close()
+        psrv.shutdown()
+        be.stop()
+
+
+def test_native_server_sampling_stop_strings_disconnect_and_engine_failure(tiny_model_path, tok):
+    eng = CpuEngine(tiny_model_path, max_rows=8, n_slots=3, max_seq_len=256)
+    real_forward = eng.forward
+    fail = {"on": False}
+
+    def flaky(*a, **kw):
+        if fail["on"]:
+            fail["on"] = False
+            raise RuntimeError("KV cache exhausted")
+        return real_forward(*a, **kw)
+
+    eng.forward = flaky
+    srv = _native(tiny_model_path, tok, engine=eng)
+    port = srv.port
+    msg = [{"role": "user", "content": "hello world"}]
+    try:
+        def ask(**kw):
+            with _post(port, {"messages": msg, **kw}) as r:
+                return json.load(r)
+        # per-request seeded sampling (host sampler on the CPU engine): same seed -> same text
+        a = ask(max_tokens=8, temperature=1.0, top_p=0.95, seed=11)
+        b = ask(max_tokens=8, temperature=1.0, top_p=0.95, seed=11)
+        c = ask(max_tokens=8, temperature=1.0, top_p=0.95, seed=12)
+        assert a["choices"][0]["message"]["content"] == b["choices"][0]["message"]["content"]
+        assert a["choices"][0]["message"]["content"] != c["choices"][0]["message"]["content"]
+        # stop string truncates the answer
+        full = ask(max_tokens=12, temperature=0.0)["choices"][0]["message"]["content"]
+        assert len(full) >= 4
+        stop = full[2:4]
+        cut = ask(max_tokens=12, temperature=0.0, stop=[stop])
+        assert cut["choices"][0]["message"]["content"] == full[:full.index(stop)]
+        assert cut["choices"][0]["finish_reason"] == "stop"
+        # a client that hangs up mid-stream frees its slot
+        generated_before = srv.stats()["generated"]
+        body = json.dumps({"messages": msg, "max_tokens": 200, "stream": True}).encode()
+        s = socket.create_connection(("127.0.0.1", port))
+        s.sendall(b"POST /v1/chat/completions HTTP/1.1\r\nHost: x\r\nContent-Type: application/json\r\n"
+                  b"Content-Length: " + str(len(body)).encode() + b"\r\n\r\n" + body)
+        assert s.recv(64).startswith(b"HTTP/1.1 200")
+        s.close()
+        t0 = time.time()
+        while time.time() - t0 < 60:
+            st = srv.stats()
+            if st["running"] == 0 and st["waiting"] == 0 and st["free_slots"] == 3:
+                break
+            time.sleep(0.05)
+        assert st["free_slots"] == 3 and st["generated"] - generated_before < 200
+        # a failing forward answers 500 for that batch only; the next request is served
+        fail["on"] = True
+        with pytest.raises(urllib.error.HTTPError) as ei:
+            ask(max_tokens=4)
+        assert ei.value.code == 500 and "exhausted" in json.load(ei.value)["error"]["message"]
+        ok = ask(max_tokens=4, temperature=0.0)
+        assert ok["usage"]["completion_tokens"] >= 1
+        st = srv.stats()
+        assert st["engine_errors"] == 1 and st["free_slots"] == 3 and srv.n_errors == 1
+        # the same failure inside an SSE stream: an `error` object in the last chunk
+        fail["on"] = True
+        with _post(port, {"messages": msg, "max_tokens": 4, "stream": True}) as r:
+            ev = _sse_events(r.read().decode("utf-8"))
+        last = json.loads(ev[-2])
+        assert ev[-1] == "[DONE]" and last["choices"][0]["finish_reason"] == "error"
+        assert "exhausted" in last["error"]["message"]
+    finally:
+        srv.close()
+
+
+def test_native_server_many_concurrent_streams(tiny_model_path, tok):
+    """More users than batch rows and slots: everybody is served, nothing leaks."""
+    eng = CpuEngine(tiny_model_path, max_rows=4, n_slots=3, max_seq_len=256)
+    srv = _native(tiny_model_path, tok, engine=eng)
+    port = srv.port
+    out = {}
+
+    def user(i):
+        with _post(port, {"messages": [{"role": "user", "content": "hello world " + "the " * (i % 5)}],
+                          "max_tokens": 5, "stream": i % 2 == 0}) as r:
+            raw = r.read().decode("utf-8")
+        if i % 2 == 0:
+            ev = _sse_events(raw)
+            out[i] = "".join(json.loads(e)["choices"][0]["delta"].get("content", "") for e in ev[:-1])
+        else:
+            out[i] = json.loads(raw)["choices"][0]["message"]["content"]
+
+    try:
+        threads = [threading.Thread(target=user, args=(i,)) for i in range(12)]
+        [t.start() for t in threads]
+        [t.join(timeout=240) for t in threads]
+        assert len(out) == 12
+        assert out[0] == out[5] == out[10] and out[1] == out[6] == out[11]          # same prompt -> same text
+        st = srv.stats()
+        assert st["requests"] == 12 and st["running"] == 0 and st["waiting"] == 0 and st["free_slots"] == 3
+    finally:
+        srv.close()
