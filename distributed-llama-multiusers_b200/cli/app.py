@@ -127,9 +127,9 @@ Options:
   --model <path.m> --tokenizer <path.t> --prompt <text> --steps <n>
   --buffer-float-type {f32,f16,q40,q80}   --max-seq-len <n>   --temperature <f> --topp <f> --seed <n>
   --workers <host:port> ...   --port <n>   --chat-template {llama2,llama3,deepSeek3}
-  --max-batch <rows>  --n-slots <sequences>  --gpu-index <i>  --device {auto,cuda,cpu}
+  --max-batch <rows>  --n-slots <sequences>  --gpu-index <i>  --device {auto,cuda,cpu,cpu-oracle}
   --api-backend {native,python}   (dllama-api: C++ epoll front end, or the Python one)
-  --nthreads / --gpu-segments / --net-turbo are accepted for compatibility (no effect on B200)."""
+  --nthreads <n>  threads of the CPU backend (no GPU); --gpu-segments / --net-turbo are accepted for compatibility."""
 
 
 # --------------------------------------------------------------------------------------------------
@@ -197,8 +197,13 @@ def serve_worker_once(port: int) -> dict:
 # --------------------------------------------------------------------------------------------------
 # engine construction
 # --------------------------------------------------------------------------------------------------
+def use_cuda_device(device: str) -> bool:
+    import torch
+    return device == "cuda" or (device == "auto" and torch.cuda.is_available())
+
+
 def build_engine(model_path: str, rank: int, world: int, max_batch: int, n_slots: int, max_seq_len: int,
-                 sync_type: int, device: str = "auto", gpu_index: int = -1):
+                 sync_type: int, device: str = "auto", gpu_index: int = -1, workers=(), n_threads: int = 0):
     import torch
     from ..formats.mfile import read_header
     h = read_header(model_path, max_seq_len)
@@ -207,7 +212,7 @@ def build_engine(model_path: str, rank: int, world: int, max_batch: int, n_slots
                          f"({world} > {h.n_kv_heads})")
     if h.weight_type == quant.Q40 and sync_type != quant.Q80:
         raise ValueError("This version supports only Q40 weights with Q80 sync type")
-    use_cuda = device == "cuda" or (device == "auto" and torch.cuda.is_available())
+    use_cuda = use_cuda_device(device)
     seq_len = h.seq_len
     slots = n_slots or max(2, min(max_batch, 64))
     if use_cuda and h.weight_type == quant.Q40:
@@ -225,10 +230,15 @@ def build_engine(model_path: str, rank: int, world: int, max_batch: int, n_slots
             torch.cuda.set_device(gpu_index)
         return F32Engine(model_path, rank=rank, world=world, max_rows=max_batch, n_slots=slots,
                          max_seq_len=min(seq_len, 8192))
-    if world > 1:
-        raise ValueError("multi-node runs need the CUDA engine")
-    from ..models.cpu_engine import CpuEngine
-    return CpuEngine(model_path, max_rows=max_batch, n_slots=slots, max_seq_len=min(seq_len, 4096))
+    if device == "cpu-oracle":
+        # the PyTorch restatement of the reference numerics (tests, debugging); single node
+        from ..models.cpu_engine import CpuEngine
+        return CpuEngine(model_path, max_rows=max_batch, n_slots=slots, max_seq_len=min(seq_len, 4096))
+    # no GPU: the native host backend; `--workers` are `dllama worker` processes reached over TCP, which get their
+    # configuration and weight slices from this root (reference: src/app.cpp:233-312)
+    from ..models.native_cpu_engine import NativeCpuEngine
+    return NativeCpuEngine(model_path, workers=list(workers), n_threads=n_threads, max_rows=max_batch, n_slots=slots,
+                           max_seq_len=min(seq_len, 8192) if max_seq_len <= 0 else seq_len, sync_type=sync_type)
 
 
 def setup_distributed(args: AppArgs):
@@ -240,6 +250,8 @@ def setup_distributed(args: AppArgs):
         rank, world, _ = init_distributed()
         ctl = ControlChannel(os.environ.get("MASTER_PORT", "0"), rank, world, args.max_batch)
         return rank, world, ctl
+    if args.workers and not use_cuda_device(args.device):
+        return 0, 1, None                               # the native CPU engine dials its workers itself
     if args.workers:
         master_port = 20000 + (os.getpid() % 20000)
         world = dial_workers(args, master_port)
@@ -254,6 +266,12 @@ def setup_distributed(args: AppArgs):
 def run_worker_app(args: AppArgs):
     """`dllama worker`: serve -> join the rendezvous -> load own weight slice -> replay batches;
     on root disconnect go back to listening (reference: runWorkerApp, src/app.cpp:405-464)."""
+    if not use_cuda_device(args.device):
+        # no GPU: a worker of the native host backend; everything it needs arrives over the socket
+        from ..models.native_cpu_engine import serve_worker
+        while True:
+            serve_worker(args.port, args.n_threads if args.n_threads > 1 else 0)
+            print("🚁 Root disconnected, waiting for a new one", flush=True)
     from ..parallel.control import ControlChannel
     from ..parallel.symm import init_distributed
     from ..serving.batch_engine import worker_loop
@@ -293,7 +311,8 @@ class InferenceContext:
         print(f"📄 RegularVocabSize: {self.tokenizer.regular_vocab_size}")
         print(f"📄 SpecialVocabSize: {self.tokenizer.special_vocab_size}")
         self.engine = build_engine(args.model_path, self.rank, self.world, args.max_batch, args.n_slots,
-                                   args.max_seq_len, args.sync_type, args.device, args.gpu_index)
+                                   args.max_seq_len, args.sync_type, args.device, args.gpu_index, args.workers,
+                                   args.n_threads if args.n_threads > 1 else 0)
         self.header = self.engine.h
         print(self.header.describe(), flush=True)
         if self.tokenizer.vocab_size != self.header.vocab_size:

@@ -53,6 +53,14 @@ class RootInference:
             self.last_ms = (time.perf_counter() - t0) * 1e3
         return out
 
+    def net(self):
+        """(sync ms, sent bytes, received bytes) of the last forward on the TCP-synchronised CPU backend, else None."""
+        f = getattr(self.engine, "network_stats", None)
+        if f is None:
+            return None
+        st = f(reset=True)
+        return st["sync_us"] / 1e3, st["sent_bytes"], st["recv_bytes"]
+
     def sync_bytes_per_row(self) -> int:
         """Peer-memory bytes this rank pushes per activation row per forward (partial sums + logits)."""
         e, h = self.engine, self.engine.h
@@ -87,10 +95,17 @@ def inference(ctx: InferenceContext):
         n = min(chunk, n_in - 1 - pos)
         inf.forward(input_tokens[pos:pos + n], pos, want_logits=False)
         pos += n
-        sent += per_row * n
-        recv += per_row * n
+        net = inf.net()
+        sync_ms = 0.0
+        if net is not None:                                # measured on the sockets (CPU backend)
+            sync_ms, ds, dr = net
+            sent += ds
+            recv += dr
+        else:
+            sent += per_row * n
+            recv += per_row * n
         print("🔷️ Eval%5d ms Sync%5d ms | Sent%6d kB Recv%6d kB | (%d tokens)" % (
-            round(inf.last_ms), 0, sent // 1024, recv // 1024, n), flush=True)
+            round(inf.last_ms), round(sync_ms), sent // 1024, recv // 1024, n), flush=True)
         eval_ms += inf.last_ms
     token = input_tokens[pos]                              # the last prompt token feeds the first prediction
     tok.reset_decoder()
@@ -100,10 +115,17 @@ def inference(ctx: InferenceContext):
         logits = inf.forward([token], pos)
         token = ctx.sampler.sample(logits)
         piece = tok.decode(token)
-        sent += per_row
-        recv += per_row
+        net = inf.net()
+        sync_ms = 0.0
+        if net is not None:
+            sync_ms, ds, dr = net
+            sent += ds
+            recv += dr
+        else:
+            sent += per_row
+            recv += per_row
         print("🔶 Pred%5d ms Sync%5d ms | Sent%6d kB Recv%6d kB | %s" % (
-            round(inf.last_ms), 0, sent // 1024, recv // 1024, piece if piece is not None else "~"), flush=True)
+            round(inf.last_ms), round(sync_ms), sent // 1024, recv // 1024, piece if piece is not None else "~"), flush=True)
         pred_ms += inf.last_ms
         pos += 1
         n_pred += 1

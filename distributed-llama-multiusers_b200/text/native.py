@@ -147,7 +147,9 @@ class Tokenizer:
 
     def decode(self, token: int) -> Optional[str]:
         n = host_lib().dl_dec_push(self._dec, token, self._buf, len(self._buf))
-        return C.string_at(self._buf, n)          # (.raw would copy the whole 64 KB buffer per token).decode("utf-8", "replace") if n > 0 else None
+        if n <= 0:
+            return None
+        return C.string_at(self._buf, n).decode("utf-8", "replace")     # (.raw would copy the whole 64 KB buffer per token)
 
     def decode_all(self, tokens: Sequence[int]) -> str:
         d = self.new_decoder()

@@ -123,3 +123,37 @@ def test_dllama_api_executable_serves_http(tiny_model_path, tok_path, backend):
         except subprocess.TimeoutExpired:
             p.kill()
             raise
+
+
+def test_root_plus_worker_over_localhost_tcp_on_cpu(tiny_model_path, tok_path):
+    """BASELINE.json configuration 1 (plumbing, no GPU): `dllama worker --port P` + `dllama inference --workers
+    127.0.0.1:P` as separate processes, q80 buffer; the worker has no model file; the text equals the single-node run."""
+    import socket
+    import subprocess
+    import time
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    exe = os.path.join(root, "dllama")
+    worker = subprocess.Popen([sys.executable, exe, "worker", "--port", str(port), "--nthreads", "2", "--device", "cpu"],
+                              stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, cwd="/")
+    try:
+        time.sleep(1.0)
+        common = ["inference", "--model", tiny_model_path, "--tokenizer", tok_path, "--buffer-float-type", "q80",
+                  "--prompt", "hello world the of and", "--steps", "12", "--max-seq-len", "128", "--device", "cpu",
+                  "--temperature", "0", "--nthreads", "2"]
+        r2 = subprocess.run([sys.executable, exe] + common + ["--workers", f"127.0.0.1:{port}"], capture_output=True,
+                            text=True, timeout=180)
+        assert r2.returncode == 0, r2.stdout + r2.stderr
+        r1 = subprocess.run([sys.executable, exe] + common, capture_output=True, text=True, timeout=180)
+        assert r1.returncode == 0, r1.stdout + r1.stderr
+        _check_inference_output(r2.stdout, 12)
+        pieces = lambda s: [ln.rsplit("|", 1)[1] for ln in s.splitlines() if "Pred" in ln and "|" in ln]
+        assert pieces(r2.stdout) and pieces(r2.stdout) == pieces(r1.stdout)        # 2 nodes == 1 node, token for token
+        sent = [int(m) for m in re.findall(r"Pred.*Sent\s*(\d+) kB", r2.stdout)]
+        assert sent and sent[-1] > 0 and "Sent     0 kB" in r1.stdout                 # real socket counters
+    finally:
+        worker.terminate()
+        out = worker.communicate(timeout=30)[0]
+    assert "Worker is ready" in out and "Weights loaded" in out, out
