@@ -41,7 +41,7 @@ class AppArgs:
     mode: Optional[str] = None
     help: bool = False
     n_batches: int = 32
-    n_threads: int = 1
+    n_threads: int = 0          # CPU backend threads per node; 0 = one per available core share
     model_path: Optional[str] = None
     tokenizer_path: Optional[str] = None
     prompt: Optional[str] = None
@@ -270,7 +270,7 @@ def run_worker_app(args: AppArgs):
         # no GPU: a worker of the native host backend; everything it needs arrives over the socket
         from ..models.native_cpu_engine import serve_worker
         while True:
-            serve_worker(args.port, args.n_threads if args.n_threads > 1 else 0)
+            serve_worker(args.port, args.n_threads)
             print("🚁 Root disconnected, waiting for a new one", flush=True)
     from ..parallel.control import ControlChannel
     from ..parallel.symm import init_distributed
@@ -312,7 +312,7 @@ class InferenceContext:
         print(f"📄 SpecialVocabSize: {self.tokenizer.special_vocab_size}")
         self.engine = build_engine(args.model_path, self.rank, self.world, args.max_batch, args.n_slots,
                                    args.max_seq_len, args.sync_type, args.device, args.gpu_index, args.workers,
-                                   args.n_threads if args.n_threads > 1 else 0)
+                                   args.n_threads)
         self.header = self.engine.h
         print(self.header.describe(), flush=True)
         if self.tokenizer.vocab_size != self.header.vocab_size:

@@ -188,10 +188,66 @@ void quantize_q80_avx2(const float* x, uint8_t* out, int n) {
     }
 }
 
-__attribute__((target("avx2,fma")))
+// horizontal sum of 8 f32 lanes (macro: helpers called from target("avx2") functions would need the attribute too)
+#define DL_HSUM8(dst, v) do { \
+    __m128 s_ = _mm_add_ps(_mm256_extractf128_ps(v, 1), _mm256_castps256_ps128(v)); \
+    s_ = _mm_add_ps(s_, _mm_movehl_ps(s_, s_)); \
+    s_ = _mm_add_ss(s_, _mm_movehdup_ps(s_)); \
+    (dst) = _mm_cvtss_f32(s_); } while (0)
+// Q40 block -> 32 signed bytes (low nibbles = elements 0..15) and their absolute values
+#define DL_UNPACK(wb, wv, aw) do { \
+    const __m128i raw_ = _mm_loadu_si128((const __m128i*)((wb) + 2)); \
+    wv = _mm256_set_m128i(_mm_srli_epi16(raw_, 4), raw_); \
+    wv = _mm256_sub_epi8(_mm256_and_si256(wv, low), eight); \
+    aw = _mm256_sign_epi8(wv, wv); } while (0)
+
+// integer dot of one Q40 block (already unpacked to int8 `wv`, |wv| in `aw`) with one Q80 block, as 8 f32 lanes
+#define DL_BLOCK_DOT(aw, wv, xptr) \
+    _mm256_cvtepi32_ps(_mm256_madd_epi16(_mm256_maddubs_epi16(aw, _mm256_sign_epi8(_mm256_loadu_si256((const __m256i*)(xptr)), wv)), ones))
+
+__attribute__((target("avx2,fma,f16c")))
 void matmul_q40_q80_avx2(const uint8_t* w, int r0, int r1, int nb, const uint8_t* xq, int M, float* y, size_t ldy) {
     const __m256i low = _mm256_set1_epi8(0x0f), eight = _mm256_set1_epi8(8), ones = _mm256_set1_epi16(1);
-    constexpr int MB = 8;                       // batch rows per pass (accumulators stay in registers)
+    // activation scales widened once per call (they are reused by every weight row)
+    std::vector<float> xd((size_t)M * nb);
+    for (int m = 0; m < M; m++)
+        for (int b = 0; b < nb; b++) {
+            uint16_t h;
+            memcpy(&h, xq + ((size_t)m * nb + b) * Q80_BYTES, 2);
+            xd[(size_t)m * nb + b] = _cvtsh_ss(h);
+        }
+    if (M == 1) {                               // decode: two independent accumulator chains per row
+        const float* sx = xd.data();
+        for (int r = r0; r < r1; r++) {
+            const uint8_t* wr = w + (size_t)r * nb * Q40_BYTES;
+            __m256 a0 = _mm256_setzero_ps(), a1 = _mm256_setzero_ps();
+            int b = 0;
+            for (; b + 2 <= nb; b += 2) {
+                const uint8_t* w0 = wr + (size_t)b * Q40_BYTES;
+                const uint8_t* w1 = w0 + Q40_BYTES;
+                uint16_t h0, h1;
+                memcpy(&h0, w0, 2);
+                memcpy(&h1, w1, 2);
+                __m256i v0, u0, v1, u1;
+                DL_UNPACK(w0, v0, u0);
+                DL_UNPACK(w1, v1, u1);
+                a0 = _mm256_fmadd_ps(_mm256_set1_ps(_cvtsh_ss(h0) * sx[b]), DL_BLOCK_DOT(u0, v0, xq + (size_t)b * Q80_BYTES + 2), a0);
+                a1 = _mm256_fmadd_ps(_mm256_set1_ps(_cvtsh_ss(h1) * sx[b + 1]), DL_BLOCK_DOT(u1, v1, xq + (size_t)(b + 1) * Q80_BYTES + 2), a1);
+            }
+            for (; b < nb; b++) {
+                const uint8_t* w0 = wr + (size_t)b * Q40_BYTES;
+                uint16_t h0;
+                memcpy(&h0, w0, 2);
+                __m256i v0, u0;
+                DL_UNPACK(w0, v0, u0);
+                a0 = _mm256_fmadd_ps(_mm256_set1_ps(_cvtsh_ss(h0) * sx[b]), DL_BLOCK_DOT(u0, v0, xq + (size_t)b * Q80_BYTES + 2), a0);
+            }
+            a0 = _mm256_add_ps(a0, a1);
+            DL_HSUM8(y[r], a0);
+        }
+        return;
+    }
+    constexpr int MB = 8;                       // batch rows per pass: weights unpacked once, accumulators in registers
     for (int r = r0; r < r1; r++) {
         const uint8_t* wr = w + (size_t)r * nb * Q40_BYTES;
         for (int m0 = 0; m0 < M; m0 += MB) {
@@ -202,27 +258,15 @@ void matmul_q40_q80_avx2(const uint8_t* w, int r0, int r1, int nb, const uint8_t
                 const uint8_t* wb = wr + (size_t)b * Q40_BYTES;
                 uint16_t dwh;
                 memcpy(&dwh, wb, 2);
-                const float dw = f16_to_f32(dwh);
-                const __m128i raw = _mm_loadu_si128((const __m128i*)(wb + 2));
-                __m256i wv = _mm256_set_m128i(_mm_srli_epi16(raw, 4), raw);        // low nibbles = elems 0..15
-                wv = _mm256_sub_epi8(_mm256_and_si256(wv, low), eight);
-                const __m256i aw = _mm256_sign_epi8(wv, wv);
+                const float dw = _cvtsh_ss(dwh);
+                __m256i wv, aw;
+                DL_UNPACK(wb, wv, aw);
                 for (int i = 0; i < mc; i++) {
-                    const uint8_t* xb = xq + ((size_t)(m0 + i) * nb + b) * Q80_BYTES;
-                    uint16_t dxh;
-                    memcpy(&dxh, xb, 2);
-                    const __m256i xv = _mm256_loadu_si256((const __m256i*)(xb + 2));
-                    const __m256i p16 = _mm256_maddubs_epi16(aw, _mm256_sign_epi8(xv, wv));
-                    const __m256 pf = _mm256_cvtepi32_ps(_mm256_madd_epi16(p16, ones));
-                    acc[i] = _mm256_fmadd_ps(_mm256_set1_ps(dw * f16_to_f32(dxh)), pf, acc[i]);
+                    const size_t xi = (size_t)(m0 + i) * nb + b;
+                    acc[i] = _mm256_fmadd_ps(_mm256_set1_ps(dw * xd[xi]), DL_BLOCK_DOT(aw, wv, xq + xi * Q80_BYTES + 2), acc[i]);
                 }
             }
-            for (int i = 0; i < mc; i++) {
-                __m128 s = _mm_add_ps(_mm256_extractf128_ps(acc[i], 1), _mm256_castps256_ps128(acc[i]));
-                s = _mm_add_ps(s, _mm_movehl_ps(s, s));
-                s = _mm_add_ss(s, _mm_movehdup_ps(s));
-                y[(size_t)(m0 + i) * ldy + r] = _mm_cvtss_f32(s);
-            }
+            for (int i = 0; i < mc; i++) DL_HSUM8(y[(size_t)(m0 + i) * ldy + r], acc[i]);
         }
     }
 }
@@ -243,7 +287,7 @@ float dot_f32_avx2(const float* a, const float* b, int n) {
 
 bool has_avx2() {
 #ifdef DL_X86
-    static const bool v = __builtin_cpu_supports("avx2") && __builtin_cpu_supports("fma")
+    static const bool v = __builtin_cpu_supports("avx2") && __builtin_cpu_supports("fma") && __builtin_cpu_supports("f16c")
                           && !getenv("DLLAMA_CPU_SCALAR");
     return v;
 #else
@@ -274,17 +318,25 @@ float dot_f32(const float* a, const float* b, int n) {
     return r;
 }
 
-// ---- persistent thread pool (reference: NnExecutor spawns nThreads-1 pthreads per forward) -----------
+// ---- persistent thread pool (reference: NnExecutor spawns nThreads-1 pthreads per forward and spins on two
+// atomics, nn-executor.cpp:134-187).  Workers spin for a few tens of microseconds between parallel regions (a forward
+// pass is hundreds of back-to-back regions) and fall asleep on a condition variable when the engine goes idle. -------
+inline void cpu_relax() {
+#ifdef DL_X86
+    _mm_pause();
+#endif
+}
+
 class Pool {
 public:
     explicit Pool(int n) : n_(std::max(1, n)) {
         for (int t = 1; t < n_; t++) workers_.emplace_back([this, t] { loop(t); });
     }
     ~Pool() {
+        quit_.store(true);
+        gen_.fetch_add(1);
         {
             std::lock_guard<std::mutex> g(mu_);
-            quit_ = true;
-            gen_++;
         }
         cv_.notify_all();
         for (auto& w : workers_) w.join();
@@ -293,17 +345,19 @@ public:
     // fn(thread, begin, end) over [0, total) split evenly (reference: SPLIT_THREADS, nn-quants.hpp:82-86)
     void run(int total, const std::function<void(int, int, int)>& fn) {
         if (n_ == 1 || total < 2) { fn(0, 0, total); return; }
-        {
-            std::lock_guard<std::mutex> g(mu_);
-            fn_ = &fn;
-            total_ = total;
-            pending_ = n_ - 1;
-            gen_++;
+        fn_ = &fn;
+        total_ = total;
+        pending_.store(n_ - 1);
+        gen_.fetch_add(1);                      // seq_cst: published before the sleepers check below
+        if (sleepers_.load() > 0) {
+            { std::lock_guard<std::mutex> g(mu_); }
+            cv_.notify_all();
         }
-        cv_.notify_all();
         work(0);
-        std::unique_lock<std::mutex> g(mu_);
-        done_.wait(g, [this] { return pending_ == 0; });
+        int spins = 0;
+        while (pending_.load(std::memory_order_acquire) != 0) {
+            if (++spins < 4096) cpu_relax(); else std::this_thread::yield();
+        }
     }
 
 private:
@@ -313,27 +367,32 @@ private:
         if (e > b) (*fn_)(t, b, e);
     }
     void loop(int t) {
+        static const int kSpin = getenv("DLLAMA_CPU_SPIN") ? atoi(getenv("DLLAMA_CPU_SPIN")) : 200000;
         unsigned long seen = 0;
         while (true) {
-            {
+            int spins = 0;
+            while (gen_.load(std::memory_order_acquire) == seen) {
+                if (++spins < kSpin) { cpu_relax(); continue; }
                 std::unique_lock<std::mutex> g(mu_);
-                cv_.wait(g, [&] { return gen_ != seen; });
-                seen = gen_;
-                if (quit_) return;
+                sleepers_.fetch_add(1);
+                cv_.wait(g, [&] { return gen_.load() != seen; });
+                sleepers_.fetch_sub(1);
             }
+            seen = gen_.load(std::memory_order_acquire);
+            if (quit_.load()) return;
             work(t);
-            std::lock_guard<std::mutex> g(mu_);
-            if (--pending_ == 0) done_.notify_one();
+            pending_.fetch_sub(1, std::memory_order_release);
         }
     }
     int n_;
     std::vector<std::thread> workers_;
     std::mutex mu_;
-    std::condition_variable cv_, done_;
+    std::condition_variable cv_;
     const std::function<void(int, int, int)>* fn_ = nullptr;
-    int total_ = 0, pending_ = 0;
-    unsigned long gen_ = 0;
-    bool quit_ = false;
+    int total_ = 0;
+    std::atomic<int> pending_{0}, sleepers_{0};
+    std::atomic<unsigned long> gen_{0};
+    std::atomic<bool> quit_{false};
 };
 
 // ---- model description ------------------------------------------------------------------------------
@@ -563,6 +622,8 @@ struct Mesh {
         for (size_t i = 0; i < recv_from.size(); i++) x.push_back({peer[recv_from[i]], false, 0, recv_bytes, nullptr, recv_ptr[i]});
         std::vector<pollfd> pf(x.size());
         size_t left = 0;
+        int idle_polls = 0;
+        static const int kSpinPolls = getenv("DLLAMA_CPU_SPIN_POLLS") ? atoi(getenv("DLLAMA_CPU_SPIN_POLLS")) : 20000;
         for (auto& t : x) if (t.total > 0) left++;
         while (left > 0) {
             for (size_t i = 0; i < x.size(); i++) {
@@ -570,9 +631,12 @@ struct Mesh {
                 pf[i].events = x[i].out ? POLLOUT : POLLIN;
                 pf[i].revents = 0;
             }
-            int rc = poll(pf.data(), pf.size(), 30000);
+            // peers reach a synchronisation point within microseconds of each other: look a few times before sleeping
+            int rc = poll(pf.data(), pf.size(), idle_polls < kSpinPolls ? 0 : 30000);
             if (rc < 0 && errno == EINTR) continue;
+            if (rc == 0 && idle_polls < kSpinPolls) { idle_polls++; cpu_relax(); continue; }
             if (rc <= 0) throw std::runtime_error("node synchronisation timed out");
+            idle_polls = 0;
             for (size_t i = 0; i < x.size(); i++) {
                 Xfer& t = x[i];
                 if (pf[i].fd < 0 || !pf[i].revents) continue;
@@ -611,7 +675,17 @@ struct Node {
     std::vector<uint8_t> yq, zq;                // Q80 casts; zq: [n_nodes][M][slice bytes]
     std::vector<std::vector<float>> scores;     // per thread [seq_len]
     std::vector<int> pos, slot;
-    bool stop_requested = false;
+    // DLLAMA_CPU_PROFILE=1: seconds per op family, printed when the node is destroyed (reference: the executor's
+    // per-step-type timers, nn-executor.cpp:150-154)
+    bool profile = getenv("DLLAMA_CPU_PROFILE") != nullptr;
+    double t_matmul = 0, t_att = 0, t_sync = 0, t_other = 0;
+    long long n_forward = 0;
+    ~Node() {
+        if (profile && n_forward > 0)
+            fprintf(stderr, "[cpu-profile] node %d: %lld forwards, per forward: matmul %.2f ms, attention %.2f ms, "
+                    "sync+merge %.2f ms, other %.2f ms\n", c.node, n_forward, 1e3 * t_matmul / n_forward,
+                    1e3 * t_att / n_forward, 1e3 * t_sync / n_forward, 1e3 * t_other / n_forward);
+    }
 
     int N() const { return c.n_nodes; }
     bool q80() const { return c.sync_q80 != 0; }
@@ -789,24 +863,41 @@ struct Node {
             if (pos[m] < 0 || pos[m] >= h.seq_len) throw std::runtime_error("position outside the context window");
             ensure_slot(slot[m]);
         }
+        using clk = std::chrono::steady_clock;
+        auto t_last = clk::now();
+        auto lap = [&](double& acc) {
+            if (!profile) return;
+            const auto t = clk::now();
+            acc += std::chrono::duration<double>(t - t_last).count();
+            t_last = t;
+        };
+        n_forward++;
         for (int l = 0; l < h.n_layers; l++) {
             LayerW& L = layers[l];
             rmsnorm(x.data(), L.rms_att.data(), y.data(), M, dim);
+            lap(t_other);
             matmul(L.wq, y.data(), dim, M, q.data(), qw);
             matmul(L.wk, y.data(), dim, M, k.data(), kvw);
             matmul(L.wv, y.data(), dim, M, v.data(), kvw);
+            lap(t_matmul);
             rope(q.data(), M, qw);
             rope(k.data(), M, kvw);
             for (int m = 0; m < M; m++) {           // (reference: OP_SHIFT, nn-cpu-ops.cpp:1253-1275)
                 memcpy(kc[slot[m]][l].data() + (size_t)pos[m] * kvw, k.data() + (size_t)m * kvw, (size_t)kvw * 4);
                 memcpy(vc[slot[m]][l].data() + (size_t)pos[m] * kvw, v.data() + (size_t)m * kvw, (size_t)kvw * 4);
             }
+            lap(t_other);
             attention(l, M);
+            lap(t_att);
             matmul(L.wo, att_out.data(), qw, M, part.data(), dim);
+            lap(t_matmul);
             sync_and_merge(M);
+            lap(t_sync);
             rmsnorm(x.data(), L.rms_ffn.data(), y.data(), M, dim);
+            lap(t_other);
             matmul(L.w1, y.data(), dim, M, hb.data(), hw);
             matmul(L.w3, y.data(), dim, M, hl.data(), hw);
+            lap(t_matmul);
             pool->run(M * hw, [&](int, int b, int e) {
                 for (int i = b; i < e; i++) {
                     float g = hb[i];
@@ -815,11 +906,16 @@ struct Node {
                     hb[i] = g * hl[i];
                 }
             });
+            lap(t_other);
             matmul(L.w2, hb.data(), hw, M, part.data(), dim);
+            lap(t_matmul);
             sync_and_merge(M);
+            lap(t_sync);
         }
         rmsnorm(x.data() + (size_t)lf * dim, rms_final.data(), y.data(), M - lf, dim);
+        lap(t_other);
         matmul(wcls, y.data(), dim, M - lf, lg.data(), h.vocab / n);
+        lap(t_matmul);
     }
 };
 
