@@ -26,6 +26,11 @@ OBJ = os.path.join(ROOT, "build", "obj")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xptxas", "-v"]
 CXX_FLAGS = ["-O3", "-std=c++17", "-fPIC", "-Wall", "-pthread"]
+# Debug / sanitizer builds (reference: `make DEBUG=1` -> -g -fsanitize=address, Makefile:8-9): extra flags from the
+# environment are appended, e.g.  CXXFLAGS="-g -O1 -fsanitize=address" python build.py --force   (run python with
+# LD_PRELOAD=$(g++ -print-file-name=libasan.so)), NVCCFLAGS="-G" for device debug info.
+CXX_FLAGS += os.environ.get("CXXFLAGS", "").split()
+NVCC_FLAGS += os.environ.get("NVCCFLAGS", "").split()
 
 
 def _find_nvcc() -> str:
@@ -96,7 +101,7 @@ def build_host(force=False, verbose=False) -> str:
         list(ex.map(lambda j: _run(j[0], verbose, j[1]), jobs))
     out = os.path.join(LIB, "libdllama_b200_host.so")
     if force or jobs or _newer(out, objs):
-        _run(["g++", "-shared", "-o", out] + objs + ["-pthread"], verbose)
+        _run(["g++", "-shared", "-o", out] + objs + ["-pthread"] + [f for f in CXX_FLAGS if f.startswith("-fsanitize")], verbose)
     return out
 
 

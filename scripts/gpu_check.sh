@@ -1,6 +1,7 @@
 #!/bin/bash
 # Run every GPU test function in its own process (a faulting kernel must not poison the CUDA context
 # of the other tests), then a short bench.  Output -> gpurun_out/.
+# SANITIZE=memcheck|racecheck|synccheck|initcheck runs every test under compute-sanitizer with that tool.
 set -u
 cd "$(dirname "$0")/.."
 mkdir -p gpurun_out
@@ -11,7 +12,11 @@ FILES="${@:-tests/test_gpu_kernels.py tests/test_gpu_model.py tests/test_f32_eng
 for f in $FILES; do
   for t in $(python -m pytest $f --collect-only -q -m gpu 2>/dev/null | grep "::" | sed 's/\[.*//' | sort -u); do
     echo "=== $t" >> $OUT
-    timeout 300 python -m pytest "$t" -q -m gpu -x --no-header -p no:cacheprovider 2>&1 | tail -n 25 >> $OUT
+    if [ -n "${SANITIZE:-}" ]; then
+      timeout 1200 compute-sanitizer --tool "$SANITIZE" --error-exitcode 1 python -m pytest "$t" -q -m gpu -x --no-header -p no:cacheprovider 2>&1 | tail -n 40 >> $OUT
+    else
+      timeout 300 python -m pytest "$t" -q -m gpu -x --no-header -p no:cacheprovider 2>&1 | tail -n 25 >> $OUT
+    fi
     echo "=== exit $? $t" >> $OUT
   done
 done

@@ -195,3 +195,26 @@ def test_tokenizer_converters(tmp_path, monkeypatch):
     assert t.piece(0x20) == b" " and t.chat_template == "x [INST] y"
     ids = t.encode("a the", add_bos=True)
     assert ids == [259, ord("a"), 258] and t.decode_all(ids) == "a the"
+
+
+def test_required_memory_estimate_matches_file_sizes_and_fits_405b_on_8_gpus():
+    """(reference: printNodeRequiredMemory) the per-node weight bytes of all nodes add up to the file's matrices, and
+    the estimate answers the BASELINE question "does Llama-3.1-405B Q40 fit 8 x 180 GB"."""
+    from dllama_b200.models.memory import B200_HBM_BYTES, required_memory
+    for name in ("llama3.2-1b", "llama3.1-8b"):
+        shape = mfile.MODEL_SHAPES[name]
+        h = mfile.LlmHeader(dim=shape["dim"], hidden_dim=shape["hidden_dim"], n_layers=shape["n_layers"],
+                            n_heads=shape["n_heads"], n_kv_heads=shape["n_kv_heads"], vocab_size=shape["vocab_size"],
+                            seq_len=4096, weight_type=quant.Q40)
+        h.header_size = 0
+        file_matrices = mfile.expected_file_size(h) - h.vocab_size * h.dim * 4          # everything but the embedding
+        for n in (1, 2, 8):
+            m = required_memory(h, n, backend="cpu")
+            replicated = (n - 1) * (2 * h.n_layers + 1) * h.dim * 4                       # norm weights live on every node
+            assert n * m["weights"] == file_matrices + replicated
+    s = mfile.MODEL_SHAPES["llama3.1-405b"]
+    h = mfile.LlmHeader(dim=s["dim"], hidden_dim=s["hidden_dim"], n_layers=s["n_layers"], n_heads=s["n_heads"],
+                        n_kv_heads=s["n_kv_heads"], vocab_size=s["vocab_size"], seq_len=8192, weight_type=quant.Q40)
+    m8 = required_memory(h, 8, max_rows=256, n_slots=34, backend="cuda")
+    assert 28e9 < m8["weights"] < 31e9 and m8["total"] < 0.5 * B200_HBM_BYTES             # ~30 GB of Q40T per rank
+    assert required_memory(h, 1, backend="cuda")["total"] > B200_HBM_BYTES                # and it does not fit one GPU
