@@ -318,6 +318,50 @@ float dot_f32(const float* a, const float* b, int n) {
     return r;
 }
 
+// ---- element-wise op kernels (one row each; the Node methods below split rows / elements over the pool) ------------
+// 1 / sqrt(mean(x^2) + eps)   (reference: invRms_F32, nn-cpu-ops.cpp:105-134)
+float inv_rms(const float* x, int n, float eps) { return 1.0f / sqrtf(dot_f32(x, x, n) / (float)n + eps); }
+
+// y = w * (inv * x)   (reference: rmsNorm_F32, nn-cpu-ops.cpp:136-180)
+void rms_norm_row(const float* x, const float* w, float inv, float* y, int n) {
+    for (int i = 0; i < n; i++) y[i] = w[i] * (inv * x[i]);
+}
+
+// SiLU (act == 1) or tanh-GELU (act == 0) in place   (reference: silu_F32 / gelu_F32, nn-cpu-ops.cpp:672-720)
+inline float activate(float g, int act) {
+    if (act == 1) return g / (1.0f + expf(-g));
+    return 0.5f * g * (1.0f + tanhf(0.797884560802865f * (g + 0.044715f * g * g * g)));
+}
+
+// rotate adjacent pairs of every head of one row at position `pos`   (reference: ropeLlamaForward_F32_F32,
+// nn-cpu-ops.cpp:1090-1120; freq[j] is the rotation frequency of pair j of a head)
+void rope_row(float* r, int width, int head_size, int pos, const float* freq) {
+    for (int i = 0; i < width; i += 2) {
+        const float ang = (float)pos * freq[(i % head_size) / 2];
+        const float cs = cosf(ang), sn = sinf(ang);
+        const float a = r[i], b = r[i + 1];
+        r[i] = a * cs - b * sn;
+        r[i + 1] = a * sn + b * cs;
+    }
+}
+
+// rotation frequency of pair j of a head, with the Llama-3.1 wavelength-dependent scaling when factor != 1
+// (reference: fullfillRopeLlama3Cache + scaleFrequencyLlama3, nn-core.cpp:307-340)
+float rope_frequency(int j, int head_size, float theta, int rope_type, float factor, float low, float high, int orig_len) {
+    float freq = 1.0f / powf(theta, (float)(2 * j) / (float)head_size);
+    if (rope_type == 2 && factor != 1.0f) {
+        const float wave = 2.0f * (float)M_PI / freq;
+        const float high_wl = (float)orig_len / high, low_wl = (float)orig_len / low;
+        if (wave < high_wl) {
+        } else if (wave > low_wl) freq = freq / factor;
+        else {
+            const float smooth = ((float)orig_len / wave - low) / (high - low);
+            freq = (1 - smooth) * freq / factor + smooth * freq;
+        }
+    }
+    return freq;
+}
+
 // ---- persistent thread pool (reference: NnExecutor spawns nThreads-1 pthreads per forward and spins on two
 // atomics, nn-executor.cpp:134-187).  Workers spin for a few tens of microseconds between parallel regions (a forward
 // pass is hundreds of back-to-back regions) and fall asleep on a condition variable when the engine goes idle. -------
@@ -715,20 +759,8 @@ struct Node {
         // rotation frequency of pair j of a head (reference: fullfillRopeLlama3Cache, nn-core.cpp:307-340)
         const int hs = h.head_size();
         rope_freq.resize(hs / 2);
-        for (int j = 0; j < hs / 2; j++) {
-            float freq = 1.0f / powf(h.rope_theta, (float)(2 * j) / (float)hs);
-            if (h.rope_type == 2 && h.rope_factor != 1.0f) {
-                const float wave = 2.0f * (float)M_PI / freq;
-                const float high_wl = (float)h.rope_orig_len / h.rope_high, low_wl = (float)h.rope_orig_len / h.rope_low;
-                if (wave < high_wl) {
-                } else if (wave > low_wl) freq = freq / h.rope_factor;
-                else {
-                    const float smooth = ((float)h.rope_orig_len / wave - h.rope_low) / (h.rope_high - h.rope_low);
-                    freq = (1 - smooth) * freq / h.rope_factor + smooth * freq;
-                }
-            }
-            rope_freq[j] = freq;
-        }
+        for (int j = 0; j < hs / 2; j++)
+            rope_freq[j] = rope_frequency(j, hs, h.rope_theta, h.rope_type, h.rope_factor, h.rope_low, h.rope_high, h.rope_orig_len);
     }
 
     void ensure_slot(int s) {
@@ -746,10 +778,7 @@ struct Node {
         pool->run(M, [&](int, int b, int e) {
             for (int m = b; m < e; m++) {
                 const float* r = in + (size_t)m * dim;
-                float ss = dot_f32(r, r, dim);
-                const float inv = 1.0f / sqrtf(ss / (float)dim + c.h.norm_eps);
-                float* o = out + (size_t)m * dim;
-                for (int i = 0; i < dim; i++) o[i] = w[i] * (inv * r[i]);
+                rms_norm_row(r, w, inv_rms(r, dim, c.h.norm_eps), out + (size_t)m * dim, dim);
             }
         });
     }
@@ -775,16 +804,7 @@ struct Node {
     void rope(float* t, int M, int width) {
         const int hs = c.h.head_size();
         pool->run(M, [&](int, int b, int e) {
-            for (int m = b; m < e; m++) {
-                float* r = t + (size_t)m * width;
-                for (int i = 0; i < width; i += 2) {
-                    const float ang = (float)pos[m] * rope_freq[(i % hs) / 2];
-                    const float cs = cosf(ang), sn = sinf(ang);
-                    const float a = r[i], bb = r[i + 1];
-                    r[i] = a * cs - bb * sn;
-                    r[i + 1] = a * sn + bb * cs;
-                }
-            }
+            for (int m = b; m < e; m++) rope_row(t + (size_t)m * width, width, hs, pos[m], rope_freq.data());
         });
     }
 
@@ -899,12 +919,7 @@ struct Node {
             matmul(L.w3, y.data(), dim, M, hl.data(), hw);
             lap(t_matmul);
             pool->run(M * hw, [&](int, int b, int e) {
-                for (int i = b; i < e; i++) {
-                    float g = hb[i];
-                    if (h.hidden_act == 1) g = g / (1.0f + expf(-g));
-                    else g = 0.5f * g * (1.0f + tanhf(0.797884560802865f * (g + 0.044715f * g * g * g)));
-                    hb[i] = g * hl[i];
-                }
+                for (int i = b; i < e; i++) hb[i] = activate(hb[i], h.hidden_act) * hl[i];
             });
             lap(t_other);
             matmul(L.w2, hb.data(), hw, M, part.data(), dim);
@@ -1328,5 +1343,16 @@ void dl_cpu_matmul_q40_q80(const uint8_t* w, int d, int n, const uint8_t* xq, in
     else matmul_q40_q80(w, 0, d, n / QK, xq, M, y, (size_t)d);
 }
 int dl_cpu_has_avx2(void) { return has_avx2() ? 1 : 0; }
+
+// ---- op-level entry points (unit tests against the reference's goldens, src/nn/nn-cpu-ops-test.cpp) ----
+float dl_cpu_inv_rms(const float* x, int n, float eps) { return inv_rms(x, n, eps); }
+void dl_cpu_rms_norm(const float* x, const float* w, float* y, int n, float eps) { rms_norm_row(x, w, inv_rms(x, n, eps), y, n); }
+void dl_cpu_activation(float* x, int n, int act /*1 = SiLU, 0 = GELU*/) { for (int i = 0; i < n; i++) x[i] = activate(x[i], act); }
+void dl_cpu_rope(float* row, int width, int head_size, int pos, float theta, int rope_type, float factor, float low,
+                 float high, int orig_len) {
+    std::vector<float> freq(head_size / 2);
+    for (int j = 0; j < head_size / 2; j++) freq[j] = rope_frequency(j, head_size, theta, rope_type, factor, low, high, orig_len);
+    rope_row(row, width, head_size, pos, freq.data());
+}
 
 }  // extern "C"

@@ -83,6 +83,8 @@ using dljson::Value;
 enum { EOS_MAYBE = 0, EOS_YES = 1, EOS_NO = 2 };
 constexpr uint64_t kListenId = 0, kEventId = 1, kFirstConnId = 16;
 constexpr size_t kMaxHeader = 64 * 1024, kMaxBody = 32u * 1024 * 1024;
+constexpr double kIdleSeconds = 30.0;       // time a client has to deliver its request
+constexpr size_t kMaxConnections = 8192;
 
 struct Conn {
     int fd = -1;
@@ -94,6 +96,7 @@ struct Conn {
     bool dispatched = false;        // a request of this connection has been routed
     bool sent_continue = false;
     bool want_out = false;          // EPOLLOUT armed
+    double t_open = 0.0;            // connections that never send a complete request are dropped after kIdleSeconds
     // shared (Server::mu)
     std::string out;
     bool close_after = false;
@@ -702,6 +705,7 @@ void on_readable(Server* s, uint64_t id) {
 void io_loop(Server* s) {
     epoll_event evs[128];
     std::vector<uint64_t> todo;
+    double last_sweep = now_s();
     while (!s->stop.load(std::memory_order_acquire)) {
         int n = epoll_wait(s->ep, evs, 128, 200);
         for (int i = 0; i < n; i++) {
@@ -716,9 +720,11 @@ void io_loop(Server* s) {
                     const uint64_t cid = s->next_conn++;
                     {
                         std::lock_guard<std::mutex> g(s->mu);
+                        if (s->conns.size() >= kMaxConnections) { close(fd); continue; }
                         Conn& c = s->conns[cid];
                         c.fd = fd;
                         c.id = cid;
+                        c.t_open = now_s();
                     }
                     epoll_event ev{};
                     ev.events = EPOLLIN | EPOLLRDHUP;
@@ -736,10 +742,18 @@ void io_loop(Server* s) {
             }
         }
         todo.clear();
+        const double now = now_s();
+        std::vector<uint64_t> stale;
         {
             std::lock_guard<std::mutex> g(s->mu);
             todo.swap(s->dirty);
+            if (now - last_sweep > 1.0) {           // slow or silent clients must not pin connections for ever
+                last_sweep = now;
+                for (auto& kv : s->conns)
+                    if (!kv.second.dispatched && now - kv.second.t_open > kIdleSeconds) stale.push_back(kv.first);
+            }
         }
+        for (uint64_t id : stale) close_conn(s, id);
         uint64_t last = 0;
         for (uint64_t id : todo) {              // the engine thread queues one entry per chunk
             if (id == last) continue;

@@ -174,3 +174,63 @@ def test_invalid_node_counts_are_rejected(tiny_model_path):
         N.NativeCpuEngine(tiny_model_path, workers=[("127.0.0.1", 1)] * 2, max_seq_len=64)
     with pytest.raises((RuntimeError, FileNotFoundError)):
         N.NativeCpuEngine("/nonexistent.m")
+
+
+# ---- op-level goldens of the reference's unit tests (src/nn/nn-cpu-ops-test.cpp, src/nn/nn-vulkan-test.cpp) -------
+def _op_lib():
+    import ctypes as C
+    L = N._lib()
+    L.dl_cpu_inv_rms.restype = C.c_float
+    L.dl_cpu_inv_rms.argtypes = [C.c_void_p, C.c_int, C.c_float]
+    L.dl_cpu_rms_norm.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_float]
+    L.dl_cpu_activation.argtypes = [C.c_void_p, C.c_int, C.c_int]
+    L.dl_cpu_rope.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, C.c_float, C.c_float, C.c_float, C.c_int]
+    return L
+
+
+def test_inv_rms_rmsnorm_and_silu_goldens():
+    L = _op_lib()
+    x = np.array([0.1, 0.3, 0.2, 0.4, 0.6, 0.5, 0.0, 0.8], dtype=np.float32)
+    assert abs(L.dl_cpu_inv_rms(x.ctypes.data, 8, 1e-5) - 1.0 / 0.4402) < 0.001            # nn-cpu-ops-test.cpp:102-118
+    # the Vulkan op test's rmsnorm goldens: rows of 256 values i/256 scaled by (b+1)  (nn-vulkan-test.cpp:91-93)
+    w = np.linspace(0.5, 1.5, 8, dtype=np.float32)
+    y = np.empty(8, dtype=np.float32)
+    L.dl_cpu_rms_norm(x.ctypes.data, w.ctypes.data, y.ctypes.data, 8, 1e-5)
+    inv = 1.0 / np.sqrt((x.astype(np.float64) ** 2).mean() + 1e-5)
+    assert np.allclose(y, w * (inv * x), rtol=1e-6)
+    # rmsNorm on Q80-rounded input stays within the reference's 0.01 of the f32 result (nn-cpu-ops-test.cpp:121-137)
+    rng = np.random.default_rng(3)
+    xr, wr = rng.uniform(-1, 1, 256).astype(np.float32), rng.uniform(-1, 1, 256).astype(np.float32)
+    xq = N.dequantize_q80(N.quantize_q80(xr), 256)
+    y1, y2 = np.empty(256, dtype=np.float32), np.empty(256, dtype=np.float32)
+    inv = L.dl_cpu_inv_rms(xr.ctypes.data, 256, 1e-5)
+    L.dl_cpu_rms_norm(xr.ctypes.data, wr.ctypes.data, y1.ctypes.data, 256, 1e-5)
+    y2[:] = wr * (inv * xq)
+    assert np.abs(y1 - y2).max() < 0.01
+    s = (np.arange(8) / 8.0).astype(np.float32)
+    L.dl_cpu_activation(s.ctypes.data, 8, 1)
+    want = [0.000000, 0.066401, 0.140544, 0.222250, 0.311233, 0.407116, 0.509461, 0.617802]   # nn-cpu-ops-test.cpp:200-216
+    assert np.abs(s - np.array(want, dtype=np.float32)).max() < 0.001
+    g = np.array([-1.0, 0.0, 1.0, 2.0], dtype=np.float32)
+    L.dl_cpu_activation(g.ctypes.data, 4, 0)
+    assert np.allclose(g, [-0.158808, 0.0, 0.841192, 1.954598], atol=1e-5)                      # tanh-GELU
+
+
+def test_rope_goldens_of_the_reference_vulkan_test():
+    """x = 1 everywhere, dim 2048 = 32 heads of 64, theta 5e5, Llama-3.1 scaling 32 / 1 / 4 / 8192, positions 6 and 31
+    (nn-vulkan-test.cpp:426-482) -- for the host kernel and for the oracle's rotation used by the CUDA tests."""
+    from dllama_b200.models.oracle import apply_rope, rope_frequencies
+    L = _op_lib()
+    gold = {6: {0: 1.239586, 1: 0.680755, 2: 0.077202, 3: -1.412105, 1988: -1.356766, 2022: 0.999923, 2023: 1.000077},
+            31: {0: 1.318780, 1: 0.510705, 1078: 0.999985, 1079: 1.000015}}
+    h = mfile.LlmHeader(dim=2048, n_heads=32, n_kv_heads=8, rope_theta=500000.0, rope_type=mfile.ROPE_LLAMA3_1,
+                        rope_scaling_factor=32.0, rope_scaling_low_freq_factor=1.0, rope_scaling_high_freq_factor=4.0,
+                        rope_scaling_orig_max_seq_len=8192)
+    f = rope_frequencies(h)
+    for pos, vals in gold.items():
+        row = np.ones(2048, dtype=np.float32)
+        L.dl_cpu_rope(row.ctypes.data, 2048, 64, pos, 500000.0, 2, 32.0, 1.0, 4.0, 8192)
+        y = apply_rope(torch.ones(1, 2048), torch.tensor([pos]), f, 64)[0].numpy()
+        for i, v in vals.items():
+            assert abs(row[i] - v) < 5e-6, (pos, i, row[i], v)
+            assert abs(y[i] - v) < 5e-6, (pos, i, y[i], v)
