@@ -304,16 +304,35 @@ def _random_q40_bytes(rng: np.random.Generator, n_blocks: int, scale: float) -> 
 
 def write_random_model(path: str, shape_name_or_dict, weight_type: int = quant.Q40, seed: int = 1,
                        n_layers: Optional[int] = None, std: float = 0.02, exact: bool = False,
-                       chunk_rows: int = 4096) -> LlmHeader:
+                       chunk_rows: int = 4096, native: Optional[bool] = None) -> LlmHeader:
     """Write a random-init `.m` of the given architecture.
 
     ``exact=True`` draws N(0,std) f32 weights and runs the real quantizer (small models / tests);
     otherwise Q40 blocks are drawn directly in the quantized domain (uniform nibbles, scales
     ~ std/8), which is statistically equivalent for benchmarking and ~100x faster for the 6 GB
-    8B file.
+    8B file.  ``native=True`` (default for files above 64 GB, or DLLAMA_FAST_WRITER=1) fills the file from several
+    threads in C++ (csrc/host/model_writer.cpp; same recipe, different random stream): the 238 GB Llama-3.1-405B
+    file takes a minute instead of twenty.
     """
     shape = MODEL_SHAPES[shape_name_or_dict] if isinstance(shape_name_or_dict, str) else shape_name_or_dict
     params = header_params(shape, weight_type, n_layers)
+    if native is None:
+        n_par = params["n_layers"] * (2 * params["dim"] ** 2 + 3 * params["dim"] * params["hidden_dim"])
+        native = os.environ.get("DLLAMA_FAST_WRITER") == "1" or n_par * 0.5625 > 64e9
+    if native and weight_type == quant.Q40 and not exact:
+        import ctypes as C
+        from ..text.native import host_lib
+        L = host_lib()
+        L.dl_write_random_model_q40.restype = C.c_longlong
+        L.dl_write_random_model_q40.argtypes = [C.c_char_p, C.POINTER(C.c_int), C.c_int, C.c_ulonglong, C.c_float, C.c_int]
+        kv = []
+        for key, value in params.items():
+            kv += [HEADER_KEYS[key], int(value)]
+        arr = (C.c_int * len(kv))(*kv)
+        rc = L.dl_write_random_model_q40(path.encode(), arr, len(kv) // 2, seed, std, 0)
+        if rc < 0:
+            raise OSError(f"native model writer failed ({rc}) for {path}")
+        return read_header(path)
     rng = np.random.default_rng(seed)
     dim, hid = params["dim"], params["hidden_dim"]
     kv_dim = dim * params["n_kv_heads"] // params["n_heads"]

@@ -218,3 +218,27 @@ def test_required_memory_estimate_matches_file_sizes_and_fits_405b_on_8_gpus():
     m8 = required_memory(h, 8, max_rows=256, n_slots=34, backend="cuda")
     assert 28e9 < m8["weights"] < 31e9 and m8["total"] < 0.5 * B200_HBM_BYTES             # ~30 GB of Q40T per rank
     assert required_memory(h, 1, backend="cuda")["total"] > B200_HBM_BYTES                # and it does not fit one GPU
+
+
+def test_native_random_model_writer_produces_a_valid_equivalent_file(tmp_path):
+    """csrc/host/model_writer.cpp (multi-threaded, for the 40-240 GB files): same layout, same size, same weight
+    statistics as the NumPy generator, deterministic per seed, loadable by the engines."""
+    a, b, c = str(tmp_path / "a.m"), str(tmp_path / "b.m"), str(tmp_path / "c.m")
+    ha = mfile.write_random_model(a, "tiny-tp8", seed=7, native=True)
+    mfile.write_random_model(b, "tiny-tp8", seed=7, native=True)
+    mfile.write_random_model(c, "tiny-tp8", seed=7, native=False)
+    assert os.path.getsize(a) == mfile.expected_file_size(ha) == os.path.getsize(c)
+    assert open(a, "rb").read() == open(b, "rb").read()                       # same seed -> same bytes, whatever the thread timing
+    ma, mc = mfile.ModelFile(a), mfile.ModelFile(c)
+    assert ma.header.dim == mc.header.dim and ma.header.n_layers == mc.header.n_layers
+    for name, layer in (("wq", 0), ("w2", 1), ("wcls", -1)):
+        wa, wc = ma.f32(name, layer), mc.f32(name, layer)
+        assert wa.shape == wc.shape and abs(wa.std() - wc.std()) < 0.05 * wc.std() and abs(wa.mean()) < 1e-3
+    assert abs(ma.f32("embedding").std() - 1.0) < 0.02 and abs(ma.f32("rms_ffn", 1).mean() - 1.0) < 0.02
+    ma.close()
+    mc.close()
+    from dllama_b200.models.native_cpu_engine import NativeCpuEngine
+    eng = NativeCpuEngine(a, n_threads=2, max_rows=4, n_slots=1, max_seq_len=64)
+    lg = eng.forward([1, 2, 3], [0, 1, 2], [0, 0, 0]).numpy()
+    assert np.isfinite(lg).all() and lg.std() > 0
+    eng.close()
