@@ -227,6 +227,7 @@ class LlamaEngine:
                                        dtype=torch.uint8, device=dev)
         self.argmax_scratch = torch.zeros(int(K.cuda_lib().dl_argmax_scratch_bytes(256)), dtype=torch.uint8,
                                           device=dev)
+        self._staging_ev: Optional[torch.cuda.Event] = None
         self._graphs: Dict[Tuple, torch.cuda.CUDAGraph] = {}
         self._graph_launches: Dict[Tuple, int] = {}
         self._graph_stream = torch.cuda.Stream(device=dev)
@@ -504,6 +505,12 @@ class LlamaEngine:
         M = len(tokens)
         assert 1 <= M <= self.max_rows
         hd = self._hd
+        # The pinned staging buffers (descriptor, block table) are read by the copy engine when the async copy
+        # EXECUTES, which can be a whole forward pass after it was enqueued (prompt chunks and worker ranks run
+        # back to back without a host sync).  Do not overwrite them before the previous copy has been consumed.
+        ev = self._staging_ev
+        if ev is not None:
+            ev.synchronize()
         if M == 1 and not self.bucket_rows:          # single-stream decode: the latency-critical host path
             hd[0, 0], hd[1, 0], hd[2, 0] = tokens[0], positions[0], slots[0]
             self._chunk = False
@@ -511,6 +518,7 @@ class LlamaEngine:
             if self.pages.dirty:
                 self._sync_block_table()
             self._desc3.copy_(self._h_desc3, non_blocking=True)
+            self._mark_staging()
             return 1
         off = 0
         if self.bucket_rows:
@@ -552,7 +560,16 @@ class LlamaEngine:
             self.desc.copy_(self.h_desc, non_blocking=True)
         else:
             self._desc3.copy_(self._h_desc3, non_blocking=True)
+        self._mark_staging()
         return M
+
+    def _mark_staging(self):
+        """Record the point in the stream after which the pinned staging buffers may be rewritten."""
+        if self.device.type != "cuda":
+            return
+        if self._staging_ev is None:
+            self._staging_ev = torch.cuda.Event()
+        self._staging_ev.record()
 
     def forward(self, tokens, positions, slots, logits_from: int = 0, greedy: bool = False) -> torch.Tensor:
         """One forward over a batch of rows (any mix of decode rows and prefill-chunk rows; rows of
