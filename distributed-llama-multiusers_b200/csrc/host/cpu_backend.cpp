@@ -247,13 +247,16 @@ void matmul_q40_q80_avx2(const uint8_t* w, int r0, int r1, int nb, const uint8_t
         }
         return;
     }
-    constexpr int MB = 8;                       // batch rows per pass: weights unpacked once, accumulators in registers
+    // batch rows: weights unpacked once per block and reused for 4 rows.  Same arithmetic per row as the decode path
+    // above (even blocks -> chain 0, odd blocks -> chain 1, chains added, then the horizontal sum), so a row's result
+    // does not depend on which other rows share its batch: continuous batching stays bit-reproducible.
+    constexpr int MB = 4;
     for (int r = r0; r < r1; r++) {
         const uint8_t* wr = w + (size_t)r * nb * Q40_BYTES;
         for (int m0 = 0; m0 < M; m0 += MB) {
             const int mc = std::min(MB, M - m0);
-            __m256 acc[MB];
-            for (int i = 0; i < MB; i++) acc[i] = _mm256_setzero_ps();
+            __m256 acc0[MB], acc1[MB];
+            for (int i = 0; i < MB; i++) { acc0[i] = _mm256_setzero_ps(); acc1[i] = _mm256_setzero_ps(); }
             for (int b = 0; b < nb; b++) {
                 const uint8_t* wb = wr + (size_t)b * Q40_BYTES;
                 uint16_t dwh;
@@ -261,12 +264,16 @@ void matmul_q40_q80_avx2(const uint8_t* w, int r0, int r1, int nb, const uint8_t
                 const float dw = _cvtsh_ss(dwh);
                 __m256i wv, aw;
                 DL_UNPACK(wb, wv, aw);
+                __m256* acc = (b & 1) && b + 1 <= (nb & ~1) ? acc1 : acc0;      // a trailing odd block joins chain 0, as above
                 for (int i = 0; i < mc; i++) {
                     const size_t xi = (size_t)(m0 + i) * nb + b;
                     acc[i] = _mm256_fmadd_ps(_mm256_set1_ps(dw * xd[xi]), DL_BLOCK_DOT(aw, wv, xq + xi * Q80_BYTES + 2), acc[i]);
                 }
             }
-            for (int i = 0; i < mc; i++) DL_HSUM8(y[(size_t)(m0 + i) * ldy + r], acc[i]);
+            for (int i = 0; i < mc; i++) {
+                const __m256 t = _mm256_add_ps(acc0[i], acc1[i]);
+                DL_HSUM8(y[(size_t)(m0 + i) * ldy + r], t);
+            }
         }
     }
 }

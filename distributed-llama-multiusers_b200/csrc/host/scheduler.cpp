@@ -3,9 +3,11 @@
 // D1-D4: here every request keeps its own prompt, position and KV slot, prompts are prefilled in
 // chunks, and any number of HTTP threads can submit concurrently).
 //
-// Policy per step: every running (decoding) request contributes one row; if rows are left, ONE
-// request that still has prompt tokens to evaluate contributes a chunk of them, placed FIRST in
-// the batch so that the rows needing logits form the contiguous tail [logits_from, n).
+// Policy per step: every running (decoding) request contributes one row; the remaining rows (at least a quarter
+// of the batch while prompts are pending) go to requests that still have prompt tokens to evaluate, in admission
+// order, at most prefill_chunk rows each.  Prompt rows that need no logits come FIRST; the last row of every prompt
+// that completes in this step is moved in front of the decode rows, so that the rows needing logits form the
+// contiguous tail [logits_from, n).
 // Thread-safe: submit/cancel from any thread; next_batch/commit from the engine loop thread.
 #include <algorithm>
 #include <chrono>

@@ -148,7 +148,6 @@ struct Server {
     std::vector<long long> cancelled;       // requests whose scheduler entry still has to be forgotten
     // engine thread only
     std::vector<long long> batch_all, batch_ids;
-    std::vector<long long> scratch_ids;
     std::vector<int> scratch_stop, scratch_fin;
     std::vector<char> piece_buf;
     // counters (Server::mu)
@@ -796,7 +795,6 @@ void* dl_srv_new(void* tokenizer, const char* model_name, int chat_type, const c
     }
     s->batch_all.resize(max_rows);
     s->batch_ids.resize(max_rows);
-    s->scratch_ids.resize(max_rows);
     s->scratch_stop.resize(max_rows);
     s->scratch_fin.resize(max_rows);
     s->batch_all.clear();

@@ -62,6 +62,15 @@ def test_q40_q80_matmul_kernels_agree_with_dequantised_f32():
     yv = N.matmul_q40_q80(wq, d, n, xq, M, force_scalar=False)
     assert np.abs(ys - want).max() < 1e-4 and np.abs(yv - want).max() < 1e-4
     assert np.abs(ys - yv).max() < 1e-5
+    # batch invariance: a row's result does not depend on its batch mates (odd block counts included)
+    for n2 in (256, 288):
+        w2 = (rng.standard_normal((d, n2)) * 0.05).astype(np.float32)
+        x2 = rng.standard_normal((M, n2)).astype(np.float32)
+        wq2 = np.frombuffer(quant.quantize_q40(w2).tobytes(), dtype=np.uint8)
+        xq2 = N.quantize_q80(x2)
+        rb = n2 // 32 * 34
+        rows = np.stack([N.matmul_q40_q80(wq2, d, n2, xq2[m * rb:(m + 1) * rb], 1)[0] for m in range(M)])
+        assert np.array_equal(N.matmul_q40_q80(wq2, d, n2, xq2, M), rows)
 
 
 def _free_ports(n):

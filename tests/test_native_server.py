@@ -227,3 +227,138 @@ def test_native_server_many_concurrent_streams(tiny_model_path, tok):
         assert st["requests"] == 12 and st["running"] == 0 and st["waiting"] == 0 and st["free_slots"] == 3
     finally:
         srv.close()
+
+
+class _FakeEngine:
+    """Engine surface without a model (fixed tokens): lets the front end be hammered quickly."""
+
+    class _Pages:
+        def __init__(self):
+            self.released = []
+
+        def release_pages(self, slot):
+            self.released.append(slot)
+
+    class _H:
+        vocab_size = 1024
+
+    def __init__(self, max_rows, n_slots, seq_len):
+        import torch
+        self.h, self.pages = self._H(), self._Pages()
+        self.max_rows, self.n_slots, self.seq_len = max_rows, n_slots, seq_len
+        self.device = torch.device("cpu")
+
+    def forward(self, tokens, positions, slots, logits_from=0, greedy=False):
+        import torch
+        n = len(tokens) - logits_from
+        lg = torch.zeros(n, 1024)
+        for i in range(n):
+            lg[i, 5 + (positions[logits_from + i] * 7 + slots[logits_from + i]) % 900] = 10.0
+        return lg
+
+    def decode_step_greedy(self, tokens, positions, slots, logits_from=0):
+        return [5 + (positions[i] * 7 + slots[i]) % 900 for i in range(logits_from, len(tokens))]
+
+
+def test_native_server_survives_a_storm_of_partial_requests_and_disconnects(tok):
+    """Clients that connect and leave at every stage (no bytes, half a header, half a body, mid-stream), pipelined
+    garbage, oversized declarations -- while well-behaved users are being served.  Nothing may leak or wedge."""
+    eng = _FakeEngine(max_rows=8, n_slots=4, seq_len=256)
+    defaults = A.InferenceParams(messages=[], temperature=0.0, top_p=0.9, seed=1)
+    srv = NativeApiServer(eng, tok, "fake.m", defaults, host="127.0.0.1", port=0, verbose=False)
+    srv.start()
+    port = srv.port
+    body = json.dumps({"messages": [{"role": "user", "content": "hello world the of and"}], "max_tokens": 40,
+                       "stream": True}).encode()
+    head = (b"POST /v1/chat/completions HTTP/1.1\r\nHost: x\r\nContent-Type: application/json\r\nContent-Length: "
+            + str(len(body)).encode() + b"\r\n\r\n")
+    good = {}
+
+    def good_user(i):
+        with _post(port, {"messages": [{"role": "user", "content": "hello world"}], "max_tokens": 16}) as r:
+            good[i] = json.load(r)
+
+    def bad_client(kind):
+        try:
+            s = socket.create_connection(("127.0.0.1", port), timeout=10)
+            if kind == 0:
+                pass                                            # connect and leave
+            elif kind == 1:
+                s.sendall(head[:25])                            # half a request line / header
+            elif kind == 2:
+                s.sendall(head + body[:10])                     # half a body
+            elif kind == 3:
+                s.sendall(head + body)                          # full request, leave while it streams
+                s.recv(200)
+            elif kind == 4:
+                s.sendall(b"\x00\xff garbage\r\n\r\n")          # not HTTP
+                s.recv(200)
+            elif kind == 5:
+                s.sendall(b"POST /v1/chat/completions HTTP/1.1\r\nContent-Length: 99999999999\r\n\r\n")
+                assert b"413" in s.recv(200)
+            elif kind == 6:
+                s.sendall(head + body + head + body)            # pipelined second request is ignored
+                s.recv(200)
+            s.close()
+        except OSError:
+            pass
+
+    try:
+        threads = [threading.Thread(target=bad_client, args=(k % 7,)) for k in range(70)]
+        threads += [threading.Thread(target=good_user, args=(i,)) for i in range(10)]
+        import random
+        random.Random(3).shuffle(threads)
+        [t.start() for t in threads]
+        [t.join(timeout=120) for t in threads]
+        assert len(good) == 10 and all(g["usage"]["completion_tokens"] >= 1 for g in good.values())
+        t0 = time.time()
+        while time.time() - t0 < 60:
+            st = srv.stats()
+            if st["running"] == 0 and st["waiting"] == 0 and st["free_slots"] == 4 and st["connections"] <= 20:
+                break
+            time.sleep(0.05)
+        assert st["running"] == 0 and st["waiting"] == 0 and st["free_slots"] == 4, st
+        # half-open clients (kinds 1, 2) are still counted until their deadline; everything else is gone
+        assert st["connections"] <= 20, st
+        with _post(port, {"messages": [{"role": "user", "content": "hello world"}], "max_tokens": 4}) as r:
+            assert json.load(r)["usage"]["completion_tokens"] >= 1
+    finally:
+        srv.close()
+
+
+def test_full_native_stack_http_server_on_the_tcp_tensor_parallel_cpu_backend(tiny_model_path, tok):
+    """HTTP -> C++ server -> C++ host backend on two nodes over loopback TCP: the whole no-GPU product with no
+    Python on any per-token path except the engine thread's three calls.  Text must equal the single-node server's."""
+    from dllama_b200.models import native_cpu_engine as NC
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        wport = s.getsockname()[1]
+    w = threading.Thread(target=NC.serve_worker, args=(wport, 1), daemon=True)
+    w.start()
+    time.sleep(0.3)
+    eng2 = NC.NativeCpuEngine(tiny_model_path, workers=[("127.0.0.1", wport)], n_threads=1, max_rows=8, n_slots=4, max_seq_len=256)
+    eng1 = NC.NativeCpuEngine(tiny_model_path, n_threads=2, max_rows=8, n_slots=4, max_seq_len=256)
+    srv2, srv1 = _native(tiny_model_path, tok, engine=eng2), _native(tiny_model_path, tok, engine=eng1)
+    try:
+        out = {}
+
+        def user(key, port, text):
+            with _post(port, {"messages": [{"role": "user", "content": text}], "max_tokens": 8}) as r:
+                out[key] = json.load(r)
+
+        texts = ["hello world", "the of and", "token model fast"]
+        threads = [threading.Thread(target=user, args=((p, i), p, t)) for p in (srv1.port, srv2.port) for i, t in enumerate(texts)]
+        [t.start() for t in threads]
+        [t.join(timeout=180) for t in threads]
+        assert len(out) == 6
+        for i in range(3):
+            a, b = out[(srv1.port, i)], out[(srv2.port, i)]
+            assert a["choices"][0]["message"]["content"] == b["choices"][0]["message"]["content"] and a["usage"] == b["usage"]
+        assert eng2.network_stats()["sent_bytes"] > 0
+    finally:
+        srv2.close()
+        srv1.close()
+        eng2.close()
+        eng1.close()
+        w.join(timeout=30)
+    assert not w.is_alive()
