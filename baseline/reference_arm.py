@@ -134,6 +134,7 @@ def run_reference_arm(args, metric: str) -> dict:
 
 
 _PORT_BASE = [9990]
+LAST_RUN = {}            # extra figures of the most recent _run_once (evaluation tok/s of the reference's summary block)
 
 
 def _run_once(binary, mpath, tpath, prompt, n_prompt, N, nthreads, W, K_):
@@ -210,6 +211,8 @@ def _run_once(binary, mpath, tpath, prompt, n_prompt, N, nthreads, W, K_):
     m = re.search(r"Prediction\s+nTokens:\s*(\d+)\s+tokens/s:\s*([\d.]+)\s*\(([\d.]+) ms/tok\)", summary)
     if not m:
         raise RuntimeError("could not parse the reference's summary: " + summary[-200:].replace("\n", " | "))
+    e = re.search(r"Evaluation\s+nBatches:\s*\d+\s+nTokens:\s*(\d+)\s+tokens/s:\s*([\d.]+)", summary)
+    LAST_RUN["eval_tokens_per_s"] = float(e.group(2)) if e else None
     timed = pred_ms[W:W + K_] if len(pred_ms) >= W + K_ else pred_ms
     # per-step times are printed in whole milliseconds; below ~20 ms use the summary block's exact mean
     ms_per_step = float(m.group(3)) if not timed or min(timed) < 20 else sum(timed) / len(timed)

@@ -278,6 +278,67 @@ void matmul_q40_q80_avx2(const uint8_t* w, int r0, int r1, int nb, const uint8_t
     }
 }
 
+// AVX-512 VNNI kernel: two Q40 blocks (64 weights) per instruction.  Activations are re-packed once per call into
+// contiguous int8 pairs of blocks + a 16-lane vector of their scales, so the inner loop is: one 64-byte load, a masked
+// negate (sign transfer), VPDPBUSD, convert, scale, accumulate.  One accumulator chain per row for every batch size, so
+// results do not depend on the batch a row travels in (same property as the AVX2 kernel).
+__attribute__((target("avx512f,avx512bw,avx512vl,avx512vnni,avx2,fma,f16c")))
+void matmul_q40_q80_vnni(const uint8_t* w, int r0, int r1, int nb, const uint8_t* xq, int M, float* y, size_t ldy) {
+    const int np = (nb + 1) / 2;
+    // [M][np][64] int8 and [M][np][16] f32 (lanes 0-7: scale of the even block, 8-15: of the odd block; padding = 0)
+    std::vector<int8_t> x8((size_t)M * np * 64 + 64, 0);
+    std::vector<float> xs((size_t)M * np * 16 + 16, 0.f);
+    for (int m = 0; m < M; m++)
+        for (int b = 0; b < nb; b++) {
+            const uint8_t* xb = xq + ((size_t)m * nb + b) * Q80_BYTES;
+            uint16_t h;
+            memcpy(&h, xb, 2);
+            const float d = _cvtsh_ss(h);
+            const size_t pi = (size_t)m * np + b / 2;
+            memcpy(&x8[pi * 64 + (b & 1) * 32], xb + 2, 32);
+            float* sv = &xs[pi * 16 + (b & 1) * 8];
+            for (int j = 0; j < 8; j++) sv[j] = d;
+        }
+    const __m512i low = _mm512_set1_epi8(0x0f), eight = _mm512_set1_epi8(8), zero = _mm512_setzero_si512();
+    constexpr int MB = 8;
+    for (int r = r0; r < r1; r++) {
+        const uint8_t* wr = w + (size_t)r * nb * Q40_BYTES;
+        for (int m0 = 0; m0 < M; m0 += MB) {
+            const int mc = std::min(MB, M - m0);
+            __m512 acc[MB];
+            for (int i = 0; i < MB; i++) acc[i] = _mm512_setzero_ps();
+            for (int p = 0; p < np; p++) {
+                const uint8_t* w0 = wr + (size_t)(2 * p) * Q40_BYTES;
+                const bool pair = 2 * p + 1 < nb;
+                uint16_t h0, h1 = 0;
+                memcpy(&h0, w0, 2);
+                const __m128i raw0 = _mm_loadu_si128((const __m128i*)(w0 + 2));
+                __m128i raw1 = _mm_setzero_si128();
+                if (pair) {
+                    memcpy(&h1, w0 + Q40_BYTES, 2);
+                    raw1 = _mm_loadu_si128((const __m128i*)(w0 + Q40_BYTES + 2));
+                }
+                const __m256i v0 = _mm256_set_m128i(_mm_srli_epi16(raw0, 4), raw0);      // low nibbles = elements 0..15
+                const __m256i v1 = _mm256_set_m128i(_mm_srli_epi16(raw1, 4), raw1);
+                __m512i wv = _mm512_inserti64x4(_mm512_castsi256_si512(v0), v1, 1);
+                wv = _mm512_sub_epi8(_mm512_and_si512(wv, low), eight);
+                const __m512i aw = _mm512_abs_epi8(wv);
+                const __mmask64 neg = _mm512_movepi8_mask(wv);
+                const __m512 dwv = _mm512_mask_blend_ps((__mmask16)0xFF00, _mm512_set1_ps(_cvtsh_ss(h0)),
+                                                        _mm512_set1_ps(pair ? _cvtsh_ss(h1) : 0.f));
+                for (int i = 0; i < mc; i++) {
+                    const size_t pi = (size_t)(m0 + i) * np + p;
+                    const __m512i xv = _mm512_loadu_si512((const void*)&x8[pi * 64]);
+                    const __m512i sx = _mm512_mask_sub_epi8(xv, neg, zero, xv);            // x with the weight's sign
+                    const __m512 pf = _mm512_cvtepi32_ps(_mm512_dpbusd_epi32(zero, aw, sx));
+                    acc[i] = _mm512_fmadd_ps(pf, _mm512_mul_ps(dwv, _mm512_loadu_ps(&xs[pi * 16])), acc[i]);
+                }
+            }
+            for (int i = 0; i < mc; i++) y[(size_t)(m0 + i) * ldy + r] = _mm512_reduce_add_ps(acc[i]);
+        }
+    }
+}
+
 __attribute__((target("avx2,fma")))
 float dot_f32_avx2(const float* a, const float* b, int n) {
     __m256 acc = _mm256_setzero_ps();
@@ -291,6 +352,17 @@ float dot_f32_avx2(const float* a, const float* b, int n) {
     return r;
 }
 #endif
+
+bool has_vnni() {
+#ifdef DL_X86
+    static const bool v = __builtin_cpu_supports("avx512f") && __builtin_cpu_supports("avx512bw") &&
+                          __builtin_cpu_supports("avx512vl") && __builtin_cpu_supports("avx512vnni") &&
+                          __builtin_cpu_supports("f16c") && !getenv("DLLAMA_CPU_SCALAR") && !getenv("DLLAMA_CPU_NO_AVX512");
+    return v;
+#else
+    return false;
+#endif
+}
 
 bool has_avx2() {
 #ifdef DL_X86
@@ -311,6 +383,7 @@ void quantize_q80(const float* x, uint8_t* out, int n) {
 
 void matmul_q40_q80(const uint8_t* w, int r0, int r1, int nb, const uint8_t* xq, int M, float* y, size_t ldy) {
 #ifdef DL_X86
+    if (has_vnni()) return matmul_q40_q80_vnni(w, r0, r1, nb, xq, M, y, ldy);
     if (has_avx2()) return matmul_q40_q80_avx2(w, r0, r1, nb, xq, M, y, ldy);
 #endif
     matmul_q40_q80_scalar(w, r0, r1, nb, xq, M, y, ldy);
@@ -1345,11 +1418,17 @@ void dl_cpu_quantize_q40(const float* x, uint8_t* out, int n) {
 unsigned short dl_cpu_f32_to_f16(float f) { return f32_to_f16(f); }
 float dl_cpu_f16_to_f32(unsigned short h) { return f16_to_f32(h); }
 // y[m][r] for rows [0, d): scalar or dispatched kernel (tests compare the two)
-void dl_cpu_matmul_q40_q80(const uint8_t* w, int d, int n, const uint8_t* xq, int M, float* y, int force_scalar) {
-    if (force_scalar) matmul_q40_q80_scalar(w, 0, d, n / QK, xq, M, y, (size_t)d);
+// which: 0 = best available (what the engine uses), 1 = scalar, 2 = AVX2 (falls back to scalar where unsupported)
+void dl_cpu_matmul_q40_q80(const uint8_t* w, int d, int n, const uint8_t* xq, int M, float* y, int which) {
+    if (which == 1) matmul_q40_q80_scalar(w, 0, d, n / QK, xq, M, y, (size_t)d);
+#ifdef DL_X86
+    else if (which == 2 && has_avx2()) matmul_q40_q80_avx2(w, 0, d, n / QK, xq, M, y, (size_t)d);
+#endif
+    else if (which == 2) matmul_q40_q80_scalar(w, 0, d, n / QK, xq, M, y, (size_t)d);
     else matmul_q40_q80(w, 0, d, n / QK, xq, M, y, (size_t)d);
 }
 int dl_cpu_has_avx2(void) { return has_avx2() ? 1 : 0; }
+int dl_cpu_has_vnni(void) { return has_vnni() ? 1 : 0; }
 
 // ---- op-level entry points (unit tests against the reference's goldens, src/nn/nn-cpu-ops-test.cpp) ----
 float dl_cpu_inv_rms(const float* x, int n, float eps) { return inv_rms(x, n, eps); }

@@ -193,8 +193,10 @@ def dequantize_q40(b: np.ndarray, n: int) -> np.ndarray:
     return y
 
 
-def matmul_q40_q80(w_q40: np.ndarray, d: int, n: int, x_q80: np.ndarray, M: int, force_scalar: bool = False) -> np.ndarray:
+def matmul_q40_q80(w_q40: np.ndarray, d: int, n: int, x_q80: np.ndarray, M: int, force_scalar: bool = False,
+                   which: int = 0) -> np.ndarray:
+    """which: 0 = the kernel the engine uses on this CPU (AVX-512 VNNI, AVX2 or scalar), 1 = scalar, 2 = AVX2."""
     y = np.empty((M, d), dtype=np.float32)
     _lib().dl_cpu_matmul_q40_q80(np.ascontiguousarray(w_q40).ctypes.data, d, n, np.ascontiguousarray(x_q80).ctypes.data, M,
-                                 y.ctypes.data, int(force_scalar))
+                                 y.ctypes.data, 1 if force_scalar else which)
     return y

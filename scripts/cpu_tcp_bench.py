@@ -84,10 +84,14 @@ def main():
                       "all_runs_ms_per_token": [r["pred_ms_per_token"] for r in runs]}), flush=True)
     if not a.skip_reference:
         binary = RA.build_reference()
-        runs = [RA._run_once(binary, mpath, tpath, prompt, n_prompt, a.nodes, a.nthreads, 0, a.steps) for _ in range(a.repeats)]
-        ms, tps, _ = min(runs, key=lambda r: r[0])
+        runs = []
+        for _ in range(a.repeats):
+            r = RA._run_once(binary, mpath, tpath, prompt, n_prompt, a.nodes, a.nthreads, 0, a.steps)
+            runs.append(r + (RA.LAST_RUN.get("eval_tokens_per_s"),))
+        ms, tps, _, ev = min(runs, key=lambda r: r[0])
         print(json.dumps({"impl": "reference (unmodified, own build)", **base, "pred_tokens_per_s": tps,
-                          "pred_ms_per_token": round(ms, 2), "all_runs_ms_per_token": [round(r[0], 2) for r in runs]}), flush=True)
+                          "pred_ms_per_token": round(ms, 2), "eval_tokens_per_s": ev,
+                          "all_runs_ms_per_token": [round(r[0], 2) for r in runs]}), flush=True)
 
 
 if __name__ == "__main__":
