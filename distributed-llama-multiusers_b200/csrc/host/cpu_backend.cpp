@@ -1073,7 +1073,7 @@ void validate_slicing(const Header& h, int n) {         // (reference: app.cpp:2
     if (n < 1 || (n & (n - 1))) throw std::runtime_error("The number of nodes must be a power of two");
     if (n > h.n_kv_heads)
         throw std::runtime_error("This version does not support more nodes than the number of KV heads in the model");
-    if (h.dim % n || h.hidden_dim % n || h.vocab % n || h.n_heads % n) throw std::runtime_error("Model dimensions are not divisible by the number of nodes");
+    if (h.dim % n || h.hidden_dim % n || h.vocab % n || h.n_heads % n || h.n_kv_heads % n) throw std::runtime_error("Model dimensions are not divisible by the number of nodes");
     if (h.weight_type == F_Q40 && ((h.dim / n) % QK || (h.hidden_dim / n) % QK))
         throw std::runtime_error("Q40 slices must be multiples of 32 elements");
     if (h.weight_type != F_Q40 && h.weight_type != F_32 && h.weight_type != F_16) throw std::runtime_error("Unsupported weight type");

@@ -310,7 +310,7 @@ def write_random_model(path: str, shape_name_or_dict, weight_type: int = quant.Q
     ``exact=True`` draws N(0,std) f32 weights and runs the real quantizer (small models / tests);
     otherwise Q40 blocks are drawn directly in the quantized domain (uniform nibbles, scales
     ~ std/8), which is statistically equivalent for benchmarking and ~100x faster for the 6 GB
-    8B file.  ``native=True`` (default for files above 64 GB, or DLLAMA_FAST_WRITER=1) fills the file from several
+    8B file.  ``native=True`` (default for files above 16 GB, or DLLAMA_FAST_WRITER=1) fills the file from several
     threads in C++ (csrc/host/model_writer.cpp; same recipe, different random stream): the 238 GB Llama-3.1-405B
     file takes a minute instead of twenty.
     """
@@ -318,7 +318,7 @@ def write_random_model(path: str, shape_name_or_dict, weight_type: int = quant.Q
     params = header_params(shape, weight_type, n_layers)
     if native is None:
         n_par = params["n_layers"] * (2 * params["dim"] ** 2 + 3 * params["dim"] * params["hidden_dim"])
-        native = os.environ.get("DLLAMA_FAST_WRITER") == "1" or n_par * 0.5625 > 64e9
+        native = os.environ.get("DLLAMA_FAST_WRITER") == "1" or n_par * 0.5625 > 16e9
     if native and weight_type == quant.Q40 and not exact:
         import ctypes as C
         from ..text.native import host_lib
