@@ -315,10 +315,13 @@ class InferenceContext:
                                    args.n_threads)
         self.header = self.engine.h
         print(self.header.describe(), flush=True)
-        from ..models.memory import describe, required_memory
-        print(describe(required_memory(self.header, max(1, getattr(self.engine, "world", 1)), self.engine.max_rows,
-                                       self.engine.n_slots, self.engine.seq_len,
-                                       "cuda" if self.engine.device.type == "cuda" else "cpu")), flush=True)
+        try:
+            from ..models.memory import describe, required_memory
+            print(describe(required_memory(self.header, max(1, getattr(self.engine, "world", 1)), self.engine.max_rows,
+                                           self.engine.n_slots, self.engine.seq_len,
+                                           "cuda" if self.engine.device.type == "cuda" else "cpu")), flush=True)
+        except Exception as e:                 # the estimate is informational: never let it stop a run
+            print(f"📀 RequiredMemory: n/a ({e})", flush=True)
         if self.tokenizer.vocab_size != self.header.vocab_size:
             print(f"⚠️  tokenizer vocab ({self.tokenizer.vocab_size}) != model vocab ({self.header.vocab_size})")
         self.sampler = T.Sampler(self.header.vocab_size, args.temperature, args.topp, args.seed)
