@@ -802,6 +802,15 @@ struct Node {
     // DLLAMA_CPU_PROFILE=1: seconds per op family, printed when the node is destroyed (reference: the executor's
     // per-step-type timers, nn-executor.cpp:150-154)
     bool profile = getenv("DLLAMA_CPU_PROFILE") != nullptr;
+    // DLLAMA_CPU_DEBUG_OPS=1: first values of every op's output for row 0 (reference: DEBUG_OP_INPUT_OUTPUT,
+    // nn-cpu-ops.cpp:14-27) -- lines can be diffed between node counts, kernels (DLLAMA_CPU_SCALAR) or engines
+    bool debug_ops = getenv("DLLAMA_CPU_DEBUG_OPS") != nullptr;
+    void dbg(const char* op, int layer, const float* v, int n) const {
+        if (!debug_ops) return;
+        fprintf(stderr, "[op] node %d layer %2d %-10s", c.node, layer, op);
+        for (int i = 0; i < std::min(n, 4); i++) fprintf(stderr, " %+.6f", v[i]);
+        fprintf(stderr, "\n");
+    }
     double t_matmul = 0, t_att = 0, t_sync = 0, t_other = 0;
     long long n_forward = 0;
     ~Node() {
@@ -975,23 +984,31 @@ struct Node {
         for (int l = 0; l < h.n_layers; l++) {
             LayerW& L = layers[l];
             rmsnorm(x.data(), L.rms_att.data(), y.data(), M, dim);
+            dbg("rms_att", l, y.data(), dim);
             lap(t_other);
             matmul(L.wq, y.data(), dim, M, q.data(), qw);
             matmul(L.wk, y.data(), dim, M, k.data(), kvw);
             matmul(L.wv, y.data(), dim, M, v.data(), kvw);
+            dbg("q", l, q.data(), qw);
+            dbg("k", l, k.data(), kvw);
+            dbg("v", l, v.data(), kvw);
             lap(t_matmul);
             rope(q.data(), M, qw);
             rope(k.data(), M, kvw);
+            dbg("q_rope", l, q.data(), qw);
             for (int m = 0; m < M; m++) {           // (reference: OP_SHIFT, nn-cpu-ops.cpp:1253-1275)
                 memcpy(kc[slot[m]][l].data() + (size_t)pos[m] * kvw, k.data() + (size_t)m * kvw, (size_t)kvw * 4);
                 memcpy(vc[slot[m]][l].data() + (size_t)pos[m] * kvw, v.data() + (size_t)m * kvw, (size_t)kvw * 4);
             }
             lap(t_other);
             attention(l, M);
+            dbg("att", l, att_out.data(), qw);
             lap(t_att);
             matmul(L.wo, att_out.data(), qw, M, part.data(), dim);
+            dbg("wo_part", l, part.data(), dim);
             lap(t_matmul);
             sync_and_merge(M);
+            dbg("x_att", l, x.data(), dim);
             lap(t_sync);
             rmsnorm(x.data(), L.rms_ffn.data(), y.data(), M, dim);
             lap(t_other);
@@ -1002,14 +1019,18 @@ struct Node {
                 for (int i = b; i < e; i++) hb[i] = activate(hb[i], h.hidden_act) * hl[i];
             });
             lap(t_other);
+            dbg("silu_mul", l, hb.data(), hw);
             matmul(L.w2, hb.data(), hw, M, part.data(), dim);
+            dbg("w2_part", l, part.data(), dim);
             lap(t_matmul);
             sync_and_merge(M);
+            dbg("x_ffn", l, x.data(), dim);
             lap(t_sync);
         }
         rmsnorm(x.data() + (size_t)lf * dim, rms_final.data(), y.data(), M - lf, dim);
         lap(t_other);
         matmul(wcls, y.data(), dim, M - lf, lg.data(), h.vocab / n);
+        dbg("logits", h.n_layers, lg.data(), h.vocab / n);
         lap(t_matmul);
     }
 };
