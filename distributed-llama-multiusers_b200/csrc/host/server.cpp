@@ -96,10 +96,13 @@ struct Conn {
     bool dispatched = false;        // a request of this connection has been routed
     bool sent_continue = false;
     bool want_out = false;          // EPOLLOUT armed
+    bool keep_alive = false;        // HTTP/1.1 client that did not ask for "Connection: close"
     double t_open = 0.0;            // connections that never send a complete request are dropped after kIdleSeconds
     // shared (Server::mu)
     std::string out;
-    bool close_after = false;
+    bool close_after = false;       // close once `out` is flushed
+    bool done_after = false;        // response complete once `out` is flushed: a keep-alive connection reads the next request
+    bool keep = false;              // copy of keep_alive for the thread that finishes the response
     long long req = 0;              // generation in flight for this connection (0 = none)
 };
 
@@ -184,12 +187,19 @@ const char* status_text(int code) {
 }
 
 // complete response with a body; the connection closes once it is flushed
-void http_response(std::string& o, int code, const char* ctype, const std::string& body, bool cors) {
+void http_response(std::string& o, int code, const char* ctype, const std::string& body, bool cors, bool keep = false) {
     appendf(o, "HTTP/1.1 %d %s\r\nServer: dllama-api-b200\r\n", code, status_text(code));
     if (cors) o += "Access-Control-Allow-Origin: *\r\n";
     if (ctype) appendf(o, "Content-Type: %s\r\n", ctype);
-    appendf(o, "Content-Length: %zu\r\nConnection: close\r\n\r\n", body.size());
+    appendf(o, "Content-Length: %zu\r\nConnection: %s\r\n\r\n", body.size(), keep ? "keep-alive" : "close");
     o += body;
+}
+
+// marks the response in c.out as complete: the connection closes after the flush, or -- keep-alive client and a
+// response with a Content-Length -- goes back to reading requests
+void end_response(Conn& c, bool can_keep) {
+    if (can_keep && c.keep) c.done_after = true;
+    else c.close_after = true;
 }
 
 std::string error_json(const std::string& msg, const char* type) {
@@ -296,7 +306,7 @@ void finalize(Server* s, long long id, const char* reason) {
             c.out += "data: [DONE]\r\n\r\n";
         } else if (failed) {
             http_response(c.out, 500, "application/json; charset=utf-8",
-                          error_json(g.error.empty() ? "generation failed" : g.error, "server_error"), true);
+                          error_json(g.error.empty() ? "generation failed" : g.error, "server_error"), true, c.keep);
         } else {
             // (reference DTO: ChatCompletion, src/api-types.hpp:86-101; `generated_text` is what the fork's
             // web-ui reads, web-ui/app.js:40)
@@ -313,9 +323,9 @@ void finalize(Server* s, long long id, const char* reason) {
             b += "}], \"generated_text\": ";
             dljson::append_quoted(b, g.text);
             b += "}";
-            http_response(c.out, 200, "application/json; charset=utf-8", b, true);
+            http_response(c.out, 200, "application/json; charset=utf-8", b, true, c.keep);
         }
-        c.close_after = true;
+        end_response(c, !g.stream);          // an SSE stream has no length: it ends with the connection
         c.req = 0;
         s->dirty.push_back(c.id);
     }
@@ -329,8 +339,9 @@ void finalize(Server* s, long long id, const char* reason) {
 // ---- I/O thread --------------------------------------------------------------------------------------
 void queue_response(Server* s, Conn& c, int code, const char* ctype, const std::string& body, bool cors = true) {
     std::lock_guard<std::mutex> g(s->mu);
-    http_response(c.out, code, ctype, body, cors);
-    c.close_after = true;
+    const bool keep = c.keep && code < 400;         // errors close the connection (the request may be half-read)
+    http_response(c.out, code, ctype, body, cors, keep);
+    if (keep) c.done_after = true; else c.close_after = true;
 }
 
 std::string lower(std::string v) {
@@ -342,6 +353,7 @@ struct HttpRequest {
     std::string method, path;
     size_t content_length = 0;
     bool expect_continue = false;
+    bool keep_alive = false;
     size_t header_bytes = 0;
 };
 
@@ -357,6 +369,7 @@ int parse_head(const std::string& in, HttpRequest& r) {
     if (a == std::string::npos || b == std::string::npos) return -1;
     r.method = line.substr(0, a);
     r.path = line.substr(a + 1, b - a - 1);
+    r.keep_alive = line.compare(b + 1, std::string::npos, "HTTP/1.1") == 0;      // 1.1 default; 1.0 closes
     size_t q = r.path.find('?');
     if (q != std::string::npos) r.path.resize(q);
     size_t p = eol + 2;
@@ -371,6 +384,11 @@ int parse_head(const std::string& in, HttpRequest& r) {
             std::string val = in.substr(v0, e - v0);
             if (key == "content-length") r.content_length = (size_t)strtoull(val.c_str(), nullptr, 10);
             else if (key == "expect" && lower(val).find("100-continue") != std::string::npos) r.expect_continue = true;
+            else if (key == "connection") {
+                const std::string v = lower(val);
+                if (v.find("close") != std::string::npos) r.keep_alive = false;
+                else if (v.find("keep-alive") != std::string::npos) r.keep_alive = true;
+            }
         }
         p = e + 2;
     }
@@ -557,8 +575,9 @@ void route(Server* s, Conn& c, const HttpRequest& r, const char* body, size_t n)
         std::lock_guard<std::mutex> g(s->mu);
         c.out += "HTTP/1.1 204 No Content\r\nServer: dllama-api-b200\r\nAccess-Control-Allow-Origin: *\r\n"
                  "Access-Control-Allow-Methods: GET, POST, PUT, DELETE\r\n"
-                 "Access-Control-Allow-Headers: Content-Type, Authorization\r\nConnection: close\r\n\r\n";
-        c.close_after = true;
+                 "Access-Control-Allow-Headers: Content-Type, Authorization\r\n";
+        c.out += c.keep ? "Connection: keep-alive\r\n\r\n" : "Connection: close\r\n\r\n";
+        if (c.keep) c.done_after = true; else c.close_after = true;
         return;
     }
     if (r.method == "GET" && r.path == "/v1/models") {
@@ -630,16 +649,23 @@ bool flush_conn(Server* s, uint64_t id) {
         c = &it->second;                    // node address is stable; only this thread erases connections
     }
     while (true) {
-        bool close_after = false;
+        bool close_after = false, done_after = false;
         if (c->woff >= c->wbuf.size()) {
             c->wbuf.clear();
             c->woff = 0;
             std::lock_guard<std::mutex> g(s->mu);
             c->wbuf.swap(c->out);
             close_after = c->close_after;
+            done_after = c->done_after;
+            if (c->wbuf.empty() && done_after) c->done_after = false;
         }
         if (c->wbuf.empty()) {
             if (close_after) { close_conn(s, id); return false; }
+            if (done_after) {                       // keep-alive: ready for the next request on this connection
+                c->dispatched = false;
+                c->sent_continue = false;
+                c->t_open = now_s();
+            }
             arm(s, *c, false);
             return true;
         }
@@ -696,6 +722,11 @@ void on_readable(Server* s, uint64_t id) {
         return;
     }
     c->dispatched = true;
+    c->keep_alive = r.keep_alive;
+    {
+        std::lock_guard<std::mutex> g(s->mu);
+        c->keep = r.keep_alive;
+    }
     route(s, *c, r, c->in.data() + r.header_bytes, r.content_length);
     std::string().swap(c->in);
     flush_conn(s, id);

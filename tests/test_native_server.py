@@ -362,3 +362,56 @@ def test_full_native_stack_http_server_on_the_tcp_tensor_parallel_cpu_backend(ti
         eng1.close()
         w.join(timeout=30)
     assert not w.is_alive()
+
+
+def test_native_server_keep_alive_connections(tok):
+    """HTTP/1.1 clients that keep their connection (httpx, requests, browsers) reuse it for several requests;
+    streams, errors and `Connection: close` requests end it."""
+    import http.client
+    eng = _FakeEngine(max_rows=8, n_slots=4, seq_len=256)
+    defaults = A.InferenceParams(messages=[], temperature=0.0, top_p=0.9, seed=1)
+    srv = NativeApiServer(eng, tok, "fake.m", defaults, host="127.0.0.1", port=0, verbose=False)
+    srv.start()
+    try:
+        c = http.client.HTTPConnection("127.0.0.1", srv.port, timeout=60)
+        body = json.dumps({"messages": [{"role": "user", "content": "hello world"}], "max_tokens": 5})
+        c.request("GET", "/v1/models")
+        r = c.getresponse()
+        assert r.status == 200 and r.getheader("Connection") == "keep-alive" and json.load(r)["object"] == "list"
+        sock = c.sock
+        texts = []
+        for _ in range(3):
+            c.request("POST", "/v1/chat/completions", body=body, headers={"Content-Type": "application/json"})
+            r = c.getresponse()
+            assert r.status == 200 and r.getheader("Connection") == "keep-alive"
+            texts.append(json.load(r)["choices"][0]["message"]["content"])
+            assert c.sock is sock                                   # same TCP connection, not a silent reconnect
+        assert srv.stats()["connections"] == 1 and texts[0] == texts[1] == texts[2]
+        c.request("OPTIONS", "/v1/chat/completions")
+        r = c.getresponse()
+        assert r.status == 204 and r.read() == b"" and c.sock is sock
+        # a stream has no length: it ends with the connection
+        c.request("POST", "/v1/chat/completions", body=json.dumps({"messages": [{"role": "user", "content": "hello"}],
+                                                                   "max_tokens": 3, "stream": True}))
+        r = c.getresponse()
+        assert r.getheader("Connection") == "close" and r.read().endswith(b"data: [DONE]\r\n\r\n")
+        c.close()
+        # errors close too; so does an explicit Connection: close
+        c = http.client.HTTPConnection("127.0.0.1", srv.port, timeout=60)
+        c.request("POST", "/v1/chat/completions", body="{\"messages\": 1}")
+        r = c.getresponse()
+        assert r.status == 400 and r.getheader("Connection") == "close"
+        r.read()
+        c.close()
+        c = http.client.HTTPConnection("127.0.0.1", srv.port, timeout=60)
+        c.request("GET", "/health", headers={"Connection": "close"})
+        r = c.getresponse()
+        assert r.status == 200 and r.getheader("Connection") == "close"
+        r.read()
+        c.close()
+        t0 = time.time()
+        while srv.stats()["connections"] and time.time() - t0 < 10:
+            time.sleep(0.05)
+        assert srv.stats()["connections"] == 0
+    finally:
+        srv.close()
