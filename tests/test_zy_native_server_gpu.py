@@ -76,3 +76,35 @@ def test_native_server_on_the_cuda_engine(tiny_model_path, tmp_path):
     finally:
         srv.close()
         eng.close()
+
+
+@pytest.mark.gpu
+def test_back_to_back_prompt_chunks_behind_a_busy_stream(tiny_model_path):
+    """Prompt chunks are launched without a host synchronisation between them, so the async copy of a chunk's batch
+    descriptor can execute long after it was enqueued.  With the stream kept busy, a descriptor staging buffer that
+    is rewritten too early makes every chunk run with the last chunk's rows; the engine has to hold the buffer until
+    the copy has been consumed (LlamaEngine.set_batch).  Checked against the CPU oracle."""
+    import numpy as np
+    import torch
+    from dllama_b200.formats.mfile import ModelFile
+    from dllama_b200.models.llama import LlamaEngine
+    from dllama_b200.models.oracle import OracleLlama
+    o = OracleLlama(ModelFile(tiny_model_path), max_seq_len=512)
+    e = LlamaEngine(tiny_model_path, max_rows=32, n_slots=3, max_seq_len=512)
+    rng = np.random.default_rng(11)
+    warm = rng.integers(1, 1024, 96).tolist()
+    e.prefill(e.alloc_slot(), warm, 0, chunk=32)                    # captures the graphs of this batch shape
+    torch.cuda.synchronize()
+    prompt = rng.integers(1, 1024, 96).tolist()
+    slot = e.alloc_slot()
+    torch.cuda._sleep(int(3e8))                                     # ~0.15 s of work queued in front of the chunks
+    got = e.prefill(slot, prompt, 0, chunk=32).float().cpu().numpy()
+    ref = o.forward(prompt, 0).numpy()
+    err = float(np.abs(got[0] - ref[-1]).max() / (np.abs(ref[-1]).max() + 1e-9))
+    assert err < 3e-2, err
+    # and the sequence's KV state is intact: one more token still agrees with the oracle
+    tok = int(np.argmax(ref[-1]))
+    got1 = e.forward([tok], [96], [slot]).float().cpu().numpy()
+    ref1 = o.forward([tok], 96).numpy()
+    assert float(np.abs(got1[0] - ref1[0]).max() / (np.abs(ref1[0]).max() + 1e-9)) < 3e-2
+    e.close()
