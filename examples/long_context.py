@@ -6,6 +6,9 @@ stable from run to run (the kernels are deterministic: fixed reduction orders, n
 
     python examples/long_context.py --model m.m --steps 2048
     torchrun --nproc-per-node 4 examples/long_context.py --model m.m --steps 2048
+    python examples/long_context.py --model m.m --steps 2048 --device cpu --nodes 4 --nthreads 2
+        (no GPU: the host backend, root + 3 workers over loopback TCP started by this script; the digest does not
+         depend on --nthreads, and a second run must print the same digest)
 """
 import argparse
 import hashlib
@@ -20,7 +23,12 @@ def main():
     ap.add_argument("--model", required=True)
     ap.add_argument("--steps", type=int, default=2048)
     ap.add_argument("--expect", default="")
+    ap.add_argument("--device", default="cuda", choices=["cuda", "cpu"])
+    ap.add_argument("--nodes", type=int, default=1, help="--device cpu: root + (nodes-1) workers over loopback TCP")
+    ap.add_argument("--nthreads", type=int, default=0)
     a = ap.parse_args()
+    if a.device == "cpu":
+        return main_cpu(a)
     import torch
     import torch.distributed as dist
     from dllama_b200.models.llama import LlamaEngine
@@ -55,5 +63,47 @@ def main():
         dist.destroy_process_group()
 
 
+def generate_cpu(model, steps, nodes, nthreads):
+    """Greedy continuation on the host backend; returns the generated token ids."""
+    import socket
+    import threading
+    import time
+    import torch
+    from dllama_b200.models import native_cpu_engine as N
+    ports, threads = [], []
+    for _ in range(nodes - 1):
+        with socket.socket() as s:
+            s.bind(("127.0.0.1", 0))
+            ports.append(s.getsockname()[1])
+    for p in ports:
+        t = threading.Thread(target=N.serve_worker, args=(p, nthreads), daemon=True)
+        t.start()
+        threads.append(t)
+    if ports:
+        time.sleep(0.3)
+    eng = N.NativeCpuEngine(model, workers=[("127.0.0.1", p) for p in ports], n_threads=nthreads, max_rows=16, n_slots=1,
+                            max_seq_len=steps + 64)
+    prompt = [1 + (i * 7919) % (eng.h.vocab_size - 1) for i in range(16)]
+    lg = eng.prefill(0, prompt, 0)
+    tok = int(torch.argmax(lg[0]))
+    out, pos = [], len(prompt)
+    for _ in range(steps):
+        out.append(tok)
+        tok = eng.decode_step_greedy([tok], [pos], [0])[0]
+        pos += 1
+    eng.close()
+    for t in threads:
+        t.join(timeout=30)
+    return out
+
+
+def main_cpu(a):
+    out = generate_cpu(a.model, a.steps, a.nodes, a.nthreads)
+    digest = hashlib.sha256(",".join(map(str, out)).encode()).hexdigest()[:16]
+    ok = not a.expect or a.expect == digest
+    print(f"tokens={len(out)} nodes={a.nodes} digest={digest} {'✅' if ok else '❌'}")
+    return 0 if ok else 1
+
+
 if __name__ == "__main__":
-    main()
+    sys.exit(main() or 0)

@@ -243,3 +243,18 @@ def test_rope_goldens_of_the_reference_vulkan_test():
         for i, v in vals.items():
             assert abs(row[i] - v) < 5e-6, (pos, i, row[i], v)
             assert abs(y[i] - v) < 5e-6, (pos, i, y[i], v)
+
+
+def test_long_greedy_continuation_is_reproducible_and_thread_count_invariant(tiny_tp_model_path):
+    """The role of the reference's examples/macbeth.sh (a long fixed-seed continuation compared exactly), runnable
+    anywhere: 4 nodes over loopback TCP, 160 tokens; the ids must not depend on the thread count (rows and output
+    ranges are split across threads, the arithmetic per output value is fixed) nor change from run to run."""
+    import importlib.util
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("long_context", os.path.join(root, "examples", "long_context.py"))
+    lc = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(lc)
+    a = lc.generate_cpu(tiny_tp_model_path, 160, 4, 1)
+    b = lc.generate_cpu(tiny_tp_model_path, 160, 4, 2)
+    assert len(a) == 160 and a == b and len(set(a)) > 8
