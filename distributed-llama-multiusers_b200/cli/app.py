@@ -270,7 +270,11 @@ def run_worker_app(args: AppArgs):
         # no GPU: a worker of the native host backend; everything it needs arrives over the socket
         from ..models.native_cpu_engine import serve_worker
         while True:
-            serve_worker(args.port, args.n_threads)
+            try:
+                serve_worker(args.port, args.n_threads)
+            except RuntimeError as e:               # a bad handshake or a root that failed during set-up
+                print(f"🚨 {e}", flush=True)
+                time.sleep(0.5)
             print("🚁 Root disconnected, waiting for a new one", flush=True)
     from ..parallel.control import ControlChannel
     from ..parallel.symm import init_distributed

@@ -1386,11 +1386,18 @@ int dl_cpu_worker_serve(int port, int n_threads, char* err, int errlen) {
             const int M = ctl[0], lf = ctl[1];
             if (M <= 0) break;
             if (M > nd.c.max_rows || lf < 0 || lf >= M) throw std::runtime_error("bad control packet");
-            recv_all(rfd, nd.pos.data(), (size_t)M * 4, &nd.mesh.stats);
-            recv_all(rfd, nd.slot.data(), (size_t)M * 4, &nd.mesh.stats);
-            recv_all(rfd, nd.x.data(), (size_t)M * dim * 4, &nd.mesh.stats);
-            nd.forward_node(M, lf);
-            send_all(rfd, nd.lg.data(), (size_t)(M - lf) * (nd.c.h.vocab / n) * 4, &nd.mesh.stats);
+            try {
+                recv_all(rfd, nd.pos.data(), (size_t)M * 4, &nd.mesh.stats);
+                recv_all(rfd, nd.slot.data(), (size_t)M * 4, &nd.mesh.stats);
+                recv_all(rfd, nd.x.data(), (size_t)M * dim * 4, &nd.mesh.stats);
+                nd.forward_node(M, lf);
+                send_all(rfd, nd.lg.data(), (size_t)(M - lf) * (nd.c.h.vocab / n) * 4, &nd.mesh.stats);
+            } catch (const std::exception& e) {
+                // a root (or peer) that dies in the middle of a batch: drop everything and wait for the next root
+                // (reference: the worker catches Nn{Read,Write}NetworkException and re-serves, src/app.cpp:455-461)
+                printf("🚨 Network is closed: %s\n", e.what());
+                break;
+            }
         }
         printf("🚁 Root disconnected\n");
         fflush(stdout);

@@ -157,3 +157,43 @@ def test_root_plus_worker_over_localhost_tcp_on_cpu(tiny_model_path, tok_path):
         worker.terminate()
         out = worker.communicate(timeout=30)[0]
     assert "Worker is ready" in out and "Weights loaded" in out, out
+
+
+def test_cpu_worker_serves_a_second_root_after_the_first_left(tiny_model_path, tok_path):
+    """`dllama worker` goes back to listening when its root stops or dies (reference: runWorkerApp, src/app.cpp:405-464):
+    one worker process serves a root that finishes, a root that is killed mid-run, and a third one."""
+    import socket
+    import subprocess
+    import time
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    exe = os.path.join(root, "dllama")
+    worker = subprocess.Popen([sys.executable, exe, "worker", "--port", str(port), "--nthreads", "1", "--device", "cpu"],
+                              stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, cwd="/")
+    argv = [sys.executable, exe, "inference", "--model", tiny_model_path, "--tokenizer", tok_path, "--buffer-float-type", "q80",
+            "--prompt", "hello world", "--max-seq-len", "128", "--device", "cpu", "--temperature", "0", "--nthreads", "1",
+            "--workers", f"127.0.0.1:{port}"]
+    try:
+        time.sleep(1.0)
+        r1 = subprocess.run(argv + ["--steps", "8"], capture_output=True, text=True, timeout=180)
+        assert r1.returncode == 0, r1.stdout + r1.stderr
+        time.sleep(0.5)
+        victim = subprocess.Popen(argv + ["--steps", "120"], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+        t0 = time.time()
+        while time.time() - t0 < 60:                       # wait until it is decoding, then kill it without warning
+            line = victim.stdout.readline()
+            if "Pred" in line or not line:
+                break
+        victim.kill()
+        victim.wait(timeout=30)
+        time.sleep(1.0)
+        r3 = subprocess.run(argv + ["--steps", "8"], capture_output=True, text=True, timeout=180)
+        assert r3.returncode == 0, r3.stdout + r3.stderr
+        pieces = lambda s: [ln.rsplit("|", 1)[1] for ln in s.splitlines() if "Pred" in ln and "|" in ln]
+        assert pieces(r1.stdout) and pieces(r1.stdout) == pieces(r3.stdout)
+    finally:
+        worker.terminate()
+        out = worker.communicate(timeout=30)[0]
+    assert out.count("Worker is ready") == 3 and out.count("waiting for a new one") >= 2, out
