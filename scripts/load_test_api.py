@@ -16,6 +16,7 @@ import os
 import sys
 import threading
 import time
+import urllib.error
 import urllib.request
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -73,7 +74,12 @@ def _client_proc(port, users, first_user, max_tokens, prompt_words, temperature,
         req = urllib.request.Request(f"http://127.0.0.1:{port}/v1/chat/completions", data=json.dumps(body).encode(),
                                      headers={"Content-Type": "application/json"}, method="POST")
         t0 = time.perf_counter()
-        with urllib.request.urlopen(req, timeout=600) as r:
+        try:
+            r = urllib.request.urlopen(req, timeout=600)
+        except urllib.error.HTTPError as e:            # e.g. 400: the prompt does not fit --max-seq-len
+            sys.stderr.write(f"[client {i}] HTTP {e.code}: {e.read()[:200]!r}\n")
+            return
+        with r:
             buf = b""
             while True:
                 chunk = r.read1(65536)
@@ -106,6 +112,7 @@ def main():
     ap.add_argument("--prompt-words", type=int, default=24)
     ap.add_argument("--temperature", type=float, default=0.0)
     ap.add_argument("--max-batch", type=int, default=64)
+    ap.add_argument("--max-seq-len", type=int, default=1024)
     ap.add_argument("--rounds", type=int, default=2, help="round 0 warms up (graph capture), later rounds are timed")
     ap.add_argument("--backend", default="native", choices=["native", "python"],
                     help="front end: csrc/host/server.cpp (default) or serving/api.py")
@@ -124,7 +131,7 @@ def main():
     ctl = None
     if a.engine == "fake":
         rank, world = 0, 1
-        eng = FakeEngine(32000, a.max_batch, a.users + 2, 1024, a.fake_step_ms)
+        eng = FakeEngine(32000, a.max_batch, a.users + 2, a.max_seq_len, a.fake_step_ms)
         path = "fake.m"
     else:
         from dllama_b200.models.llama import LlamaEngine
@@ -135,7 +142,7 @@ def main():
             mfile.write_random_model(path, a.model, seed=1)
         if world > 1:
             torch.distributed.barrier()
-        eng = LlamaEngine(path, rank=rank, world=world, max_rows=a.max_batch, n_slots=a.users + 2, max_seq_len=1024,
+        eng = LlamaEngine(path, rank=rank, world=world, max_rows=a.max_batch, n_slots=a.users + 2, max_seq_len=a.max_seq_len,
                           bucket_rows=True)
         if world > 1:
             from dllama_b200.parallel.control import ControlChannel
