@@ -415,3 +415,58 @@ def test_native_server_keep_alive_connections(tok):
         assert srv.stats()["connections"] == 0
     finally:
         srv.close()
+
+
+def test_native_server_answers_every_mutated_request_body(tok):
+    """Mutation fuzzing of the JSON body (truncations, byte flips, deep nesting, huge numbers, odd escapes, wrong
+    types): every request gets a well-formed 200 or 400 and the server keeps its slots.  (scripts/host_sanitizers.sh
+    runs this file under ASan / TSan.)"""
+    import random
+    eng = _FakeEngine(max_rows=8, n_slots=4, seq_len=256)
+    defaults = A.InferenceParams(messages=[], temperature=0.0, top_p=0.9, seed=1)
+    srv = NativeApiServer(eng, tok, "fake.m", defaults, host="127.0.0.1", port=0, verbose=False)
+    srv.start()
+    rnd = random.Random(7)
+    base = json.dumps({"messages": [{"role": "system", "content": "be \"brief\" \\ \u00e9\u4e16\U0001F600"},
+                                    {"role": "user", "content": [{"type": "text", "text": "hello world"}]}],
+                       "max_tokens": 3, "temperature": 0.5, "top_p": 0.9, "seed": 42, "stop": ["zz", "q"],
+                       "stream": False, "stream_options": {"include_usage": True}}).encode()
+    bodies = [b"", b"{}", b"[]", b"null", b"[" * 200 + b"]" * 200, b"{\"messages\": " + b"[" * 100 + b"]" * 100 + b"}",
+              b"{\"messages\": [{\"role\": \"user\", \"content\": \"\\ud800\"}], \"max_tokens\": 2}",
+              b"{\"messages\": [{\"role\": \"user\", \"content\": \"a\\u0000b\"}], \"max_tokens\": 2}",
+              b"{\"messages\": [{\"role\": \"user\", \"content\": \"hi\"}], \"max_tokens\": 1e400}",
+              b"{\"messages\": [{\"role\": \"user\", \"content\": \"hi\"}], \"seed\": 99999999999999999999999, \"max_tokens\": 2}",
+              b"{\"messages\": [{\"role\": \"user\", \"content\": \"hi\"}], \"temperature\": \"hot\"}",
+              b"{\"messages\": [{\"role\": 5, \"content\": \"hi\"}]}", b"\xff\xfe\x00\x01"]
+    for _ in range(150):
+        b = bytearray(base)
+        kind = rnd.randrange(4)
+        if kind == 0:
+            b = b[:rnd.randrange(len(b))]
+        elif kind == 1:
+            for _ in range(rnd.randrange(1, 4)):
+                b[rnd.randrange(len(b))] = rnd.randrange(256)
+        elif kind == 2:
+            i = rnd.randrange(len(b))
+            b[i:i] = bytes(rnd.randrange(32, 127) for _ in range(rnd.randrange(1, 6)))
+        else:
+            i, j = sorted((rnd.randrange(len(b)), rnd.randrange(len(b))))
+            del b[i:j]
+        bodies.append(bytes(b))
+    codes = {}
+    try:
+        for body in bodies:
+            req = urllib.request.Request(f"http://127.0.0.1:{srv.port}/v1/chat/completions", data=body, method="POST")
+            try:
+                with urllib.request.urlopen(req, timeout=60) as r:
+                    d = json.load(r)
+                    assert d["object"] == "chat.completion"
+                    codes[200] = codes.get(200, 0) + 1
+            except urllib.error.HTTPError as e:
+                assert e.code == 400 and "error" in json.load(e), (e.code, body)
+                codes[400] = codes.get(400, 0) + 1
+        assert codes.get(400, 0) > 50 and codes.get(200, 0) >= 3, codes
+        st = srv.stats()
+        assert st["running"] == 0 and st["waiting"] == 0 and st["free_slots"] == 4 and st["engine_errors"] == 0
+    finally:
+        srv.close()
