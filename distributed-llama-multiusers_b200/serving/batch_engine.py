@@ -166,7 +166,8 @@ class BatchEngine:
             rows = [self.reqs.get(i) for i in sampling]
         greedy = all(r is not None and r.temperature == 0.0 for r in rows) and len(rows) > 0
         if self.control is not None:
-            self.control.send(OP_FORWARD, toks, pos, slots, lf, greedy, released)
+            # workers replay exactly the root's launch: a pure prompt step computes the last row's logits only
+            self.control.send(OP_FORWARD, toks, pos, slots, lf if sampling else len(toks) - 1, greedy, released)
         eng = self.engine
         n_s = len(sampling)
         t_b = time.perf_counter()

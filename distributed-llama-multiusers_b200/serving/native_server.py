@@ -144,7 +144,8 @@ class NativeApiServer:
             return 0
         toks, pos, slots = d[0, :n].tolist(), d[1, :n].tolist(), d[2, :n].tolist()
         if self.control is not None:
-            self.control.send(OP_FORWARD, toks, pos, slots, lf, greedy, released)
+            # workers replay exactly the root's launch: a pure prompt step computes the last row's logits only
+            self.control.send(OP_FORWARD, toks, pos, slots, lf if n_s else n - 1, greedy, released)
         if n_s == 0:
             eng.forward(toks, pos, slots, logits_from=n - 1)                  # pure prompt chunk
             rc = L.dl_srv_commit(h, 0, None)
