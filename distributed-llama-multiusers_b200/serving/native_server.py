@@ -50,6 +50,7 @@ class NativeApiServer:
         pin = (lambda t: t.pin_memory()) if torch.cuda.is_available() else (lambda t: t)
         # batch descriptor + sampling parameters are written by the server straight into (pinned) host tensors
         self._desc = torch.zeros(3, R, dtype=torch.int32)                       # tokens | positions | slots
+        self._desc_np = self._desc.numpy()                                       # same memory, cheaper slicing
         self._h_params = pin(torch.zeros(3, R, dtype=torch.float32))            # temperature | topp | coin
         self._h_tok = pin(torch.zeros(R, dtype=torch.int32))
         self._released = (C.c_int * 256)()
@@ -142,7 +143,8 @@ class NativeApiServer:
             eng.pages.release_pages(s)
         if n <= 0:
             return 0
-        toks, pos, slots = d[0, :n].tolist(), d[1, :n].tolist(), d[2, :n].tolist()
+        dn = self._desc_np
+        toks, pos, slots = dn[0, :n].tolist(), dn[1, :n].tolist(), dn[2, :n].tolist()
         if self.control is not None:
             # workers replay exactly the root's launch: a pure prompt step computes the last row's logits only
             self.control.send(OP_FORWARD, toks, pos, slots, lf if n_s else n - 1, greedy, released)
