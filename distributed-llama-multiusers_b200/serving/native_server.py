@@ -54,6 +54,8 @@ class NativeApiServer:
         self._h_params = pin(torch.zeros(3, R, dtype=torch.float32))            # temperature | topp | coin
         self._h_tok = pin(torch.zeros(R, dtype=torch.int32))
         self._released = (C.c_int * 256)()
+        self._ptrs = tuple(t.data_ptr() for t in (self._desc[0], self._desc[1], self._desc[2], self._h_params[0],
+                                                  self._h_params[1], self._h_params[2]))
         self._lf, self._ns, self._greedy, self._nrel = C.c_int(0), C.c_int(0), C.c_int(0), C.c_int(0)
         if self._device_sampler:
             from ..ops import kernels as _K
@@ -132,9 +134,8 @@ class NativeApiServer:
     def step(self) -> int:
         """One scheduler step = one forward pass.  Returns the number of rows run."""
         L, h, eng, R = self._L, self._h, self.engine, self.max_rows
-        d, hp = self._desc, self._h_params
-        n = L.dl_srv_next_batch(h, d[0].data_ptr(), d[1].data_ptr(), d[2].data_ptr(), R, C.byref(self._lf),
-                                C.byref(self._ns), hp[0].data_ptr(), hp[1].data_ptr(), hp[2].data_ptr(),
+        p = self._ptrs
+        n = L.dl_srv_next_batch(h, p[0], p[1], p[2], R, C.byref(self._lf), C.byref(self._ns), p[3], p[4], p[5],
                                 int(self._device_sampler), C.byref(self._greedy), C.addressof(self._released), 256,
                                 C.byref(self._nrel))
         lf, n_s, greedy, n_rel = self._lf.value, self._ns.value, bool(self._greedy.value), self._nrel.value
