@@ -230,4 +230,36 @@ inline void append_quoted(std::string& o, const char* s, size_t n) {
 }
 inline void append_quoted(std::string& o, const std::string& s) { append_quoted(o, s.data(), s.size()); }
 
+// serialises a Value (numbers: integers exactly, the rest with 17 significant digits; non-finite -> null)
+inline void dump(const Value& v, std::string& o) {
+    switch (v.type) {
+        case Value::NUL: o += "null"; break;
+        case Value::BOOL: o += v.b ? "true" : "false"; break;
+        case Value::NUM: {
+            char b[40];
+            if (v.is_int) snprintf(b, sizeof b, "%lld", v.inum);
+            else if (!std::isfinite(v.num)) snprintf(b, sizeof b, "null");
+            else snprintf(b, sizeof b, "%.17g", v.num);
+            o += b;
+            break;
+        }
+        case Value::STR: append_quoted(o, v.str); break;
+        case Value::ARR:
+            o.push_back('[');
+            for (size_t i = 0; i < v.arr.size(); i++) { if (i) o.push_back(','); dump(v.arr[i], o); }
+            o.push_back(']');
+            break;
+        case Value::OBJ:
+            o.push_back('{');
+            for (size_t i = 0; i < v.obj.size(); i++) {
+                if (i) o.push_back(',');
+                append_quoted(o, v.obj[i].first);
+                o.push_back(':');
+                dump(v.obj[i].second, o);
+            }
+            o.push_back('}');
+            break;
+    }
+}
+
 }  // namespace dljson

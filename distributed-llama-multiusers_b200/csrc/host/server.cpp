@@ -1028,6 +1028,19 @@ int dl_srv_fail_batch(void* sv, const char* message) {
 
 int dl_srv_port(void* sv) { return ((Server*)sv)->port; }
 
+// parse + re-serialise a JSON document with the server's own reader (tests): length written (NUL-terminated),
+// -1 = rejected, -2 = `cap` too small
+int dl_json_roundtrip(const char* in, int n, char* out, int cap) {
+    Value v;
+    std::string err, o;
+    if (!dljson::Parser(in, (size_t)n).parse(v, err)) return -1;
+    dljson::dump(v, o);
+    if ((int)o.size() + 1 > cap) return -2;
+    memcpy(out, o.data(), o.size());
+    out[o.size()] = 0;
+    return (int)o.size();
+}
+
 // out[0..9]: requests, errors, steps, generated tokens, rows, waiting, running, free slots, open connections,
 // failed engine steps
 void dl_srv_stats(void* sv, long long* out) {

@@ -4,7 +4,7 @@
 #   bash scripts/host_sanitizers.sh          -> prints the number of reports per tool (0 = clean)
 set -u
 cd "$(dirname "$0")/.."
-TESTS="tests/test_native_server.py tests/test_native_cpu.py tests/test_text.py tests/test_serving.py tests/test_formats.py"
+TESTS="tests/test_json_reader.py tests/test_native_server.py tests/test_native_cpu.py tests/test_text.py tests/test_serving.py tests/test_formats.py"
 STD=$(g++ -print-file-name=libstdc++.so)
 run() {   # tool, flags, runtime library, options variable
   rm -f /tmp/dllama_san_log*
