@@ -133,6 +133,7 @@ struct Server {
     float def_temp = 0.8f, def_topp = 0.9f;
     unsigned long long def_seed = 0;
     int max_default_tokens = 128;
+    int max_waiting = 4096;             // admission queue bound (DLLAMA_MAX_WAITING): beyond it requests get 503
     int verbose = 0;
     std::vector<int> eos_ids;
     std::vector<std::string> eos_pieces;
@@ -547,6 +548,19 @@ void handle_completion(Server* s, Conn& c, const char* body, size_t n) {
     const long long id = g.id;
     int rc;
     {
+        int w = 0, run = 0, fr = 0;
+        dl_sched_stats(s->sched, &w, &run, &fr);
+        if (w >= s->max_waiting) {              // shed load instead of queueing without bound
+            free_gen_handles(g);
+            {
+                std::lock_guard<std::mutex> lk(s->mu);
+                s->n_errors++;
+            }
+            return queue_response(s, c, 503, "application/json; charset=utf-8",
+                                  error_json("server is overloaded, try again later", "server_error"));
+        }
+    }
+    {
         std::lock_guard<std::mutex> lk(s->mu);
         rc = dl_sched_submit(s->sched, id, tokens.data(), nt, max_tokens);
         if (rc == 0) {
@@ -816,6 +830,7 @@ void* dl_srv_new(void* tokenizer, const char* model_name, int chat_type, const c
     s->max_default_tokens = max_default_tokens > 0 ? max_default_tokens : 128;
     s->verbose = verbose;
     s->sched = dl_sched_new(max_rows, n_slots, prefill_chunk, max_seq_len);
+    if (const char* mw = getenv("DLLAMA_MAX_WAITING")) s->max_waiting = std::max(0, atoi(mw));
     const int ne = dl_tok_n_eos(tokenizer);
     for (int i = 0; i < ne; i++) {
         int id = dl_tok_eos(tokenizer, i), len = 0;

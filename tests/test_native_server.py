@@ -470,3 +470,40 @@ def test_native_server_answers_every_mutated_request_body(tok):
         assert st["running"] == 0 and st["waiting"] == 0 and st["free_slots"] == 4 and st["engine_errors"] == 0
     finally:
         srv.close()
+
+
+def test_native_server_sheds_load_when_the_admission_queue_is_full(tok, monkeypatch):
+    """DLLAMA_MAX_WAITING bounds the admission queue: requests beyond it are answered 503 at once instead of
+    queueing without limit; the admitted ones finish normally."""
+    monkeypatch.setenv("DLLAMA_MAX_WAITING", "2")
+    eng = _FakeEngine(max_rows=4, n_slots=1, seq_len=256)
+    real = eng.decode_step_greedy
+
+    def slow(*a, **kw):
+        time.sleep(0.02)
+        return real(*a, **kw)
+
+    eng.decode_step_greedy = slow
+    defaults = A.InferenceParams(messages=[], temperature=0.0, top_p=0.9, seed=1)
+    srv = NativeApiServer(eng, tok, "fake.m", defaults, host="127.0.0.1", port=0, verbose=False)
+    srv.start()
+    codes = []
+
+    def user():
+        try:
+            with _post(srv.port, {"messages": [{"role": "user", "content": "hello"}], "max_tokens": 20}) as r:
+                json.load(r)
+                codes.append(200)
+        except urllib.error.HTTPError as e:
+            codes.append(e.code)
+            assert "overloaded" in json.load(e)["error"]["message"]
+
+    try:
+        threads = [threading.Thread(target=user) for _ in range(12)]
+        [t.start() for t in threads]
+        [t.join(timeout=120) for t in threads]
+        assert len(codes) == 12 and set(codes) == {200, 503} and 2 <= codes.count(200) <= 6, codes
+        st = srv.stats()
+        assert st["free_slots"] == 1 and st["waiting"] == 0 and st["running"] == 0
+    finally:
+        srv.close()
