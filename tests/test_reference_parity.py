@@ -87,3 +87,75 @@ def test_reference_loads_our_files_and_agrees_with_oracle(tmp_path, shape):
         # the reference prints '~' while a UTF-8 sequence is incomplete and U+FFFD for invalid bytes
         assert out.decode("utf-8", "replace").replace("�", "") == \
             ref_bytes.decode("utf-8", "replace").replace("�", ""), (prompt, pieces, out)
+
+
+def test_host_backend_on_two_nodes_generates_what_the_reference_generates_on_two_nodes(tmp_path):
+    """Root + 1 worker over loopback TCP, Q40 weights, Q80 sync pipe: this repo's host backend (C++) and the unmodified
+    reference must produce the same greedy continuation from the same files."""
+    import socket
+    import threading
+    from dllama_b200.formats import mfile, tfile
+    from dllama_b200.models import native_cpu_engine as N
+    from dllama_b200.text.native import Tokenizer
+    binary = _binary()
+    m, t = str(tmp_path / "p.m"), str(tmp_path / "p.t")
+    h = mfile.write_random_model(m, "tiny-tp8", exact=True, seed=9)
+    tfile.write_synthetic_tokenizer(t, h.vocab_size)
+    tok = Tokenizer(t)
+
+    def free_port():
+        with socket.socket() as s:
+            s.bind(("127.0.0.1", 0))
+            return s.getsockname()[1]
+
+    # the reference: worker process + root through a pty (it never exits, D5)
+    rport = free_port()
+    rworker = subprocess.Popen([binary, "worker", "--port", str(rport), "--nthreads", "1"], stdout=subprocess.DEVNULL,
+                               stderr=subprocess.DEVNULL, preexec_fn=os.setsid)
+    time.sleep(1.0)
+    prompt, n_new = "a b c", 6
+    ids = tok.encode(prompt, add_bos=True, add_special_tokens=False)
+    try:
+        master, slave = pty.openpty()
+        p = subprocess.Popen([binary, "inference", "--model", m, "--tokenizer", t, "--buffer-float-type", "q80", "--prompt", prompt,
+                              "--steps", str(len(ids) - 1 + n_new), "--nthreads", "1", "--temperature", "0", "--seed", "1",
+                              "--workers", f"127.0.0.1:{rport}"], stdout=slave, stderr=slave, preexec_fn=os.setsid)
+        os.close(slave)
+        buf, t0 = b"", time.time()
+        while b"Prediction" not in buf and time.time() - t0 < 90:
+            try:
+                chunk = os.read(master, 65536)
+            except OSError:
+                break
+            if not chunk:
+                break
+            buf += chunk
+    finally:
+        for proc in (p, rworker):
+            try:
+                os.killpg(os.getpgid(proc.pid), signal.SIGKILL)
+            except Exception:
+                pass
+            proc.wait(timeout=10)
+        os.close(master)
+    text = buf.decode("utf-8", "replace")
+    pieces = [l.split("|")[-1].strip() for l in text.split("\n") if "Pred" in l and "Sync" in l]
+    assert len(pieces) == n_new, text[-600:]
+    # this repo: worker thread + root engine, fed like the reference feeds (D8: token 0 after the prompt)
+    wport = free_port()
+    w = threading.Thread(target=N.serve_worker, args=(wport, 1), daemon=True)
+    w.start()
+    time.sleep(0.3)
+    eng = N.NativeCpuEngine(m, workers=[("127.0.0.1", wport)], n_threads=1, max_rows=8, n_slots=1, max_seq_len=256)
+    if len(ids) > 1:
+        eng.forward(ids[:-1], list(range(len(ids) - 1)), [0] * (len(ids) - 1))
+    token, pos, out = 0, len(ids) - 1, b""
+    for _ in range(n_new):
+        token = eng.decode_step_greedy([token], [pos], [0])[0]
+        pos += 1
+        out += tok.piece(token)
+    eng.close()
+    w.join(timeout=30)
+    ref_bytes = "".join(x for x in pieces if x != "~").encode("utf-8")
+    assert out.decode("utf-8", "replace").replace("�", "") == ref_bytes.decode("utf-8", "replace").replace("�", ""), \
+        (pieces, out)
