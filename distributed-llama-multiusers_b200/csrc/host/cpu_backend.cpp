@@ -389,6 +389,24 @@ void matmul_q40_q80(const uint8_t* w, int r0, int r1, int nb, const uint8_t* xq,
     matmul_q40_q80_scalar(w, r0, r1, nb, xq, M, y, ldy);
 }
 
+#ifdef DL_X86
+__attribute__((target("avx2,fma")))
+void axpy_f32_avx2(float a, const float* x, float* y, int n) {
+    const __m256 av = _mm256_set1_ps(a);
+    int i = 0;
+    for (; i + 8 <= n; i += 8) _mm256_storeu_ps(y + i, _mm256_fmadd_ps(av, _mm256_loadu_ps(x + i), _mm256_loadu_ps(y + i)));
+    for (; i < n; i++) y[i] += a * x[i];
+}
+#endif
+
+// y += a * x
+void axpy_f32(float a, const float* x, float* y, int n) {
+#ifdef DL_X86
+    if (has_avx2()) return axpy_f32_avx2(a, x, y, n);
+#endif
+    for (int i = 0; i < n; i++) y[i] += a * x[i];
+}
+
 float dot_f32(const float* a, const float* b, int n) {
 #ifdef DL_X86
     if (has_avx2()) return dot_f32_avx2(a, b, n);
@@ -797,7 +815,7 @@ struct Node {
     // activations
     std::vector<float> x, y, q, k, v, att_out, part, hb, hl, lg;
     std::vector<uint8_t> yq, zq;                // Q80 casts; zq: [n_nodes][M][slice bytes]
-    std::vector<std::vector<float>> scores;     // per thread [seq_len]
+    std::vector<std::vector<float>> scores;     // per thread: [rep][seq_len], grown on demand
     std::vector<int> pos, slot;
     // DLLAMA_CPU_PROFILE=1: seconds per op family, printed when the node is destroyed (reference: the executor's
     // per-step-type timers, nn-executor.cpp:150-154)
@@ -901,29 +919,38 @@ struct Node {
     // nn-cpu-ops.cpp:749-784; here per-row position and KV slot)
     void attention(int l, int M) {
         const int hs = c.h.head_size(), nh = c.h.n_heads / N(), nkv = c.h.n_kv_heads / N(), rep = nh / nkv;
-        const int kvw = nkv * hs, qw = nh * hs;
+        const int kvw = nkv * hs, qw = nh * hs, S = c.h.seq_len;
         const float scale = 1.0f / sqrtf((float)hs);
-        pool->run(M * nh, [&](int t, int b, int e) {
+        // one work item = (row, KV head): the `rep` query heads that share a KV head are processed together, so every
+        // cached K and V row is read once per group instead of once per query head (grouped-query attention).
+        // (Also sharing the K/V rows between the rows of a prompt chunk was measured and is slower: the score matrix of
+        // a whole chunk no longer fits the L1/L2 working set, and the kernel is bound by dot / exp work, not by K/V traffic.)
+        pool->run(M * nkv, [&](int t, int b, int e) {
+            if (scores[t].size() < (size_t)rep * S) scores[t].resize((size_t)rep * S);
             float* sc = scores[t].data();
             for (int it = b; it < e; it++) {
-                const int m = it / nh, hd = it % nh, kvh = hd / rep, P = pos[m];
+                const int m = it / nkv, kvh = it % nkv, P = pos[m];
                 const float* kk = kc[slot[m]][l].data() + (size_t)kvh * hs;
                 const float* vv = vc[slot[m]][l].data() + (size_t)kvh * hs;
-                const float* qq = q.data() + (size_t)m * qw + (size_t)hd * hs;
-                float mx = -INFINITY;
+                const float* qq = q.data() + (size_t)m * qw + (size_t)kvh * rep * hs;
                 for (int p = 0; p <= P; p++) {
-                    sc[p] = dot_f32(qq, kk + (size_t)p * kvw, hs) * scale;
-                    mx = std::max(mx, sc[p]);
+                    const float* kr = kk + (size_t)p * kvw;
+                    for (int g = 0; g < rep; g++) sc[(size_t)g * S + p] = dot_f32(qq + (size_t)g * hs, kr, hs) * scale;
                 }
-                float sum = 0.f;
-                for (int p = 0; p <= P; p++) { sc[p] = expf(sc[p] - mx); sum += sc[p]; }
-                const float inv = 1.0f / sum;
-                float* o = att_out.data() + (size_t)m * qw + (size_t)hd * hs;
-                for (int i = 0; i < hs; i++) o[i] = 0.f;
+                for (int g = 0; g < rep; g++) {          // softmax with max subtraction (reference: softmax_F32)
+                    float* sg = sc + (size_t)g * S;
+                    float mx = -INFINITY;
+                    for (int p = 0; p <= P; p++) mx = std::max(mx, sg[p]);
+                    float sum = 0.f;
+                    for (int p = 0; p <= P; p++) { sg[p] = expf(sg[p] - mx); sum += sg[p]; }
+                    const float inv = 1.0f / sum;
+                    for (int p = 0; p <= P; p++) sg[p] *= inv;
+                }
+                float* o = att_out.data() + (size_t)m * qw + (size_t)kvh * rep * hs;
+                for (int i = 0; i < rep * hs; i++) o[i] = 0.f;
                 for (int p = 0; p <= P; p++) {
-                    const float a = sc[p] * inv;
                     const float* vr = vv + (size_t)p * kvw;
-                    for (int i = 0; i < hs; i++) o[i] += a * vr[i];
+                    for (int g = 0; g < rep; g++) axpy_f32(sc[(size_t)g * S + p], vr, o + (size_t)g * hs, hs);
                 }
             }
         });
