@@ -5,7 +5,9 @@ import json
 import math
 
 import pytest
-from hypothesis import given, settings, strategies as st
+
+pytest.importorskip("hypothesis")
+from hypothesis import given, settings, strategies as st  # noqa: E402
 
 from dllama_b200.text.native import host_lib
 

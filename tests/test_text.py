@@ -233,6 +233,7 @@ def test_eos_detector_long_and_no_padding():
 def test_encode_decode_roundtrip_property(tmp_path):
     """Any UTF-8 text survives encode -> streaming decode (token by token, multi-byte characters split across
     tokens included), and the native server's tokenizer path (same C++ encoder) agrees on the token count."""
+    pytest.importorskip("hypothesis")
     from hypothesis import given, settings, strategies as st
     p = str(tmp_path / "prop.t")
     tfile.write_synthetic_tokenizer(p, 2048)
