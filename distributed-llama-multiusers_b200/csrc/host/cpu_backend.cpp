@@ -399,6 +399,147 @@ void axpy_f32_avx2(float a, const float* x, float* y, int n) {
 }
 #endif
 
+#ifdef DL_X86
+// exp(x) for x <= 0 (softmax arguments after max subtraction), 8 lanes: range reduction x = n ln2 + r, degree-6
+// polynomial on r in [-ln2/2, ln2/2] (Cephes coefficients), relative error ~1e-7; inputs below -87 give 0
+// (reference: the custom exp polynomials of its AVX2 / NEON softmax, nn-cpu-ops.cpp:82-102)
+__attribute__((target("avx2,fma")))
+static inline __m256 exp8_neg(__m256 x) {
+    const __m256 lo = _mm256_set1_ps(-87.0f);
+    const __m256 under = _mm256_cmp_ps(x, lo, _CMP_LT_OQ);
+    x = _mm256_max_ps(x, lo);
+    __m256 n = _mm256_round_ps(_mm256_mul_ps(x, _mm256_set1_ps(1.44269504088896341f)), _MM_FROUND_TO_NEAREST_INT | _MM_FROUND_NO_EXC);
+    __m256 r = _mm256_fnmadd_ps(n, _mm256_set1_ps(0.693359375f), x);
+    r = _mm256_fnmadd_ps(n, _mm256_set1_ps(-2.12194440e-4f), r);
+    __m256 p = _mm256_set1_ps(1.9875691500e-4f);
+    p = _mm256_fmadd_ps(p, r, _mm256_set1_ps(1.3981999507e-3f));
+    p = _mm256_fmadd_ps(p, r, _mm256_set1_ps(8.3334519073e-3f));
+    p = _mm256_fmadd_ps(p, r, _mm256_set1_ps(4.1665795894e-2f));
+    p = _mm256_fmadd_ps(p, r, _mm256_set1_ps(1.6666665459e-1f));
+    p = _mm256_fmadd_ps(p, r, _mm256_set1_ps(5.0000001201e-1f));
+    p = _mm256_fmadd_ps(p, _mm256_mul_ps(r, r), _mm256_add_ps(r, _mm256_set1_ps(1.0f)));
+    const __m256i e = _mm256_slli_epi32(_mm256_add_epi32(_mm256_cvtps_epi32(n), _mm256_set1_epi32(127)), 23);
+    return _mm256_andnot_ps(under, _mm256_mul_ps(p, _mm256_castsi256_ps(e)));
+}
+
+// s[0..n) <- softmax(s[0..n)) in place; elements are processed 8 at a time, the tail with the same polynomial through
+// a padded register, sums in lane order -- deterministic for a given n
+__attribute__((target("avx2,fma")))
+void softmax_inplace_avx2(float* s, int n) {
+    float mx = -INFINITY;
+    for (int i = 0; i < n; i++) mx = std::max(mx, s[i]);
+    const __m256 mv = _mm256_set1_ps(mx);
+    __m256 acc = _mm256_setzero_ps();
+    int i = 0;
+    for (; i + 8 <= n; i += 8) {
+        const __m256 e = exp8_neg(_mm256_sub_ps(_mm256_loadu_ps(s + i), mv));
+        _mm256_storeu_ps(s + i, e);
+        acc = _mm256_add_ps(acc, e);
+    }
+    float sum;
+    DL_HSUM8(sum, acc);
+    if (i < n) {
+        float tmp[8];
+        for (int k = 0; k < 8; k++) tmp[k] = i + k < n ? s[i + k] : -INFINITY;
+        const __m256 e = exp8_neg(_mm256_sub_ps(_mm256_loadu_ps(tmp), mv));
+        _mm256_storeu_ps(tmp, e);
+        for (int k = 0; i + k < n; k++) { s[i + k] = tmp[k]; sum += tmp[k]; }
+    }
+    const float inv = 1.0f / sum;
+    const __m256 iv = _mm256_set1_ps(inv);
+    for (i = 0; i + 8 <= n; i += 8) _mm256_storeu_ps(s + i, _mm256_mul_ps(_mm256_loadu_ps(s + i), iv));
+    for (; i < n; i++) s[i] *= inv;
+}
+#endif
+
+// softmax with max subtraction (reference: softmax_F32, nn-cpu-ops.cpp)
+void softmax_inplace(float* s, int n) {
+#ifdef DL_X86
+    if (has_avx2()) return softmax_inplace_avx2(s, n);
+#endif
+    float mx = -INFINITY;
+    for (int i = 0; i < n; i++) mx = std::max(mx, s[i]);
+    float sum = 0.f;
+    for (int i = 0; i < n; i++) { s[i] = expf(s[i] - mx); sum += s[i]; }
+    const float inv = 1.0f / sum;
+    for (int i = 0; i < n; i++) s[i] *= inv;
+}
+
+#ifdef DL_X86
+// out[g] = scale * dot(q + g*n, k) for g < rep: the K row is loaded once for four query heads at a time and the four
+// accumulators are reduced together (two hadd levels) instead of one horizontal sum per dot
+__attribute__((target("avx2,fma")))
+void dots_avx2(const float* q, const float* k, int n, int rep, float scale, float* out, size_t out_stride) {
+    int g = 0;
+    for (; g + 4 <= rep; g += 4) {
+        const float* q0 = q + (size_t)g * n;
+        __m256 a0 = _mm256_setzero_ps(), a1 = a0, a2 = a0, a3 = a0;
+        for (int i = 0; i + 8 <= n; i += 8) {
+            const __m256 kv = _mm256_loadu_ps(k + i);
+            a0 = _mm256_fmadd_ps(_mm256_loadu_ps(q0 + i), kv, a0);
+            a1 = _mm256_fmadd_ps(_mm256_loadu_ps(q0 + n + i), kv, a1);
+            a2 = _mm256_fmadd_ps(_mm256_loadu_ps(q0 + 2 * n + i), kv, a2);
+            a3 = _mm256_fmadd_ps(_mm256_loadu_ps(q0 + 3 * n + i), kv, a3);
+        }
+        const __m256 h = _mm256_hadd_ps(_mm256_hadd_ps(a0, a1), _mm256_hadd_ps(a2, a3));     // per 128-bit lane: sums of a0..a3
+        __m128 r = _mm_add_ps(_mm256_castps256_ps128(h), _mm256_extractf128_ps(h, 1));
+        r = _mm_mul_ps(r, _mm_set1_ps(scale));
+        float t[4];
+        _mm_storeu_ps(t, r);
+        for (int j = 0; j < 4; j++) out[(size_t)(g + j) * out_stride] = t[j];
+    }
+    for (; g < rep; g++) out[(size_t)g * out_stride] = dot_f32_avx2(q + (size_t)g * n, k, n) * scale;
+}
+#endif
+
+void axpy_f32(float a, const float* x, float* y, int n);
+
+#ifdef DL_X86
+// o[0..n) = sum_p w[p] * v[p * v_stride + 0..n): the output stays in registers (64 floats at a time) over the whole
+// position loop instead of being loaded and stored once per position
+__attribute__((target("avx2,fma")))
+void weighted_sum_avx2(const float* w, const float* v, size_t v_stride, int count, float* o, int n) {
+    for (int c0 = 0; c0 < n; c0 += 64) {
+        __m256 a0 = _mm256_setzero_ps(), a1 = a0, a2 = a0, a3 = a0, a4 = a0, a5 = a0, a6 = a0, a7 = a0;
+        for (int p = 0; p < count; p++) {
+            const __m256 wp = _mm256_set1_ps(w[p]);
+            const float* vr = v + (size_t)p * v_stride + c0;
+            a0 = _mm256_fmadd_ps(wp, _mm256_loadu_ps(vr), a0);
+            a1 = _mm256_fmadd_ps(wp, _mm256_loadu_ps(vr + 8), a1);
+            a2 = _mm256_fmadd_ps(wp, _mm256_loadu_ps(vr + 16), a2);
+            a3 = _mm256_fmadd_ps(wp, _mm256_loadu_ps(vr + 24), a3);
+            a4 = _mm256_fmadd_ps(wp, _mm256_loadu_ps(vr + 32), a4);
+            a5 = _mm256_fmadd_ps(wp, _mm256_loadu_ps(vr + 40), a5);
+            a6 = _mm256_fmadd_ps(wp, _mm256_loadu_ps(vr + 48), a6);
+            a7 = _mm256_fmadd_ps(wp, _mm256_loadu_ps(vr + 56), a7);
+        }
+        float* oc = o + c0;
+        _mm256_storeu_ps(oc, a0); _mm256_storeu_ps(oc + 8, a1); _mm256_storeu_ps(oc + 16, a2); _mm256_storeu_ps(oc + 24, a3);
+        _mm256_storeu_ps(oc + 32, a4); _mm256_storeu_ps(oc + 40, a5); _mm256_storeu_ps(oc + 48, a6); _mm256_storeu_ps(oc + 56, a7);
+    }
+}
+#endif
+
+// o = sum_p w[p] * v[p]   (the softmax-weighted sum of the cached V rows of one head)
+void weighted_sum_f32(const float* w, const float* v, size_t v_stride, int count, float* o, int n) {
+#ifdef DL_X86
+    if (has_avx2() && n % 64 == 0) return weighted_sum_avx2(w, v, v_stride, count, o, n);
+#endif
+    for (int i = 0; i < n; i++) o[i] = 0.f;
+    for (int p = 0; p < count; p++) axpy_f32(w[p], v + (size_t)p * v_stride, o, n);
+}
+
+void dots_f32(const float* q, const float* k, int n, int rep, float scale, float* out, size_t out_stride) {
+#ifdef DL_X86
+    if (has_avx2() && n % 8 == 0) return dots_avx2(q, k, n, rep, scale, out, out_stride);
+#endif
+    for (int g = 0; g < rep; g++) {
+        float r = 0.f;
+        for (int i = 0; i < n; i++) r += q[(size_t)g * n + i] * k[i];
+        out[(size_t)g * out_stride] = r * scale;
+    }
+}
+
 // y += a * x
 void axpy_f32(float a, const float* x, float* y, int n) {
 #ifdef DL_X86
@@ -935,23 +1076,11 @@ struct Node {
                 const float* qq = q.data() + (size_t)m * qw + (size_t)kvh * rep * hs;
                 for (int p = 0; p <= P; p++) {
                     const float* kr = kk + (size_t)p * kvw;
-                    for (int g = 0; g < rep; g++) sc[(size_t)g * S + p] = dot_f32(qq + (size_t)g * hs, kr, hs) * scale;
+                    dots_f32(qq, kr, hs, rep, scale, sc + p, (size_t)S);
                 }
-                for (int g = 0; g < rep; g++) {          // softmax with max subtraction (reference: softmax_F32)
-                    float* sg = sc + (size_t)g * S;
-                    float mx = -INFINITY;
-                    for (int p = 0; p <= P; p++) mx = std::max(mx, sg[p]);
-                    float sum = 0.f;
-                    for (int p = 0; p <= P; p++) { sg[p] = expf(sg[p] - mx); sum += sg[p]; }
-                    const float inv = 1.0f / sum;
-                    for (int p = 0; p <= P; p++) sg[p] *= inv;
-                }
+                for (int g = 0; g < rep; g++) softmax_inplace(sc + (size_t)g * S, P + 1);
                 float* o = att_out.data() + (size_t)m * qw + (size_t)kvh * rep * hs;
-                for (int i = 0; i < rep * hs; i++) o[i] = 0.f;
-                for (int p = 0; p <= P; p++) {
-                    const float* vr = vv + (size_t)p * kvw;
-                    for (int g = 0; g < rep; g++) axpy_f32(sc[(size_t)g * S + p], vr, o + (size_t)g * hs, hs);
-                }
+                for (int g = 0; g < rep; g++) weighted_sum_f32(sc + (size_t)g * S, vv, (size_t)kvw, P + 1, o + (size_t)g * hs, hs);
             }
         });
     }
@@ -1488,6 +1617,7 @@ int dl_cpu_has_vnni(void) { return has_vnni() ? 1 : 0; }
 // ---- op-level entry points (unit tests against the reference's goldens, src/nn/nn-cpu-ops-test.cpp) ----
 float dl_cpu_inv_rms(const float* x, int n, float eps) { return inv_rms(x, n, eps); }
 void dl_cpu_rms_norm(const float* x, const float* w, float* y, int n, float eps) { rms_norm_row(x, w, inv_rms(x, n, eps), y, n); }
+void dl_cpu_softmax(float* x, int n) { softmax_inplace(x, n); }
 void dl_cpu_activation(float* x, int n, int act /*1 = SiLU, 0 = GELU*/) { for (int i = 0; i < n; i++) x[i] = activate(x[i], act); }
 void dl_cpu_rope(float* row, int width, int head_size, int pos, float theta, int rope_type, float factor, float low,
                  float high, int orig_len) {

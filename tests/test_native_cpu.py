@@ -194,7 +194,32 @@ def _op_lib():
     L.dl_cpu_rms_norm.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_float]
     L.dl_cpu_activation.argtypes = [C.c_void_p, C.c_int, C.c_int]
     L.dl_cpu_rope.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, C.c_float, C.c_float, C.c_float, C.c_int]
+    L.dl_cpu_softmax.argtypes = [C.c_void_p, C.c_int]
     return L
+
+
+def test_attention_softmax_kernel_golden_and_accuracy():
+    """The vectorised softmax of the attention kernel: the reference's 8-value golden within its tolerance
+    (nn-cpu-ops-test.cpp:187-198; its own values come from an approximate exp) and float64 accuracy for every tail
+    length, large ranges and fully masked-out magnitudes."""
+    L = _op_lib()
+    y = (np.arange(8) / 8.0).astype(np.float32)
+    L.dl_cpu_softmax(y.ctypes.data, 8)
+    gold = [0.077399, 0.087780, 0.099500, 0.112761, 0.127778, 0.144793, 0.164072, 0.185917]
+    assert np.abs(y - np.array(gold, dtype=np.float32)).max() < 0.001
+    rng = np.random.default_rng(0)
+    for n in (1, 2, 7, 8, 9, 15, 16, 17, 100, 1000, 2049):
+        for scale in (0.1, 1.0, 10.0, 60.0):
+            x = (rng.standard_normal(n) * scale).astype(np.float32)
+            got = x.copy()
+            L.dl_cpu_softmax(got.ctypes.data, n)
+            x64 = x.astype(np.float64)
+            ref = np.exp(x64 - x64.max())
+            ref /= ref.sum()
+            assert np.abs(got - ref).max() < 1e-6 * ref.max() + 1e-12 and abs(float(got.sum()) - 1.0) < 1e-5
+    x = np.array([-200.0, 0.0, -100.0], dtype=np.float32)
+    L.dl_cpu_softmax(x.ctypes.data, 3)
+    assert x.tolist() == [0.0, 1.0, 0.0]
 
 
 def test_inv_rms_rmsnorm_and_silu_goldens():
