@@ -92,7 +92,8 @@ class LlamaEngine:
     def __init__(self, model_path: str, rank: int = 0, world: int = 1, group=None, max_rows: int = 32,
                  n_slots: int = 4, max_seq_len: int = 2048, kv_dtype: torch.dtype = torch.float16,
                  sync_q80: bool = True, use_pdl: bool = True, use_graphs: bool = True, n_pages: Optional[int] = None,
-                 device: Optional[torch.device] = None, verbose: bool = False, bucket_rows: bool = False):
+                 device: Optional[torch.device] = None, verbose: bool = False, bucket_rows: bool = False,
+                 use_mega: Optional[bool] = None):
         self.mf = ModelFile(model_path, max_seq_len=max_seq_len)
         h = self.h = self.mf.header
         if h.weight_type != quant.Q40:
@@ -104,6 +105,9 @@ class LlamaEngine:
         self.max_rows = max_rows
         self.use_pdl, self.use_graphs = use_pdl, use_graphs
         self.sync_q80 = sync_q80
+        # decode batches of <= 4 rows run as ONE persistent cooperative kernel (csrc/cuda/decode_mega.cu) instead of
+        # the launch sequence below; DLLAMA_MEGA=0 / use_mega=False keeps the multi-kernel path (comparison, debugging)
+        self.use_mega = (os.environ.get("DLLAMA_MEGA", "1") != "0") if use_mega is None else bool(use_mega)
         self.seq_len = min(h.seq_len, max_seq_len)
         self.n_sms = K.cuda_lib().dl_device_sm_count()
         dev = self.device
@@ -170,7 +174,12 @@ class LlamaEngine:
         self._off_att_ll, self._off_ffn_ll = 2 * part_bytes, 2 * part_bytes + ll_bytes
         self._off_logits = 2 * part_bytes + 2 * ll_bytes
         self._off_flags = _round_up(self._off_logits + logit_bytes, 256)
-        total = self._off_flags + 4096
+        # persistent decode kernel: Q80 LL-word exchange buffers (wo / w2 partial sums, greedy candidates)
+        mega_ll = K.mega_ll_bytes(N, h.dim)
+        self._off_mega_att = self._off_flags + 4096
+        self._off_mega_ffn = self._off_mega_att + mega_ll
+        self._off_mega_tok = self._off_mega_ffn + mega_ll
+        total = self._off_mega_tok + _round_up(N * K.MEGA_MAX_ROWS * 2 * 8, 256)
         self.symm = SymmetricBuffer(total, rank, world, group)
         sp = self.symm.ptrs
         self.part_att = [p + self._off_att for p in sp]
@@ -227,11 +236,105 @@ class LlamaEngine:
                                        dtype=torch.uint8, device=dev)
         self.argmax_scratch = torch.zeros(int(K.cuda_lib().dl_argmax_scratch_bytes(256)), dtype=torch.uint8,
                                           device=dev)
+        self._init_mega(kv_dtype)
         self._staging_ev: Optional[torch.cuda.Event] = None
         self._graphs: Dict[Tuple, torch.cuda.CUDAGraph] = {}
         self._graph_launches: Dict[Tuple, int] = {}
         self._graph_stream = torch.cuda.Stream(device=dev)
         torch.cuda.synchronize()
+
+    # ------------------------------------------------------------------------------------------------
+    # persistent decode kernel (csrc/cuda/decode_mega.cu)
+    # ------------------------------------------------------------------------------------------------
+    def _init_mega(self, kv_dtype):
+        h, dev, N = self.h, self.device, self.world
+        self._mega_ok_cache: Dict[int, bool] = {}
+        self.mega_grid = 0
+        if not self.use_mega or dev.type != "cuda" or kv_dtype != torch.float16 or (N > 1 and not self.sync_q80):
+            self.use_mega = False
+            return
+        from ..ops.lib import DlDecodeLayer
+        R4 = K.MEGA_MAX_ROWS
+        self.mega_grid = min(self.n_sms, int(os.environ.get("DLLAMA_MEGA_CTAS", str(self.n_sms))))
+        tab = (DlDecodeLayer * h.n_layers)()
+        for l, W in enumerate(self.layers):
+            tab[l].qkv, tab[l].wo, tab[l].w13, tab[l].w2 = (W[k].data_ptr() for k in ("qkv", "wo", "w13", "w2"))
+            tab[l].rms_att, tab[l].rms_ffn = W["rms_att"].data_ptr(), W["rms_ffn"].data_ptr()
+            tab[l].k_cache, tab[l].v_cache = self.k_cache[l].data_ptr(), self.v_cache[l].data_ptr()
+        raw = np.frombuffer(bytes(tab), dtype=np.uint8).copy()
+        self._mega_layers = torch.from_numpy(raw).to(dev)
+        self._mega_x = torch.zeros(2, R4, h.dim, dtype=torch.float32, device=dev)
+        self._mega_q = torch.zeros(R4, self.q_loc, dtype=torch.float32, device=dev)
+        self._mega_h = torch.zeros(R4, self.hid_loc, dtype=torch.float32, device=dev)
+        self._mega_att_o = torch.zeros(R4 * self.n_heads_loc * self.max_splits * self.hs, dtype=torch.float32, device=dev)
+        self._mega_att_ml = torch.zeros(R4 * self.n_heads_loc * self.max_splits * 2, dtype=torch.float32, device=dev)
+        self._mega_best = torch.zeros(self.mega_grid * R4 * 2, dtype=torch.float32, device=dev)
+        self._mega_bar = torch.zeros(2, dtype=torch.int64, device=dev)
+        self._mega_out = torch.zeros(R4, dtype=torch.int32, device=dev)
+        # a time-out inside the kernel traps (the context is lost); the reason is left in mapped host memory
+        self._mega_debug = torch.zeros(16, dtype=torch.int32).pin_memory()
+        self._mega_trace: Optional[torch.Tensor] = None
+        self._mega_timeout_ns = int(float(os.environ.get("DLLAMA_MEGA_TIMEOUT_S", "20")) * 1e9)
+
+    def _mega_args(self, M: int, row0: int, greedy: bool, device_loop: bool):
+        from ..ops.lib import DlDecodeArgs
+        h, N = self.h, self.world
+        a = DlDecodeArgs()
+        a.n_layers, a.dim, a.q_dim, a.kv_dim, a.hid = h.n_layers, h.dim, self.q_loc, self.kv_loc, self.hid_loc
+        a.vocab_loc, a.vocab, a.head_size = self.vocab_loc, h.vocab_size, self.hs
+        a.n_heads, a.n_kv_heads = self.n_heads_loc, self.n_kv_loc
+        a.rank, a.world = self.rank, N
+        a.eps = h.norm_epsilon
+        a.act_gelu = 0 if h.hidden_act == HIDDEN_ACT_SILU else 1
+        a.q80_sync = 1 if self.sync_q80 else 0
+        a.layers = self._mega_layers.data_ptr()
+        a.rms_final, a.wcls = self.rms_final.data_ptr(), self.wcls.data_ptr()
+        a.embedding, a.rope_freqs = self.embedding.data_ptr(), self.rope_freqs.data_ptr()
+        a.M, a.row0 = M, row0
+        a.tokens, a.pos, a.slot = self.tokens.data_ptr(), self.pos.data_ptr(), self.slot.data_ptr()
+        a.block_table, a.max_pages = self.block_table.data_ptr(), self.max_pages
+        a.x[0], a.x[1] = self._mega_x[0].data_ptr(), self._mega_x[1].data_ptr()
+        a.q, a.h = self._mega_q.data_ptr(), self._mega_h.data_ptr()
+        a.att_o, a.att_ml = self._mega_att_o.data_ptr(), self._mega_att_ml.data_ptr()
+        a.max_splits = self.max_splits
+        a.att_splits = max(1, min(self.max_splits, self.mega_grid // max(1, M * self.n_kv_loc)))
+        a.cta_best = self._mega_best.data_ptr()
+        a.grid_bar = self._mega_bar.data_ptr()
+        a.step_counter = self.step_counter
+        sp = self.symm.ptrs
+        for p in range(N):
+            a.ll_att[p] = sp[p] + self._off_mega_att
+            a.ll_ffn[p] = sp[p] + self._off_mega_ffn
+            a.ll_tok[p] = sp[p] + self._off_mega_tok
+            a.logits[p] = self.logits_ptrs[p]
+            a.flag_logits[p] = self.flags_log_peer[p]
+        a.greedy = 1 if greedy else 0
+        a.tokens_out = self.out_tokens.data_ptr()
+        a.advance = 1 if device_loop else 0
+        a.history = self.history.data_ptr() if device_loop else None
+        a.history_cap = self.history_cap
+        a.timeout_ns = self._mega_timeout_ns
+        a.debug = self._mega_debug.data_ptr()
+        a.trace = self._mega_trace.data_ptr() if self._mega_trace is not None else None
+        return a
+
+    def _mega_usable(self, M: int, chunk: bool) -> bool:
+        if not self.use_mega or chunk or M > K.MEGA_MAX_ROWS:
+            return False
+        ok = self._mega_ok_cache.get(M)
+        if ok is None:
+            ok = K.decode_mega_supported(self._mega_args(M, 0, True, False), self.mega_grid)
+            self._mega_ok_cache[M] = ok
+        return ok
+
+    def enable_mega_trace(self, on: bool = True):
+        """Per-phase globaltimer stamps of CTA 0 (8 per layer + 2): read with mega_trace_ns() after a forward.
+        Graphs captured before the switch keep their old setting."""
+        self._mega_trace = torch.zeros(self.h.n_layers * 8 + 8, dtype=torch.int64, device=self.device) if on else None
+        self._graphs.clear()
+
+    def mega_trace_ns(self) -> np.ndarray:
+        return self._mega_trace.cpu().numpy().astype(np.int64)
 
     # ------------------------------------------------------------------------------------------------
     def _load_weights(self, verbose: bool):
@@ -334,6 +437,11 @@ class LlamaEngine:
     def _launch_forward(self, M: int, row0: int, greedy: bool, device_loop: bool, chunk: bool = False):
         """Enqueue one forward over rows 0..M-1 of the descriptor; logits for rows row0..M-1."""
         h, N, pdl = self.h, self.world, self.use_pdl
+        if self._mega_usable(M, chunk):
+            K.decode_mega(self._mega_args(M, row0, greedy, device_loop), self.mega_grid)
+            if not greedy and N > 1:
+                K.wait_flags(self.flags_log_local, N, self.step_counter, 1, 0)
+            return
         gemv = M <= GEMV_PATH_MAX_M
         xq = lambda t: t if gemv else None
         xh = lambda t: None if gemv else t

@@ -269,6 +269,33 @@ def gemm_f32(w: torch.Tensor, x: torch.Tensor, out: Optional[torch.Tensor] = Non
     return out
 
 
+MEGA_MAX_ROWS = 4
+MEGA_LL_WORDS = 9          # 8-byte LL words per 32-value Q80 block (8 x {4 int8, epoch} + {fp16 scale, epoch})
+
+
+def mega_ll_bytes(world: int, dim: int) -> int:
+    """Bytes of one exchange buffer of the persistent decode kernel: [world][4 rows][dim/32][9] LL words."""
+    return world * MEGA_MAX_ROWS * (dim // 32) * MEGA_LL_WORDS * 8
+
+
+def decode_mega_supported(args: "lib.DlDecodeArgs", grid: int) -> bool:
+    return cuda_lib().dl_decode_mega_supported(C.byref(args), grid) == 0
+
+
+def decode_mega(args: "lib.DlDecodeArgs", grid: int):
+    """One persistent cooperative launch = one whole forward pass for args.M <= 4 rows."""
+    check(cuda_lib().dl_decode_mega(C.byref(args), grid, _stream()), "dl_decode_mega")
+    lib.count_launch()
+
+
+def decode_mega_plan(d: int, n: int, align: int, grid: int, cta: int):
+    """(first row, end row, pipeline chunks) of CTA `cta` for a [d][n] matmul phase (host helper)."""
+    r0, r1, nc = C.c_int(), C.c_int(), C.c_int()
+    check(cuda_lib().dl_decode_mega_plan(d, n, align, grid, cta, C.byref(r0), C.byref(r1), C.byref(nc)),
+          "dl_decode_mega_plan")
+    return r0.value, r1.value, nc.value
+
+
 def choose_tc_split(d: int, n: int, M: int, n_sms: int) -> int:
     """Cluster split-K factor of the tcgen05 GEMM: a power of two (<= 8) that fills the chip without
     ever launching more CTAs than SMs (one CTA per SM: a second wave of half-empty CTAs costs more

@@ -76,6 +76,59 @@ class DlNormProlog(C.Structure):
     ]
 
 
+class DlDecodeLayer(C.Structure):
+    """Mirror of ``DlDecodeLayer`` (per-layer device pointers of the persistent decode kernel)."""
+    _fields_ = [("qkv", C.c_void_p), ("wo", C.c_void_p), ("w13", C.c_void_p), ("w2", C.c_void_p),
+                ("rms_att", C.c_void_p), ("rms_ffn", C.c_void_p), ("k_cache", C.c_void_p), ("v_cache", C.c_void_p)]
+
+
+class DlDecodeArgs(C.Structure):
+    """Mirror of ``DlDecodeArgs`` in include/dllama_b200.h (field order and types must match)."""
+    _fields_ = [
+        ("n_layers", C.c_int), ("dim", C.c_int), ("q_dim", C.c_int), ("kv_dim", C.c_int), ("hid", C.c_int),
+        ("vocab_loc", C.c_int), ("vocab", C.c_int), ("head_size", C.c_int), ("n_heads", C.c_int),
+        ("n_kv_heads", C.c_int),
+        ("rank", C.c_int), ("world", C.c_int),
+        ("eps", C.c_float),
+        ("act_gelu", C.c_int),
+        ("q80_sync", C.c_int),
+        ("layers", C.c_void_p),
+        ("rms_final", C.c_void_p),
+        ("wcls", C.c_void_p),
+        ("embedding", C.c_void_p),
+        ("rope_freqs", C.c_void_p),
+        ("M", C.c_int), ("row0", C.c_int),
+        ("tokens", C.c_void_p),
+        ("pos", C.c_void_p),
+        ("slot", C.c_void_p),
+        ("block_table", C.c_void_p),
+        ("max_pages", C.c_int),
+        ("x", C.c_void_p * 2),
+        ("q", C.c_void_p),
+        ("h", C.c_void_p),
+        ("att_o", C.c_void_p),
+        ("att_ml", C.c_void_p),
+        ("max_splits", C.c_int),
+        ("att_splits", C.c_int),
+        ("cta_best", C.c_void_p),
+        ("grid_bar", C.c_void_p),
+        ("step_counter", C.c_void_p),
+        ("ll_att", C.c_void_p * DL_MAX_PEERS),
+        ("ll_ffn", C.c_void_p * DL_MAX_PEERS),
+        ("ll_tok", C.c_void_p * DL_MAX_PEERS),
+        ("logits", C.c_void_p * DL_MAX_PEERS),
+        ("flag_logits", C.c_void_p * DL_MAX_PEERS),
+        ("greedy", C.c_int),
+        ("tokens_out", C.c_void_p),
+        ("advance", C.c_int),
+        ("history", C.c_void_p),
+        ("history_cap", C.c_int),
+        ("timeout_ns", C.c_ulonglong),
+        ("debug", C.c_void_p),
+        ("trace", C.c_void_p),
+    ]
+
+
 _cuda = None
 
 
@@ -119,6 +172,12 @@ def cuda_lib():
     L.dl_ipc_close.argtypes = [vp]
     L.dl_ipc_free.argtypes = [vp]
     L.dl_peer_barrier.argtypes = [C.POINTER(vp), vp, i32, i32, u32, vp]
+    L.dl_decode_mega_supported.argtypes = [C.POINTER(DlDecodeArgs), i32]
+    L.dl_decode_mega_supported.restype = i32
+    L.dl_decode_mega.argtypes = [C.POINTER(DlDecodeArgs), i32, vp]
+    L.dl_decode_mega.restype = i32
+    L.dl_decode_mega_plan.argtypes = [i32, i32, i32, i32, i32, C.POINTER(i32), C.POINTER(i32), C.POINTER(i32)]
+    L.dl_decode_mega_plan.restype = i32
     for name in ("dl_q40_repack", "dl_q40t_dequant", "dl_reduce_norm_quant", "dl_quant_q80", "dl_embedding",
                  "dl_sample_rows", "dl_gemm_f32", "dl_gemv_q40", "dl_gemm_q40_tc", "dl_attention", "dl_attention_prefill", "dl_argmax", "dl_ipc_alloc", "dl_ipc_open",
                  "dl_ipc_close", "dl_ipc_free", "dl_peer_barrier", "dl_wait_flags"):

@@ -174,6 +174,84 @@ int dl_argmax_noalloc(const float* logits, int M, int vocab, int ld, int* tokens
 int dl_wait_flags(const uint32_t* flags, int n, const uint32_t* step_counter, uint32_t flag_mul,
                   uint32_t flag_add, void* stream);
 
+/* ---- persistent decode step ----------------------------------------------------------------
+ * One cooperative kernel runs a whole forward pass for 1..4 rows (decode): embedding, every layer's
+ * norm -> qkv(+RoPE, KV write) -> paged attention -> wo -> norm -> w1|w3 (SiLU*mul) -> w2, final norm,
+ * logits, greedy pick.  Phases are separated by device-side grid barriers instead of kernel
+ * boundaries and the Q40T weight stream is prefetched across them, so the per-kernel fixed latency
+ * of the launch sequence is paid once per token.  Tensor-parallel partial sums travel as Q80 LL
+ * words ({4 x int8 | fp16 scale, epoch} in one 8-byte store) written straight into every peer's
+ * exchange buffer; the next phase polls the words themselves (no fence, counter or flag).
+ * (reference: the whole per-token step list of NnExecutor::forward, src/nn/nn-executor.cpp:134-163,
+ * over the graph of src/llm.cpp:126-438; SYNC_NODE_SLICES + OP_MERGE_ADD, src/nn/nn-network.cpp:537-569) */
+#define DL_MEGA_MAX_ROWS 4
+typedef struct {
+    const uint8_t* qkv;               /* Q40T [q_dim + 2 kv_dim][dim]                      */
+    const uint8_t* wo;                /* Q40T [dim][q_dim]                                 */
+    const uint8_t* w13;               /* Q40T [2 hid][dim], rows interleaved (gate, up)    */
+    const uint8_t* w2;                /* Q40T [dim][hid]                                   */
+    const float* rms_att;
+    const float* rms_ffn;
+    void* k_cache;                    /* fp16 [n_pages][n_kv_heads][32][head_size]         */
+    void* v_cache;
+} DlDecodeLayer;
+
+typedef struct {
+    /* model, per-rank slice sizes */
+    int n_layers, dim, q_dim, kv_dim, hid, vocab_loc, vocab, head_size, n_heads, n_kv_heads;
+    int rank, world;
+    float eps;
+    int act_gelu;
+    int q80_sync;                     /* Q80 round trip of the wo / w2 outputs (always on when world > 1) */
+    const DlDecodeLayer* layers;      /* device array [n_layers] */
+    const float* rms_final;
+    const uint8_t* wcls;              /* Q40T [vocab_loc][dim] */
+    const float* embedding;           /* [vocab][dim] f32 */
+    const float* rope_freqs;          /* [head_size/2] */
+    /* batch */
+    int M, row0;                      /* rows; logits / tokens are produced for rows row0..M-1 */
+    int* tokens;                      /* [M] */
+    int* pos;                         /* [M] */
+    const int* slot;                  /* [M] */
+    const int* block_table;           /* [n_slots][max_pages] */
+    int max_pages;
+    /* activations and scratch of this rank (device) */
+    float* x[2];                      /* residual stream [4][dim]; x[1] only used when world > 1 */
+    float* q;                         /* [4][q_dim] */
+    float* h;                         /* [4][hid] */
+    float* att_o;                     /* [4][n_heads][max_splits][head_size] */
+    float* att_ml;                    /* [4][n_heads][max_splits][2] */
+    int max_splits;                   /* capacity of the split dimension above (<= 32) */
+    int att_splits;                   /* split-KV grid: CTAs per (row, kv head) */
+    float* cta_best;                  /* [grid][4][2] greedy candidates */
+    unsigned long long* grid_bar;     /* one zero-initialised, monotonically increasing counter */
+    uint32_t* step_counter;
+    /* tensor-parallel exchange: rank p's buffers as mapped into this process (p < world) */
+    uint8_t* ll_att[DL_MAX_PEERS];    /* [world src][4][dim/32][9] 8-byte LL words */
+    uint8_t* ll_ffn[DL_MAX_PEERS];
+    uint8_t* ll_tok[DL_MAX_PEERS];    /* [world src][4][2] LL words: best logit, its index */
+    float* logits[DL_MAX_PEERS];      /* [rows][vocab] on every rank (only logits[rank] when world == 1) */
+    uint32_t* flag_logits[DL_MAX_PEERS]; /* word to release on rank p once this rank's logits slice is there */
+    /* output */
+    int greedy;                       /* 1: pick argmax in the kernel (logits are not written) */
+    int* tokens_out;                  /* [M - row0] (greedy) */
+    int advance;                      /* 1: tokens[m] = pick, pos[m] += 1 (device-resident loop) */
+    int* history;                     /* NULL or [cap][M] ring indexed by step - 1 */
+    int history_cap;
+    unsigned long long timeout_ns;    /* spin limit before the kernel traps (0 = none) */
+    uint32_t* debug;                  /* NULL or a word in mapped pinned host memory: 0x80000000 | wait code << 16 | CTA
+                                       * is stored there before a time-out trap (device memory is lost with the context) */
+    unsigned long long* trace;        /* NULL or [n_layers * 8 + 8] globaltimer stamps of CTA 0 */
+} DlDecodeArgs;
+
+/* 0 if the shapes fit the persistent kernel (shared memory, register-resident row, head size), else -1
+ * with the reason in dl_last_error(); callers fall back to the multi-kernel launch sequence. */
+int dl_decode_mega_supported(const DlDecodeArgs* args /*host*/, int grid);
+int dl_decode_mega(const DlDecodeArgs* args /*host*/, int grid /*CTAs, <= SM count*/, void* stream);
+/* work split of one matmul phase for CTA `cta` of `grid`: rows [r0, r1) and the number of pipeline
+ * chunks they take (host helper, used by tests) */
+int dl_decode_mega_plan(int d, int n, int align, int grid, int cta, int* r0, int* r1, int* n_chunks);
+
 /* ---- peer memory (symmetric buffers over NVLink) ------------------------------------------ */
 int dl_ipc_alloc(void** dev_ptr, long long bytes, uint8_t* handle_out /*64 B host*/);
 int dl_ipc_open(const uint8_t* handle /*64 B host*/, void** dev_ptr);
