@@ -29,7 +29,9 @@
 
 #define MG_NS 12                          // weight ring stages (9216 B each)
 #define MG_CONS 512                       // consumer threads (16 warps, 4 groups of 128)
-#define MG_THREADS 576                    // + weight producer warp (16) + KV page producer warp (17)
+#define MG_NPROD 3                        // weight producer warps (16..18): chunk `it` belongs to producer it % 3
+#define MG_KV_WARP (16 + MG_NPROD)        // KV page producer warp
+#define MG_THREADS (MG_CONS + 32 * MG_NPROD + 32)   // 20 warps = 5 per scheduler: still 96 registers per thread
 #define MG_MAX_M DL_MEGA_MAX_ROWS
 #define MG_ACT_BYTES 98304                // XQ slabs of the current phase | KV page stages + attention merge scratch
 #define MG_KV_STAGES 4
@@ -45,31 +47,27 @@
 #define SM_RED (SM_ACT + MG_ACT_BYTES)                    // [4 groups * kpack][MT][nr]  <= 4*128*4 floats
 #define SM_OUT (SM_RED + 4 * 128 * MG_MAX_M * 4)          // out_s [MT][128]
 #define SM_QS (SM_OUT + 128 * MG_MAX_M * 4)               // q_s [8][128] f32 (attention)
-#define SM_MISC (SM_QS + 8 * 128 * 4)                     // ssq / argmax / w_ml scratch (4 KB)
-#define SM_TOTAL (SM_MISC + 4096)
+#define SM_MISC (SM_QS + 8 * 128 * 4)                     // ssq / argmax / w_ml scratch (2.5 KB)
+#define SM_ROWS (SM_MISC + 2560)                          // per-row constants of this launch (MgRowInfo[4]) + RoPE table
+#define SM_ROPE (SM_ROWS + 256)                           // [4 rows][64 pairs] (cos, sin)
+#define SM_ARGS (SM_ROPE + MG_MAX_M * 64 * 8)             // copy of the kernel arguments (see mg_args())
+#define SM_HBAR (SM_ARGS + 1024)                          // mbarrier of the hidden-activation bulk copy
+#define SM_TOTAL (SM_HBAR + 16)
+static_assert(sizeof(DlDecodeArgs) <= 1024, "DlDecodeArgs outgrew its shared-memory copy");
 
 extern void dl_set_error(const char* fmt, ...);
 
+// Spin guard: every wait loop ticks a per-thread counter; every 2^16 ticks it compares the global timer with the
+// deadline of the launch (kernel start + timeout_ns, kept in shared memory) and traps when it has passed -- the launch dies
+// with an error instead of hanging the GPU.  `code` says which wait it was (left in mapped host memory, see DlDecodeArgs).
+__device__ __noinline__ void mg_deadline_check(int code);
 struct MgSpin {
-    unsigned long long limit, t0;
-    uint32_t* dbg;
     unsigned n;
-    DL_DEVINL void init(unsigned long long lim, uint32_t* d) { limit = lim; t0 = 0; n = 0; dbg = d; }
-    // called from spin loops; traps (kills the launch with an error instead of hanging the GPU) after `limit` ns
+    DL_DEVINL void init(unsigned long long, uint32_t*) { n = 0; }
     DL_DEVINL void tick(int code) {
-        if (((++n) & 0x3ffu) != 0u || limit == 0ull) return;
-        const unsigned long long now = globaltimer_ns();
-        if (t0 == 0ull) { t0 = now; return; }
-        if (now - t0 > limit) {
-            // the launch dies with an error instead of hanging the GPU; `code` says which wait it was
-            if (dbg != nullptr) {
-                asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(dbg), "r"(0x80000000u | (uint32_t)code * 65536u | blockIdx.x) : "memory");
-                __threadfence_system();
-            }
-            __trap();
-        }
+        if (((++n) & 0xffffu) == 0u) mg_deadline_check(code);
     }
-    DL_DEVINL void reset() { t0 = 0; n = 0; }
+    DL_DEVINL void reset() {}
 };
 
 DL_DEVINL void mg_mbar_wait(uint64_t* bar, uint32_t parity, MgSpin& sp, int code) {
@@ -94,15 +92,24 @@ DL_DEVINL void st_volatile_u64(void* p, unsigned long long v) {
     asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
-// Grid barrier among the consumer threads of all CTAs (all CTAs are co-resident: cooperative launch).
-// The counter only grows: a CTA's ticket t belongs to barrier instance t / G, which completes at (t/G + 1) * G.
-DL_DEVINL void grid_sync(unsigned long long* bar, unsigned G, MgSpin& sp) {
+// Grid barrier among the consumer threads of all CTAs (all CTAs are co-resident: cooperative launch).  The counter
+// starts at 0 in every launch (the last CTA to leave the kernel clears it), so the k-th barrier completes at k * G:
+// one fire-and-forget release-add per CTA, then an acquire spin -- no ticket round trip.
+DL_DEVINL void red_release_gpu_add(unsigned* p, unsigned v) {
+    asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+DL_DEVINL unsigned ld_acquire_gpu_u32(const unsigned* p) {
+    unsigned v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+DL_DEVINL void grid_sync(unsigned* bar, unsigned G, unsigned& k, MgSpin& sp) {
+    k++;
     cons_bar();
     if (threadIdx.x == 0) {
-        __threadfence();
-        const unsigned long long t = atomicAdd(bar, 1ull);
-        const unsigned long long target = (t / G + 1ull) * G;
-        while (ld_acquire_gpu_u64(bar) < target) sp.tick(1);
+        red_release_gpu_add(bar, 1u);
+        const unsigned target = k * G;
+        while (ld_acquire_gpu_u32(bar) < target) sp.tick(1);
         sp.reset();
     }
     cons_bar();
@@ -120,10 +127,17 @@ DL_DEVINL int mg_n_eff(int pos, int att_splits) {
 // shared memory is carved with fixed offsets from the dynamic base, so every (non-inlined) phase function finds its
 // regions without a pointer table travelling through local memory
 extern __shared__ __align__(1024) uint8_t mg_smem[];
+// what the phases need to know about a batch row, fetched ONCE per launch: positions, slots and block tables do not
+// change inside a step, and every global load after a grid barrier is an L2 round trip shared with 147 other CTAs
+struct MgRowInfo {
+    int pos, page, n_eff, token, slot, pad0, pad1, pad2;   // position, KV page of that position, attention splits in use, input token
+};
 struct MgCtx {
     uint64_t *full, *empty, *kv_full, *kv_empty;
     uint8_t *ring, *act;
     float *red, *out_s, *q_s, *misc;
+    struct MgRowInfo* rows;
+    float2* rope;
     int tid, cta, G;
     DL_DEVINL MgCtx() {
         full = reinterpret_cast<uint64_t*>(mg_smem + SM_BARS);
@@ -136,11 +150,29 @@ struct MgCtx {
         out_s = reinterpret_cast<float*>(mg_smem + SM_OUT);
         q_s = reinterpret_cast<float*>(mg_smem + SM_QS);
         misc = reinterpret_cast<float*>(mg_smem + SM_MISC);
+        rows = reinterpret_cast<struct MgRowInfo*>(mg_smem + SM_ROWS);
+        rope = reinterpret_cast<float2*>(mg_smem + SM_ROPE);
         tid = threadIdx.x;
         cta = blockIdx.x;
         G = gridDim.x;
     }
 };
+
+// The phase functions are real calls (one copy of each in the instruction stream).  Reaching the kernel parameters
+// through a reference from there means generic loads from parameter space, which miss after every acquire of a grid
+// barrier (~0.8 us per phase entry, measured); a copy in shared memory costs one LDS instead.
+DL_DEVINL const DlDecodeArgs& mg_args() { return *reinterpret_cast<const DlDecodeArgs*>(mg_smem + SM_ARGS); }
+
+__device__ __noinline__ void mg_deadline_check(int code) {
+    const DlDecodeArgs& a = mg_args();
+    const unsigned long long deadline = *reinterpret_cast<const unsigned long long*>(mg_smem + SM_HBAR + 8);
+    if (a.timeout_ns == 0ull || globaltimer_ns() < deadline) return;
+    if (a.debug != nullptr) {
+        asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(a.debug), "r"(0x80000000u | (uint32_t)code * 65536u | blockIdx.x) : "memory");
+        __threadfence_system();
+    }
+    __trap();
+}
 
 // the five matmul phases of a layer (+ logits): shape, row alignment and weights, shared by producer and consumers
 enum { PH_QKV = 0, PH_WO = 1, PH_W13 = 2, PH_W2 = 3, PH_CLS = 4 };
@@ -163,55 +195,96 @@ DL_DEVINL MgPhase mg_phase(const DlDecodeArgs& a, const DlDecodeLayer* L, int ph
 // =================================================================================================
 // weight producer warp: the schedule of every matmul phase of the whole forward pass
 // =================================================================================================
-__device__ __noinline__ void produce_matrix(const uint8_t* w, int d, int n, int align, uint32_t& it_io, uint64_t pol,
-                                            unsigned long long timeout_ns, uint32_t* dbg) {
+// Walks this CTA's pieces (row slices of one Q40T row tile over the full K extent) through every phase of every layer,
+// in the order the consumers eat them.
+struct MgPieceCursor {
+    int l, ph, r, R1;
+    const uint8_t* tile0;          // first k-tile of the piece's row tile
+    int r0, nr, kpack, nch, KT;
+    uint32_t it0, it_next;         // global chunk index of the piece's first chunk / of the piece after it
+    bool done;
+    DL_DEVINL void init() { l = 0; ph = PH_QKV - 1; r = 0; R1 = 0; it0 = 0; it_next = 0; done = false; }
+    DL_DEVINL bool next(const DlDecodeArgs& a, int cta, int G) {
+        const uint8_t* w = nullptr;
+        while (r >= R1) {                                   // next phase with rows for this CTA
+            if (ph == PH_CLS) { done = true; return false; }
+            ph++;
+            if (ph > PH_W2 && l + 1 < a.n_layers) { l++; ph = PH_QKV; }
+            const MgPhase p = mg_phase(a, a.layers + l, ph);
+            int R0;
+            mg_cta_rows(p.d, G, p.align, cta, R0, R1);
+            r = R0;
+            KT = p.n >> 7;
+        }
+        w = mg_phase(a, a.layers + l, ph).w;
+        const int rt = r >> 7;
+        r0 = r & 127;
+        nr = min(128 - r0, R1 - r);
+        kpack = mg_kpack(nr);
+        nch = (KT + kpack - 1) / kpack;
+        tile0 = w + (size_t)rt * KT * Q40T_TILE_BYTES;
+        it0 = it_next;
+        it_next = it0 + nch;
+        r += nr;
+        return true;
+    }
+};
+
+DL_DEVINL void bulk_prefetch_l2(const void* gsrc, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gsrc), "r"(bytes) : "memory");
+}
+
+// The three producer warps: warp `me` owns the chunks with it % 3 == me.  Besides the shared-memory ring they run an L2
+// prefetch cursor MG_PF_DIST chunks (+ one piece) ahead, so HBM keeps streaming while the consumers sit in a prologue,
+// an attention phase or a barrier -- the ring alone holds only ~2.5 us worth of the stream.
+__device__ __noinline__ void weight_producer() {
+    const DlDecodeArgs& a = mg_args();
     const MgCtx c;
     MgSpin sp;
-    sp.init(timeout_ns, dbg);
+    sp.init(a.timeout_ns, a.debug);
+    const uint64_t pol = l2_policy_evict_first();
     const int lane = c.tid & 31;
-    const int KT = n >> 7;
-    uint32_t it = it_io;
-    int R0, R1;
-    mg_cta_rows(d, c.G, align, c.cta, R0, R1);
-    int r = R0;
-    while (r < R1) {
-        const int rt = r >> 7, r0 = r & 127;
-        const int nr = min(128 - r0, R1 - r);
-        const int kpack = mg_kpack(nr);
-        const uint8_t* tile0 = w + (size_t)rt * KT * Q40T_TILE_BYTES;
+    const uint32_t me = (uint32_t)((c.tid >> 5) - 16);
+    MgPieceCursor ld, pf;
+    ld.init();
+    pf.init();
+    if (a.pf_dist > 0) pf.next(a, c.cta, c.G); else pf.done = true;
 #pragma unroll 1
-        for (int kt0 = 0; kt0 < KT; kt0 += kpack) {
-            const int nkt = min(kpack, KT - kt0);
-            const int s = it % MG_NS;
-            if (it >= MG_NS) mg_mbar_wait(&c.empty[s], ((it / MG_NS) & 1) ^ 1, sp, 2);
+    while (ld.next(a, c.cta, c.G)) {
+        // ---- L2 prefetch of the pieces ahead (k-tiles dealt over the 96 producer lanes) ----
+#pragma unroll 1
+        while (!pf.done && pf.it0 < ld.it0 + (uint32_t)a.pf_dist) {
+            if (pf.it0 >= ld.it_next) {                     // pieces the ring is about to load anyway are skipped
+#pragma unroll 1
+                for (int kt = (int)me * 32 + lane; kt < pf.KT; kt += 32 * MG_NPROD) {
+                    const uint8_t* t = pf.tile0 + (size_t)kt * Q40T_TILE_BYTES;
+                    bulk_prefetch_l2(t + pf.r0 * 64, (uint32_t)(pf.nr * 64));
+                    bulk_prefetch_l2(t + Q40T_SCALE_OFF + pf.r0 * 8, (uint32_t)(pf.nr * 8));
+                }
+            }
+            pf.next(a, c.cta, c.G);
+        }
+        // ---- my chunks of this piece into the ring: ci with (it0 + ci) % MG_NPROD == me ----
+        int ci = (int)((me + MG_NPROD - ld.it0 % MG_NPROD) % MG_NPROD);
+#pragma unroll 1
+        for (; ci < ld.nch; ci += MG_NPROD) {
+            const uint32_t itc = ld.it0 + ci;
+            const int kt0 = ci * ld.kpack;
+            const int nkt = min(ld.kpack, ld.KT - kt0);
+            const int nr = ld.nr;
+            const int s = itc % MG_NS;
+            if (itc >= MG_NS) mg_mbar_wait(&c.empty[s], ((itc / MG_NS) & 1) ^ 1, sp, 2);
             uint8_t* st = c.ring + s * Q40T_TILE_BYTES;
             if (lane == 0) mbar_arrive_expect_tx(&c.full[s], (uint32_t)(nkt * nr * 72));
             __syncwarp();
             if (lane < nkt) {
-                const uint8_t* t = tile0 + (size_t)(kt0 + lane) * Q40T_TILE_BYTES;
-                bulk_g2s_hint(st + lane * nr * 64, t + r0 * 64, (uint32_t)(nr * 64), &c.full[s], pol);
+                const uint8_t* t = ld.tile0 + (size_t)(kt0 + lane) * Q40T_TILE_BYTES;
+                bulk_g2s_hint(st + lane * nr * 64, t + ld.r0 * 64, (uint32_t)(nr * 64), &c.full[s], pol);
             } else if (lane >= 16 && lane - 16 < nkt) {
                 const int j = lane - 16;
-                const uint8_t* t = tile0 + (size_t)(kt0 + j) * Q40T_TILE_BYTES;
-                bulk_g2s_hint(st + Q40T_NIB_BYTES + j * nr * 8, t + Q40T_SCALE_OFF + r0 * 8, (uint32_t)(nr * 8), &c.full[s], pol);
+                const uint8_t* t = ld.tile0 + (size_t)(kt0 + j) * Q40T_TILE_BYTES;
+                bulk_g2s_hint(st + Q40T_NIB_BYTES + j * nr * 8, t + Q40T_SCALE_OFF + ld.r0 * 8, (uint32_t)(nr * 8), &c.full[s], pol);
             }
-            it++;
-        }
-        r += nr;
-    }
-    it_io = it;
-}
-
-DL_DEVINL void weight_producer(const DlDecodeArgs& a) {
-    const uint64_t pol = l2_policy_evict_first();
-    uint32_t it = 0;
-#pragma unroll 1
-    for (int l = 0; l <= a.n_layers; l++) {
-        const DlDecodeLayer* L = a.layers + (l < a.n_layers ? l : 0);
-#pragma unroll 1
-        for (int ph = (l < a.n_layers ? PH_QKV : PH_CLS); ph <= (l < a.n_layers ? PH_W2 : PH_CLS); ph++) {
-            const MgPhase p = mg_phase(a, L, ph);
-            produce_matrix(p.w, p.d, p.n, p.align, it, pol, a.timeout_ns, a.debug);
         }
     }
 }
@@ -219,7 +292,8 @@ DL_DEVINL void weight_producer(const DlDecodeArgs& a) {
 // =================================================================================================
 // KV page producer warp: bulk copies of the K and V pages of this CTA's attention work items
 // =================================================================================================
-__device__ __noinline__ void kv_producer(const DlDecodeArgs& a) {
+__device__ __noinline__ void kv_producer() {
+    const DlDecodeArgs& a = mg_args();
     const MgCtx c;
     MgSpin sp;
     sp.init(a.timeout_ns, a.debug);
@@ -238,13 +312,13 @@ __device__ __noinline__ void kv_producer(const DlDecodeArgs& a) {
             const int sp_i = item % a.att_splits;
             const int kvh = (item / a.att_splits) % a.n_kv_heads;
             const int m = item / (a.att_splits * a.n_kv_heads);
-            const int pos = a.pos[m];
-            const int n_eff = mg_n_eff(pos, a.att_splits);
+            const int pos = c.rows[m].pos;
+            const int n_eff = c.rows[m].n_eff;
             if (sp_i >= n_eff) continue;
             const int n_pages = pos / MG_PAGE + 1;
             const int pps = (n_pages + n_eff - 1) / n_eff;
             const int pg0 = sp_i * pps, pg1 = min(n_pages, pg0 + pps);
-            const int* bt = a.block_table + (size_t)a.slot[m] * a.max_pages;
+            const int* bt = a.block_table + (size_t)c.rows[m].slot * a.max_pages;
             for (int i0 = pg0; i0 < pg1; i0 += 32) {
                 const int my_page = (i0 + lane < pg1) ? bt[i0 + lane] : 0;
                 const int cnt = min(32, pg1 - i0);
@@ -269,32 +343,6 @@ __device__ __noinline__ void kv_producer(const DlDecodeArgs& a) {
 // =================================================================================================
 // consumer side
 // =================================================================================================
-// Q80-quantise 4 consecutive values held by each of the 8 lanes of a 32-value block and store the block into the
-// resident activation slab ([kt][M][160] B: 128 int8 | 4 f32 scales | 4 x 8*sum(q)).  All 32 lanes must call.
-DL_DEVINL void q80_block8_to_act(float4 v, uint8_t* act, int M, int m, int blk, int sub, bool live) {
-    float amax = fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w)));
-    amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
-    amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
-    amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 4));
-    const float d = amax / 127.0f;
-    const float id = (d != 0.0f) ? (1.0f / d) : 0.0f;
-    const int q0 = __float2int_rn(v.x * id), q1 = __float2int_rn(v.y * id);
-    const int q2 = __float2int_rn(v.z * id), q3 = __float2int_rn(v.w * id);
-    int sumq = q0 + q1 + q2 + q3;
-    sumq += __shfl_xor_sync(0xffffffffu, sumq, 1);
-    sumq += __shfl_xor_sync(0xffffffffu, sumq, 2);
-    sumq += __shfl_xor_sync(0xffffffffu, sumq, 4);
-    if (!live) return;
-    uint8_t* rowp = act + ((size_t)(blk >> 2) * M + m) * XQ_ROW_BYTES;
-    const int kb = blk & 3;
-    reinterpret_cast<uint32_t*>(rowp + kb * 32)[sub] = (uint32_t)(q0 & 0xff) | ((uint32_t)(q1 & 0xff) << 8) |
-                                                      ((uint32_t)(q2 & 0xff) << 16) | ((uint32_t)(q3 & 0xff) << 24);
-    if (sub == 0) {
-        reinterpret_cast<float*>(rowp + 128)[kb] = __half2float(__float2half_rn(d));
-        reinterpret_cast<int*>(rowp + 144)[kb] = 8 * sumq;
-    }
-}
-
 DL_DEVINL float4 ll_dequant4(unsigned long long wd, unsigned long long ws) {
     const uint32_t p = (uint32_t)wd;
     const float d = __half2float(__ushort_as_half((unsigned short)(ws & 0xffffu)));
@@ -302,13 +350,61 @@ DL_DEVINL float4 ll_dequant4(unsigned long long wd, unsigned long long ws) {
                        (float)(int8_t)((p >> 16) & 0xff) * d, (float)(int8_t)(p >> 24) * d);
 }
 
+// Q80-quantise one 32-value block held by ONE thread (8 float4) into the resident act slab.  One thread per block keeps
+// the instruction count low: the prologues are replicated on every SM and were issue-bound with 8 lanes per block.
+// (quantizeF32toQ80, src/nn/nn-quants.cpp:126-139: d = amax / 127, q = round-half-even(x / d), scale stored as fp16)
+DL_DEVINL void q80_block_to_act(const float4 (&v)[8], uint8_t* act, int Ms, int m, int blk) {
+    float amax = 0.0f;
+#pragma unroll
+    for (int j = 0; j < 8; j++)
+        amax = fmaxf(amax, fmaxf(fmaxf(fabsf(v[j].x), fabsf(v[j].y)), fmaxf(fabsf(v[j].z), fabsf(v[j].w))));
+    const float d = amax / 127.0f;
+    const float id = (d != 0.0f) ? (1.0f / d) : 0.0f;
+    int sumq = 0;
+    uint32_t pk[8];
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+        const int q0 = __float2int_rn(v[j].x * id), q1 = __float2int_rn(v[j].y * id);
+        const int q2 = __float2int_rn(v[j].z * id), q3 = __float2int_rn(v[j].w * id);
+        sumq += q0 + q1 + q2 + q3;
+        pk[j] = (uint32_t)(q0 & 0xff) | ((uint32_t)(q1 & 0xff) << 8) | ((uint32_t)(q2 & 0xff) << 16) | ((uint32_t)(q3 & 0xff) << 24);
+    }
+    uint8_t* rowp = act + ((size_t)(blk >> 2) * Ms + m) * XQ_ROW_BYTES;
+    const int kb = blk & 3;
+    uint4* qd = reinterpret_cast<uint4*>(rowp + kb * 32);
+    qd[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+    qd[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+    reinterpret_cast<float*>(rowp + 128)[kb] = __half2float(__float2half_rn(d));
+    reinterpret_cast<int*>(rowp + 144)[kb] = 8 * sumq;
+}
+
+// All CTAs read the same activation rows at the same moment; starting each CTA at a different offset spreads the requests
+// over the L2 slices instead of queueing 148 of them on the same line.
+// debug timeline inside the phase functions: slot 16 + k of the current layer (kept in shared memory by the kernel)
+#define MG_ISTAMP(k)                                                                                          \
+    do {                                                                                                      \
+        if (a.trace != nullptr && blockIdx.x == a.trace_cta && threadIdx.x == 0)                              \
+            a.trace[(size_t)c.rows[0].pad0 * 32 + 16 + (k)] = globaltimer_ns();                               \
+    } while (0)
+
+DL_DEVINL int mg_rot(int cta, int total, int gran) {
+    const int w = total / gran;
+    return w > 0 ? ((cta * 5) % w) * gran : 0;
+}
+DL_DEVINL int mg_wrap(int i, int total) { return i >= total ? i - total : i; }
+
 // ---- prologue 1: x = x_in + sum of the ranks' Q80 partial sums; RMSNorm; Q80 -> act slabs -------------------------
 // (OP_MERGE_ADD + OP_INV_RMS + OP_RMS_NORM + OP_CAST, src/llm.cpp:204-239,317-342,394-419)
-// Every CTA does the whole row (M*dim <= 16384 floats, L2 reads), so no CTA waits for another one.  The merged row is
-// parked in shared memory behind the slabs between the two passes.
-// xsrc: residual rows ([M][dim] f32), or NULL = embedding rows of a.tokens (layer 0: OP_EMBEDDING, src/llm.cpp:185-192)
-__device__ __noinline__ void prologue_norm(const DlDecodeArgs& a, const float* xsrc, float* x_out, const uint8_t* ll,
-                                           uint32_t epoch, const float* norm_w) {
+// Every CTA does the whole row (M*dim <= 16384 floats, L2 reads), so no CTA waits for another one.  Pass 1 (one float4
+// per thread and step, loads batched: a dependent L2 round trip costs ~0.7 us here) merges, parks the row in shared
+// memory behind the slabs and sums the squares; pass 2 (one 32-value block per thread) normalises and quantises.
+// xsrc: residual rows ([M][dim] f32), or NULL = embedding rows of the batch tokens (layer 0: OP_EMBEDDING,
+// src/llm.cpp:185-192).  Ms: row stride of the act slabs (the matmul phase's MT).
+#define MG_PB 4       // float4 chunks per thread and batch in pass 1
+#define MG_XS_STRIDE 9    // float4 per parked block (8 + 1 pad: lane-per-block reads stay bank-conflict free)
+__device__ __noinline__ void prologue_norm(int Ms, const float* xsrc, float* x_out, const uint8_t* ll, uint32_t epoch,
+                                           const float* norm_w) {
+    const DlDecodeArgs& a = mg_args();
     const MgCtx c;
     MgSpin sp;
     sp.init(a.timeout_ns, a.debug);
@@ -317,51 +413,75 @@ __device__ __noinline__ void prologue_norm(const DlDecodeArgs& a, const float* x
     const int total = M * cpr;
     const int nblk = dim >> 5;
     const int N = (ll != nullptr) ? a.world : 0;
-    float4* xs = reinterpret_cast<float4*>(c.act + (size_t)(dim >> 7) * M * XQ_ROW_BYTES);     // [M][dim] f32
+    float4* xs = reinterpret_cast<float4*>(c.act + (size_t)(dim >> 7) * Ms * XQ_ROW_BYTES);     // [M * nblk][9] float4
+    const int rot = mg_rot(c.cta, total, 32);              // slot sl of the sweep handles chunk (sl + rot) % total
     float ss[MG_MAX_M];
 #pragma unroll
     for (int m = 0; m < MG_MAX_M; m++) ss[m] = 0.0f;
 #pragma unroll 1
-    for (int ch = tid; ch < total; ch += MG_CONS) {
-        const int m = ch / cpr, e4 = ch - m * cpr;
-        // the residual rows are rewritten by other CTAs every phase: read them from L2, never from a stale L1 line
-        float4 x4 = (xsrc != nullptr) ? __ldcg(reinterpret_cast<const float4*>(xsrc + (size_t)m * dim) + e4)
-                                      : reinterpret_cast<const float4*>(a.embedding + (size_t)a.tokens[m] * dim)[e4];
+    for (int ch0 = tid; ch0 < total; ch0 += MG_PB * MG_CONS) {
+        float4 x4[MG_PB];
+#pragma unroll
+        for (int u = 0; u < MG_PB; u++) {
+            const int sl = ch0 + u * MG_CONS;
+            x4[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (sl < total) {
+                const int ch = mg_wrap(sl + rot, total);
+                const int m = ch / cpr, e4 = ch - m * cpr;
+                // the residual rows are rewritten by another CTA every phase: read them from L2, never from a stale L1 line
+                x4[u] = (xsrc != nullptr) ? __ldcg(reinterpret_cast<const float4*>(xsrc + (size_t)m * dim) + e4)
+                                          : reinterpret_cast<const float4*>(a.embedding + (size_t)c.rows[m].token * dim)[e4];
+            }
+        }
         if (N > 0) {
-            const int blk = e4 >> 3, sub = e4 & 7;
-            // word (src, m, blk, w) lives at index ((src*4 + m)*nblk + blk)*9 + w
-            const unsigned long long* base = reinterpret_cast<const unsigned long long*>(ll) + ((size_t)m * nblk + blk) * MG_LLW;
+            // word (src, m, blk, w) lives at index ((src*4 + m)*nblk + blk)*9 + w; poll until every word carries the epoch
             const size_t sstride = (size_t)MG_MAX_M * nblk * MG_LLW;
-            unsigned long long wd[DL_MAX_PEERS], ws[DL_MAX_PEERS];
-            bool ok;
-            do {
-                ok = true;
+#pragma unroll 1
+            for (int s = 0; s < N; s++) {
+                unsigned long long wd[MG_PB], ws[MG_PB];
+                bool ok;
+                do {
+                    ok = true;
 #pragma unroll
-                for (int s = 0; s < DL_MAX_PEERS; s++) {
-                    if (s < N) {
-                        wd[s] = ld_volatile_u64(base + s * sstride + sub);
-                        ws[s] = ld_volatile_u64(base + s * sstride + 8);
+                    for (int u = 0; u < MG_PB; u++) {
+                        const int sl = ch0 + u * MG_CONS;
+                        if (sl < total) {
+                            const int ch = mg_wrap(sl + rot, total);
+                            const int m = ch / cpr, e4 = ch - m * cpr;
+                            const unsigned long long* base = reinterpret_cast<const unsigned long long*>(ll) + s * sstride +
+                                                             ((size_t)m * nblk + (e4 >> 3)) * MG_LLW;
+                            wd[u] = ld_volatile_u64(base + (e4 & 7));
+                            ws[u] = ld_volatile_u64(base + 8);
+                        }
                     }
-                }
 #pragma unroll
-                for (int s = 0; s < DL_MAX_PEERS; s++)
-                    if (s < N) ok = ok && ((uint32_t)(wd[s] >> 32) == epoch) && ((uint32_t)(ws[s] >> 32) == epoch);
-                if (!ok) sp.tick(4);
-            } while (!ok);
-            sp.reset();
+                    for (int u = 0; u < MG_PB; u++)
+                        if (ch0 + u * MG_CONS < total) ok = ok && ((uint32_t)(wd[u] >> 32) == epoch) && ((uint32_t)(ws[u] >> 32) == epoch);
+                    if (!ok) sp.tick(4);
+                } while (!ok);
+                sp.reset();
 #pragma unroll
-            for (int s = 0; s < DL_MAX_PEERS; s++) {
-                if (s < N) {
-                    const float4 p = ll_dequant4(wd[s], ws[s]);
-                    x4.x += p.x; x4.y += p.y; x4.z += p.z; x4.w += p.w;
+                for (int u = 0; u < MG_PB; u++) {
+                    if (ch0 + u * MG_CONS < total) {
+                        const float4 p = ll_dequant4(wd[u], ws[u]);
+                        x4[u].x += p.x; x4[u].y += p.y; x4[u].z += p.z; x4[u].w += p.w;
+                    }
                 }
             }
         }
-        if (x_out != nullptr) reinterpret_cast<float4*>(x_out + (size_t)m * dim)[e4] = x4;
-        xs[ch] = x4;
-        const float sq = x4.x * x4.x + x4.y * x4.y + x4.z * x4.z + x4.w * x4.w;
 #pragma unroll
-        for (int q = 0; q < MG_MAX_M; q++) ss[q] += (m == q) ? sq : 0.0f;
+        for (int u = 0; u < MG_PB; u++) {
+            const int sl = ch0 + u * MG_CONS;
+            if (sl < total) {
+                const int ch = mg_wrap(sl + rot, total);
+                const int m = ch / cpr, e4 = ch - m * cpr;
+                if (x_out != nullptr) reinterpret_cast<float4*>(x_out + (size_t)m * dim)[e4] = x4[u];
+                xs[(size_t)(m * nblk + (e4 >> 3)) * MG_XS_STRIDE + (e4 & 7)] = x4[u];
+                const float sq = x4[u].x * x4[u].x + x4[u].y * x4[u].y + x4[u].z * x4[u].z + x4[u].w * x4[u].w;
+#pragma unroll
+                for (int q = 0; q < MG_MAX_M; q++) ss[q] += (m == q) ? sq : 0.0f;
+            }
+        }
     }
     float* ssq_w = c.misc;                // [16 warps][4]
     const int warp = tid >> 5, lane = tid & 31;
@@ -380,68 +500,144 @@ __device__ __noinline__ void prologue_norm(const DlDecodeArgs& a, const float* x
         inv[m] = 1.0f / sqrtf(t / (float)dim + a.eps);
     }
 #pragma unroll 1
-    for (int ch0 = 0; ch0 < total; ch0 += MG_CONS) {       // total is a multiple of 32: warps are all-live or all-dead
-        const int ch = ch0 + tid;
-        if (ch - lane >= total) break;
-        const bool live = ch < total;
-        const int m = live ? ch / cpr : 0, e4 = live ? ch - m * cpr : 0;
+    for (int b = tid; b < M * nblk; b += MG_CONS) {
+        const int m = b / nblk, blk = b - m * nblk;
         float im = inv[0];
 #pragma unroll
         for (int q = 1; q < MG_MAX_M; q++) im = (m == q) ? inv[q] : im;
-        const float4 w4 = reinterpret_cast<const float4*>(norm_w)[e4];
-        const float4 x4 = live ? xs[ch] : make_float4(0.f, 0.f, 0.f, 0.f);
-        float4 y;
-        y.x = w4.x * (im * x4.x); y.y = w4.y * (im * x4.y);
-        y.z = w4.z * (im * x4.z); y.w = w4.w * (im * x4.w);
-        q80_block8_to_act(y, c.act, M, m, e4 >> 3, e4 & 7, live);
+        const float4* wn = reinterpret_cast<const float4*>(norm_w) + blk * 8;
+        const float4* xb = xs + (size_t)b * MG_XS_STRIDE;
+        float4 y[8];
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            const float4 w4 = wn[j], x4 = xb[j];
+            y[j].x = w4.x * (im * x4.x); y[j].y = w4.y * (im * x4.y);
+            y[j].z = w4.z * (im * x4.z); y[j].w = w4.w * (im * x4.w);
+        }
+        q80_block_to_act(y, c.act, Ms, m, blk);
     }
     cons_bar();
 }
 
 // ---- prologue 2: merge the attention splits, Q80 -> act slabs (K = q_dim)  (OP_CAST y->yq_slice, src/llm.cpp:296-301)
-__device__ __noinline__ void prologue_att(const DlDecodeArgs& a, bool merged) {
+// pass 1: one float4 per thread (coalesced L2 reads of the split partials) -> merged, normalised output parked in shared
+// memory; pass 2: one 32-value block per thread -> Q80.
+__device__ __noinline__ void prologue_att(int Ms, bool merged) {
+    const DlDecodeArgs& a = mg_args();
     const MgCtx c;
-    const int M = a.M, cpr = a.q_dim >> 2, total = M * cpr, hs = a.head_size, tid = c.tid, lane = tid & 31;
-#pragma unroll 1
-    for (int ch0 = 0; ch0 < total; ch0 += MG_CONS) {
-        const int ch = ch0 + tid;
-        if (ch - lane >= total) break;
-        const bool live = ch < total;
-        const int m = live ? ch / cpr : 0, e4 = live ? ch - m * cpr : 0;
+    const int M = a.M, cpr = a.q_dim >> 2, total = M * cpr, nblk = a.q_dim >> 5, hs = a.head_size, tid = c.tid;
+    float4* xs = reinterpret_cast<float4*>(c.act + (size_t)(a.q_dim >> 7) * Ms * XQ_ROW_BYTES);     // [M * nblk][9] float4
+    const int rot = mg_rot(c.cta, total, 8);
+#pragma unroll 2
+    for (int sl = tid; sl < total; sl += MG_CONS) {
+        const int ch = mg_wrap(sl + rot, total);
+        const int m = ch / cpr, e4 = ch - m * cpr;
         const int head = (e4 * 4) / hs, dd = (e4 * 4) - head * hs;
-        const int n_eff = merged ? 1 : mg_n_eff(a.pos[m], a.att_splits);
+        const int n_eff = merged ? 1 : c.rows[m].n_eff;        // <= MG_SMALL_SPLITS here
         const size_t base = ((size_t)m * a.n_heads + head) * a.max_splits;
+        float2 ml[MG_SMALL_SPLITS];
+        float4 o[MG_SMALL_SPLITS];
+#pragma unroll
+        for (int sp = 0; sp < MG_SMALL_SPLITS; sp++) {
+            ml[sp] = make_float2(-INFINITY, 0.0f);
+            o[sp] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (sp < n_eff) {
+                ml[sp] = __ldcg(reinterpret_cast<const float2*>(a.att_ml + (base + sp) * 2));
+                o[sp] = __ldcg(reinterpret_cast<const float4*>(a.att_o + (base + sp) * hs + dd));
+            }
+        }
         float Mx = -INFINITY;
-        for (int s = 0; s < n_eff; s++) Mx = fmaxf(Mx, __ldcg(&a.att_ml[(base + s) * 2]));
+#pragma unroll
+        for (int sp = 0; sp < MG_SMALL_SPLITS; sp++) Mx = fmaxf(Mx, ml[sp].x);
         const float Mu = (Mx == -INFINITY) ? 0.0f : Mx;
         float L = 0.0f;
         float4 O = make_float4(0.f, 0.f, 0.f, 0.f);
-        for (int s = 0; s < n_eff; s++) {
-            const float e = __expf(__ldcg(&a.att_ml[(base + s) * 2]) - Mu);
-            L += __ldcg(&a.att_ml[(base + s) * 2 + 1]) * e;
-            const float4 o = __ldcg(reinterpret_cast<const float4*>(a.att_o + (base + s) * hs + dd));
-            O.x += o.x * e; O.y += o.y * e; O.z += o.z * e; O.w += o.w * e;
+#pragma unroll
+        for (int sp = 0; sp < MG_SMALL_SPLITS; sp++) {
+            const float e = (sp < n_eff) ? __expf(ml[sp].x - Mu) : 0.0f;
+            L += ml[sp].y * e;
+            O.x += o[sp].x * e; O.y += o[sp].y * e; O.z += o[sp].z * e; O.w += o[sp].w * e;
         }
         const float il = (L > 0.0f) ? 1.0f / L : 0.0f;
         O.x *= il; O.y *= il; O.z *= il; O.w *= il;
-        q80_block8_to_act(O, c.act, M, m, e4 >> 3, e4 & 7, live);
+        xs[(size_t)(m * nblk + (e4 >> 3)) * MG_XS_STRIDE + (e4 & 7)] = O;
+    }
+    cons_bar();
+#pragma unroll 1
+    for (int b = tid; b < M * nblk; b += MG_CONS) {
+        const int m = b / nblk, blk = b - m * nblk;
+        const float4* xb = xs + (size_t)b * MG_XS_STRIDE;
+        float4 y[8];
+#pragma unroll
+        for (int j = 0; j < 8; j++) y[j] = xb[j];
+        q80_block_to_act(y, c.act, Ms, m, blk);
     }
     cons_bar();
 }
 
 // ---- prologue 3: hidden activation f32 -> Q80 act slabs (K = hid)  (OP_CAST d->dq, src/llm.cpp:367-374)
-__device__ __noinline__ void prologue_hidden(const DlDecodeArgs& a) {
+// The rows arrive with ONE bulk async copy into shared memory behind the slabs (a per-thread 128-byte stride over global
+// memory costs 32 line requests per load: 3.6 us measured); then one thread per 32-value block, reading its block in a
+// lane-rotated order so the 128-byte stride is bank-conflict free.
+__device__ __noinline__ void prologue_hidden(int Ms, uint32_t parity) {
+    const DlDecodeArgs& a = mg_args();
     const MgCtx c;
-    const int M = a.M, cpr = a.hid >> 2, total = M * cpr, tid = c.tid, lane = tid & 31;
+    MgSpin sp;
+    sp.init(a.timeout_ns, a.debug);
+    const int M = a.M, nblk = a.hid >> 5, total = M * nblk, tid = c.tid, lane = tid & 31;
+    const size_t slab_bytes = (size_t)(a.hid >> 7) * Ms * XQ_ROW_BYTES;
+    const size_t row_bytes = (size_t)M * a.hid * 4;
+    uint64_t* hbar = reinterpret_cast<uint64_t*>(mg_smem + SM_HBAR);
+    if (slab_bytes + row_bytes <= MG_ACT_BYTES) {
+        float4* stage = reinterpret_cast<float4*>(c.act + slab_bytes);
+        if (tid == 0) {
+            fence_proxy_async_all();                  // h was written with generic stores (other CTAs, before the grid barrier)
+            mbar_arrive_expect_tx(hbar, (uint32_t)row_bytes);
+            for (size_t off = 0; off < row_bytes; off += 32768) {
+                const uint32_t n = (uint32_t)((row_bytes - off < 32768) ? (row_bytes - off) : 32768);
+                bulk_g2s(reinterpret_cast<uint8_t*>(stage) + off, reinterpret_cast<const uint8_t*>(a.h) + off, n, hbar);
+            }
+        }
+        mg_mbar_wait(hbar, parity, sp, 8);
 #pragma unroll 1
-    for (int ch0 = 0; ch0 < total; ch0 += MG_CONS) {
-        const int ch = ch0 + tid;
-        if (ch - lane >= total) break;
-        const bool live = ch < total;
-        const int m = live ? ch / cpr : 0, e4 = live ? ch - m * cpr : 0;
-        float4 h4 = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (live) h4 = __ldcg(reinterpret_cast<const float4*>(a.h + (size_t)m * a.hid) + e4);
-        q80_block8_to_act(h4, c.act, M, m, e4 >> 3, e4 & 7, live);
+        for (int b = tid; b < total; b += MG_CONS) {
+            const int m = b / nblk, blk = b - m * nblk;
+            const float4* hp = stage + (size_t)b * 8;
+            float4 h4[8];
+#pragma unroll
+            for (int j = 0; j < 8; j++) h4[j] = hp[(j + lane) & 7];           // order inside the block does not matter for amax
+            // quantise with the rotated order: word (j + lane) & 7 of the block
+            float amax = 0.0f;
+#pragma unroll
+            for (int j = 0; j < 8; j++)
+                amax = fmaxf(amax, fmaxf(fmaxf(fabsf(h4[j].x), fabsf(h4[j].y)), fmaxf(fabsf(h4[j].z), fabsf(h4[j].w))));
+            const float d = amax / 127.0f;
+            const float id = (d != 0.0f) ? (1.0f / d) : 0.0f;
+            uint8_t* rowp = c.act + ((size_t)(blk >> 2) * Ms + m) * XQ_ROW_BYTES;
+            const int kb = blk & 3;
+            int sumq = 0;
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                const int q0 = __float2int_rn(h4[j].x * id), q1 = __float2int_rn(h4[j].y * id);
+                const int q2 = __float2int_rn(h4[j].z * id), q3 = __float2int_rn(h4[j].w * id);
+                sumq += q0 + q1 + q2 + q3;
+                reinterpret_cast<uint32_t*>(rowp + kb * 32)[(j + lane) & 7] =
+                    (uint32_t)(q0 & 0xff) | ((uint32_t)(q1 & 0xff) << 8) | ((uint32_t)(q2 & 0xff) << 16) | ((uint32_t)(q3 & 0xff) << 24);
+            }
+            reinterpret_cast<float*>(rowp + 128)[kb] = __half2float(__float2half_rn(d));
+            reinterpret_cast<int*>(rowp + 144)[kb] = 8 * sumq;
+        }
+    } else {
+        // rows too long for the staging area (several rows of a big model): per-thread global loads
+#pragma unroll 1
+        for (int b = tid; b < total; b += MG_CONS) {
+            const int m = b / nblk, blk = b - m * nblk;
+            const float4* hp = reinterpret_cast<const float4*>(a.h + (size_t)m * a.hid) + blk * 8;
+            float4 h4[8];
+#pragma unroll
+            for (int j = 0; j < 8; j++) h4[j] = __ldcg(hp + j);
+            q80_block_to_act(h4, c.act, Ms, m, blk);
+        }
     }
     cons_bar();
 }
@@ -457,29 +653,29 @@ DL_DEVINL void epi_qkv(const DlDecodeArgs& a, const MgCtx& c, const DlDecodeLaye
         const int region = (grow < a.q_dim) ? 0 : ((grow < a.q_dim + a.kv_dim) ? 1 : 2);
         const int rrow = (region == 0) ? grow : ((region == 1) ? grow - a.q_dim : grow - a.q_dim - a.kv_dim);
         const int hd = rrow % hs, kvh = rrow / hs;
-        const int p = a.pos[m];
+        const int p = c.rows[m].pos;
         if (region < 2) {
-            float sn, cs;
-            sincosf((float)p * a.rope_freqs[hd >> 1], &sn, &cs);
-            const float r0v = v0 * cs - v1 * sn, r1v = v0 * sn + v1 * cs;
+            const float2 csn = c.rope[m * 64 + (hd >> 1)];          // (cos, sin) of pos * freq, tabulated once per launch
+            const float r0v = v0 * csn.x - v1 * csn.y, r1v = v0 * csn.y + v1 * csn.x;
             v0 = r0v; v1 = r1v;
         }
         if (region == 0) {
             *reinterpret_cast<float2*>(a.q + (size_t)m * a.q_dim + rrow) = make_float2(v0, v1);
         } else {
-            const int page = a.block_table[(size_t)a.slot[m] * a.max_pages + p / MG_PAGE];
+            const int page = c.rows[m].page;
             const size_t off = (((size_t)page * a.n_kv_heads + kvh) * MG_PAGE + (p % MG_PAGE)) * hs + hd;
             __half* base = reinterpret_cast<__half*>(region == 1 ? L->k_cache : L->v_cache);
             *reinterpret_cast<__half2*>(base + off) = __floats2half2_rn(v0, v1);
+            fence_proxy_async_all();  // this KV row is read by bulk copies (async proxy) after the next grid barrier
         }
     }
-    fence_proxy_async_all();          // the KV rows just written are read by bulk copies after the next grid barrier
 }
 
-// ---- epilogue: Q80 cast of a partial sum (32-row blocks), residual add (1 GPU) or LL push to every rank ----------
-// (OP_CAST y->ZQ slice + SYNC_NODE_SLICES + OP_MERGE_ADD, src/llm.cpp:308-322,381-387)
-// x_emb: the residual comes from the embedding rows (layer 0 on one GPU) instead of a.x[0]
-DL_DEVINL void epi_residual(const DlDecodeArgs& a, const MgCtx& c, int row, int nr, bool x_emb, uint8_t* const* ll, uint32_t epoch) {
+// ---- epilogue: Q80 cast of a partial sum (32-row blocks) pushed as LL words into every rank's exchange buffer -------
+// (OP_CAST y->ZQ slice + SYNC_NODE_SLICES, src/llm.cpp:308-314,381-387; the merge-add happens in the next prologue).
+// One GPU uses the same hand-off (one source): the words themselves tell the next phase that the rows are there,
+// which is cheaper than a grid barrier.
+DL_DEVINL void epi_residual(const DlDecodeArgs& a, const MgCtx& c, int row, int nr, uint8_t* const* ll, uint32_t epoch) {
     const int M = a.M, warp = c.tid >> 5, lane = c.tid & 31;
     const int nb = nr >> 5;                                    // 32-row blocks in this piece
     const int nblk = a.dim >> 5;
@@ -493,22 +689,16 @@ DL_DEVINL void epi_residual(const DlDecodeArgs& a, const MgCtx& c, int row, int 
         const float id = (d != 0.0f) ? (1.0f / d) : 0.0f;
         const int q = __float2int_rn(val * id);
         const __half d16 = __float2half_rn(d);
-        if (ll == nullptr) {
-            const float vq = a.q80_sync ? (float)q * __half2float(d16) : val;
-            const float xi = x_emb ? a.embedding[(size_t)a.tokens[m] * a.dim + grow] : __ldcg(&a.x[0][(size_t)m * a.dim + grow]);
-            a.x[0][(size_t)m * a.dim + grow] = xi + vq;
-        } else {
-            uint32_t bts = ((uint32_t)q & 0xffu) << (8 * (lane & 3));
-            bts |= __shfl_xor_sync(0xffffffffu, bts, 1);
-            bts |= __shfl_xor_sync(0xffffffffu, bts, 2);
-            const uint32_t wj = __shfl_sync(0xffffffffu, bts, (lane & 7) * 4);
-            const uint32_t payload = (lane < 8) ? wj : (uint32_t)__half_as_ushort(d16);
-            if (lane < MG_LLW) {
-                const unsigned long long word = ((unsigned long long)epoch << 32) | payload;
-                const size_t widx = ((((size_t)a.rank * MG_MAX_M + m) * nblk) + (grow >> 5)) * MG_LLW + lane;
-                for (int p = 0; p < a.world; p++)
-                    st_volatile_u64(reinterpret_cast<unsigned long long*>(ll[p]) + widx, word);
-            }
+        uint32_t bts = ((uint32_t)q & 0xffu) << (8 * (lane & 3));
+        bts |= __shfl_xor_sync(0xffffffffu, bts, 1);
+        bts |= __shfl_xor_sync(0xffffffffu, bts, 2);
+        const uint32_t wj = __shfl_sync(0xffffffffu, bts, (lane & 7) * 4);
+        const uint32_t payload = (lane < 8) ? wj : (uint32_t)__half_as_ushort(d16);
+        if (lane < MG_LLW) {
+            const unsigned long long word = ((unsigned long long)epoch << 32) | payload;
+            const size_t widx = ((((size_t)a.rank * MG_MAX_M + m) * nblk) + (grow >> 5)) * MG_LLW + lane;
+            for (int p = 0; p < a.world; p++)
+                st_volatile_u64(reinterpret_cast<unsigned long long*>(ll[p]) + widx, word);
         }
     }
 }
@@ -523,15 +713,22 @@ DL_DEVINL void epi_silu(const DlDecodeArgs& a, const MgCtx& c, int row, int nr) 
         const float hv = (a.act_gelu ? act_gelu(gt) : act_silu(gt)) * up;
         a.h[(size_t)m * a.hid + ((row >> 1) + pr)] = hv;
     }
+    fence_proxy_async_all();          // h is fetched by a bulk copy (async proxy) after the next grid barrier
 }
 
+// unsigned bytes x signed bytes, 32-bit signed accumulate
+DL_DEVINL int dp4a_us(uint32_t a_u8x4, int b_s8x4, int c) {
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a_u8x4), "r"(b_s8x4), "r"(c));
+    return d;
+}
 DL_DEVINL void argmax_combine2(float& best, int& bi, float ov, int oi) {
     if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
 }
 
 // ---- epilogue: logits slice -> every rank, or (greedy) the running best of this CTA in shared memory ----------------
 // (logits gather SYNC_NODE_SLICES_EXCEPT_ROOT, src/llm.cpp:426-432; Sampler::sample temperature == 0, src/tokenizer.cpp:472-502)
-#define MG_BEST_OFF 512      // floats into misc: [4 warps][4][2] scratch, then [4][2] running best
+#define MG_BEST_OFF 256      // floats into misc: [4 warps][4][2] scratch, then [4][2] running best
 DL_DEVINL void epi_logits(const DlDecodeArgs& a, const MgCtx& c, int row, int nr) {
     const int M = a.M, tid = c.tid;
     if (!a.greedy) {
@@ -570,7 +767,8 @@ DL_DEVINL void epi_logits(const DlDecodeArgs& a, const MgCtx& c, int row, int nr
 // ---- the matmul phase: this CTA's rows of a [d][n] Q40T matrix against the resident act slabs ------------------
 // After each piece out_s[m*128 + local row] holds the f32 products and the phase's epilogue runs on it.
 template <int MT>
-__device__ __noinline__ void gemv_phase(const DlDecodeArgs& a, int ph, int layer, uint32_t& it_io, uint32_t epoch) {
+__device__ __noinline__ void gemv_phase(int ph, int layer, uint32_t& it_io, uint32_t epoch) {
+    const DlDecodeArgs& a = mg_args();
     const MgCtx c;
     MgSpin sp;
     sp.init(a.timeout_ns, a.debug);
@@ -583,80 +781,146 @@ __device__ __noinline__ void gemv_phase(const DlDecodeArgs& a, int ph, int layer
     int R0, R1;
     mg_cta_rows(P.d, c.G, P.align, c.cta, R0, R1);
     int r = R0;
+    if (ph == PH_QKV) MG_ISTAMP(4);
+    if (ph == PH_W2) MG_ISTAMP(9);
 #pragma unroll 1
     while (r < R1) {
         const int r0 = r & 127;
         const int nr = min(128 - r0, R1 - r);
         const int kpack = mg_kpack(nr);
         const int nch = (KT + kpack - 1) / kpack;
-        const int j = t / nr, lr = t - j * nr;
-        const bool mine = j < kpack;
-        const int rot = (r0 + lr) >> 1;
-        float acc[MT];
+        // Thread -> work: the 128 threads of a group see a stage as up to 128 (k-tile, row) pairs of 4 blocks each.  A
+        // quarter-warp owns ONE k-block index kb and 8 consecutive pairs per step (4 steps of 32 pairs), so the Q80
+        // activations of its k-block sit in registers across the rows instead of being re-read from shared memory for
+        // every row (the broadcast re-reads were most of the shared-memory traffic: the loop ran at ~0.2 us per 9 KB
+        // stage whether the weights came from HBM or were already resident).
+        const int npair = kpack * nr;
+        const int wq = t >> 5, kb = lane >> 3, r8 = lane & 7;
+        // pairs beyond the piece are clamped to its last pair and computed anyway (their sums are dropped): the four
+        // steps stay branch-free, so their loads and dot-product chains overlap
+        int pj[4], plr[4], ppc[4];
+        unsigned pvalid = 0;
 #pragma unroll
-        for (int m = 0; m < MT; m++) acc[m] = 0.0f;
+        for (int i = 0; i < 4; i++) {
+            const int pp = wq * 8 + r8 + 32 * i;
+            if (pp < npair) pvalid |= 1u << i;
+            ppc[i] = min(pp, npair - 1);
+            pj[i] = ppc[i] / nr;
+            plr[i] = ppc[i] - pj[i] * nr;
+        }
+        float acc[4][MT];
+#pragma unroll
+        for (int i = 0; i < 4; i++)
+#pragma unroll
+            for (int m = 0; m < MT; m++) acc[i][m] = 0.0f;
 #pragma unroll 1
         for (int ci = 0; ci < nch; ci++) {
             const uint32_t itc = it + ci;
             if ((int)(itc & 3u) != g) continue;
             const int s = itc % MG_NS;
             mg_mbar_wait(&c.full[s], (itc / MG_NS) & 1, sp, 5);
-            const int kt = ci * kpack + j;
-            if (mine && kt < KT) {
-                const uint8_t* st = c.ring + s * Q40T_TILE_BYTES;
-                const uint8_t* nibp = st + (j * nr + lr) * 64;
-                const uint8_t* scp = st + Q40T_NIB_BYTES + (j * nr + lr) * 8;
-                const uint8_t* actp = c.act + (size_t)kt * M * XQ_ROW_BYTES;
+            const uint8_t* st = c.ring + s * Q40T_TILE_BYTES;
+            // one (pair, k-block) against the MT activation rows held in registers
+            auto block = [&](int i, bool live, const int4 (&xl)[MT], const int4 (&xh)[MT], const float (&dx)[MT], const int (&s8)[MT]) {
+                const int pp = ppc[i];
+                const uint4 nb = *reinterpret_cast<const uint4*>(st + pp * 64 + (((kb + ((r0 + plr[i]) >> 1)) & 3) << 4));
+                const float dw = __half2float(*reinterpret_cast<const __half*>(st + Q40T_NIB_BYTES + pp * 8 + kb * 2));
+                // low nibbles as they are; high nibbles stay in place (16 * nibble, unsigned bytes) and the /16 is
+                // applied to their exact integer sum: 8 mask ops instead of 12 mask + shift ops per block
+                const uint32_t lo0 = nb.x & 0x0F0F0F0Fu, hi0 = nb.x & 0xF0F0F0F0u;
+                const uint32_t lo1 = nb.y & 0x0F0F0F0Fu, hi1 = nb.y & 0xF0F0F0F0u;
+                const uint32_t lo2 = nb.z & 0x0F0F0F0Fu, hi2 = nb.z & 0xF0F0F0F0u;
+                const uint32_t lo3 = nb.w & 0x0F0F0F0Fu, hi3 = nb.w & 0xF0F0F0F0u;
 #pragma unroll
-                for (int kb = 0; kb < 4; kb++) {
-                    const uint4 nb = *reinterpret_cast<const uint4*>(nibp + (((kb + rot) & 3) << 4));
-                    const float dw = __half2float(*reinterpret_cast<const __half*>(scp + kb * 2));
-                    const int lo0 = nb.x & 0x0F0F0F0F, hi0 = (nb.x >> 4) & 0x0F0F0F0F;
-                    const int lo1 = nb.y & 0x0F0F0F0F, hi1 = (nb.y >> 4) & 0x0F0F0F0F;
-                    const int lo2 = nb.z & 0x0F0F0F0F, hi2 = (nb.z >> 4) & 0x0F0F0F0F;
-                    const int lo3 = nb.w & 0x0F0F0F0F, hi3 = (nb.w >> 4) & 0x0F0F0F0F;
+                for (int m = 0; m < MT; m++) {
+                    int is0 = dp4a_us(lo0, xl[m].x, 0), is1 = dp4a_us(hi0, xh[m].x, 0);
+                    is0 = dp4a_us(lo1, xl[m].y, is0); is1 = dp4a_us(hi1, xh[m].y, is1);
+                    is0 = dp4a_us(lo2, xl[m].z, is0); is1 = dp4a_us(hi2, xh[m].z, is1);
+                    is0 = dp4a_us(lo3, xl[m].w, is0); is1 = dp4a_us(hi3, xh[m].w, is1);
+                    const float term = (float)(is0 + (is1 >> 4) - s8[m]) * (dw * dx[m]);
+                    acc[i][m] = live ? acc[i][m] + term : acc[i][m];
+                }
+            };
+            // the Q80 activations of (k-tile kt, k-block kb) for the MT rows; slabs are [kt][MT][160], no row test
+            auto load_act = [&](int kt, int4 (&xl)[MT], int4 (&xh)[MT], float (&dx)[MT], int (&s8)[MT]) {
+                const uint8_t* actp = c.act + (size_t)kt * MT * XQ_ROW_BYTES;
 #pragma unroll
-                    for (int m = 0; m < MT; m++) {
-                        if (m < M) {
-                            const uint8_t* xr = actp + m * XQ_ROW_BYTES;
-                            const int4 xl = *reinterpret_cast<const int4*>(xr + kb * 32);
-                            const int4 xh = *reinterpret_cast<const int4*>(xr + kb * 32 + 16);
-                            int is0 = __dp4a(lo0, xl.x, 0), is1 = __dp4a(hi0, xh.x, 0);
-                            is0 = __dp4a(lo1, xl.y, is0); is1 = __dp4a(hi1, xh.y, is1);
-                            is0 = __dp4a(lo2, xl.z, is0); is1 = __dp4a(hi2, xh.z, is1);
-                            is0 = __dp4a(lo3, xl.w, is0); is1 = __dp4a(hi3, xh.w, is1);
-                            const float dx = reinterpret_cast<const float*>(xr + 128)[kb];
-                            const int s8 = reinterpret_cast<const int*>(xr + 144)[kb];
-                            acc[m] += (float)(is0 + is1 - s8) * (dw * dx);
-                        }
-                    }
+                for (int m = 0; m < MT; m++) {
+                    const uint8_t* xr = actp + m * XQ_ROW_BYTES;
+                    xl[m] = *reinterpret_cast<const int4*>(xr + kb * 32);
+                    xh[m] = *reinterpret_cast<const int4*>(xr + kb * 32 + 16);
+                    dx[m] = reinterpret_cast<const float*>(xr + 128)[kb];
+                    s8[m] = reinterpret_cast<const int*>(xr + 144)[kb];
+                }
+            };
+            if (kpack == 1) {
+                // a stage is one k-tile of up to 128 rows: the activations are loaded once and serve every row
+                int4 xl[MT], xh[MT];
+                float dx[MT];
+                int s8[MT];
+                load_act(ci, xl, xh, dx, s8);
+#pragma unroll
+                for (int i = 0; i < 4; i++) block(i, true, xl, xh, dx, s8);
+            } else {
+                // several k-tiles per stage; the last stage of a piece may hold fewer (their slots are stale: dropped)
+#pragma unroll
+                for (int i = 0; i < 4; i++) {
+                    const int kt = ci * kpack + pj[i];
+                    int4 xl[MT], xh[MT];
+                    float dx[MT];
+                    int s8[MT];
+                    load_act(min(kt, KT - 1), xl, xh, dx, s8);
+                    block(i, kt < KT, xl, xh, dx, s8);
                 }
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(&c.empty[s]);
         }
         it += nch;
-        if (mine) {
+        if (ph == PH_QKV) MG_ISTAMP(5);
+        if (ph == PH_W2) MG_ISTAMP(10);
+        // fold the four k-blocks of a pair (the four quarter-warps), then one partial per (group, k-tile, row)
 #pragma unroll
-            for (int m = 0; m < MT; m++) c.red[((g * kpack + j) * MT + m) * nr + lr] = acc[m];
+        for (int i = 0; i < 4; i++) {
+#pragma unroll
+            for (int m = 0; m < MT; m++) {
+                float v = acc[i][m];
+                v += __shfl_xor_sync(0xffffffffu, v, 8);
+                v += __shfl_xor_sync(0xffffffffu, v, 16);
+                if (kb == 0 && ((pvalid >> i) & 1u)) c.red[((g * kpack + pj[i]) * MT + m) * nr + plr[i]] = v;
+            }
         }
         cons_bar();
+        // out_s[m][row] = sum of the (group, k-tile) partials: four lanes per output (one per group), fixed order
 #pragma unroll 1
-        for (int idx = tid; idx < MT * nr; idx += MG_CONS) {
-            const int m = idx / nr, l2 = idx - m * nr;
+        for (int base = 0; base < MT * nr * 4; base += MG_CONS) {
+            const int o4 = base + tid;
+            const bool live = o4 < MT * nr * 4;
+            const int o = live ? (o4 >> 2) : 0, gg = o4 & 3;
+            const int m = o / nr, l2 = o - m * nr;
             float vs = 0.0f;
-            for (int q = 0; q < 4 * kpack; q++) vs += c.red[(q * MT + m) * nr + l2];
-            c.out_s[m * 128 + l2] = vs;
+            if (live) {
+                for (int q = 0; q < kpack; q++) vs += c.red[((gg * kpack + q) * MT + m) * nr + l2];
+            }
+            vs += __shfl_xor_sync(0xffffffffu, vs, 1);
+            vs += __shfl_xor_sync(0xffffffffu, vs, 2);
+            if (live && gg == 0) c.out_s[m * 128 + l2] = vs;
         }
         cons_bar();
+        if (ph == PH_QKV) MG_ISTAMP(6);
+        if (ph == PH_W2) MG_ISTAMP(11);
         switch (ph) {
             case PH_QKV: epi_qkv(a, c, Lw, r, nr); break;
-            case PH_WO: epi_residual(a, c, r, nr, layer == 0, a.world > 1 ? a.ll_att : nullptr, epoch); break;
+            case PH_WO: epi_residual(a, c, r, nr, a.ll_att, epoch); break;
             case PH_W13: epi_silu(a, c, r, nr); break;
-            case PH_W2: epi_residual(a, c, r, nr, false, a.world > 1 ? a.ll_ffn : nullptr, epoch); break;
+            case PH_W2: epi_residual(a, c, r, nr, a.ll_ffn, epoch); break;
             default: epi_logits(a, c, r, nr); break;
         }
+        if (ph == PH_QKV) MG_ISTAMP(7);
+        if (ph == PH_W2) MG_ISTAMP(12);
         cons_bar();
+        if (ph == PH_QKV) MG_ISTAMP(8);
+        if (ph == PH_W2) MG_ISTAMP(13);
         r += nr;
     }
     it_io = it;
@@ -682,7 +946,8 @@ DL_DEVINL float warp_transpose_reduce32_m(float (&v)[32], int lane) {
 }
 
 template <int HS, int NCH>
-__device__ __noinline__ void attention_phase(const DlDecodeArgs& a, uint32_t& ai_io) {
+__device__ __noinline__ void attention_phase(uint32_t& ai_io) {
+    const DlDecodeArgs& a = mg_args();
     constexpr int DPL = HS / 32;
     constexpr int GMAX = NCH * 4;
     constexpr int NGA = (NCH == 1) ? 4 : 2;                 // warp groups working on pages concurrently
@@ -704,8 +969,8 @@ __device__ __noinline__ void attention_phase(const DlDecodeArgs& a, uint32_t& ai
         const int sp_i = item % a.att_splits;
         const int kvh = (item / a.att_splits) % a.n_kv_heads;
         const int m = item / (a.att_splits * a.n_kv_heads);
-        const int pos = a.pos[m];
-        const int n_eff = mg_n_eff(pos, a.att_splits);
+        const int pos = c.rows[m].pos;
+        const int n_eff = c.rows[m].n_eff;
         if (sp_i >= n_eff) continue;
         const int T = pos + 1;
         const int n_pages = pos / MG_PAGE + 1;
@@ -843,14 +1108,15 @@ __device__ __noinline__ void attention_phase(const DlDecodeArgs& a, uint32_t& ai
 }
 
 // long contexts (> 4 splits): one warp per (row, head) folds the splits into split slot 0, normalised
-__device__ __noinline__ void attention_merge_coop(const DlDecodeArgs& a) {
+__device__ __noinline__ void attention_merge_coop() {
+    const DlDecodeArgs& a = mg_args();
     const MgCtx c;
     const int hs = a.head_size, warp = c.tid >> 5, lane = c.tid & 31;
     const int n_items = a.M * a.n_heads;
 #pragma unroll 1
     for (int item = c.cta * (MG_CONS / 32) + warp; item < n_items; item += c.G * (MG_CONS / 32)) {
         const int m = item / a.n_heads;
-        const int n_eff = mg_n_eff(a.pos[m], a.att_splits);
+        const int n_eff = c.rows[m].n_eff;
         const size_t base = (size_t)item * a.max_splits;
         float ms = -INFINITY, ls = 0.0f;
         if (lane < n_eff) {
@@ -891,99 +1157,128 @@ __global__ void __launch_bounds__(MG_THREADS, 1) decode_mega_kernel(const __grid
             mbar_init(&c.kv_full[s], 1);
             mbar_init(&c.kv_empty[s], 4);
         }
+        mbar_init(reinterpret_cast<uint64_t*>(mg_smem + SM_HBAR), 1);
+        *reinterpret_cast<unsigned long long*>(mg_smem + SM_HBAR + 8) = globaltimer_ns() + a.timeout_ns;
         mbar_fence_init();
     }
+    // the arguments, once, into shared memory for the phase functions (see mg_args())
+    for (int i = tid; i < (int)(sizeof(DlDecodeArgs) / 4); i += MG_THREADS)
+        reinterpret_cast<uint32_t*>(mg_smem + SM_ARGS)[i] = reinterpret_cast<const uint32_t*>(&a)[i];
     if (tid < MG_MAX_M) {                                    // running greedy best of this CTA
         float* run = c.misc + MG_BEST_OFF + 4 * MG_MAX_M * 2;
         run[tid * 2] = -INFINITY;
         run[tid * 2 + 1] = __int_as_float(0x7fffffff);
     }
+    if (tid < a.M) {
+        MgRowInfo ri;
+        ri.pos = a.pos[tid];
+        ri.slot = a.slot[tid];
+        ri.token = a.tokens[tid];
+        ri.page = a.block_table[(size_t)ri.slot * a.max_pages + ri.pos / MG_PAGE];
+        ri.n_eff = mg_n_eff(ri.pos, a.att_splits);
+        ri.pad0 = ri.pad1 = ri.pad2 = 0;
+        c.rows[tid] = ri;
+    }
+    for (int i = tid; i < a.M * (a.head_size >> 1); i += MG_THREADS) {      // RoPE angles (OP_ROPE_LLAMA, nn-cpu-ops.cpp:1090-1120)
+        const int m = i / (a.head_size >> 1), pr = i - m * (a.head_size >> 1);
+        float sn, cs;
+        sincosf((float)a.pos[m] * a.rope_freqs[pr], &sn, &cs);
+        c.rope[m * 64 + pr] = make_float2(cs, sn);
+    }
     __syncthreads();
     const uint32_t step = ld_volatile_u32(a.step_counter) + 1u;          // nobody writes it before the last grid barrier
 
-    if (warp == 16) { weight_producer(a); return; }
-    if (warp == 17) { kv_producer(a); return; }
+    if (warp >= 16 && warp < MG_KV_WARP) { weight_producer(); return; }
+    if (warp == MG_KV_WARP) { kv_producer(); return; }
 
     // ------------------------------------------ consumers ------------------------------------------
     MgSpin sp;
     sp.init(a.timeout_ns, a.debug);
     const int M = a.M, L = a.n_layers, N = a.world;
-    const bool multi = N > 1;
     const uint32_t ebase = step * (uint32_t)(2 * L);       // LL epochs of this step: ebase + 2l + 1 (wo), ebase + 2l + 2 (w2)
     uint32_t it = 0, ai = 0;
+    unsigned nbar = 0;
     int cur = 0;
-    unsigned long long* tr = (a.trace != nullptr && c.cta == 0 && tid == 0) ? a.trace : nullptr;
+    // optional timeline: 16 globaltimer stamps per layer (+ 2 at the end) of the CTA selected by trace_cta
+    unsigned long long* tr = (a.trace != nullptr && c.cta == a.trace_cta && tid == 0) ? a.trace : nullptr;
+#define MG_STAMP(l, k) do { if (tr) { tr[(l) * 32 + (k)] = globaltimer_ns(); if ((k) == 0) c.rows[0].pad0 = (l); } } while (0)
     // do any rows need the cooperative split merge?  (uniform over the grid: same inputs everywhere)
     bool coop = false;
-    for (int m = 0; m < M; m++) coop = coop || (mg_n_eff(a.pos[m], a.att_splits) > MG_SMALL_SPLITS);
+    for (int m = 0; m < M; m++) coop = coop || (c.rows[m].n_eff > MG_SMALL_SPLITS);
     const int att_sel = a.head_size * 8 + (a.n_heads / a.n_kv_heads > 4 ? 2 : 1);
     int R0, R1;
 
+    // The residual stream x is replicated: every CTA rebuilds the row it needs in its norm prologue from the previous x
+    // and the ranks' Q80 partial sums (LL words), CTA 0 writes it back for the next prologue (ping-pong buffers; the
+    // grid barriers in between order those writes against the reads of the other CTAs).
 #pragma unroll 1
     for (int l = 0; l < L; l++) {
-        if (tr) tr[l * 8 + 0] = globaltimer_ns();
+        MG_STAMP(l, 0);
         // ---- attention block: norm -> qkv ----
         {
             mg_cta_rows(a.q_dim + 2 * a.kv_dim, c.G, 2, c.cta, R0, R1);
-            const bool merge = multi && l > 0;
-            // with a replicated residual (world > 1) CTA 0 materialises x of this layer
-            float* xo = (multi && c.cta == 0) ? a.x[l == 0 ? 0 : (cur ^ 1)] : nullptr;
+            float* xo = (c.cta == 0) ? a.x[l == 0 ? 0 : (cur ^ 1)] : nullptr;
             if (R1 > R0 || xo != nullptr)
-                prologue_norm(a, l == 0 ? nullptr : a.x[cur], xo, merge ? a.ll_ffn[a.rank] : nullptr,
+                prologue_norm(MT, l == 0 ? nullptr : a.x[cur], xo, l > 0 ? a.ll_ffn[a.rank] : nullptr,
                               ebase + 2 * l /* w2 of layer l-1 */, a.layers[l].rms_att);
-            if (merge) cur ^= 1;
+            if (l > 0) cur ^= 1;
         }
-        if (tr) tr[l * 8 + 1] = globaltimer_ns();
-        gemv_phase<MT>(a, PH_QKV, l, it, 0u);
-        grid_sync(a.grid_bar, c.G, sp);
-        if (tr) tr[l * 8 + 2] = globaltimer_ns();
+        MG_STAMP(l, 1);
+        gemv_phase<MT>(PH_QKV, l, it, 0u);
+        MG_STAMP(l, 2);
+        grid_sync(a.grid_bar, c.G, nbar, sp);
+        MG_STAMP(l, 3);
         // ---- attention ----
         cons_kv_bar();
         switch (att_sel) {
-            case 32 * 8 + 1: attention_phase<32, 1>(a, ai); break;
-            case 32 * 8 + 2: attention_phase<32, 2>(a, ai); break;
-            case 64 * 8 + 1: attention_phase<64, 1>(a, ai); break;
-            case 64 * 8 + 2: attention_phase<64, 2>(a, ai); break;
-            case 128 * 8 + 1: attention_phase<128, 1>(a, ai); break;
-            default: attention_phase<128, 2>(a, ai); break;
+            case 32 * 8 + 1: attention_phase<32, 1>(ai); break;
+            case 32 * 8 + 2: attention_phase<32, 2>(ai); break;
+            case 64 * 8 + 1: attention_phase<64, 1>(ai); break;
+            case 64 * 8 + 2: attention_phase<64, 2>(ai); break;
+            case 128 * 8 + 1: attention_phase<128, 1>(ai); break;
+            default: attention_phase<128, 2>(ai); break;
         }
-        grid_sync(a.grid_bar, c.G, sp);
+        MG_STAMP(l, 4);
+        grid_sync(a.grid_bar, c.G, nbar, sp);
         if (coop) {
-            attention_merge_coop(a);
-            grid_sync(a.grid_bar, c.G, sp);
+            attention_merge_coop();
+            grid_sync(a.grid_bar, c.G, nbar, sp);
         }
-        if (tr) tr[l * 8 + 3] = globaltimer_ns();
+        MG_STAMP(l, 5);
         // ---- wo ----
         mg_cta_rows(a.dim, c.G, 32, c.cta, R0, R1);
-        if (R1 > R0) prologue_att(a, coop);
-        gemv_phase<MT>(a, PH_WO, l, it, ebase + 2 * l + 1);
-        if (!multi) grid_sync(a.grid_bar, c.G, sp);
-        if (tr) tr[l * 8 + 4] = globaltimer_ns();
+        if (R1 > R0) prologue_att(MT, coop);
+        MG_STAMP(l, 6);
+        gemv_phase<MT>(PH_WO, l, it, ebase + 2 * l + 1);
+        MG_STAMP(l, 7);
+        MG_STAMP(l, 8);
         // ---- feed-forward block: norm -> w1|w3 ----
         {
             mg_cta_rows(2 * a.hid, c.G, 2, c.cta, R0, R1);
-            float* xo = (multi && c.cta == 0) ? a.x[cur ^ 1] : nullptr;
+            float* xo = (c.cta == 0) ? a.x[cur ^ 1] : nullptr;
             if (R1 > R0 || xo != nullptr)
-                prologue_norm(a, a.x[cur], xo, multi ? a.ll_att[a.rank] : nullptr, ebase + 2 * l + 1, a.layers[l].rms_ffn);
-            if (multi) cur ^= 1;
+                prologue_norm(MT, a.x[cur], xo, a.ll_att[a.rank], ebase + 2 * l + 1, a.layers[l].rms_ffn);
+            cur ^= 1;
         }
-        if (tr) tr[l * 8 + 5] = globaltimer_ns();
-        gemv_phase<MT>(a, PH_W13, l, it, 0u);
-        grid_sync(a.grid_bar, c.G, sp);
-        if (tr) tr[l * 8 + 6] = globaltimer_ns();
+        MG_STAMP(l, 9);
+        gemv_phase<MT>(PH_W13, l, it, 0u);
+        MG_STAMP(l, 10);
+        grid_sync(a.grid_bar, c.G, nbar, sp);
+        MG_STAMP(l, 11);
         // ---- w2 ----
         mg_cta_rows(a.dim, c.G, 32, c.cta, R0, R1);
-        if (R1 > R0) prologue_hidden(a);
-        gemv_phase<MT>(a, PH_W2, l, it, ebase + 2 * l + 2);
-        if (!multi) grid_sync(a.grid_bar, c.G, sp);
-        if (tr) tr[l * 8 + 7] = globaltimer_ns();
+        if (R1 > R0) prologue_hidden(MT, (uint32_t)(l & 1));
+        MG_STAMP(l, 12);
+        gemv_phase<MT>(PH_W2, l, it, ebase + 2 * l + 2);
+        MG_STAMP(l, 13);
+        MG_STAMP(l, 14);
     }
 
     // ---- final norm -> logits (OP_MATMUL wcls + logits gather, src/llm.cpp:394-432) ----
     mg_cta_rows(a.vocab_loc, c.G, 2, c.cta, R0, R1);
-    if (R1 > R0) prologue_norm(a, a.x[cur], nullptr, multi ? a.ll_ffn[a.rank] : nullptr, ebase + 2 * L, a.rms_final);
-    gemv_phase<MT>(a, PH_CLS, 0, it, 0u);
-    if (tr) tr[L * 8 + 0] = globaltimer_ns();
+    if (R1 > R0) prologue_norm(MT, a.x[cur], nullptr, a.ll_ffn[a.rank], ebase + 2 * L, a.rms_final);
+    gemv_phase<MT>(PH_CLS, 0, it, 0u);
+    MG_STAMP(L, 1);
     if (a.greedy) {
         // CTA candidates -> global; CTA 0 reduces them, exchanges the per-rank winners as LL words, picks the token
         if (tid < M) {
@@ -991,11 +1286,20 @@ __global__ void __launch_bounds__(MG_THREADS, 1) decode_mega_kernel(const __grid
             a.cta_best[((size_t)c.cta * MG_MAX_M + tid) * 2] = run[tid * 2];
             a.cta_best[((size_t)c.cta * MG_MAX_M + tid) * 2 + 1] = run[tid * 2 + 1];
         }
-    } else if (multi) {
+    } else if (N > 1) {
         cons_bar();
         if (tid == 0) __threadfence_system();      // this CTA's logits stores to the peers, before the grid barrier
     }
-    grid_sync(a.grid_bar, c.G, sp);
+    grid_sync(a.grid_bar, c.G, nbar, sp);
+    MG_STAMP(L, 2);
+    if (tid == 0) {
+        // the last CTA to get here clears the barrier words for the next launch (everybody has left the last spin)
+        const unsigned prev = atomicAdd(a.grid_bar + 1, 1u);
+        if (prev == (unsigned)c.G - 1u) {
+            a.grid_bar[0] = 0u;
+            a.grid_bar[1] = 0u;
+        }
+    }
     if (c.cta != 0) return;
     if (a.greedy) {
         if (warp < M && warp >= a.row0) {
@@ -1008,7 +1312,7 @@ __global__ void __launch_bounds__(MG_THREADS, 1) decode_mega_kernel(const __grid
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1)
                 argmax_combine2(bv, bi, __shfl_xor_sync(0xffffffffu, bv, o), __shfl_xor_sync(0xffffffffu, bi, o));
-            if (multi) {
+            if (N > 1) {
                 // rank winners travel as two LL words per (source rank, row); every rank picks the same token
                 if (lane < 2 * N) {
                     const int p = lane >> 1, wsel = lane & 1;
@@ -1041,14 +1345,11 @@ __global__ void __launch_bounds__(MG_THREADS, 1) decode_mega_kernel(const __grid
                 if (a.history != nullptr) a.history[(size_t)((step - 1u) % (uint32_t)a.history_cap) * M + m] = bi;
             }
         }
-    } else if (multi) {
+    } else if (N > 1) {
         if (tid < N) st_release_sys(a.flag_logits[tid], step);
     }
     cons_bar();
-    if (tid == 0) {
-        *a.step_counter = step;
-        if (tr) tr[L * 8 + 1] = globaltimer_ns();
-    }
+    if (tid == 0) *a.step_counter = step;
 }
 
 // =================================================================================================
@@ -1076,12 +1377,13 @@ extern "C" int dl_decode_mega_supported(const DlDecodeArgs* a, int grid) {
     if (a->n_kv_heads < 1 || a->n_heads % a->n_kv_heads != 0 || a->n_heads / a->n_kv_heads > 8) { dl_set_error("decode_mega: %d query heads on %d kv heads (max 8 per kv head)", a->n_heads, a->n_kv_heads); return -1; }
     if (a->dim % 128 || a->q_dim % 128 || a->hid % 128) { dl_set_error("decode_mega: dim/q_dim/hid must be multiples of 128"); return -1; }
     if ((a->q_dim + 2 * a->kv_dim) % 2 || a->vocab_loc % 2 || a->kv_dim % 2 || a->head_size % 2) { dl_set_error("decode_mega: odd row counts"); return -1; }
+    const int mt = a->M == 1 ? 1 : (a->M == 2 ? 2 : 4);         // rows the activation slabs carry
     // prologue_norm parks the merged row (f32) behind its Q80 slabs
-    if ((long long)a->M * a->dim * 4 + (long long)(a->dim / 128) * a->M * XQ_ROW_BYTES > MG_ACT_BYTES) { dl_set_error("decode_mega: M*dim=%lld does not fit the shared-memory row buffer", (long long)a->M * a->dim); return -1; }
+    if ((long long)a->M * (a->dim / 32) * MG_XS_STRIDE * 16 + (long long)(a->dim / 128) * mt * XQ_ROW_BYTES > MG_ACT_BYTES) { dl_set_error("decode_mega: M*dim=%lld does not fit the shared-memory row buffer", (long long)a->M * a->dim); return -1; }
     const long long kmax = a->hid > a->dim ? (a->hid > a->q_dim ? a->hid : a->q_dim) : (a->dim > a->q_dim ? a->dim : a->q_dim);
-    if (kmax / 128 * a->M * XQ_ROW_BYTES > MG_ACT_BYTES) { dl_set_error("decode_mega: activation slabs (%lld B) exceed %d B of shared memory", kmax / 128 * a->M * XQ_ROW_BYTES, MG_ACT_BYTES); return -1; }
+    if (kmax / 128 * mt * XQ_ROW_BYTES > MG_ACT_BYTES) { dl_set_error("decode_mega: activation slabs (%lld B) exceed %d B of shared memory", kmax / 128 * mt * XQ_ROW_BYTES, MG_ACT_BYTES); return -1; }
     if (a->world < 1 || a->world > DL_MAX_PEERS || a->rank < 0 || a->rank >= a->world) { dl_set_error("decode_mega: rank/world"); return -1; }
-    if (a->world > 1 && !a->q80_sync) { dl_set_error("decode_mega: world > 1 ships Q80 partial sums (q80_sync must be on)"); return -1; }
+    if (!a->q80_sync) { dl_set_error("decode_mega: the wo / w2 partial sums always travel as Q80 words (q80_sync must be on)"); return -1; }
     if (a->att_splits < 1 || a->att_splits > a->max_splits || a->max_splits > 32) { dl_set_error("decode_mega: att_splits=%d max_splits=%d", a->att_splits, a->max_splits); return -1; }
     if (grid < 1) { dl_set_error("decode_mega: grid=%d", grid); return -1; }
     return 0;

@@ -250,7 +250,7 @@ class LlamaEngine:
         h, dev, N = self.h, self.device, self.world
         self._mega_ok_cache: Dict[int, bool] = {}
         self.mega_grid = 0
-        if not self.use_mega or dev.type != "cuda" or kv_dtype != torch.float16 or (N > 1 and not self.sync_q80):
+        if not self.use_mega or dev.type != "cuda" or kv_dtype != torch.float16 or not self.sync_q80:
             self.use_mega = False
             return
         from ..ops.lib import DlDecodeLayer
@@ -274,6 +274,8 @@ class LlamaEngine:
         # a time-out inside the kernel traps (the context is lost); the reason is left in mapped host memory
         self._mega_debug = torch.zeros(16, dtype=torch.int32).pin_memory()
         self._mega_trace: Optional[torch.Tensor] = None
+        self._mega_trace_cta = 0
+        self._mega_pf_dist = int(os.environ.get("DLLAMA_MEGA_PF", "0"))
         self._mega_timeout_ns = int(float(os.environ.get("DLLAMA_MEGA_TIMEOUT_S", "20")) * 1e9)
 
     def _mega_args(self, M: int, row0: int, greedy: bool, device_loop: bool):
@@ -316,6 +318,8 @@ class LlamaEngine:
         a.timeout_ns = self._mega_timeout_ns
         a.debug = self._mega_debug.data_ptr()
         a.trace = self._mega_trace.data_ptr() if self._mega_trace is not None else None
+        a.trace_cta = self._mega_trace_cta
+        a.pf_dist = self._mega_pf_dist
         return a
 
     def _mega_usable(self, M: int, chunk: bool) -> bool:
@@ -327,10 +331,11 @@ class LlamaEngine:
             self._mega_ok_cache[M] = ok
         return ok
 
-    def enable_mega_trace(self, on: bool = True):
-        """Per-phase globaltimer stamps of CTA 0 (8 per layer + 2): read with mega_trace_ns() after a forward.
+    def enable_mega_trace(self, on: bool = True, cta: int = 0):
+        """Per-phase globaltimer stamps of one CTA (16 per layer + 2): read with mega_trace_ns() after a forward.
         Graphs captured before the switch keep their old setting."""
-        self._mega_trace = torch.zeros(self.h.n_layers * 8 + 8, dtype=torch.int64, device=self.device) if on else None
+        self._mega_trace = torch.zeros(self.h.n_layers * 32 + 32, dtype=torch.int64, device=self.device) if on else None
+        self._mega_trace_cta = cta
         self._graphs.clear()
 
     def mega_trace_ns(self) -> np.ndarray:

@@ -126,6 +126,8 @@ class DlDecodeArgs(C.Structure):
         ("timeout_ns", C.c_ulonglong),
         ("debug", C.c_void_p),
         ("trace", C.c_void_p),
+        ("trace_cta", C.c_int),
+        ("pf_dist", C.c_int),
     ]
 
 

@@ -202,7 +202,7 @@ typedef struct {
     int rank, world;
     float eps;
     int act_gelu;
-    int q80_sync;                     /* Q80 round trip of the wo / w2 outputs (always on when world > 1) */
+    int q80_sync;                     /* must be 1: the wo / w2 partial sums travel as Q80 words */
     const DlDecodeLayer* layers;      /* device array [n_layers] */
     const float* rms_final;
     const uint8_t* wcls;              /* Q40T [vocab_loc][dim] */
@@ -216,7 +216,7 @@ typedef struct {
     const int* block_table;           /* [n_slots][max_pages] */
     int max_pages;
     /* activations and scratch of this rank (device) */
-    float* x[2];                      /* residual stream [4][dim]; x[1] only used when world > 1 */
+    float* x[2];                      /* residual stream [4][dim], ping-pong */
     float* q;                         /* [4][q_dim] */
     float* h;                         /* [4][hid] */
     float* att_o;                     /* [4][n_heads][max_splits][head_size] */
@@ -224,7 +224,7 @@ typedef struct {
     int max_splits;                   /* capacity of the split dimension above (<= 32) */
     int att_splits;                   /* split-KV grid: CTAs per (row, kv head) */
     float* cta_best;                  /* [grid][4][2] greedy candidates */
-    unsigned long long* grid_bar;     /* one zero-initialised, monotonically increasing counter */
+    unsigned* grid_bar;               /* two zero-initialised words: arrival counter, exit counter (the kernel leaves them at zero) */
     uint32_t* step_counter;
     /* tensor-parallel exchange: rank p's buffers as mapped into this process (p < world) */
     uint8_t* ll_att[DL_MAX_PEERS];    /* [world src][4][dim/32][9] 8-byte LL words */
@@ -241,7 +241,10 @@ typedef struct {
     unsigned long long timeout_ns;    /* spin limit before the kernel traps (0 = none) */
     uint32_t* debug;                  /* NULL or a word in mapped pinned host memory: 0x80000000 | wait code << 16 | CTA
                                        * is stored there before a time-out trap (device memory is lost with the context) */
-    unsigned long long* trace;        /* NULL or [n_layers * 8 + 8] globaltimer stamps of CTA 0 */
+    unsigned long long* trace;        /* NULL or [n_layers * 32 + 32] globaltimer stamps of CTA trace_cta */
+    int trace_cta;
+    int pf_dist;                      /* pipeline chunks (<= 9 KB) the L2 prefetch of the weight stream runs ahead of the
+                                       * shared-memory ring; 0 = no L2 prefetch */
 } DlDecodeArgs;
 
 /* 0 if the shapes fit the persistent kernel (shared memory, register-resident row, head size), else -1

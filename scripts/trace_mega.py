@@ -1,5 +1,6 @@
 #!/usr/bin/env python3
-"""Per-phase timeline of the persistent decode kernel (CTA 0, globaltimer): python scripts/trace_mega.py [--model llama3.1-8b]
+"""Per-phase timeline of the persistent decode kernel (one CTA, globaltimer):
+    python scripts/trace_mega.py [--model llama3.1-8b] [--cta 0,73,146]
 Under torchrun it prints rank 0's timeline of a tensor-parallel step."""
 import argparse
 import os
@@ -9,6 +10,9 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np  # noqa: E402
 import torch  # noqa: E402
 
+NAMES = ["norm prologue", "qkv gemv", "barrier", "attention", "barrier (+merge)", "att-merge prologue", "wo gemv",
+         "barrier (1 GPU)", "ffn norm prologue", "w13 gemv", "barrier", "hidden prologue", "w2 gemv", "barrier (1 GPU)"]
+
 
 def main():
     ap = argparse.ArgumentParser()
@@ -16,6 +20,8 @@ def main():
     ap.add_argument("--model-dir", default=os.environ.get("DLLAMA_MODEL_DIR", "/dev/shm"))
     ap.add_argument("--ctx", type=int, default=128)
     ap.add_argument("--rows", type=int, default=1)
+    ap.add_argument("--cta", default="0")
+    ap.add_argument("--intra", action="store_true")
     a = ap.parse_args()
     import torch.distributed as dist
     from dllama_b200.formats import mfile
@@ -28,7 +34,7 @@ def main():
         mfile.write_random_model(path, a.model, quant.Q40, seed=1)
     if world > 1:
         dist.barrier()
-    eng = LlamaEngine(path, rank=rank, world=world, max_rows=256, n_slots=a.rows + 1, max_seq_len=max(512, a.ctx + 64))
+    eng = LlamaEngine(path, rank=rank, world=world, max_rows=256, n_slots=a.rows + 1, max_seq_len=max(512, a.ctx + 128))
     rng = np.random.default_rng(0)
     slots, toks = [], []
     for u in range(a.rows):
@@ -36,31 +42,41 @@ def main():
         lg = eng.prefill(s, rng.integers(1, eng.h.vocab_size, a.ctx).tolist(), 0)
         slots.append(s)
         toks.append(int(torch.argmax(lg[0])))
-    eng.enable_mega_trace(True)
     for s in slots:
-        eng.ensure_capacity(s, a.ctx + 16)
+        eng.ensure_capacity(s, a.ctx + 100)
     eng.set_batch(toks, [a.ctx] * a.rows, slots)
-    eng.decode_greedy_device(6, a.rows)
-    torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
-    t = eng.mega_trace_ns()
     L = eng.h.n_layers
-    if rank == 0:
-        names = ["norm+qkv prologue", "qkv gemv", "grid barrier + attention", "wo prologue+gemv(+barrier)", "ffn norm prologue",
-                 "w13 gemv + barrier", "w2 prologue+gemv(+barrier)"]
-        per = np.zeros((L, 7))
+    for cta in [int(x) for x in a.cta.split(",")]:
+        eng.enable_mega_trace(True, cta)
+        eng.decode_greedy_device(6, a.rows)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        t = eng.mega_trace_ns()
+        if rank != 0:
+            continue
+        per = np.zeros((L, 14))
+        intra = np.zeros((L, 16))
         for l in range(L):
-            b = t[l * 8: l * 8 + 8]
-            nxt = t[(l + 1) * 8] if l + 1 < L else t[L * 8]
-            # stamps: 0 start, 1 after prologue, 2 after qkv+barrier, 3 after attention(+merge), 4 after wo, 5 after ffn prologue, 6 after w13+barrier, 7 after w2
-            per[l] = [b[1] - b[0], b[2] - b[1], b[3] - b[2], b[4] - b[3], b[5] - b[4], b[6] - b[5], b[7] - b[6]]
-        print(f"[trace_mega] world={world} model={a.model} rows={a.rows} ctx={a.ctx}: us per phase (median over layers 1..)")
-        for i, n in enumerate(names):
-            print(f"  {n:34s} {np.median(per[1:, i]) / 1e3:7.2f}  (min {per[1:, i].min() / 1e3:.2f}, max {per[1:, i].max() / 1e3:.2f})")
-        print(f"  layer total (median)               {np.median(per[1:].sum(1)) / 1e3:7.2f}")
-        print(f"  logits phase                       {(t[L * 8] - t[(L - 1) * 8 + 7]) / 1e3:7.2f}")
-        print(f"  whole kernel                       {(t[L * 8 + 1] - t[0]) / 1e3:7.2f}")
+            b = t[l * 32: l * 32 + 15]
+            per[l] = np.diff(b)
+            intra[l] = t[l * 32 + 16: l * 32 + 32]
+        print(f"[trace_mega] world={world} model={a.model} rows={a.rows} ctx={a.ctx} cta={cta}: us per phase (median / min / max over layers 1..)")
+        for i, n in enumerate(NAMES):
+            print(f"  {n:22s} {np.median(per[1:, i]) / 1e3:7.2f} {per[1:, i].min() / 1e3:7.2f} {per[1:, i].max() / 1e3:7.2f}")
+        print(f"  layer total (median)   {np.median(per[1:].sum(1)) / 1e3:7.2f}")
+        print(f"  logits phase           {(t[L * 32 + 1] - t[(L - 1) * 32 + 14]) / 1e3:7.2f}   final barrier {(t[L * 32 + 2] - t[L * 32 + 1]) / 1e3:.2f}")
+        print(f"  whole kernel           {(t[L * 32 + 2] - t[0]) / 1e3:7.2f}")
+        if a.intra:
+            def d(i, j):
+                return float(np.median(intra[1:, j] - intra[1:, i])) / 1e3
+            l11 = np.array([t[l * 32 + 11] for l in range(L)])
+            l1 = np.array([t[l * 32 + 1] for l in range(L)])
+            print("  -- inside prologue_hidden: call overhead %.2f | loads %.2f | quantise+store %.2f | bar %.2f" %
+                  (float(np.median(intra[1:, 0] - l11[1:])) / 1e3, d(0, 1), d(1, 2), d(2, 3)))
+            print("  -- inside qkv gemv: entry %.2f | chunk loop %.2f | reduce %.2f | epilogue %.2f | bar %.2f" %
+                  (float(np.median(intra[1:, 4] - l1[1:])) / 1e3, d(4, 5), d(5, 6), d(6, 7), d(7, 8)))
+            print("  -- inside w2 gemv:  chunk loop %.2f | reduce %.2f | epilogue %.2f | bar %.2f" % (d(9, 10), d(10, 11), d(11, 12), d(12, 13)))
     eng.close()
     if world > 1:
         dist.barrier()

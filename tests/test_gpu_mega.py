@@ -19,15 +19,21 @@ def test_mega_plan_covers_every_row_once(d, n, align, grid):
     """Every row of a matmul phase belongs to exactly one CTA, ranges are aligned, and the busiest CTA is within one
     alignment unit of the ideal share."""
     plan = _plan(d, n, align, grid)
-    nxt = 0
+    covered = np.zeros(d, dtype=np.int32)
     for r0, r1, chunks in plan:
-        assert r0 == min(nxt, d) and r0 <= r1 <= d
+        assert 0 <= r0 <= r1 <= d
         assert r0 % align == 0 and (r1 % align == 0 or r1 == d)
         assert (chunks > 0) == (r1 > r0)
-        nxt = max(nxt, r1)
-    assert nxt == d
+        covered[r0:r1] += 1
+    assert (covered == 1).all()
     busiest = max(r1 - r0 for r0, r1, _ in plan)
-    assert busiest <= -(-d // grid) + align - 1
+    tiles = -(-d // 128)
+    if tiles <= grid:        # tile-by-tile split: no CTA straddles a 128-row tile
+        assert all(r0 // 128 == (r1 - 1) // 128 for r0, r1, _ in plan if r1 > r0)
+        cpt = grid // tiles
+        assert busiest <= -(-(-(-128 // cpt)) // align) * align
+    else:
+        assert busiest <= -(-d // grid) + align - 1
 
 
 # ------------------------------------------------------------------------------------------------------------
