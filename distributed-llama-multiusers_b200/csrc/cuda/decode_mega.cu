@@ -53,6 +53,7 @@
 #define SM_ARGS (SM_ROPE + MG_MAX_M * 64 * 8)             // copy of the kernel arguments (see mg_args())
 #define SM_HBAR (SM_ARGS + 1024)                          // mbarrier of the hidden-activation bulk copy
 #define SM_TOTAL (SM_HBAR + 16)
+static_assert(sizeof(DlDecodeLayer) == 64, "layer table entry");
 static_assert(sizeof(DlDecodeArgs) <= 1024, "DlDecodeArgs outgrew its shared-memory copy");
 
 extern void dl_set_error(const char* fmt, ...);
@@ -74,8 +75,17 @@ DL_DEVINL void mg_mbar_wait(uint64_t* bar, uint32_t parity, MgSpin& sp, int code
     while (!mbar_try_wait(bar, parity)) sp.tick(code);
     sp.reset();
 }
+// for the producer warps: they share their schedulers with four consumer warps each, and a hot try_wait loop (210 M
+// instructions per token, measured) takes issue slots from them
+DL_DEVINL void mg_mbar_wait_idle(uint64_t* bar, uint32_t parity, MgSpin& sp, int code) {
+    while (!mbar_try_wait(bar, parity)) {
+        __nanosleep(200);
+        sp.tick(code);
+    }
+}
 DL_DEVINL void cons_bar() { asm volatile("bar.sync 1, %0;" ::"n"(MG_CONS) : "memory"); }
 DL_DEVINL void cons_kv_bar() { asm volatile("bar.sync 2, %0;" ::"n"(MG_CONS + 32) : "memory"); }
+DL_DEVINL void cons_kv_bar2() { asm volatile("bar.sync 3, %0;" ::"n"(MG_CONS + 32) : "memory"); }
 DL_DEVINL void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
 
 DL_DEVINL unsigned long long ld_acquire_gpu_u64(const unsigned long long* p) {
@@ -137,6 +147,7 @@ struct MgCtx {
     uint8_t *ring, *act;
     float *red, *out_s, *q_s, *misc;
     struct MgRowInfo* rows;
+    DlDecodeLayer* lay;            // [2]: the layer table entries of layers l and l + 1 (slot l & 1), see the kernel
     float2* rope;
     int tid, cta, G;
     DL_DEVINL MgCtx() {
@@ -151,6 +162,7 @@ struct MgCtx {
         q_s = reinterpret_cast<float*>(mg_smem + SM_QS);
         misc = reinterpret_cast<float*>(mg_smem + SM_MISC);
         rows = reinterpret_cast<struct MgRowInfo*>(mg_smem + SM_ROWS);
+        lay = reinterpret_cast<DlDecodeLayer*>(mg_smem + SM_ROWS + 128);
         rope = reinterpret_cast<float2*>(mg_smem + SM_ROPE);
         tid = threadIdx.x;
         cta = blockIdx.x;
@@ -234,9 +246,11 @@ DL_DEVINL void bulk_prefetch_l2(const void* gsrc, uint32_t bytes) {
     asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gsrc), "r"(bytes) : "memory");
 }
 
-// The three producer warps: warp `me` owns the chunks with it % 3 == me.  Besides the shared-memory ring they run an L2
-// prefetch cursor MG_PF_DIST chunks (+ one piece) ahead, so HBM keeps streaming while the consumers sit in a prologue,
-// an attention phase or a barrier -- the ring alone holds only ~2.5 us worth of the stream.
+// The three producer warps: warp `me` owns the stages (chunks) with it % 3 == me.  While its next ring slot is still
+// occupied -- the consumers are in a prologue, the attention phase or a barrier and the ring (~2.5 us of the stream) is
+// full -- the warp spends the time pulling ITS stages up to pf_dist ahead into L2 (cp.async.bulk.prefetch.L2), so HBM
+// keeps streaming through the bubbles of the dependency chain and the next matmul phases are fed from L2.  Prefetches are
+// only issued while blocked: they never compete with the ring's own loads for issue slots.
 __device__ __noinline__ void weight_producer() {
     const DlDecodeArgs& a = mg_args();
     const MgCtx c;
@@ -248,23 +262,24 @@ __device__ __noinline__ void weight_producer() {
     MgPieceCursor ld, pf;
     ld.init();
     pf.init();
-    if (a.pf_dist > 0) pf.next(a, c.cta, c.G); else pf.done = true;
+    // prefetch cursor: piece pf, my next stage pf_ci inside it (global index pf.it0 + pf_ci)
+    int pf_ci = 0;
+    bool pf_on = a.pf_dist > 0;
+    auto pf_seek = [&]() {            // position pf_ci on my first stage of the current prefetch piece
+        pf_ci = (int)((me + MG_NPROD - pf.it0 % MG_NPROD) % MG_NPROD);
+    };
+    auto pf_advance = [&]() {         // next stage of my share, crossing pieces; clears pf_on at the end of the schedule
+        pf_ci += MG_NPROD;
+        while (pf_on && pf_ci >= pf.nch) {
+            if (!pf.next(a, c.cta, c.G)) { pf_on = false; break; }
+            pf_seek();
+        }
+    };
+    if (pf_on) {
+        if (pf.next(a, c.cta, c.G)) { pf_seek(); pf_ci -= MG_NPROD; pf_advance(); } else pf_on = false;
+    }
 #pragma unroll 1
     while (ld.next(a, c.cta, c.G)) {
-        // ---- L2 prefetch of the pieces ahead (k-tiles dealt over the 96 producer lanes) ----
-#pragma unroll 1
-        while (!pf.done && pf.it0 < ld.it0 + (uint32_t)a.pf_dist) {
-            if (pf.it0 >= ld.it_next) {                     // pieces the ring is about to load anyway are skipped
-#pragma unroll 1
-                for (int kt = (int)me * 32 + lane; kt < pf.KT; kt += 32 * MG_NPROD) {
-                    const uint8_t* t = pf.tile0 + (size_t)kt * Q40T_TILE_BYTES;
-                    bulk_prefetch_l2(t + pf.r0 * 64, (uint32_t)(pf.nr * 64));
-                    bulk_prefetch_l2(t + Q40T_SCALE_OFF + pf.r0 * 8, (uint32_t)(pf.nr * 8));
-                }
-            }
-            pf.next(a, c.cta, c.G);
-        }
-        // ---- my chunks of this piece into the ring: ci with (it0 + ci) % MG_NPROD == me ----
         int ci = (int)((me + MG_NPROD - ld.it0 % MG_NPROD) % MG_NPROD);
 #pragma unroll 1
         for (; ci < ld.nch; ci += MG_NPROD) {
@@ -273,7 +288,26 @@ __device__ __noinline__ void weight_producer() {
             const int nkt = min(ld.kpack, ld.KT - kt0);
             const int nr = ld.nr;
             const int s = itc % MG_NS;
-            if (itc >= MG_NS) mg_mbar_wait(&c.empty[s], ((itc / MG_NS) & 1) ^ 1, sp, 2);
+            if (itc >= MG_NS) {
+                const uint32_t par = ((itc / MG_NS) & 1) ^ 1;
+                // Blocked on the consumers?  Use the time for the stages ahead.  The burst polls with test_wait:
+                // try_wait suspends the warp for a hardware time slice, which leaves room for only a few prefetches
+                // in a bubble of a few microseconds.
+                while (pf_on && !mbar_test_wait(&c.empty[s], par)) {
+                    while (pf_on && pf.it0 + (uint32_t)pf_ci <= itc) pf_advance();             // never behind the ring
+                    if (!pf_on || pf.it0 + (uint32_t)pf_ci >= itc + (uint32_t)a.pf_dist) break;
+                    const int pk0 = pf_ci * pf.kpack;
+                    const int pn = min(pf.kpack, pf.KT - pk0);
+                    if (lane < pn) {
+                        const uint8_t* t = pf.tile0 + (size_t)(pk0 + lane) * Q40T_TILE_BYTES;
+                        bulk_prefetch_l2(t + pf.r0 * 64, (uint32_t)(pf.nr * 64));
+                        bulk_prefetch_l2(t + Q40T_SCALE_OFF + pf.r0 * 8, (uint32_t)(pf.nr * 8));
+                    }
+                    __syncwarp();
+                    pf_advance();
+                }
+                mg_mbar_wait_idle(&c.empty[s], par, sp, 2);
+            }
             uint8_t* st = c.ring + s * Q40T_TILE_BYTES;
             if (lane == 0) mbar_arrive_expect_tx(&c.full[s], (uint32_t)(nkt * nr * 72));
             __syncwarp();
@@ -301,13 +335,54 @@ __device__ __noinline__ void kv_producer() {
     const int page_bytes = MG_PAGE * a.head_size * 2;
     uint8_t* stages = c.act;
     const int n_items = a.M * a.n_kv_heads * a.att_splits;
+    // Positions, slots and block tables are the same for every layer of a step: the page list of this CTA's first work
+    // item (usually its only one) is read once, and only the page that receives this step's K/V row has to wait for the
+    // grid barrier behind the qkv phase -- the older pages are in flight while the CTA still sits in that barrier.
+    int f_m = 0, f_kvh = 0, f_pg0 = 0, f_pg1 = 0, f_tail = -1, f_page = 0;
+    if (c.cta < n_items) {
+        const int item = c.cta;
+        const int sp_i = item % a.att_splits;
+        f_kvh = (item / a.att_splits) % a.n_kv_heads;
+        f_m = item / (a.att_splits * a.n_kv_heads);
+        const int n_eff = c.rows[f_m].n_eff;
+        if (sp_i < n_eff) {
+            const int n_pages = c.rows[f_m].pos / MG_PAGE + 1;
+            const int pps = (n_pages + n_eff - 1) / n_eff;
+            f_pg0 = sp_i * pps;
+            f_pg1 = min(n_pages, f_pg0 + pps);
+            f_tail = n_pages - 1;
+            if (f_pg0 + lane < f_pg1) f_page = a.block_table[(size_t)c.rows[f_m].slot * a.max_pages + f_pg0 + lane];
+        }
+    }
     uint32_t ai = 0;
+    auto issue = [&](const uint8_t* kc, const uint8_t* vc, int page, int kvh) {     // lane 0 only
+        const int s = ai % MG_KV_STAGES;
+        if (ai >= MG_KV_STAGES) mg_mbar_wait_idle(&c.kv_empty[s], ((ai / MG_KV_STAGES) & 1) ^ 1, sp, 3);
+        const size_t poff = ((size_t)page * a.n_kv_heads + kvh) * (size_t)page_bytes;
+        mbar_arrive_expect_tx(&c.kv_full[s], 2 * page_bytes);
+        bulk_g2s(stages + (s * 2 + 0) * page_bytes, kc + poff, page_bytes, &c.kv_full[s]);
+        bulk_g2s(stages + (s * 2 + 1) * page_bytes, vc + poff, page_bytes, &c.kv_full[s]);
+    };
 #pragma unroll 1
     for (int l = 0; l < a.n_layers; l++) {
-        cons_kv_bar();                 // the consumers passed the grid barrier behind this layer's KV writes
-        fence_proxy_async_all();       // generic-proxy stores (this token's K/V) -> async-proxy reads below
         const uint8_t* kc = reinterpret_cast<const uint8_t*>(a.layers[l].k_cache);
         const uint8_t* vc = reinterpret_cast<const uint8_t*>(a.layers[l].v_cache);
+        cons_kv_bar();                 // (1) this CTA's qkv phase is over: the staging area is free
+        // first item, pages that do not change in this step: at most one ring-full, so nothing here waits on a consumer
+        int early = 0;
+        {
+            const int cnt = min(min(32, f_pg1 - f_pg0), MG_KV_STAGES);
+            for (int j = 0; j < cnt; j++) {
+                if (f_pg0 + j == f_tail) break;
+                const int page = __shfl_sync(0xffffffffu, f_page, j);
+                if (lane == 0) issue(kc, vc, page, f_kvh);
+                ai++;
+                early++;
+                __syncwarp();
+            }
+        }
+        cons_kv_bar2();                // (2) the grid barrier behind the KV writes has been passed
+        fence_proxy_async_all();       // generic-proxy stores (this step's K/V row) -> async-proxy reads below
         for (int item = c.cta; item < n_items; item += c.G) {
             const int sp_i = item % a.att_splits;
             const int kvh = (item / a.att_splits) % a.n_kv_heads;
@@ -319,19 +394,14 @@ __device__ __noinline__ void kv_producer() {
             const int pps = (n_pages + n_eff - 1) / n_eff;
             const int pg0 = sp_i * pps, pg1 = min(n_pages, pg0 + pps);
             const int* bt = a.block_table + (size_t)c.rows[m].slot * a.max_pages;
-            for (int i0 = pg0; i0 < pg1; i0 += 32) {
-                const int my_page = (i0 + lane < pg1) ? bt[i0 + lane] : 0;
-                const int cnt = min(32, pg1 - i0);
-                for (int j = 0; j < cnt; j++) {
+            const bool first = item == c.cta;
+            for (int base = pg0; base < pg1; base += 32) {
+                const bool cached = first && base == pg0;                 // the window read before the layer loop
+                const int my_page = cached ? f_page : ((base + lane < pg1) ? bt[base + lane] : 0);
+                const int cnt = min(32, pg1 - base);
+                for (int j = cached ? early : 0; j < cnt; j++) {
                     const int page = __shfl_sync(0xffffffffu, my_page, j);
-                    const int s = ai % MG_KV_STAGES;
-                    if (lane == 0) {
-                        if (ai >= MG_KV_STAGES) mg_mbar_wait(&c.kv_empty[s], ((ai / MG_KV_STAGES) & 1) ^ 1, sp, 3);
-                        const size_t poff = ((size_t)page * a.n_kv_heads + kvh) * (size_t)page_bytes;
-                        mbar_arrive_expect_tx(&c.kv_full[s], 2 * page_bytes);
-                        bulk_g2s(stages + (s * 2 + 0) * page_bytes, kc + poff, page_bytes, &c.kv_full[s]);
-                        bulk_g2s(stages + (s * 2 + 1) * page_bytes, vc + poff, page_bytes, &c.kv_full[s]);
-                    }
+                    if (lane == 0) issue(kc, vc, page, kvh);
                     ai++;
                     __syncwarp();
                 }
@@ -384,7 +454,7 @@ DL_DEVINL void q80_block_to_act(const float4 (&v)[8], uint8_t* act, int Ms, int 
 #define MG_ISTAMP(k)                                                                                          \
     do {                                                                                                      \
         if (a.trace != nullptr && blockIdx.x == a.trace_cta && threadIdx.x == 0)                              \
-            a.trace[(size_t)c.rows[0].pad0 * 32 + 16 + (k)] = globaltimer_ns();                               \
+            a.trace[(size_t)c.rows[0].pad0 * 32 + 16 + (k)] = (unsigned long long)clock64();                               \
     } while (0)
 
 DL_DEVINL int mg_rot(int cta, int total, int gran) {
@@ -402,6 +472,7 @@ DL_DEVINL int mg_wrap(int i, int total) { return i >= total ? i - total : i; }
 // src/llm.cpp:185-192).  Ms: row stride of the act slabs (the matmul phase's MT).
 #define MG_PB 4       // float4 chunks per thread and batch in pass 1
 #define MG_XS_STRIDE 9    // float4 per parked block (8 + 1 pad: lane-per-block reads stay bank-conflict free)
+#define MG_MERGERS 16     // CTAs that reduce the ranks' partial sums (each 1/16 of the row) for everybody else
 __device__ __noinline__ void prologue_norm(int Ms, const float* xsrc, float* x_out, const uint8_t* ll, uint32_t epoch,
                                            const float* norm_w) {
     const DlDecodeArgs& a = mg_args();
@@ -415,6 +486,64 @@ __device__ __noinline__ void prologue_norm(int Ms, const float* xsrc, float* x_o
     const int N = (ll != nullptr) ? a.world : 0;
     float4* xs = reinterpret_cast<float4*>(c.act + (size_t)(dim >> 7) * Ms * XQ_ROW_BYTES);     // [M * nblk][9] float4
     const int rot = mg_rot(c.cta, total, 32);              // slot sl of the sweep handles chunk (sl + rot) % total
+    // model weights do not depend on the exchange: start them towards L1 now, pass 2 finds them there
+    if (tid < nblk) asm volatile("prefetch.global.L1 [%0];" ::"l"(norm_w + tid * 32));
+    MG_ISTAMP(0);
+    if (N > 0) {
+        // ---- merge-add, done ONCE per rank: polling the exchange words costs about a cycle per lane and word (8-byte
+        // volatile loads), 16 k lane-loads per CTA with 8 ranks -- 10 us when every CTA did it for itself.  Merger CTA k
+        // reduces blocks [k, k+1) * nb / K of the row(s), writes the merged residual to x_out and releases flag k.
+        const int K = min(MG_MERGERS, c.G);
+        unsigned* flags = a.grid_bar + 16;
+        if (c.cta < K) {
+            const int nb = M * nblk;
+            const int b_lo = (int)((long long)nb * c.cta / K), b_hi = (int)((long long)nb * (c.cta + 1) / K);
+            const size_t sstride = (size_t)MG_MAX_M * nblk * MG_LLW;
+#pragma unroll 1
+            for (int ch = b_lo * 8 + tid; ch < b_hi * 8; ch += MG_CONS) {
+                const int m = ch / cpr, e4 = ch - m * cpr;
+                float4 xv = (xsrc != nullptr) ? __ldcg(reinterpret_cast<const float4*>(xsrc + (size_t)m * dim) + e4)
+                                              : reinterpret_cast<const float4*>(a.embedding + (size_t)c.rows[m].token * dim)[e4];
+                // word (src, m, blk, w) lives at index ((src*4 + m)*nblk + blk)*9 + w; all sources are requested together
+                const unsigned long long* base = reinterpret_cast<const unsigned long long*>(ll) + ((size_t)m * nblk + (e4 >> 3)) * MG_LLW;
+                unsigned long long wd[DL_MAX_PEERS], ws[DL_MAX_PEERS];
+                bool ok;
+                do {
+                    ok = true;
+#pragma unroll
+                    for (int sr = 0; sr < DL_MAX_PEERS; sr++) {
+                        if (sr < N) {
+                            wd[sr] = ld_volatile_u64(base + sr * sstride + (e4 & 7));
+                            ws[sr] = ld_volatile_u64(base + sr * sstride + 8);
+                        }
+                    }
+#pragma unroll
+                    for (int sr = 0; sr < DL_MAX_PEERS; sr++)
+                        if (sr < N) ok = ok && ((uint32_t)(wd[sr] >> 32) == epoch) && ((uint32_t)(ws[sr] >> 32) == epoch);
+                    if (!ok) sp.tick(4);
+                } while (!ok);
+                // the same order on every rank: x + p0 + p1 + ... (bit-identical replicas of the residual stream)
+#pragma unroll
+                for (int sr = 0; sr < DL_MAX_PEERS; sr++) {
+                    if (sr < N) {
+                        const float4 p = ll_dequant4(wd[sr], ws[sr]);
+                        xv.x += p.x; xv.y += p.y; xv.z += p.z; xv.w += p.w;
+                    }
+                }
+                reinterpret_cast<float4*>(x_out + (size_t)m * dim)[e4] = xv;
+            }
+            cons_bar();
+            if (tid == 0) {
+                __threadfence();
+                asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(flags + c.cta), "r"(epoch) : "memory");
+            }
+        }
+        if (tid < K) {
+            while ((int)(ld_acquire_gpu_u32(flags + tid) - epoch) < 0) sp.tick(9);
+        }
+        cons_bar();
+        xsrc = x_out;                                       // everybody reads the merged row
+    }
     float ss[MG_MAX_M];
 #pragma unroll
     for (int m = 0; m < MG_MAX_M; m++) ss[m] = 0.0f;
@@ -428,45 +557,9 @@ __device__ __noinline__ void prologue_norm(int Ms, const float* xsrc, float* x_o
             if (sl < total) {
                 const int ch = mg_wrap(sl + rot, total);
                 const int m = ch / cpr, e4 = ch - m * cpr;
-                // the residual rows are rewritten by another CTA every phase: read them from L2, never from a stale L1 line
+                // the residual rows are rewritten by other CTAs every phase: read them from L2, never from a stale L1 line
                 x4[u] = (xsrc != nullptr) ? __ldcg(reinterpret_cast<const float4*>(xsrc + (size_t)m * dim) + e4)
                                           : reinterpret_cast<const float4*>(a.embedding + (size_t)c.rows[m].token * dim)[e4];
-            }
-        }
-        if (N > 0) {
-            // word (src, m, blk, w) lives at index ((src*4 + m)*nblk + blk)*9 + w; poll until every word carries the epoch
-            const size_t sstride = (size_t)MG_MAX_M * nblk * MG_LLW;
-#pragma unroll 1
-            for (int s = 0; s < N; s++) {
-                unsigned long long wd[MG_PB], ws[MG_PB];
-                bool ok;
-                do {
-                    ok = true;
-#pragma unroll
-                    for (int u = 0; u < MG_PB; u++) {
-                        const int sl = ch0 + u * MG_CONS;
-                        if (sl < total) {
-                            const int ch = mg_wrap(sl + rot, total);
-                            const int m = ch / cpr, e4 = ch - m * cpr;
-                            const unsigned long long* base = reinterpret_cast<const unsigned long long*>(ll) + s * sstride +
-                                                             ((size_t)m * nblk + (e4 >> 3)) * MG_LLW;
-                            wd[u] = ld_volatile_u64(base + (e4 & 7));
-                            ws[u] = ld_volatile_u64(base + 8);
-                        }
-                    }
-#pragma unroll
-                    for (int u = 0; u < MG_PB; u++)
-                        if (ch0 + u * MG_CONS < total) ok = ok && ((uint32_t)(wd[u] >> 32) == epoch) && ((uint32_t)(ws[u] >> 32) == epoch);
-                    if (!ok) sp.tick(4);
-                } while (!ok);
-                sp.reset();
-#pragma unroll
-                for (int u = 0; u < MG_PB; u++) {
-                    if (ch0 + u * MG_CONS < total) {
-                        const float4 p = ll_dequant4(wd[u], ws[u]);
-                        x4[u].x += p.x; x4[u].y += p.y; x4[u].z += p.z; x4[u].w += p.w;
-                    }
-                }
             }
         }
 #pragma unroll
@@ -475,7 +568,7 @@ __device__ __noinline__ void prologue_norm(int Ms, const float* xsrc, float* x_o
             if (sl < total) {
                 const int ch = mg_wrap(sl + rot, total);
                 const int m = ch / cpr, e4 = ch - m * cpr;
-                if (x_out != nullptr) reinterpret_cast<float4*>(x_out + (size_t)m * dim)[e4] = x4[u];
+                if (N == 0 && x_out != nullptr) reinterpret_cast<float4*>(x_out + (size_t)m * dim)[e4] = x4[u];   // layer 0: CTA 0 keeps x
                 xs[(size_t)(m * nblk + (e4 >> 3)) * MG_XS_STRIDE + (e4 & 7)] = x4[u];
                 const float sq = x4[u].x * x4[u].x + x4[u].y * x4[u].y + x4[u].z * x4[u].z + x4[u].w * x4[u].w;
 #pragma unroll
@@ -483,6 +576,7 @@ __device__ __noinline__ void prologue_norm(int Ms, const float* xsrc, float* x_o
             }
         }
     }
+    MG_ISTAMP(1);
     float* ssq_w = c.misc;                // [16 warps][4]
     const int warp = tid >> 5, lane = tid & 31;
 #pragma unroll
@@ -499,6 +593,7 @@ __device__ __noinline__ void prologue_norm(int Ms, const float* xsrc, float* x_o
         for (int w = 0; w < MG_CONS / 32; w++) t += ssq_w[w * MG_MAX_M + m];
         inv[m] = 1.0f / sqrtf(t / (float)dim + a.eps);
     }
+    MG_ISTAMP(2);
 #pragma unroll 1
     for (int b = tid; b < M * nblk; b += MG_CONS) {
         const int m = b / nblk, blk = b - m * nblk;
@@ -517,6 +612,7 @@ __device__ __noinline__ void prologue_norm(int Ms, const float* xsrc, float* x_o
         q80_block_to_act(y, c.act, Ms, m, blk);
     }
     cons_bar();
+    MG_ISTAMP(3);
 }
 
 // ---- prologue 2: merge the attention splits, Q80 -> act slabs (K = q_dim)  (OP_CAST y->yq_slice, src/llm.cpp:296-301)
@@ -576,56 +672,46 @@ __device__ __noinline__ void prologue_att(int Ms, bool merged) {
 }
 
 // ---- prologue 3: hidden activation f32 -> Q80 act slabs (K = hid)  (OP_CAST d->dq, src/llm.cpp:367-374)
-// The rows arrive with ONE bulk async copy into shared memory behind the slabs (a per-thread 128-byte stride over global
-// memory costs 32 line requests per load: 3.6 us measured); then one thread per 32-value block, reading its block in a
-// lane-rotated order so the 128-byte stride is bank-conflict free.
-__device__ __noinline__ void prologue_hidden(int Ms, uint32_t parity) {
+// pass 1: coalesced float4 loads (a per-thread 128-byte stride over global memory costs 32 line requests per load:
+// 3.6 us measured), parked in shared memory behind the slabs with one pad float4 per block; pass 2: one thread per
+// 32-value block.  Plain loads on purpose: a bulk copy would need fence.proxy.async in every thread of the producing
+// epilogue, which showed up as ~2 us of membar stalls per layer.
+__device__ __noinline__ void prologue_hidden(int Ms) {
     const DlDecodeArgs& a = mg_args();
     const MgCtx c;
-    MgSpin sp;
-    sp.init(a.timeout_ns, a.debug);
-    const int M = a.M, nblk = a.hid >> 5, total = M * nblk, tid = c.tid, lane = tid & 31;
+    const int M = a.M, nblk = a.hid >> 5, total = M * nblk, tid = c.tid;
     const size_t slab_bytes = (size_t)(a.hid >> 7) * Ms * XQ_ROW_BYTES;
-    const size_t row_bytes = (size_t)M * a.hid * 4;
-    uint64_t* hbar = reinterpret_cast<uint64_t*>(mg_smem + SM_HBAR);
-    if (slab_bytes + row_bytes <= MG_ACT_BYTES) {
-        float4* stage = reinterpret_cast<float4*>(c.act + slab_bytes);
-        if (tid == 0) {
-            fence_proxy_async_all();                  // h was written with generic stores (other CTAs, before the grid barrier)
-            mbar_arrive_expect_tx(hbar, (uint32_t)row_bytes);
-            for (size_t off = 0; off < row_bytes; off += 32768) {
-                const uint32_t n = (uint32_t)((row_bytes - off < 32768) ? (row_bytes - off) : 32768);
-                bulk_g2s(reinterpret_cast<uint8_t*>(stage) + off, reinterpret_cast<const uint8_t*>(a.h) + off, n, hbar);
+    if (slab_bytes + (size_t)total * MG_XS_STRIDE * 16 <= MG_ACT_BYTES) {
+        float4* xs = reinterpret_cast<float4*>(c.act + slab_bytes);               // [M * nblk][9] float4
+        const int nch = total * 8;                                                // float4 chunks, rows are contiguous
+        const int rot = mg_rot(c.cta, nch, 32);
+        const float4* hp = reinterpret_cast<const float4*>(a.h);
+#pragma unroll 1
+        for (int ch0 = tid; ch0 < nch; ch0 += 8 * MG_CONS) {
+            float4 v[8];
+#pragma unroll
+            for (int u = 0; u < 8; u++) {
+                const int sl = ch0 + u * MG_CONS;
+                if (sl < nch) v[u] = __ldcg(hp + mg_wrap(sl + rot, nch));
+            }
+#pragma unroll
+            for (int u = 0; u < 8; u++) {
+                const int sl = ch0 + u * MG_CONS;
+                if (sl < nch) {
+                    const int ch = mg_wrap(sl + rot, nch);
+                    xs[(size_t)(ch >> 3) * MG_XS_STRIDE + (ch & 7)] = v[u];
+                }
             }
         }
-        mg_mbar_wait(hbar, parity, sp, 8);
+        cons_bar();
 #pragma unroll 1
         for (int b = tid; b < total; b += MG_CONS) {
             const int m = b / nblk, blk = b - m * nblk;
-            const float4* hp = stage + (size_t)b * 8;
-            float4 h4[8];
+            const float4* xb = xs + (size_t)b * MG_XS_STRIDE;
+            float4 y[8];
 #pragma unroll
-            for (int j = 0; j < 8; j++) h4[j] = hp[(j + lane) & 7];           // order inside the block does not matter for amax
-            // quantise with the rotated order: word (j + lane) & 7 of the block
-            float amax = 0.0f;
-#pragma unroll
-            for (int j = 0; j < 8; j++)
-                amax = fmaxf(amax, fmaxf(fmaxf(fabsf(h4[j].x), fabsf(h4[j].y)), fmaxf(fabsf(h4[j].z), fabsf(h4[j].w))));
-            const float d = amax / 127.0f;
-            const float id = (d != 0.0f) ? (1.0f / d) : 0.0f;
-            uint8_t* rowp = c.act + ((size_t)(blk >> 2) * Ms + m) * XQ_ROW_BYTES;
-            const int kb = blk & 3;
-            int sumq = 0;
-#pragma unroll
-            for (int j = 0; j < 8; j++) {
-                const int q0 = __float2int_rn(h4[j].x * id), q1 = __float2int_rn(h4[j].y * id);
-                const int q2 = __float2int_rn(h4[j].z * id), q3 = __float2int_rn(h4[j].w * id);
-                sumq += q0 + q1 + q2 + q3;
-                reinterpret_cast<uint32_t*>(rowp + kb * 32)[(j + lane) & 7] =
-                    (uint32_t)(q0 & 0xff) | ((uint32_t)(q1 & 0xff) << 8) | ((uint32_t)(q2 & 0xff) << 16) | ((uint32_t)(q3 & 0xff) << 24);
-            }
-            reinterpret_cast<float*>(rowp + 128)[kb] = __half2float(__float2half_rn(d));
-            reinterpret_cast<int*>(rowp + 144)[kb] = 8 * sumq;
+            for (int j = 0; j < 8; j++) y[j] = xb[j];
+            q80_block_to_act(y, c.act, Ms, m, blk);
         }
     } else {
         // rows too long for the staging area (several rows of a big model): per-thread global loads
@@ -713,7 +799,6 @@ DL_DEVINL void epi_silu(const DlDecodeArgs& a, const MgCtx& c, int row, int nr) 
         const float hv = (a.act_gelu ? act_gelu(gt) : act_silu(gt)) * up;
         a.h[(size_t)m * a.hid + ((row >> 1) + pr)] = hv;
     }
-    fence_proxy_async_all();          // h is fetched by a bulk copy (async proxy) after the next grid barrier
 }
 
 // unsigned bytes x signed bytes, 32-bit signed accumulate
@@ -767,12 +852,12 @@ DL_DEVINL void epi_logits(const DlDecodeArgs& a, const MgCtx& c, int row, int nr
 // ---- the matmul phase: this CTA's rows of a [d][n] Q40T matrix against the resident act slabs ------------------
 // After each piece out_s[m*128 + local row] holds the f32 products and the phase's epilogue runs on it.
 template <int MT>
-__device__ __noinline__ void gemv_phase(int ph, int layer, uint32_t& it_io, uint32_t epoch) {
+__device__ __noinline__ uint32_t gemv_phase(int ph, int layer, uint32_t it_io, uint32_t epoch) {
     const DlDecodeArgs& a = mg_args();
     const MgCtx c;
     MgSpin sp;
     sp.init(a.timeout_ns, a.debug);
-    const DlDecodeLayer* Lw = a.layers + (ph == PH_CLS ? 0 : layer);
+    const DlDecodeLayer* Lw = c.lay + (layer & 1);          // shared-memory copy (the weight pointers are not used here)
     const MgPhase P = mg_phase(a, Lw, ph);
     const int M = a.M;
     const int KT = P.n >> 7;
@@ -789,89 +874,61 @@ __device__ __noinline__ void gemv_phase(int ph, int layer, uint32_t& it_io, uint
         const int nr = min(128 - r0, R1 - r);
         const int kpack = mg_kpack(nr);
         const int nch = (KT + kpack - 1) / kpack;
-        // Thread -> work: the 128 threads of a group see a stage as up to 128 (k-tile, row) pairs of 4 blocks each.  A
-        // quarter-warp owns ONE k-block index kb and 8 consecutive pairs per step (4 steps of 32 pairs), so the Q80
-        // activations of its k-block sit in registers across the rows instead of being re-read from shared memory for
-        // every row (the broadcast re-reads were most of the shared-memory traffic: the loop ran at ~0.2 us per 9 KB
-        // stage whether the weights came from HBM or were already resident).
-        const int npair = kpack * nr;
-        const int wq = t >> 5, kb = lane >> 3, r8 = lane & 7;
-        // pairs beyond the piece are clamped to its last pair and computed anyway (their sums are dropped): the four
-        // steps stay branch-free, so their loads and dot-product chains overlap
-        int pj[4], plr[4], ppc[4];
-        unsigned pvalid = 0;
+        // Thread -> work: the 128 threads of a group see a stage as up to 128 (k-tile, row) pairs; a thread owns one pair
+        // and walks its 4 blocks.  The loop is bound by instruction issue (measured: its time tracks the instruction
+        // count, not the memory pipeline), so everything here is about instructions per block: the activations of a
+        // block are broadcast loads, the 4 scales of the row come with one 64-bit load, the high nibbles stay in place
+        // (16 * nibble, unsigned bytes; the /16 is applied to their exact integer sum), the dot products accumulate
+        // in the dp4a instructions themselves.
+        const int j = t / nr, lr = t - j * nr;
+        const bool mine = j < kpack;
+        const int rot = (r0 + lr) >> 1;
+        const int pofs = (mine ? t : 0);                           // pair slot inside a stage (idle threads alias pair 0)
+        float acc[MT];
 #pragma unroll
-        for (int i = 0; i < 4; i++) {
-            const int pp = wq * 8 + r8 + 32 * i;
-            if (pp < npair) pvalid |= 1u << i;
-            ppc[i] = min(pp, npair - 1);
-            pj[i] = ppc[i] / nr;
-            plr[i] = ppc[i] - pj[i] * nr;
-        }
-        float acc[4][MT];
-#pragma unroll
-        for (int i = 0; i < 4; i++)
-#pragma unroll
-            for (int m = 0; m < MT; m++) acc[i][m] = 0.0f;
+        for (int m = 0; m < MT; m++) acc[m] = 0.0f;
+        // this group's stages of the piece: it + ci == g (mod 4)   (no loop over the other groups' stages: the skipped
+        // iterations cost more in branch-resolving stalls than a third of the dot-product body, measured with ncu)
 #pragma unroll 1
-        for (int ci = 0; ci < nch; ci++) {
+        for (int ci = (int)(((uint32_t)g - it) & 3u); ci < nch; ci += 4) {
             const uint32_t itc = it + ci;
-            if ((int)(itc & 3u) != g) continue;
             const int s = itc % MG_NS;
-            mg_mbar_wait(&c.full[s], (itc / MG_NS) & 1, sp, 5);
+            if (!(a.dbg & 2)) mg_mbar_wait(&c.full[s], (itc / MG_NS) & 1, sp, 5);       // dbg 2: do not wait for the data (timing probe)
             const uint8_t* st = c.ring + s * Q40T_TILE_BYTES;
-            // one (pair, k-block) against the MT activation rows held in registers
-            auto block = [&](int i, bool live, const int4 (&xl)[MT], const int4 (&xh)[MT], const float (&dx)[MT], const int (&s8)[MT]) {
-                const int pp = ppc[i];
-                const uint4 nb = *reinterpret_cast<const uint4*>(st + pp * 64 + (((kb + ((r0 + plr[i]) >> 1)) & 3) << 4));
-                const float dw = __half2float(*reinterpret_cast<const __half*>(st + Q40T_NIB_BYTES + pp * 8 + kb * 2));
-                // low nibbles as they are; high nibbles stay in place (16 * nibble, unsigned bytes) and the /16 is
-                // applied to their exact integer sum: 8 mask ops instead of 12 mask + shift ops per block
-                const uint32_t lo0 = nb.x & 0x0F0F0F0Fu, hi0 = nb.x & 0xF0F0F0F0u;
-                const uint32_t lo1 = nb.y & 0x0F0F0F0Fu, hi1 = nb.y & 0xF0F0F0F0u;
-                const uint32_t lo2 = nb.z & 0x0F0F0F0Fu, hi2 = nb.z & 0xF0F0F0F0u;
-                const uint32_t lo3 = nb.w & 0x0F0F0F0Fu, hi3 = nb.w & 0xF0F0F0F0u;
+            const int kt = min(ci * kpack + j, KT - 1);            // a short last stage leaves stale slots: computed, dropped
+            const bool live = mine && (ci * kpack + j < KT);
+            if (!(a.dbg & 1)) {
+                const uint8_t* nibp = st + pofs * 64;
+                const uint2 sc2 = *reinterpret_cast<const uint2*>(st + Q40T_NIB_BYTES + pofs * 8);      // 4 fp16 scales
+                const uint8_t* actp = c.act + (size_t)kt * MT * XQ_ROW_BYTES;     // slabs carry MT rows: no row test
+                float accl[MT];
 #pragma unroll
-                for (int m = 0; m < MT; m++) {
-                    int is0 = dp4a_us(lo0, xl[m].x, 0), is1 = dp4a_us(hi0, xh[m].x, 0);
-                    is0 = dp4a_us(lo1, xl[m].y, is0); is1 = dp4a_us(hi1, xh[m].y, is1);
-                    is0 = dp4a_us(lo2, xl[m].z, is0); is1 = dp4a_us(hi2, xh[m].z, is1);
-                    is0 = dp4a_us(lo3, xl[m].w, is0); is1 = dp4a_us(hi3, xh[m].w, is1);
-                    const float term = (float)(is0 + (is1 >> 4) - s8[m]) * (dw * dx[m]);
-                    acc[i][m] = live ? acc[i][m] + term : acc[i][m];
+                for (int m = 0; m < MT; m++) accl[m] = 0.0f;
+#pragma unroll
+                for (int kb = 0; kb < 4; kb++) {
+                    const uint4 nb = *reinterpret_cast<const uint4*>(nibp + (((kb + rot) & 3) << 4));
+                    const uint32_t sw = (kb < 2) ? sc2.x : sc2.y;
+                    const float dw = __half2float(__ushort_as_half((unsigned short)((kb & 1) ? (sw >> 16) : (sw & 0xffffu))));
+                    const uint32_t lo0 = nb.x & 0x0F0F0F0Fu, hi0 = nb.x & 0xF0F0F0F0u;
+                    const uint32_t lo1 = nb.y & 0x0F0F0F0Fu, hi1 = nb.y & 0xF0F0F0F0u;
+                    const uint32_t lo2 = nb.z & 0x0F0F0F0Fu, hi2 = nb.z & 0xF0F0F0F0u;
+                    const uint32_t lo3 = nb.w & 0x0F0F0F0Fu, hi3 = nb.w & 0xF0F0F0F0u;
+#pragma unroll
+                    for (int m = 0; m < MT; m++) {
+                        const uint8_t* xr = actp + m * XQ_ROW_BYTES;
+                        const int4 xl = *reinterpret_cast<const int4*>(xr + kb * 32);
+                        const int4 xh = *reinterpret_cast<const int4*>(xr + kb * 32 + 16);
+                        int is0 = dp4a_us(lo0, xl.x, 0), is1 = dp4a_us(hi0, xh.x, 0);
+                        is0 = dp4a_us(lo1, xl.y, is0); is1 = dp4a_us(hi1, xh.y, is1);
+                        is0 = dp4a_us(lo2, xl.z, is0); is1 = dp4a_us(hi2, xh.z, is1);
+                        is0 = dp4a_us(lo3, xl.w, is0); is1 = dp4a_us(hi3, xh.w, is1);
+                        const float dx = reinterpret_cast<const float*>(xr + 128)[kb];
+                        const int s8 = reinterpret_cast<const int*>(xr + 144)[kb];
+                        accl[m] += (float)(is0 + (is1 >> 4) - s8) * (dw * dx);
+                    }
                 }
-            };
-            // the Q80 activations of (k-tile kt, k-block kb) for the MT rows; slabs are [kt][MT][160], no row test
-            auto load_act = [&](int kt, int4 (&xl)[MT], int4 (&xh)[MT], float (&dx)[MT], int (&s8)[MT]) {
-                const uint8_t* actp = c.act + (size_t)kt * MT * XQ_ROW_BYTES;
 #pragma unroll
-                for (int m = 0; m < MT; m++) {
-                    const uint8_t* xr = actp + m * XQ_ROW_BYTES;
-                    xl[m] = *reinterpret_cast<const int4*>(xr + kb * 32);
-                    xh[m] = *reinterpret_cast<const int4*>(xr + kb * 32 + 16);
-                    dx[m] = reinterpret_cast<const float*>(xr + 128)[kb];
-                    s8[m] = reinterpret_cast<const int*>(xr + 144)[kb];
-                }
-            };
-            if (kpack == 1) {
-                // a stage is one k-tile of up to 128 rows: the activations are loaded once and serve every row
-                int4 xl[MT], xh[MT];
-                float dx[MT];
-                int s8[MT];
-                load_act(ci, xl, xh, dx, s8);
-#pragma unroll
-                for (int i = 0; i < 4; i++) block(i, true, xl, xh, dx, s8);
-            } else {
-                // several k-tiles per stage; the last stage of a piece may hold fewer (their slots are stale: dropped)
-#pragma unroll
-                for (int i = 0; i < 4; i++) {
-                    const int kt = ci * kpack + pj[i];
-                    int4 xl[MT], xh[MT];
-                    float dx[MT];
-                    int s8[MT];
-                    load_act(min(kt, KT - 1), xl, xh, dx, s8);
-                    block(i, kt < KT, xl, xh, dx, s8);
-                }
+                for (int m = 0; m < MT; m++) acc[m] = live ? acc[m] + accl[m] : acc[m];
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(&c.empty[s]);
@@ -879,16 +936,9 @@ __device__ __noinline__ void gemv_phase(int ph, int layer, uint32_t& it_io, uint
         it += nch;
         if (ph == PH_QKV) MG_ISTAMP(5);
         if (ph == PH_W2) MG_ISTAMP(10);
-        // fold the four k-blocks of a pair (the four quarter-warps), then one partial per (group, k-tile, row)
+        if (mine) {
 #pragma unroll
-        for (int i = 0; i < 4; i++) {
-#pragma unroll
-            for (int m = 0; m < MT; m++) {
-                float v = acc[i][m];
-                v += __shfl_xor_sync(0xffffffffu, v, 8);
-                v += __shfl_xor_sync(0xffffffffu, v, 16);
-                if (kb == 0 && ((pvalid >> i) & 1u)) c.red[((g * kpack + pj[i]) * MT + m) * nr + plr[i]] = v;
-            }
+            for (int m = 0; m < MT; m++) c.red[((g * kpack + j) * MT + m) * nr + lr] = acc[m];
         }
         cons_bar();
         // out_s[m][row] = sum of the (group, k-tile) partials: four lanes per output (one per group), fixed order
@@ -923,7 +973,7 @@ __device__ __noinline__ void gemv_phase(int ph, int layer, uint32_t& it_io, uint
         if (ph == PH_W2) MG_ISTAMP(13);
         r += nr;
     }
-    it_io = it;
+    return it;
 }
 
 // =================================================================================================
@@ -946,7 +996,7 @@ DL_DEVINL float warp_transpose_reduce32_m(float (&v)[32], int lane) {
 }
 
 template <int HS, int NCH>
-__device__ __noinline__ void attention_phase(uint32_t& ai_io) {
+__device__ __noinline__ uint32_t attention_phase(uint32_t ai_io) {
     const DlDecodeArgs& a = mg_args();
     constexpr int DPL = HS / 32;
     constexpr int GMAX = NCH * 4;
@@ -1104,7 +1154,7 @@ __device__ __noinline__ void attention_phase(uint32_t& ai_io) {
         }
         cons_bar();
     }
-    ai_io = ai;
+    return ai;
 }
 
 // long contexts (> 4 splits): one warp per (row, head) folds the splits into split slot 0, normalised
@@ -1179,6 +1229,8 @@ __global__ void __launch_bounds__(MG_THREADS, 1) decode_mega_kernel(const __grid
         ri.pad0 = ri.pad1 = ri.pad2 = 0;
         c.rows[tid] = ri;
     }
+    if (tid >= 32 && tid < 48)                               // layer table entry of layer 0 (see the layer loop)
+        reinterpret_cast<uint32_t*>(c.lay)[tid - 32] = reinterpret_cast<const uint32_t*>(a.layers)[tid - 32];
     for (int i = tid; i < a.M * (a.head_size >> 1); i += MG_THREADS) {      // RoPE angles (OP_ROPE_LLAMA, nn-cpu-ops.cpp:1090-1120)
         const int m = i / (a.head_size >> 1), pr = i - m * (a.head_size >> 1);
         float sn, cs;
@@ -1214,29 +1266,35 @@ __global__ void __launch_bounds__(MG_THREADS, 1) decode_mega_kernel(const __grid
 #pragma unroll 1
     for (int l = 0; l < L; l++) {
         MG_STAMP(l, 0);
+        // the consumers take their per-layer pointers from shared memory; the entry of the NEXT layer is fetched now,
+        // a whole layer before it is needed (slot (l + 1) & 1 was last read in layer l - 1, grid barriers ago)
+        if (tid >= 32 && tid < 48 && l + 1 < L)
+            reinterpret_cast<uint32_t*>(c.lay + ((l + 1) & 1))[tid - 32] = reinterpret_cast<const uint32_t*>(a.layers + l + 1)[tid - 32];
         // ---- attention block: norm -> qkv ----
         {
             mg_cta_rows(a.q_dim + 2 * a.kv_dim, c.G, 2, c.cta, R0, R1);
-            float* xo = (c.cta == 0) ? a.x[l == 0 ? 0 : (cur ^ 1)] : nullptr;
-            if (R1 > R0 || xo != nullptr)
+            // layer 0: CTA 0 keeps the embedding rows as x; later layers: the merger CTAs write the merged row for everybody
+            float* xo = (l == 0) ? (c.cta == 0 ? a.x[0] : nullptr) : a.x[cur ^ 1];
+            if (R1 > R0 || c.cta < MG_MERGERS)
                 prologue_norm(MT, l == 0 ? nullptr : a.x[cur], xo, l > 0 ? a.ll_ffn[a.rank] : nullptr,
-                              ebase + 2 * l /* w2 of layer l-1 */, a.layers[l].rms_att);
+                              ebase + 2 * l /* w2 of layer l-1 */, c.lay[l & 1].rms_att);
             if (l > 0) cur ^= 1;
         }
         MG_STAMP(l, 1);
-        gemv_phase<MT>(PH_QKV, l, it, 0u);
+        it = gemv_phase<MT>(PH_QKV, l, it, 0u);
         MG_STAMP(l, 2);
+        cons_kv_bar();                 // the staging area is free: the KV warp starts on the pages this step does not write
         grid_sync(a.grid_bar, c.G, nbar, sp);
         MG_STAMP(l, 3);
         // ---- attention ----
-        cons_kv_bar();
+        cons_kv_bar2();
         switch (att_sel) {
-            case 32 * 8 + 1: attention_phase<32, 1>(ai); break;
-            case 32 * 8 + 2: attention_phase<32, 2>(ai); break;
-            case 64 * 8 + 1: attention_phase<64, 1>(ai); break;
-            case 64 * 8 + 2: attention_phase<64, 2>(ai); break;
-            case 128 * 8 + 1: attention_phase<128, 1>(ai); break;
-            default: attention_phase<128, 2>(ai); break;
+            case 32 * 8 + 1: ai = attention_phase<32, 1>(ai); break;
+            case 32 * 8 + 2: ai = attention_phase<32, 2>(ai); break;
+            case 64 * 8 + 1: ai = attention_phase<64, 1>(ai); break;
+            case 64 * 8 + 2: ai = attention_phase<64, 2>(ai); break;
+            case 128 * 8 + 1: ai = attention_phase<128, 1>(ai); break;
+            default: ai = attention_phase<128, 2>(ai); break;
         }
         MG_STAMP(l, 4);
         grid_sync(a.grid_bar, c.G, nbar, sp);
@@ -1249,35 +1307,35 @@ __global__ void __launch_bounds__(MG_THREADS, 1) decode_mega_kernel(const __grid
         mg_cta_rows(a.dim, c.G, 32, c.cta, R0, R1);
         if (R1 > R0) prologue_att(MT, coop);
         MG_STAMP(l, 6);
-        gemv_phase<MT>(PH_WO, l, it, ebase + 2 * l + 1);
+        it = gemv_phase<MT>(PH_WO, l, it, ebase + 2 * l + 1);
         MG_STAMP(l, 7);
         MG_STAMP(l, 8);
         // ---- feed-forward block: norm -> w1|w3 ----
         {
             mg_cta_rows(2 * a.hid, c.G, 2, c.cta, R0, R1);
-            float* xo = (c.cta == 0) ? a.x[cur ^ 1] : nullptr;
-            if (R1 > R0 || xo != nullptr)
-                prologue_norm(MT, a.x[cur], xo, a.ll_att[a.rank], ebase + 2 * l + 1, a.layers[l].rms_ffn);
+            float* xo = a.x[cur ^ 1];
+            if (R1 > R0 || c.cta < MG_MERGERS)
+                prologue_norm(MT, a.x[cur], xo, a.ll_att[a.rank], ebase + 2 * l + 1, c.lay[l & 1].rms_ffn);
             cur ^= 1;
         }
         MG_STAMP(l, 9);
-        gemv_phase<MT>(PH_W13, l, it, 0u);
+        it = gemv_phase<MT>(PH_W13, l, it, 0u);
         MG_STAMP(l, 10);
         grid_sync(a.grid_bar, c.G, nbar, sp);
         MG_STAMP(l, 11);
         // ---- w2 ----
         mg_cta_rows(a.dim, c.G, 32, c.cta, R0, R1);
-        if (R1 > R0) prologue_hidden(MT, (uint32_t)(l & 1));
+        if (R1 > R0) prologue_hidden(MT);
         MG_STAMP(l, 12);
-        gemv_phase<MT>(PH_W2, l, it, ebase + 2 * l + 2);
+        it = gemv_phase<MT>(PH_W2, l, it, ebase + 2 * l + 2);
         MG_STAMP(l, 13);
         MG_STAMP(l, 14);
     }
 
     // ---- final norm -> logits (OP_MATMUL wcls + logits gather, src/llm.cpp:394-432) ----
     mg_cta_rows(a.vocab_loc, c.G, 2, c.cta, R0, R1);
-    if (R1 > R0) prologue_norm(MT, a.x[cur], nullptr, a.ll_ffn[a.rank], ebase + 2 * L, a.rms_final);
-    gemv_phase<MT>(PH_CLS, 0, it, 0u);
+    if (R1 > R0 || c.cta < MG_MERGERS) prologue_norm(MT, a.x[cur], a.x[cur ^ 1], a.ll_ffn[a.rank], ebase + 2 * L, a.rms_final);
+    it = gemv_phase<MT>(PH_CLS, 0, it, 0u);
     MG_STAMP(L, 1);
     if (a.greedy) {
         // CTA candidates -> global; CTA 0 reduces them, exchanges the per-rank winners as LL words, picks the token

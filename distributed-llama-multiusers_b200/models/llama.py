@@ -105,9 +105,15 @@ class LlamaEngine:
         self.max_rows = max_rows
         self.use_pdl, self.use_graphs = use_pdl, use_graphs
         self.sync_q80 = sync_q80
-        # decode batches of <= 4 rows run as ONE persistent cooperative kernel (csrc/cuda/decode_mega.cu) instead of
-        # the launch sequence below; DLLAMA_MEGA=0 / use_mega=False keeps the multi-kernel path (comparison, debugging)
-        self.use_mega = (os.environ.get("DLLAMA_MEGA", "1") != "0") if use_mega is None else bool(use_mega)
+        # Decode batches of <= 4 rows can run as ONE persistent cooperative kernel (csrc/cuda/decode_mega.cu) instead of the
+        # launch sequence below.  Measured on 8B single-stream decode (tok/s, launch sequence vs persistent kernel):
+        # 1 GPU 592 / 477, 2 GPUs 628 / 573, 4 GPUs 573 / 586, 8 GPUs 463 / 517 -- a step is a chain of ~8 grid-wide
+        # hand-offs per layer either way; the persistent kernel wins where the launch sequence's fence + counter + flag
+        # exchange dominates.  Default: on for world >= 4.  DLLAMA_MEGA=1 / 0 or use_mega=True / False force it.
+        env_mega = os.environ.get("DLLAMA_MEGA", "auto")
+        if use_mega is None:
+            use_mega = (world >= 4) if env_mega == "auto" else (env_mega != "0")
+        self.use_mega = bool(use_mega)
         self.seq_len = min(h.seq_len, max_seq_len)
         self.n_sms = K.cuda_lib().dl_device_sm_count()
         dev = self.device
@@ -269,7 +275,7 @@ class LlamaEngine:
         self._mega_att_o = torch.zeros(R4 * self.n_heads_loc * self.max_splits * self.hs, dtype=torch.float32, device=dev)
         self._mega_att_ml = torch.zeros(R4 * self.n_heads_loc * self.max_splits * 2, dtype=torch.float32, device=dev)
         self._mega_best = torch.zeros(self.mega_grid * R4 * 2, dtype=torch.float32, device=dev)
-        self._mega_bar = torch.zeros(2, dtype=torch.int64, device=dev)
+        self._mega_bar = torch.zeros(64, dtype=torch.int32, device=dev)     # barrier words [0, 2), merger flags [16, 32)
         self._mega_out = torch.zeros(R4, dtype=torch.int32, device=dev)
         # a time-out inside the kernel traps (the context is lost); the reason is left in mapped host memory
         self._mega_debug = torch.zeros(16, dtype=torch.int32).pin_memory()
@@ -320,6 +326,7 @@ class LlamaEngine:
         a.trace = self._mega_trace.data_ptr() if self._mega_trace is not None else None
         a.trace_cta = self._mega_trace_cta
         a.pf_dist = self._mega_pf_dist
+        a.dbg = int(os.environ.get("DLLAMA_MEGA_DBG", "0"))
         return a
 
     def _mega_usable(self, M: int, chunk: bool) -> bool:

@@ -127,6 +127,7 @@ class DlDecodeArgs(C.Structure):
         ("debug", C.c_void_p),
         ("trace", C.c_void_p),
         ("trace_cta", C.c_int),
+        ("dbg", C.c_int),
         ("pf_dist", C.c_int),
     ]
 

@@ -224,7 +224,8 @@ typedef struct {
     int max_splits;                   /* capacity of the split dimension above (<= 32) */
     int att_splits;                   /* split-KV grid: CTAs per (row, kv head) */
     float* cta_best;                  /* [grid][4][2] greedy candidates */
-    unsigned* grid_bar;               /* two zero-initialised words: arrival counter, exit counter (the kernel leaves them at zero) */
+    unsigned* grid_bar;               /* 64 zero-initialised words: [0] arrival counter, [1] exit counter (left at zero by the
+                                       * kernel), [16, 32) release flags of the merge-add CTAs (epochs, only grow) */
     uint32_t* step_counter;
     /* tensor-parallel exchange: rank p's buffers as mapped into this process (p < world) */
     uint8_t* ll_att[DL_MAX_PEERS];    /* [world src][4][dim/32][9] 8-byte LL words */
@@ -243,6 +244,7 @@ typedef struct {
                                        * is stored there before a time-out trap (device memory is lost with the context) */
     unsigned long long* trace;        /* NULL or [n_layers * 32 + 32] globaltimer stamps of CTA trace_cta */
     int trace_cta;
+    int dbg;                          /* timing probes (results are garbage): 1 = matmul phases skip the arithmetic, 2 = they do not wait for the weights */
     int pf_dist;                      /* pipeline chunks (<= 9 KB) the L2 prefetch of the weight stream runs ahead of the
                                        * shared-memory ring; 0 = no L2 prefetch */
 } DlDecodeArgs;

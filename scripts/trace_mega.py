@@ -53,6 +53,16 @@ def main():
         if world > 1:
             dist.barrier()
         t = eng.mega_trace_ns()
+        if world > 1:          # one line per rank: who waits in the exchange, who is waited for
+            Lr = eng.h.n_layers
+            ia = np.array([[t[l * 32 + 16 + k] for k in range(4)] for l in range(1, Lr)], dtype=np.float64)
+            mine = (rank, float(np.median(ia[:, 1] - ia[:, 0])) / 1.9e3, float(np.median([t[l * 32 + 1] - t[l * 32] for l in range(1, Lr)])) / 1e3,
+                    float(np.median([t[l * 32 + 9] - t[l * 32 + 8] for l in range(1, Lr)])) / 1e3, float(t[Lr * 32 + 2] - t[0]) / 1e3)
+            allr = [None] * world
+            dist.all_gather_object(allr, mine)
+            if rank == 0:
+                for r_, mp, n1, n2, tot in allr:
+                    print(f"  rank {r_}: ffn-norm merge pass {mp:6.2f} us | att norm prologue {n1:6.2f} | ffn norm prologue {n2:6.2f} | kernel {tot:8.1f} us")
         if rank != 0:
             continue
         per = np.zeros((L, 14))
@@ -68,15 +78,14 @@ def main():
         print(f"  logits phase           {(t[L * 32 + 1] - t[(L - 1) * 32 + 14]) / 1e3:7.2f}   final barrier {(t[L * 32 + 2] - t[L * 32 + 1]) / 1e3:.2f}")
         print(f"  whole kernel           {(t[L * 32 + 2] - t[0]) / 1e3:7.2f}")
         if a.intra:
+            ghz = 1.9          # intra-phase stamps are SM clocks (sub-us resolution; the global timer ticks every 256 ns)
+
             def d(i, j):
-                return float(np.median(intra[1:, j] - intra[1:, i])) / 1e3
-            l11 = np.array([t[l * 32 + 11] for l in range(L)])
-            l1 = np.array([t[l * 32 + 1] for l in range(L)])
-            print("  -- inside prologue_hidden: call overhead %.2f | loads %.2f | quantise+store %.2f | bar %.2f" %
-                  (float(np.median(intra[1:, 0] - l11[1:])) / 1e3, d(0, 1), d(1, 2), d(2, 3)))
-            print("  -- inside qkv gemv: entry %.2f | chunk loop %.2f | reduce %.2f | epilogue %.2f | bar %.2f" %
-                  (float(np.median(intra[1:, 4] - l1[1:])) / 1e3, d(4, 5), d(5, 6), d(6, 7), d(7, 8)))
-            print("  -- inside w2 gemv:  chunk loop %.2f | reduce %.2f | epilogue %.2f | bar %.2f" % (d(9, 10), d(10, 11), d(11, 12), d(12, 13)))
+                return float(np.median(intra[1:, j] - intra[1:, i])) / (ghz * 1e3)
+            print("  -- inside ffn prologue_norm: merge pass (x + exchange words) %.2f | sum of squares + bar %.2f | normalise + quantise %.2f" %
+                  (d(0, 1), d(1, 2), d(2, 3)))
+            print("  -- inside qkv gemv: stage loop %.2f | reduce %.2f | epilogue %.2f | bar %.2f" % (d(4, 5), d(5, 6), d(6, 7), d(7, 8)))
+            print("  -- inside w2 gemv:  stage loop %.2f | reduce %.2f | epilogue %.2f | bar %.2f" % (d(9, 10), d(10, 11), d(11, 12), d(12, 13)))
     eng.close()
     if world > 1:
         dist.barrier()
