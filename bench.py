@@ -40,10 +40,11 @@ def parse_args():
     ap.add_argument("--layers", type=int, default=0, help="debug only: override layer count (invalid as a bench)")
     ap.add_argument("--prompt-len", type=int, default=128)
     ap.add_argument("--prefill-chunk", type=int, default=256, help="rows per prefill forward (engine max_rows)")
-    ap.add_argument("--b2-cache", type=int, default=0, help="nccl_cublas arm: keep bf16 copies of the weights (1) or dequantise per call (0)")
+    ap.add_argument("--b2-cache", type=int, default=1, help="nccl_cublas arm: keep bf16 copies of the weights (1) or dequantise per call (0)")
+    ap.add_argument("--b2-graph", type=int, default=1, help="nccl_cublas arm: replay the decode step from a CUDA graph with the argmax on the device (1) or run eagerly (0)")
     ap.add_argument("--no-pdl", action="store_true")
     ap.add_argument("--no-graphs", action="store_true")
-    ap.add_argument("--users", type=int, default=0, help="also measure an N-user batched decode (extra key)")
+    ap.add_argument("--users", type=int, default=32, help="also measure an N-user batched decode (key multi_user; 0 = skip)")
     ap.add_argument("--model-dir", default=os.environ.get("DLLAMA_MODEL_DIR", "/dev/shm"))
     ap.add_argument("--nthreads", type=int, default=0, help="reference arm: threads per node (0 = auto)")
     return ap.parse_args()
@@ -140,10 +141,10 @@ def run_b200(args):
     # ---------------- device-timed: K graph replays of the decode step ----------------
     eng.ensure_capacity(slot, pos + W + K_ + 1)
     eng.set_batch([tok], [pos], [slot])
-    eng.decode_greedy_device(W, 1)
-    barrier()
     sampler = ClockSampler(torch.cuda.current_device())
     sampler.start()
+    eng.decode_greedy_device(W, 1)
+    barrier()
     n0 = lib.launch_count
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
@@ -152,28 +153,45 @@ def run_b200(args):
     barrier()
     launches = lib.launch_count - n0
     dev_ms = ev0.elapsed_time(ev1)
-    pos += W + K_
+    # (the first use of a batch shape runs one untimed, uncaptured forward before the graph: count back from the end)
+    tokens_dev = eng.read_history(W + K_, 1, eng.current_step() - (W + K_))[:, 0].tolist()
 
-    # ---------------- end to end through the public API ----------------
-    tok_host = int(eng.tokens[0].item())
-    for _ in range(min(W, 4)):
-        tok_host = eng.decode_greedy_host([tok_host], [pos], [slot])[0]
-        pos += 1
-    eng.ensure_capacity(slot, pos + K_ + 1)
+    # ---------------- end to end through the public API, on a second sequence with the same prompt ----------------
+    # every step: pinned-host descriptor -> device, forward, device argmax, token id -> host.  Starting from the same
+    # prompt the host loop must reproduce the tokens of the device-resident loop exactly (same kernels, greedy).
+    slot2 = eng.alloc_slot()
+    logits2 = eng.prefill(slot2, prompt, 0)
+    tok_host = int(torch.argmax(logits2[0]))
+    pos2 = len(prompt)
+    eng.ensure_capacity(slot2, pos2 + W + K_ + 1)
+    tokens_host = []
+    for _ in range(W):
+        tok_host = eng.decode_greedy_host([tok_host], [pos2], [slot2])[0]
+        tokens_host.append(tok_host)
+        pos2 += 1
     barrier()
     t0 = time.perf_counter()
     for _ in range(K_):
-        tok_host = eng.decode_greedy_host([tok_host], [pos], [slot])[0]
-        pos += 1
+        tok_host = eng.decode_greedy_host([tok_host], [pos2], [slot2])[0]
+        tokens_host.append(tok_host)
+        pos2 += 1
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
     barrier()
-    clocks = sampler.stop()
+    tokens_match = tokens_host == tokens_dev
+    if not tokens_match:
+        bad = next(i for i, (x, y) in enumerate(zip(tokens_host, tokens_dev)) if x != y)
+        raise SystemExit(f"[bench] device-resident loop and host loop disagree at step {bad}: {tokens_dev[bad]} vs {tokens_host[bad]}")
+    eng.free_slot(slot2)
+    pos += W + K_
 
     t = torch.tensor([dev_ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     dev_ms, e2e_ms = float(t[0]), float(t[1])
+    ttft = bench_ttft(eng, args, barrier, world, dist, prompt)
+    multi = bench_users(eng, args, barrier, world, dist) if args.users > 1 else None
+    clocks = sampler.stop()
     ms_per_step = dev_ms / K_
     value = 1000.0 / ms_per_step
     wbytes = eng.weight_bytes()
@@ -200,11 +218,13 @@ def run_b200(args):
         "roofline": {"weight_bytes_per_gpu_per_step": wbytes, "hbm_gbs_measured": hbm,
                      "hbm_floor_ms": round(wbytes / (hbm * 1e9) * 1e3, 4),
                      "achieved_fraction_of_measured_hbm": round(wbytes / (hbm * 1e9) * 1e3 / ms_per_step, 4)},
-        "ttft": bench_ttft(eng, args, barrier, world, dist, prompt),
+        "tokens_match_host_loop": tokens_match,
+        "persistent_kernel": bool(eng.use_mega),
+        "ttft": ttft,
         "impl": "b200",
     }
-    if args.users > 1:
-        result["multi_user"] = bench_users(eng, args, barrier, world, dist)
+    if multi is not None:
+        result["multi_user"] = multi
     if rank == 0:
         print(json.dumps(result), flush=True)
     eng.close()
@@ -293,17 +313,27 @@ def run_nccl_cublas(args):
     prompt = rng.integers(1, eng.h.vocab_size, args.prompt_len).tolist()
     lg = eng.forward(prompt, 0)
     tok, pos = int(lg[-1].argmax()), len(prompt)
-    for _ in range(W):
-        tok = int(eng.forward([tok], pos)[0].argmax())
-        pos += 1
+    use_graph = bool(args.b2_graph)
+    if use_graph:
+        # one CUDA graph per step, greedy pick on the device: the honest form of "NCCL + cuBLAS"
+        eng.start_graph_decode(tok, pos)
+        for _ in range(W):
+            eng.graph_step()
+    else:
+        for _ in range(W):
+            tok = int(eng.forward([tok], pos)[0].argmax())
+            pos += 1
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
     for _ in range(K_):
-        tok = int(eng.forward([tok], pos)[0].argmax())
-        pos += 1
+        if use_graph:
+            eng.graph_step()
+        else:
+            tok = int(eng.forward([tok], pos)[0].argmax())
+            pos += 1
     ev1.record()
     torch.cuda.synchronize()
     t = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device="cuda")
@@ -313,7 +343,7 @@ def run_nccl_cublas(args):
     if rank == 0:
         print(json.dumps({"metric": METRIC, "value": round(1000.0 / ms, 2), "unit": "tokens/s", "n_gpus": world,
                           "steps": K_, "warmup": W, "ms_per_step": round(ms, 4), "higher_is_better": True,
-                          "scaling": "strong", "vs_baseline": None, "dtype": "bf16 cuBLAS on dequantised Q40 (%s), NCCL all-reduce" % ("bf16 copies cached in HBM" if args.b2_cache else "dequantised on every call"),
+                          "scaling": "strong", "vs_baseline": None, "dtype": "bf16 cuBLAS on dequantised Q40 (%s), NCCL all-reduce, %s" % ("bf16 copies cached in HBM" if args.b2_cache else "dequantised on every call", "one CUDA graph per step, device argmax" if use_graph else "eager, host argmax"),
                           "data": "synthetic", "impl": "nccl_cublas",
                           "config": {"model": args.model, "global_batch": 1, "parallelism": f"tp{world}"}}), flush=True)
     eng.close()

@@ -109,5 +109,74 @@ class NcclCublasEngine:
             lg = torch.cat(out, dim=-1)
         return lg
 
+    # ---------------------------------------------------------------------------------------------------
+    # The strongest form of this baseline: ONE CUDA graph per decode step, greedy pick on the device, no host
+    # round trip per token (bench.py --impl nccl_cublas --b2-graph 1).  Same math as forward() for one row.
+    # ---------------------------------------------------------------------------------------------------
+    @torch.no_grad()
+    def _step_static(self):
+        c, h = self.core, self.h
+        pos = self.s_pos                                            # [1] int64, device
+        x = c.embedding[self.s_tok]                                 # [1, dim]
+        G = c.n_heads_loc // c.n_kv_loc
+        S = self.seq_len
+        mask = torch.arange(S, device=self.device)[None, :] > pos[:, None]            # [1, S]
+        for l, W in enumerate(c.layers):
+            y = self._rms(x, W["rms_att"])
+            qkv = self._mm(y, W["qkv"], c.qkv_d, h.dim)
+            q = self._rope(qkv[:, :c.q_loc], pos)
+            k = self._rope(qkv[:, c.q_loc:c.q_loc + c.kv_loc], pos)
+            v = qkv[:, c.q_loc + c.kv_loc:]
+            self.k_cache[l].index_copy_(0, pos, k.reshape(1, c.n_kv_loc, c.hs))
+            self.v_cache[l].index_copy_(0, pos, v.reshape(1, c.n_kv_loc, c.hs))
+            kk = self.k_cache[l].repeat_interleave(G, dim=1)          # whole cache, masked beyond pos
+            vv = self.v_cache[l].repeat_interleave(G, dim=1)
+            qh = q.reshape(1, c.n_heads_loc, c.hs)
+            sc = torch.einsum("thd,shd->hts", qh, kk) / math.sqrt(c.hs)
+            sc = sc.masked_fill(mask[None], float("-inf"))
+            att = torch.einsum("hts,shd->thd", torch.softmax(sc, dim=-1), vv).reshape(1, c.q_loc)
+            part = q80_rt(self._mm(att, W["wo"], h.dim, c.q_loc))
+            if self.world > 1:
+                dist.all_reduce(part)
+            x = x + part
+            y = self._rms(x, W["rms_ffn"])
+            gu = self._mm(y, W["w13"], 2 * c.hid_loc, h.dim)
+            g, u = gu[:, 0::2], gu[:, 1::2]
+            part = q80_rt(self._mm(torch.nn.functional.silu(g) * u, W["w2"], h.dim, c.hid_loc))
+            if self.world > 1:
+                dist.all_reduce(part)
+            x = x + part
+        y = self._rms(x, c.rms_final)
+        lg = self._mm(y, c.wcls, c.vocab_loc, h.dim)
+        if self.world > 1:
+            dist.all_gather_into_tensor(self.s_logits, lg.contiguous())
+            lg = self.s_logits.reshape(self.world, -1).reshape(1, -1)
+        self.s_tok.copy_(torch.argmax(lg, dim=-1))
+        self.s_pos.add_(1)
+
+    def start_graph_decode(self, token: int, pos: int):
+        """Capture the decode step (weights must be cached: --b2-cache 1) and position it at (token, pos)."""
+        self.s_tok = torch.tensor([token], dtype=torch.long, device=self.device)
+        self.s_pos = torch.tensor([pos], dtype=torch.long, device=self.device)
+        self.s_logits = torch.empty(self.world * self.core.vocab_loc, dtype=torch.float32, device=self.device)
+        st = torch.cuda.Stream(device=self.device)
+        st.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(st):
+            for _ in range(2):                                      # warm-up: cuBLAS handles, NCCL channels, weight cache
+                self._step_static()
+        torch.cuda.current_stream().wait_stream(st)
+        torch.cuda.synchronize()
+        self.s_tok.fill_(token)
+        self.s_pos.fill_(pos)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph, stream=st):
+            self._step_static()
+        self.s_tok.fill_(token)
+        self.s_pos.fill_(pos)
+        torch.cuda.synchronize()
+
+    def graph_step(self):
+        self.graph.replay()
+
     def close(self):
         self.core.close()

@@ -132,13 +132,15 @@ def test_gemv_q80_roundtrip_epilogue():
     np.testing.assert_allclose(got, ref_rt, rtol=0, atol=scale / 127.0 * 1.01)
 
 
-def _gemm_case(d, n, M, S, seed=0):
+def _gemm_case(d, n, M, S, seed=0, ncap_override=0):
     k = K()
     raw, wdq = _rand_q40(d, n, seed)
     w = k.make_q40t(torch.from_numpy(raw).cuda(), d, n)
     rng = np.random.default_rng(seed + 1)
     x = rng.standard_normal((M, n), dtype=np.float32)
     ncap = 16 if M <= 16 else 32 if M <= 32 else 64 if M <= 64 else (M + 127) // 128 * 128
+    if ncap_override:
+        ncap = ncap_override
     xh = k.alloc_xh(n, ncap, "cuda")
     k.quant_q80(torch.from_numpy(x).cuda(), M, n, ncap, None, xh)
     ref = quant.q80_roundtrip(x).astype(np.float64) @ wdq.astype(np.float64).T
@@ -160,6 +162,96 @@ def test_gemm_q40_tc_matches_reference(d, n, M, S):
     scale = np.abs(ref).max()
     # fp16 rounding of (nibble-8)*d and q*d: ~2^-11 relative per operand, random over K
     np.testing.assert_allclose(got, ref, rtol=2e-3, atol=2e-3 * scale)
+
+
+def _tc_tile(d, M, S, ncap, n_sms=148):
+    """The activation tile width dl_gemm_q40_tc picks (mirror of gemm_q40_tc.cu:388-396), so the wide-tile tests
+    below fail loudly if a change of the heuristic stops exercising the plans they are meant to cover."""
+    row_tiles = (d + 127) // 128
+    nt = 16 if M <= 16 else 32 if M <= 32 else 64 if M <= 64 else 128
+    if M > 128 and ncap % 256 == 0 and row_tiles * ((M + 255) // 256) * S >= n_sms // 2:
+        nt = 256
+    while nt > 32 and row_tiles * ((M + nt - 1) // nt) * S < n_sms // 2:
+        nt >>= 1
+    return nt
+
+
+@pytest.mark.parametrize("d,n,M,S,ncap,want_nt", [
+    (9600, 1024, 64, 1, 64, 64), (9600, 1024, 50, 1, 64, 64), (9600, 1024, 128, 1, 128, 128), (9600, 1024, 100, 2, 128, 128),
+    (9600, 1024, 256, 1, 256, 256), (9600, 1024, 300, 1, 512, 256), (4864, 1024, 256, 2, 256, 256), (9600, 512, 200, 1, 256, 256),
+])
+def test_gemm_q40_tc_wide_tiles(d, n, M, S, ncap, want_nt):
+    """The prefill configurations: 64-, 128- and 256-wide activation tiles (different stage counts, accumulator
+    counts, TMEM column maps and the chunked 256-wide epilogue) at shapes that really select them."""
+    sms = torch.cuda.get_device_properties(0).multi_processor_count
+    assert _tc_tile(d, M, S, ncap, sms) == want_nt, "the tile heuristic changed: pick shapes that select this tile again"
+    got, ref = _gemm_case(d, n, M, S, seed=d + n + M, ncap_override=ncap)
+    assert not np.isnan(got).any()
+    scale = np.abs(ref).max()
+    np.testing.assert_allclose(got, ref, rtol=2e-3, atol=2e-3 * scale)
+
+
+@pytest.mark.parametrize("M,ncap,want_nt", [(64, 64, 64), (128, 128, 128), (256, 256, 256)])
+def test_wide_tile_epilogues(M, ncap, want_nt):
+    """SiLU*mul -> Q80 slabs and RoPE + q / paged-KV write through the wide tensor-core tiles (the TTFT path)."""
+    k = K()
+    from dllama_b200.formats.mfile import LlmHeader
+    from dllama_b200.models.oracle import apply_rope, rope_frequencies
+    sms = torch.cuda.get_device_properties(0).multi_processor_count
+    dim = 512
+    rng = np.random.default_rng(100 + M)
+    x = rng.standard_normal((M, dim), dtype=np.float32) * 2
+    xdq = quant.q80_roundtrip(x)
+    xh = k.alloc_xh(dim, ncap, "cuda")
+    k.quant_q80(torch.from_numpy(x).cuda(), M, dim, ncap, None, xh)
+    # ---- SiLU * mul: 2 * hid rows interleaved (gate, up) ----
+    hid = 4864                                       # 2 * hid = 76 row tiles; a multiple of 128 (XH slabs are per k-tile)
+    assert _tc_tile(2 * hid, M, 1, ncap, sms) == want_nt
+    raw1, w1 = _rand_q40(hid, dim, 31)
+    raw3, w3 = _rand_q40(hid, dim, 32)
+    w = torch.zeros(k.q40t_bytes(2 * hid, dim), dtype=torch.uint8, device="cuda")
+    k.q40_repack(torch.from_numpy(raw1).cuda(), hid, dim, w, 2 * hid, 0, 2)
+    k.q40_repack(torch.from_numpy(raw3).cuda(), hid, dim, w, 2 * hid, 1, 2)
+    g, u = xdq @ w1.T, xdq @ w3.T
+    ref = quant.q80_roundtrip((g / (1 + np.exp(-g)) * u).astype(np.float32))
+    out = k.alloc_xh(hid, ncap, "cuda")
+    k.gemm_q40_tc(w, 2 * hid, dim, xh, ncap, M, k.epi_silu_mul(None, out, ncap), 1)
+    torch.cuda.synchronize()
+    got = _decode_xh(out, hid, ncap, M)
+    amax = np.abs(ref).max()
+    np.testing.assert_allclose(got, ref, rtol=0, atol=amax / 127 * 1.01 + 5e-3 * amax)
+    # ---- RoPE + q store + paged KV write ----
+    hs, n_heads, n_kv = 128, 59, 8                  # q_dim 7552 + 2 * 1024 = 9600 rows: 75 row tiles
+    q_dim, kv_dim = n_heads * hs, n_kv * hs
+    d = q_dim + 2 * kv_dim
+    assert _tc_tile(d, M, 1, ncap, sms) == want_nt
+    h = LlmHeader(dim=q_dim, n_heads=n_heads, n_kv_heads=n_kv, rope_theta=500000.0, rope_type=2, rope_scaling_factor=8.0,
+                  rope_scaling_low_freq_factor=1.0, rope_scaling_high_freq_factor=4.0, rope_scaling_orig_max_seq_len=8192)
+    freqs = rope_frequencies(h)
+    raw, wdq = _rand_q40(d, dim, 33)
+    wq = k.make_q40t(torch.from_numpy(raw).cuda(), d, dim)
+    y = torch.from_numpy(xdq @ wdq.T)
+    positions = (np.arange(M) * 3 + 5).tolist()
+    pos = torch.tensor(positions, dtype=torch.int32)
+    q_ref = apply_rope(y[:, :q_dim], pos, freqs, hs)
+    k_ref = apply_rope(y[:, q_dim:q_dim + kv_dim], pos, freqs, hs)
+    v_ref = y[:, q_dim + kv_dim:]
+    max_pages = (max(positions) + 32) // 32
+    bt = torch.arange(max_pages, dtype=torch.int32).flip(0).reshape(1, max_pages).contiguous()        # one sequence, pages reversed
+    Kc = torch.zeros(max_pages, n_kv, 32, hs, dtype=torch.float16, device="cuda")
+    Vc = torch.zeros_like(Kc)
+    q_out = torch.zeros(M, q_dim, device="cuda")
+    epi = k.epi_qkv_rope(q_out, q_dim, kv_dim, hs, freqs.cuda(), pos.cuda(), torch.zeros(M, dtype=torch.int32, device="cuda"),
+                         bt.cuda(), max_pages, n_kv, Kc, Vc)
+    k.gemm_q40_tc(wq, d, dim, xh, ncap, M, epi, 1)
+    torch.cuda.synchronize()
+    sc = float(np.abs(q_ref.numpy()).max())
+    np.testing.assert_allclose(q_out.cpu().numpy(), q_ref.numpy(), rtol=4e-3, atol=4e-3 * sc)
+    for m in (0, 1, M // 2, M - 1):
+        p = positions[m]
+        page = int(bt[0, p // 32])
+        np.testing.assert_allclose(Kc[page, :, p % 32, :].float().cpu().numpy().reshape(-1), k_ref[m].numpy(), rtol=6e-3, atol=6e-3 * sc)
+        np.testing.assert_allclose(Vc[page, :, p % 32, :].float().cpu().numpy().reshape(-1), v_ref[m].numpy(), rtol=6e-3, atol=6e-3 * sc)
 
 
 @pytest.mark.parametrize("d,n,M,acc", [(64, 256, 1, False), (100, 512, 3, False), (37, 1024, 8, True), (256, 4096, 20, False),
