@@ -32,11 +32,16 @@ struct Req {
     int pos = 0;             // next position to write
     int last_token = -1;     // token to feed on the next decode row
     int n_generated = 0;
+    int pages = 0;           // KV pages reserved for this request while it holds a slot
     bool cancelled = false;
 };
 
 struct Sched {
     int max_rows, n_slots, prefill_chunk, max_seq_len;
+    // KV page budget: a request is admitted only if the pages of its whole life (prompt + max_new tokens) fit next to
+    // the reservations of the running ones, so the engine's page allocator can never run dry in the middle of a step.
+    // 0 pages = no page accounting (admission by free slot only).
+    int n_pages = 0, page_size = 32, pages_reserved = 0;
     std::mutex mu;
     std::condition_variable cv;
     std::deque<long long> waiting;                       // FIFO admission
@@ -65,6 +70,16 @@ void* dl_sched_new(int max_rows, int n_slots, int prefill_chunk, int max_seq_len
 
 void dl_sched_free(void* p) { delete (Sched*)p; }
 
+// KV page pool of the engine (pages shared by all sequences) and tokens per page; call before the first submit
+void dl_sched_set_pages(void* p, int n_pages, int page_size) {
+    auto* s = (Sched*)p;
+    std::lock_guard<std::mutex> g(s->mu);
+    s->n_pages = n_pages > 0 ? n_pages : 0;
+    s->page_size = page_size > 0 ? page_size : 32;
+}
+
+static int pages_for(const Sched* s, int n_tokens) { return (n_tokens + s->page_size - 1) / s->page_size; }
+
 // 0 = queued; -1 = prompt (+ max_new) does not fit max_seq_len; -2 = duplicate id; -3 = empty prompt
 int dl_sched_submit(void* p, long long req_id, const int* tokens, int n, int max_new) {
     auto* s = (Sched*)p;
@@ -72,6 +87,8 @@ int dl_sched_submit(void* p, long long req_id, const int* tokens, int n, int max
     if (n >= s->max_seq_len) return -1;
     std::lock_guard<std::mutex> g(s->mu);
     if (s->reqs.count(req_id)) return -2;
+    // a request that could never be admitted (its own pages exceed the whole pool) is refused now, not queued forever
+    if (s->n_pages > 0 && pages_for(s, n + std::max(1, std::min(max_new, s->max_seq_len - n))) > s->n_pages) return -1;
     Req r;
     r.id = req_id;
     r.prompt.assign(tokens, tokens + n);
@@ -108,6 +125,8 @@ static void finish_locked(Sched* s, Req& r) {
         s->free_slots.push_back(r.slot);
         r.slot = -1;
     }
+    s->pages_reserved -= r.pages;
+    r.pages = 0;
     r.state = DONE;
     s->running.erase(std::remove(s->running.begin(), s->running.end(), r.id), s->running.end());
 }
@@ -129,6 +148,10 @@ int dl_sched_next_batch(void* p, long long* req_ids, int* tokens, int* pos, int*
     // admit waiting requests while slots are free
     while (!s->waiting.empty() && !s->free_slots.empty()) {
         Req& r = s->reqs[s->waiting.front()];
+        const int need = s->n_pages > 0 ? pages_for(s, (int)r.prompt.size() + r.max_new) : 0;
+        if (s->n_pages > 0 && s->pages_reserved + need > s->n_pages) break;    // FIFO: wait until enough pages come back
+        r.pages = need;
+        s->pages_reserved += need;
         s->waiting.pop_front();
         r.slot = s->free_slots.back();
         s->free_slots.pop_back();

@@ -64,6 +64,7 @@ int dl_stop_append(void* d, int token, const char* piece, int piece_len);
 const char* dl_stop_delta(void* d, int* len);
 void* dl_sched_new(int max_rows, int n_slots, int prefill_chunk, int max_seq_len);
 void dl_sched_free(void* p);
+void dl_sched_set_pages(void* p, int n_pages, int page_size);
 int dl_sched_submit(void* p, long long req_id, const int* tokens, int n, int max_new);
 int dl_sched_cancel(void* p, long long req_id);
 int dl_sched_wait(void* p, int timeout_ms);
@@ -898,6 +899,9 @@ void dl_srv_shutdown(void* sv) {
     close(s->evfd);
     s->listen_fd = s->ep = s->evfd = -1;
 }
+
+// KV page pool of the engine: admission reserves the pages of a request's whole life (see scheduler.cpp)
+void dl_srv_set_pages(void* p, int n_pages, int page_size) { dl_sched_set_pages(((Server*)p)->sched, n_pages, page_size); }
 
 void dl_srv_free(void* sv) {
     auto* s = (Server*)sv;

@@ -226,6 +226,12 @@ class LlamaEngine:
                 print(f"💡 KV page pool capped at {fit} pages ({fit * page_bytes >> 20} MiB) instead of "
                       f"{self.n_pages} (n_slots x max_seq_len); sequences share it on demand", flush=True)
                 self.n_pages = fit
+        if world > 1 and n_pages is None and dev.type == "cuda":
+            # every rank replays the same batches with the same page tables: agree on the smallest pool
+            import torch.distributed as dist
+            t = torch.tensor([self.n_pages], dtype=torch.int64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MIN, group=group)
+            self.n_pages = int(t.item())
         self.pages = PageAllocator(self.n_pages, n_slots, self.max_pages)
         self.block_table = torch.zeros(n_slots, self.max_pages, dtype=torch.int32, device=dev)
         self.h_block_table = torch.zeros(n_slots, self.max_pages, dtype=torch.int32).pin_memory()
@@ -418,6 +424,10 @@ class LlamaEngine:
     # ------------------------------------------------------------------------------------------------
     # slots / pages
     # ------------------------------------------------------------------------------------------------
+    def usable_pages(self) -> int:
+        """Pages the scheduler may hand out to requests (the padding sequence of bucket_rows keeps one)."""
+        return self.n_pages - (1 if self.bucket_rows else 0)
+
     def alloc_slot(self) -> int:
         return self.pages.alloc_slot()
 

@@ -31,29 +31,72 @@ class ControlChannel:
         self.path = os.path.join("/dev/shm", f"dllama_b200_ctl_{name}")
         nbytes = 64 + 8 * 64 + 4 * self.n_words
         create = (rank == 0) if create is None else create
+        self.send_timeout_s = float(os.environ.get("DLLAMA_CTL_TIMEOUT_S", "120"))
         if create:
-            with open(self.path, "wb") as f:
+            # a file of a crashed run with the same name must never be mapped by this run's workers: write the new
+            # mailbox under a temporary name and rename it into place (workers that still map the old inode keep a
+            # dead file; new workers check the run nonce below)
+            tmp = self.path + f".{os.getpid()}.tmp"
+            with open(tmp, "wb") as f:
                 f.write(b"\0" * nbytes)
+                f.seek(8)
+                f.write(np.int64(self._nonce()).tobytes())
+            os.replace(tmp, self.path)
         else:
             t0 = time.time()
-            while not os.path.exists(self.path) or os.path.getsize(self.path) < nbytes:
+            while True:
+                try:
+                    if os.path.getsize(self.path) >= nbytes:
+                        with open(self.path, "rb") as f:
+                            f.seek(8)
+                            if np.frombuffer(f.read(8), dtype=np.int64)[0] == self._nonce():
+                                break
+                except OSError:
+                    pass
                 if time.time() - t0 > 60:
-                    raise TimeoutError(f"control mailbox {self.path} did not appear")
+                    raise TimeoutError(f"control mailbox {self.path} of this run did not appear")
                 time.sleep(0.01)
         self._f = open(self.path, "r+b")
         self._mm = mmap.mmap(self._f.fileno(), nbytes)
         self.seq = np.frombuffer(self._mm, dtype=np.int64, count=1, offset=0)
+        self.fail = np.frombuffer(self._mm, dtype=np.int64, count=1, offset=16)      # set by a worker whose step failed
         self.ack = np.frombuffer(self._mm, dtype=np.int64, count=64, offset=64)
         self.payload = np.frombuffer(self._mm, dtype=np.int32, count=self.n_words, offset=64 + 8 * 64)
         self._seen = 0
+
+    def _nonce(self) -> int:
+        """Identifies the run.  The mailbox name already does in worker mode (it carries the root's pid); under
+        torchrun the name is only the rendezvous port, so the launcher's pid (the common parent of all ranks) is added."""
+        key = os.path.basename(self.path) + ":" + os.environ.get("DLLAMA_RUN_NONCE", "")
+        if "TORCHELASTIC_RUN_ID" in os.environ:
+            key += ":" + os.environ["TORCHELASTIC_RUN_ID"] + ":" + str(os.getppid())
+        h = 1469598103934665603
+        for ch in key.encode():
+            h = ((h ^ ch) * 1099511628211) & 0x7FFFFFFFFFFFFFFF
+        return h or 1
+
+    def report_failure(self, msg: str):
+        """Worker side: tell the root that this rank cannot go on (the root's next send raises)."""
+        import sys
+        sys.stderr.write(f"[control] rank {self.rank} failed: {msg}\n")
+        self.fail[0] = self.rank + 1
 
     # ---- root -------------------------------------------------------------------------------
     def send(self, op: int, tokens: Sequence[int] = (), positions: Sequence[int] = (), slots: Sequence[int] = (),
              logits_from: int = 0, greedy: bool = False, released: Sequence[int] = ()):
         k = int(self.seq[0])
+        t0 = time.time()
         for r in range(1, self.world):                      # previous packet consumed by everyone?
+            spins = 0
             while int(self.ack[r]) < k:
-                pass
+                spins += 1
+                if spins & 0xFFFF == 0:
+                    if int(self.fail[0]) != 0:
+                        raise RuntimeError(f"worker rank {int(self.fail[0]) - 1} reported a failed step")
+                    if time.time() - t0 > self.send_timeout_s:
+                        raise TimeoutError(f"worker rank {r} did not take the previous batch within {self.send_timeout_s:.0f} s")
+        if int(self.fail[0]) != 0:
+            raise RuntimeError(f"worker rank {int(self.fail[0]) - 1} reported a failed step")
         M, R = len(tokens), self.max_rows
         p = self.payload
         p[0], p[1], p[2], p[3], p[4] = op, M, logits_from, int(greedy), len(released)

@@ -24,6 +24,9 @@ from ..parallel.control import OP_FORWARD, OP_STOP, OP_WARMUP, ControlChannel
 from ..text import native as T
 
 
+PAGE_TOKENS = 32          # tokens per KV page (ops.kernels.PAGE_SIZE)
+
+
 @dataclass
 class GenerationRequest:
     prompt_tokens: List[int]
@@ -61,6 +64,8 @@ class BatchEngine:
         self.tok = tokenizer
         self.max_rows = engine.max_rows
         self.sched = T.Scheduler(self.max_rows, engine.n_slots, prefill_chunk or self.max_rows, engine.seq_len)
+        if hasattr(engine, "usable_pages"):                   # paged KV: admit by free pages, not only by free slot
+            self.sched.set_pages(engine.usable_pages(), PAGE_TOKENS)
         self.control = control
         self.reqs = {}
         self._ids = itertools.count(1)
@@ -167,6 +172,8 @@ class BatchEngine:
         greedy = all(r is not None and r.temperature == 0.0 for r in rows) and len(rows) > 0
         if self.control is not None:
             # workers replay exactly the root's launch: a pure prompt step computes the last row's logits only
+            for s_, p_ in zip(slots, pos):          # a page shortage must surface before the workers are told to run
+                self.engine.ensure_capacity(int(s_), int(p_) + 1)
             self.control.send(OP_FORWARD, toks, pos, slots, lf if sampling else len(toks) - 1, greedy, released)
         eng = self.engine
         n_s = len(sampling)
@@ -283,17 +290,23 @@ class BatchEngine:
 
 
 def worker_loop(engine, control: ControlChannel):
-    """Worker ranks: replay the root's batches (reference: runWorkerApp loop, src/app.cpp:405-464)."""
+    """Worker ranks: replay the root's batches (reference: runWorkerApp loop, src/app.cpp:405-464).  A step that
+    fails on a worker is reported to the root through the mailbox (the root's next send raises) instead of leaving the
+    root's kernels spinning on a rank that is gone."""
     torch.cuda.set_device(engine.device)
     while True:
         pkt = control.recv()
         if pkt is None or pkt["op"] == OP_STOP:
             return
-        for s in pkt["released"]:
-            engine.pages.release_pages(s)
-        if pkt["op"] == OP_WARMUP:
-            engine.warmup_graphs()
-            continue
-        if pkt["op"] == OP_FORWARD and pkt["M"] > 0:
-            M = engine.set_batch(pkt["tokens"], pkt["positions"], pkt["slots"])
-            engine._run_batch(M, pkt["logits_from"], pkt["greedy"])
+        try:
+            for s in pkt["released"]:
+                engine.pages.release_pages(s)
+            if pkt["op"] == OP_WARMUP:
+                engine.warmup_graphs()
+                continue
+            if pkt["op"] == OP_FORWARD and pkt["M"] > 0:
+                M = engine.set_batch(pkt["tokens"], pkt["positions"], pkt["slots"])
+                engine._run_batch(M, pkt["logits_from"], pkt["greedy"])
+        except Exception as exc:        # noqa: BLE001 -- whatever it is, the root has to hear about it
+            control.report_failure(f"{type(exc).__name__}: {exc}")
+            raise

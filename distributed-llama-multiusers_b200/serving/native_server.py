@@ -44,6 +44,8 @@ class NativeApiServer:
                                      int(defaults.seed) & 0xFFFFFFFFFFFFFFFF, max_default_tokens, int(verbose))
         if not self._h:
             raise RuntimeError("dl_srv_new failed")
+        if hasattr(engine, "usable_pages"):                   # paged KV: admit by free pages, not only by free slot
+            self._L.dl_srv_set_pages(self._h, engine.usable_pages(), 32)
         dev = getattr(engine, "device", torch.device("cpu"))
         self._cuda = dev.type == "cuda"
         self._device_sampler = self._cuda and os.environ.get("DLLAMA_HOST_SAMPLER", "0") != "1"
@@ -148,6 +150,8 @@ class NativeApiServer:
         toks, pos, slots = dn[0, :n].tolist(), dn[1, :n].tolist(), dn[2, :n].tolist()
         if self.control is not None:
             # workers replay exactly the root's launch: a pure prompt step computes the last row's logits only
+            for s_, p_ in zip(slots, pos):          # a page shortage must surface before the workers are told to run
+                self.engine.ensure_capacity(int(s_), int(p_) + 1)
             self.control.send(OP_FORWARD, toks, pos, slots, lf if n_s else n - 1, greedy, released)
         if n_s == 0:
             eng.forward(toks, pos, slots, logits_from=n - 1)                  # pure prompt chunk

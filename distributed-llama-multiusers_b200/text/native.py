@@ -41,6 +41,7 @@ def host_lib():
         "dl_stop_reset": (None, [vp]), "dl_stop_append": (i32, [vp, i32, cp, i32]),
         "dl_stop_delta": (vp, [vp, ip]),
         "dl_sched_new": (vp, [i32, i32, i32, i32]), "dl_sched_free": (None, [vp]),
+        "dl_sched_set_pages": (None, [vp, i32, i32]), "dl_srv_set_pages": (None, [vp, i32, i32]),
         "dl_sched_submit": (i32, [vp, ll, ip, i32, i32]), "dl_sched_cancel": (i32, [vp, ll]),
         "dl_sched_wait": (i32, [vp, i32]),
         "dl_sched_next_batch": (i32, [vp, C.POINTER(ll), ip, ip, ip, i32, ip]),
@@ -311,6 +312,11 @@ class Scheduler:
         self._tok = (C.c_int * R)()
         self._pos = (C.c_int * R)()
         self._slot = (C.c_int * R)()
+
+    def set_pages(self, n_pages: int, page_size: int = 32):
+        """KV page pool of the engine: a request is admitted only if the pages of its whole life (prompt + max_new
+        tokens) fit beside the reservations of the running requests, so a step can never run out of pages."""
+        host_lib().dl_sched_set_pages(self._h, n_pages, page_size)
 
     def __del__(self):
         try:

@@ -51,6 +51,32 @@ def test_scheduler_batches_prefill_first_and_decodes_together():
     assert s.stats()["free_slots"] == 2
 
 
+def test_scheduler_admits_by_free_kv_pages():
+    """Page-aware admission: a request holds the pages of its whole life (prompt + max_new tokens) while it runs, so
+    the engine's page allocator can never run dry in the middle of a step; requests that do not fit wait (FIFO), and
+    one that could never fit is refused at submit."""
+    s = T.Scheduler(max_rows=64, n_slots=4, prefill_chunk=64, max_seq_len=512)
+    s.set_pages(6, 32)                                     # 6 pages of 32 tokens
+    assert s.submit(1, list(range(40)), 60) == 0           # 100 tokens -> 4 pages
+    assert s.submit(2, list(range(20)), 40) == 0           # 60 tokens  -> 2 pages
+    assert s.submit(3, [1, 2, 3], 5) == 0                  # 1 page: free slots exist, but no pages are left
+    assert s.submit(4, list(range(100)), 200) == -1        # 10 pages: can never be admitted
+    ids, *_ = s.next_batch()
+    assert set(ids) == {1, 2} and s.stats()["waiting"] == 1
+    # finish request 2: its pages come back and request 3 gets in
+    while True:
+        ids, toks, pos, slots, lf, samp = s.next_batch()
+        if not samp:
+            s.commit([], [])
+            continue
+        done = s.commit([7] * len(samp), [r == 2 for r in samp])
+        if any(d and r == 2 for d, r in zip(done, samp)):
+            break
+    s.pop_released()
+    ids, *_ = s.next_batch()
+    assert 3 in ids and s.stats()["waiting"] == 0
+
+
 def test_scheduler_cancel_and_round_robin():
     s = T.Scheduler(max_rows=2, n_slots=3, prefill_chunk=2, max_seq_len=64)
     for i in (1, 2, 3):
