@@ -2,13 +2,15 @@
 (`--buffer-float-type f32`): the reference's "f32 / f32" path (matmul_F32_F32_F32, nn-cpu-ops.cpp:
 182-220; merge-add of f32 slices :835-852; no Q80 cast anywhere).
 
-Weights stay f32 in HBM.  On a GPU the matmuls are this repo's `gemm_f32_kernel` (csrc/cuda/gemm_f32.cu:
-plain f32 FMAs, weights streamed once per <= 8 activation rows); chunks wider than 64 rows (prefill) fall
-back to a cuBLAS SGEMM with TF32 disabled.  The wo / w2 partial sums are combined with an NCCL
-all-reduce, and RMSNorm / RoPE / attention / SiLU*mul are PyTorch ops -- the tuned, fused kernels of
-this repo are Q40 x Q80 (what the published models use); this path is about running f32 models at all.  What it shares with ``LlamaEngine`` is the
-public surface -- slots, batched rows with per-row positions, tensor-parallel slicing by rank -- so
-the scheduler, the HTTP API and the CLI run f32 models on GPUs unchanged.
+Weights stay f32 in HBM.  On a GPU the whole forward pass runs on this repo's kernels: `gemm_f32_kernel` (plain f32
+FMAs, weights streamed once per <= 8 activation rows), `reduce_norm_quant_kernel` (merge-add of the ranks' f32 partial
+sums + residual + RMSNorm, f32 output), `rope_kv_f32` (RoPE + paged KV-cache write), `attention_kernel` over an f32
+paged cache, `silu_mul_f32`, and for tensor parallelism `push_f32` (this rank's partial sums stored into every rank's
+exchange buffer over NVLink + release flags: the reference's SYNC_NODE_SLICES of f32 slices) -- no cuBLAS, no NCCL on the
+data path, no eager PyTorch ops.  The tuned, fused kernels of this repo are Q40 x Q80 (what the published models use);
+this path is about running f32 models natively at all.  Without a GPU the same engine falls back to PyTorch CPU ops.
+What it shares with ``LlamaEngine`` is the public surface -- slots, batched rows with per-row positions, tensor-parallel
+slicing by rank -- so the scheduler, the HTTP API and the CLI run f32 models on GPUs unchanged.
 
 Slicing follows the reference (llm.cpp:131-142): q/k/v/w1/w3/wcls by output rows, wo/w2 by input
 columns, KV cache by kv head, residual stream replicated.
@@ -94,16 +96,136 @@ class F32Engine:
             self.wcls = up(self.mf.f32("wcls"))
         self.freqs = rope_frequencies(h).to(self.device)
         L = h.n_layers
-        self.k_cache = torch.zeros(n_slots, L, self.seq_len, self.n_kv_loc, hs, device=self.device)
-        self.v_cache = torch.zeros(n_slots, L, self.seq_len, self.n_kv_loc, hs, device=self.device)
-        self.pages = _Slots(n_slots)
-        self.logits = torch.zeros(max_rows, h.vocab_size, device=self.device)
         self.act_gelu = h.hidden_act != HIDDEN_ACT_SILU
         self.native = self.device.type == "cuda"
         if self.native:
             from ..ops import kernels as _K          # fails loudly if the CUDA library is missing on a GPU box
             _K.cuda_lib()
             self._K = _K
+            self._init_native()
+        else:
+            self.k_cache = torch.zeros(n_slots, L, self.seq_len, self.n_kv_loc, hs, device=self.device)
+            self.v_cache = torch.zeros(n_slots, L, self.seq_len, self.n_kv_loc, hs, device=self.device)
+            self.pages = _Slots(n_slots)
+            self.logits = torch.zeros(max_rows, h.vocab_size, device=self.device)
+
+    # ---- native GPU path ---------------------------------------------------------------------------
+    def _init_native(self):
+        from ..parallel.symm import SymmetricBuffer
+        from .llama import PAGE, PageAllocator
+        K, h, dev, N, R = self._K, self.h, self.device, self.world, self.max_rows
+        if h.dim % 32 or self.q_loc % 4 or self.hid_loc % 4 or (self.vocab_loc or h.vocab_size) % 4:
+            raise ValueError("f32 GPU path: dim must be a multiple of 32, the per-rank widths multiples of 4")
+        if self.vocab_loc is None and N > 1:
+            raise ValueError("f32 GPU path with tensor parallelism needs vocab_size divisible by the number of ranks")
+        self.max_pages = (self.seq_len + PAGE - 1) // PAGE
+        self.n_pages = self.n_slots * self.max_pages
+        self.pages = PageAllocator(self.n_pages, self.n_slots, self.max_pages)
+        self.block_table = torch.zeros(self.n_slots, self.max_pages, dtype=torch.int32, device=dev)
+        kv_shape = (self.n_pages, self.n_kv_loc, PAGE, self.hs)
+        self.k_cache = [torch.zeros(kv_shape, dtype=torch.float32, device=dev) for _ in range(h.n_layers)]
+        self.v_cache = [torch.zeros(kv_shape, dtype=torch.float32, device=dev) for _ in range(h.n_layers)]
+        self.desc = torch.zeros(3, R, dtype=torch.int32, device=dev)          # tokens | pos | slot
+        self.h_desc = torch.zeros(3, R, dtype=torch.int32).pin_memory()
+        self.x = [torch.zeros(R, h.dim, device=dev) for _ in range(2)]
+        self.y = torch.zeros(R, h.dim, device=dev)
+        self.qkv = torch.zeros(R, self.q_loc + 2 * self.kv_loc, device=dev)
+        self.q = torch.zeros(R, self.q_loc, device=dev)
+        self.att = torch.zeros(R, self.q_loc, device=dev)
+        self.g = torch.zeros(R, self.hid_loc, device=dev)
+        self.u = torch.zeros(R, self.hid_loc, device=dev)
+        self.hbuf = torch.zeros(R, self.hid_loc, device=dev)
+        self.part = torch.zeros(R, h.dim, device=dev)
+        self.lg_loc = torch.zeros(R, self.vocab_loc or h.vocab_size, device=dev)
+        self.out_tokens = torch.zeros(R, dtype=torch.int32, device=dev)
+        self.max_splits = 8
+        self.att_scratch = torch.zeros(K.attention_scratch_bytes(R, self.n_heads_loc, self.hs, self.max_splits),
+                                       dtype=torch.uint8, device=dev)
+        # symmetric exchange area: [att partials N x R x dim][ffn partials][logits R x vocab][flags]
+        part_bytes = N * R * h.dim * 4
+        self._off_att, self._off_ffn, self._off_logits = 0, part_bytes, 2 * part_bytes
+        self._off_flags = (2 * part_bytes + R * h.vocab_size * 4 + 255) // 256 * 256
+        self.symm = SymmetricBuffer(self._off_flags + 4096, self.rank, N, self.group)
+        sp, r = self.symm.ptrs, self.rank
+        fl = [p + self._off_flags for p in sp]
+        self._part_att = [p + self._off_att for p in sp]
+        self._part_ffn = [p + self._off_ffn for p in sp]
+        self._logit_ptrs = [p + self._off_logits for p in sp]
+        self._flags_att_local, self._flags_ffn_local, self._flags_log_local = fl[r], fl[r] + 32, fl[r] + 64
+        self._flags_att_peer = [p + 4 * r for p in fl]
+        self._flags_ffn_peer = [p + 32 + 4 * r for p in fl]
+        self._flags_log_peer = [p + 64 + 4 * r for p in fl]
+        self.step_counter = fl[r] + 96
+        self._counters = [fl[r] + 128 + 4 * i for i in range(3)]
+        self.logits = self.symm.tensor(self._off_logits, (R, h.vocab_size), torch.float32)
+        torch.cuda.synchronize()
+
+    def _forward_native(self, tokens, positions, slots, logits_from: int, greedy: bool):
+        """The launch sequence of one forward pass (reference graph: src/llm.cpp:185-432 without the Q80 casts)."""
+        from .llama import _IntPtr, _Off
+        K, h, N, L = self._K, self.h, self.world, self.h.n_layers
+        M = len(tokens)
+        hd = self.h_desc.numpy()
+        hd[0, :M], hd[1, :M], hd[2, :M] = tokens, positions, slots
+        for s_, p_ in zip(slots, positions):
+            self.pages.ensure(int(s_), int(p_) + 1)
+        if self.pages.dirty:
+            self.block_table.copy_(torch.from_numpy(self.pages.table), non_blocking=False)
+            self.pages.dirty = False
+        self.desc.copy_(self.h_desc, non_blocking=True)
+        tok, pos, slot = self.desc[0], self.desc[1], self.desc[2]
+        sc, R, dim = self.step_counter, self.max_rows, h.dim
+        stride = R * dim
+        multi = N > 1
+        K.embedding(self.embedding, tok, self.x[0], M, dim, _IntPtr(sc))
+        cur = 0
+        n_splits = max(1, min(self.max_splits, self.max_pages // 8))
+
+        def norm(pending, flag_add, w, rows=M, x_off=0):
+            """y = rmsnorm(x + merge of the pending partial sums) * w; the merged residual goes to the other x buffer."""
+            nonlocal cur
+            x_in = _Off(self.x[cur], x_off)
+            if pending is None:
+                K.reduce_norm_quant(x_in, None, None, 0, stride, None, sc, L, flag_add, w, h.norm_epsilon, dim, rows, rows,
+                                    None, None, y_out=self.y)
+                return
+            parts, flags = pending
+            K.reduce_norm_quant(x_in, _Off(self.x[cur ^ 1], x_off), parts + x_off, N, stride, flags if multi else None, sc, L,
+                                flag_add, w, h.norm_epsilon, dim, rows, rows, None, None, y_out=self.y)
+            cur ^= 1
+
+        def push(partial, bufs, flags_peer, flag_add, counter):
+            K.f32_push(partial, M, dim, bufs, self.rank * stride, dim, flags_peer if multi else None, sc, L, flag_add, counter)
+
+        pending = None
+        for l, W in enumerate(self.layers):
+            norm(pending, l, W["rms_att"])
+            K.gemm_f32(W["qkv"], self.y[:M], self.qkv[:M])
+            K.f32_rope_kv(self.qkv, M, self.q_loc, self.kv_loc, self.hs, self.n_kv_loc, self.freqs, pos, slot, self.block_table,
+                          self.max_pages, self.q, self.k_cache[l], self.v_cache[l])
+            K.attention(self.q, M, self.n_heads_loc, self.n_kv_loc, self.hs, self.k_cache[l], self.v_cache[l], pos, slot,
+                        self.block_table, self.max_pages, n_splits, self.att_scratch, None, None, M, y_out=self.att)
+            K.gemm_f32(W["wo"], self.att[:M], self.part[:M])
+            push(self.part, self._part_att, self._flags_att_peer, l + 1, self._counters[0])
+            pending = (self._part_att[self.rank], self._flags_att_local)
+            norm(pending, l + 1, W["rms_ffn"])
+            K.gemm_f32(W["w1"], self.y[:M], self.g[:M])
+            K.gemm_f32(W["w3"], self.y[:M], self.u[:M])
+            K.f32_silu_mul(self.g[:M], self.u[:M], self.hbuf[:M], gelu=self.act_gelu)
+            K.gemm_f32(W["w2"], self.hbuf[:M], self.part[:M])
+            push(self.part, self._part_ffn, self._flags_ffn_peer, l + 1, self._counters[1])
+            pending = (self._part_ffn[self.rank], self._flags_ffn_local)
+        Ml = M - logits_from
+        norm(pending, L, self.rms_final, rows=Ml, x_off=logits_from * dim * 4)
+        vl = self.vocab_loc or h.vocab_size
+        K.gemm_f32(self.wcls, self.y[:Ml], self.lg_loc[:Ml])
+        K.f32_push(self.lg_loc, Ml, vl, self._logit_ptrs, self.rank * vl, h.vocab_size,
+                   self._flags_log_peer if multi else None, sc, 1, 0, self._counters[2])
+        if multi:
+            K.wait_flags(self._flags_log_local, N, sc, 1, 0)
+        if greedy:
+            K.argmax(self.logits, Ml, h.vocab_size, h.vocab_size, self.out_tokens)
+        return self.logits[:Ml]
 
     # ---- LlamaEngine surface ---------------------------------------------------------------------
     def alloc_slot(self) -> int:
@@ -115,11 +237,14 @@ class F32Engine:
     def ensure_capacity(self, slot: int, n_tokens: int):
         if n_tokens > self.seq_len:
             raise RuntimeError(f"sequence of {n_tokens} tokens exceeds max_seq_len")
+        if self.native:
+            self.pages.ensure(slot, n_tokens)
 
     def weight_bytes(self) -> int:
         n = sum(t.numel() for L in self.layers for t in L.values()) + self.wcls.numel() + self.rms_final.numel()
         return 4 * n
 
+    # ---- CPU fallback (no GPU on the machine): PyTorch ops, gloo all-reduce ----------------------------------------
     def _all_reduce(self, t: torch.Tensor) -> torch.Tensor:
         if self.world > 1:
             dist.all_reduce(t, group=self.group)
@@ -127,8 +252,6 @@ class F32Engine:
 
     def _mm(self, x: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
         """x[M][n] @ w[d][n]^T in f32."""
-        if self.native and x.shape[0] <= 64:
-            return self._K.gemm_f32(w, x.contiguous())
         return x @ w.t()
 
     def _rms(self, x, w):
@@ -148,6 +271,8 @@ class F32Engine:
         """Rows may mix sequences; rows of one sequence must be in increasing position order."""
         h, M = self.h, len(tokens)
         assert 1 <= M <= self.max_rows
+        if self.native:
+            return self._forward_native(tokens, positions, slots, logits_from, greedy)
         dev = self.device
         pos = torch.tensor(list(positions), device=dev, dtype=torch.long)
         slot_t = torch.tensor(list(slots), device=dev, dtype=torch.long)
@@ -205,6 +330,9 @@ class F32Engine:
         return out
 
     def decode_step_greedy(self, tokens, positions, slots, logits_from: int = 0) -> List[int]:
+        if self.native:                                   # device argmax: only token ids cross PCIe
+            self.forward(tokens, positions, slots, logits_from, greedy=True)
+            return self.out_tokens[:len(tokens) - logits_from].cpu().tolist()
         lg = self.forward(tokens, positions, slots, logits_from)
         return [int(t) for t in torch.argmax(lg, dim=-1).cpu()]
 
@@ -212,4 +340,7 @@ class F32Engine:
         return self.decode_step_greedy(tokens, positions, slots, 0)
 
     def close(self):
+        if self.native:
+            torch.cuda.synchronize()
+            self.symm.close()
         self.mf.close()

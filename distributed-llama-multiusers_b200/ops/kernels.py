@@ -269,6 +269,33 @@ def gemm_f32(w: torch.Tensor, x: torch.Tensor, out: Optional[torch.Tensor] = Non
     return out
 
 
+def f32_rope_kv(qkv: torch.Tensor, M: int, q_dim: int, kv_dim: int, head_size: int, n_kv_heads: int, freqs, pos, slot,
+                block_table, max_pages: int, q_out: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor):
+    """f32 path: RoPE on q / k, q -> q_out, k / v -> paged KV cache."""
+    check(cuda_lib().dl_f32_rope_kv(qkv.data_ptr(), M, q_dim, kv_dim, head_size, n_kv_heads, freqs.data_ptr(), pos.data_ptr(),
+                                    slot.data_ptr(), block_table.data_ptr(), max_pages, q_out.data_ptr(), k_cache.data_ptr(),
+                                    v_cache.data_ptr(), 1 if k_cache.dtype == torch.float32 else 0, _stream()), "dl_f32_rope_kv")
+    lib.count_launch()
+
+
+def f32_silu_mul(g: torch.Tensor, u: torch.Tensor, out: torch.Tensor, gelu: bool = False):
+    check(cuda_lib().dl_f32_silu_mul(g.data_ptr(), u.data_ptr(), out.data_ptr(), g.numel(), 1 if gelu else 0, _stream()),
+          "dl_f32_silu_mul")
+    lib.count_launch()
+
+
+def f32_push(src: torch.Tensor, M: int, w: int, dst: Sequence[int], dst_off: int, ld_dst: int,
+             flags: Optional[Sequence[int]] = None, step_counter: Optional[int] = None, flag_mul: int = 0, flag_add: int = 0,
+             cta_counter: Optional[int] = None):
+    """f32 path: this rank's slice -> every rank's exchange buffer (+ release flags)."""
+    n = len(dst)
+    d = (C.c_void_p * n)(*dst)
+    f = (C.c_void_p * n)(*flags) if flags is not None else None
+    check(cuda_lib().dl_f32_push(src.data_ptr(), M, w, src.stride(0), d, n, dst_off, ld_dst, f, step_counter, flag_mul, flag_add,
+                                 cta_counter, _stream()), "dl_f32_push")
+    lib.count_launch()
+
+
 MEGA_MAX_ROWS = 4
 MEGA_LL_WORDS = 9          # 8-byte LL words per 32-value Q80 block (8 x {4 int8, epoch} + {fp16 scale, epoch})
 

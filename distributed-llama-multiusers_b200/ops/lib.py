@@ -175,6 +175,11 @@ def cuda_lib():
     L.dl_ipc_close.argtypes = [vp]
     L.dl_ipc_free.argtypes = [vp]
     L.dl_peer_barrier.argtypes = [C.POINTER(vp), vp, i32, i32, u32, vp]
+    L.dl_f32_rope_kv.argtypes = [vp, i32, i32, i32, i32, i32, vp, vp, vp, vp, i32, vp, vp, vp, i32, vp]
+    L.dl_f32_silu_mul.argtypes = [vp, vp, vp, i64, i32, vp]
+    L.dl_f32_push.argtypes = [vp, i32, i32, i32, C.POINTER(vp), i32, i64, i32, C.POINTER(vp), vp, u32, u32, vp, vp]
+    for name in ("dl_f32_rope_kv", "dl_f32_silu_mul", "dl_f32_push"):
+        getattr(L, name).restype = i32
     L.dl_decode_mega_supported.argtypes = [C.POINTER(DlDecodeArgs), i32]
     L.dl_decode_mega_supported.restype = i32
     L.dl_decode_mega.argtypes = [C.POINTER(DlDecodeArgs), i32, vp]

@@ -117,6 +117,22 @@ int dl_sample_rows(const float* logits, int M, int vocab, int ld, const float* t
 int dl_gemm_f32(const float* w, int d, int n, long long ldw, const float* x, int M, int ldx, float* y, int ldy,
                 int accumulate, void* stream);
 
+/* The other kernels of the f32 path (no Q80 cast anywhere; with dl_gemm_f32, dl_reduce_norm_quant (y_out), dl_attention,
+ * dl_embedding and dl_argmax they cover the whole forward pass):
+ * RoPE on the q and k rows of qkv[M][q_dim + 2 kv_dim], q -> q_out, k / v -> the paged KV cache
+ * (reference: OP_ROPE_LLAMA + OP_SHIFT, nn-cpu-ops.cpp:1090-1120,1253-1275) */
+int dl_f32_rope_kv(const float* qkv, int M, int q_dim, int kv_dim, int head_size, int n_kv_heads, const float* freqs,
+                   const int* pos, const int* slot, const int* block_table, int max_pages, float* q_out,
+                   void* k_cache, void* v_cache, int kv_f32, void* stream);
+/* out = act(g) * u, act = SiLU or tanh-GELU (reference: OP_SILU / OP_GELU + OP_MUL, nn-cpu-ops.cpp:1058-1078,1163-1183) */
+int dl_f32_silu_mul(const float* g, const float* u, float* out, long long n, int gelu, void* stream);
+/* store src[M][w] into every destination buffer (peer memory) at dst_off + m*ld_dst and release one flag per destination
+ * with epoch *step_counter*flag_mul+flag_add (reference: SYNC_NODE_SLICES of f32 slices, nn-network.cpp:537-569; the
+ * merge-add of nn-cpu-ops.cpp:835-852 is done by the consumer, dl_reduce_norm_quant) */
+int dl_f32_push(const float* src, int M, int w, int ld_src, float* const* dst /*host array*/, int n_dst, long long dst_off,
+                int ld_dst, uint32_t* const* flags /*host array or NULL*/, const uint32_t* step_counter, uint32_t flag_mul,
+                uint32_t flag_add, uint32_t* cta_counter /*zero-initialised, self-resetting*/, void* stream);
+
 /* ---- Q40 x Q80 matmuls ------------------------------------------------------------------- */
 /* dp4a GEMV, M <= 8 rows: bulk-copy fed, cluster split-K (reference: matmul_Q80_Q40_F32,
  * src/nn/nn-cpu-ops.cpp:222-440) */

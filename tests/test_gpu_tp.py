@@ -15,17 +15,17 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def _run_tp_check(world: int, mega: str, port: int):
+def _run_tp_check(world: int, mega: str, port: int, script: str = "tp_check.py", marker: str = "TP_CHECK PASS"):
     env = dict(os.environ)
     env["DLLAMA_MEGA"] = mega
     env["DLLAMA_MEGA_TIMEOUT_S"] = "20"
     env.pop("RANK", None)
     env.pop("WORLD_SIZE", None)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
-           "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "scripts", "tp_check.py")]
+           "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "scripts", script)]
     p = subprocess.run(cmd, cwd=ROOT, env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
     tail = "\n".join(p.stdout.splitlines()[-40:])
-    assert p.returncode == 0 and f"TP_CHECK PASS world={world}" in p.stdout, tail
+    assert p.returncode == 0 and f"{marker} world={world}" in p.stdout, tail
     assert "FAIL" not in p.stdout, tail
 
 
@@ -34,3 +34,11 @@ def test_tensor_parallel_matches_oracle(world, mega):
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs, this box has {torch.cuda.device_count()}")
     _run_tp_check(world, mega, 29600 + 10 * world + int(mega))
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_f32_path_tensor_parallel(world):
+    """The native f32 path (gemm_f32 + f32 peer-store exchange, no NCCL on the data path) on 2 and 4 ranks."""
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs, this box has {torch.cuda.device_count()}")
+    _run_tp_check(world, "auto", 29700 + world, script="tp_check_f32.py", marker="TP_CHECK_F32 PASS")
