@@ -14,8 +14,65 @@ KEYS = ["UTCHMMA", "UTCBAR", "UTCATOMSWS", "LDTM", "STTM", "UBLKCP", "SYNCS", "A
         "REDUX", "SHFL", "ATOMG", "RED."]
 
 
+def write_listings(out: str):
+    """One SASS listing per kernel under profiles/sass/ (instruction text only: the 128-bit encodings are dropped to keep
+    the files reviewable).  Template families keep every instantiation."""
+    ddir = os.path.join(ROOT, "profiles", "sass")
+    os.makedirs(ddir, exist_ok=True)
+    for f in os.listdir(ddir):
+        if f.endswith(".sass"):
+            os.remove(os.path.join(ddir, f))
+    demangle = {}
+    try:
+        names = sorted(set(re.findall(r"Function : (\S+)", out)))
+        dm = subprocess.run(["cu++filt"] + names, capture_output=True, text=True).stdout.splitlines()
+        demangle = dict(zip(names, dm))
+    except Exception:
+        pass
+    cur, buf, index = None, [], []
+    # template families: one or two representative instantiations are enough for review (the others differ in unroll counts)
+    keep_variants = {"attention_kernel": ("int)128, (int)1, __half", "int)64, (int)1, float"), "decode_mega_kernel": ("(int)1>",),
+                     "gemv_q40_kernel": ("(int)1>", "(int)4>"), "gemm_f32_kernel": ("(int)8>",), "attention_prefill_kernel": ("(int)128>",)}
+
+    def flush():
+        if cur is None:
+            return
+        nice = demangle.get(cur, cur)
+        for fam, pats in keep_variants.items():
+            if fam + "<" in nice and not any(p in nice for p in pats):
+                return
+        base = nice.replace("void ", "")
+        base = base[:base.rfind("(")] if "(" in base else base                   # drop the parameter list, keep template arguments
+        fname = re.sub(r"[^A-Za-z0-9_]+", "_", base).strip("_")[:80] + ".sass"
+        with open(os.path.join(ddir, fname), "w") as f:
+            f.write(f"// {nice}\n// cuobjdump -sass libdllama_b200_cuda.so (sm_100a), encodings stripped\n" + "\n".join(buf) + "\n")
+        index.append((fname, nice, len(buf)))
+
+    for line in out.splitlines():
+        m = re.search(r"Function : (\S+)", line)
+        if m:
+            flush()
+            cur, buf = m.group(1), []
+            continue
+        if cur is None:
+            continue
+        if re.match(r"\s+/\* 0x[0-9a-f]{16} \*/\s*$", line):          # second half of an encoding
+            continue
+        line = re.sub(r"\s*/\* 0x[0-9a-f]{16} \*/\s*$", "", line)
+        if line.strip():
+            buf.append(line.rstrip())
+    flush()
+    with open(os.path.join(ddir, "INDEX.md"), "w") as f:
+        f.write("# SASS listings (sm_100a), one file per kernel -- regenerate with `python scripts/sass_evidence.py`\n\n")
+        for fname, nice, n in sorted(index):
+            f.write(f"* `{fname}` ({n} lines): `{nice}`\n")
+    return index
+
+
 def main():
     out = subprocess.run(["cuobjdump", "-sass", LIB], capture_output=True, text=True).stdout
+    idx = write_listings(out)
+    print(f"wrote {len(idx)} listings to profiles/sass/")
     kernels = collections.OrderedDict()
     cur = None
     for line in out.splitlines():
