@@ -45,6 +45,7 @@ def parse_args():
     ap.add_argument("--no-pdl", action="store_true")
     ap.add_argument("--no-graphs", action="store_true")
     ap.add_argument("--users", type=int, default=32, help="also measure an N-user batched decode (key multi_user; 0 = skip)")
+    ap.add_argument("--long-prompt", type=int, default=4096, help="also measure the TTFT of one long prompt run as a single batch on fp16-expanded weights (key ttft_long; 0 = skip)")
     ap.add_argument("--model-dir", default=os.environ.get("DLLAMA_MODEL_DIR", "/dev/shm"))
     ap.add_argument("--nthreads", type=int, default=0, help="reference arm: threads per node (0 = auto)")
     return ap.parse_args()
@@ -225,9 +226,13 @@ def run_b200(args):
     }
     if multi is not None:
         result["multi_user"] = multi
+    eng.close()
+    del eng
+    torch.cuda.empty_cache()
+    if args.long_prompt > 0:
+        result["ttft_long"] = bench_ttft_long(args, path, rank, world, barrier, dist)
     if rank == 0:
         print(json.dumps(result), flush=True)
-    eng.close()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -263,6 +268,41 @@ def bench_ttft(eng, args, barrier, world, dist, prompt):
     p50 = times[len(times) // 2]
     return {"prompt_tokens": len(prompt), "chunk_rows": args.prefill_chunk, "p50_ms": round(p50, 3), "min_ms": round(times[0], 3),
             "prefill_tokens_per_s": round(len(prompt) * 1000.0 / p50, 1)}
+
+
+def bench_ttft_long(args, path, rank, world, barrier, dist):
+    """TTFT of one long prompt evaluated as ONE batch (an engine with max_rows = prompt length): the matmuls run as the
+    two-phase GEMM on resident fp16-expanded weights (gemm_wh_tc.cu), attention on the tensor-core prefill kernel.
+    Same clock as bench_ttft: host timer around H2D of the descriptor ... D2H of the first token, max over ranks."""
+    import numpy as np
+    import torch
+    from dllama_b200.models.llama import LlamaEngine
+    n = args.long_prompt
+    eng = LlamaEngine(path, rank=rank, world=world, max_rows=n, n_slots=2, max_seq_len=n + 64, use_pdl=not args.no_pdl,
+                      use_graphs=not args.no_graphs)
+    prompt = np.random.default_rng(1).integers(1, eng.h.vocab_size, n).tolist()
+    times = []
+    for rep in range(4):
+        slot = eng.alloc_slot()
+        barrier()
+        t0 = time.perf_counter()
+        out = eng.decode_step_greedy(prompt, list(range(n)), [slot] * n, logits_from=n - 1)
+        ms = (time.perf_counter() - t0) * 1e3
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        if rep > 0:
+            times.append(float(t[0]))
+        eng.free_slot(slot)
+        assert out is not None
+    times.sort()
+    p50 = times[len(times) // 2]
+    flops = 2.0 * n * (eng.weight_bytes() - eng.wcls.numel()) / 9216 * 16384       # 128 x 128 weights per 9216-byte tile
+    res = {"prompt_tokens": n, "chunk_rows": n, "p50_ms": round(p50, 3), "min_ms": round(times[0], 3),
+           "prefill_tokens_per_s": round(n * 1000.0 / p50, 1), "weights": eng.wh_mode, "fp16_weight_copy_bytes": eng.wh_bytes(),
+           "matmul_tflops_per_gpu_at_p50": round(flops / p50 / 1e9, 1)}
+    eng.close()
+    return res
 
 
 def bench_users(eng, args, barrier, world, dist):

@@ -40,6 +40,12 @@ GEMV_PATH_MAX_M = int(os.environ.get("DLLAMA_GEMV_MAX_M", "3"))
 LL_MAX_ROWS = 32             # batches up to this many rows use the LL exchange (see LlamaEngine.__init__)
 LL_MAX_WORLD = 4             # largest tensor-parallel group that exchanges partial sums as LL words
 PREFILL_MAX_SEG = 8          # prompt-chunk segments per batch (attention_prefill.cu: PF_MAX_SEG)
+# Prompt-sized batches run on pre-expanded fp16 weights ("WH", csrc/cuda/gemm_wh_tc.cu): a plain SS-mode tcgen05 GEMM with
+# CTA pairs instead of the fused dequantising one.  Measured on the 8B shapes (TFLOP/s, fused kernel -> WH kernel):
+# w13 M=512 756 -> 897, M=1024 845 -> 1079, M=2048 908 -> 1193; qkv M=1024 623 -> 730, M=2048 832 -> 1061;
+# wo / w2 break even at 1024 rows and gain 17-21 % at 2048.  The expansion itself runs at 4.3-6.0 TB/s (w13: 50 us).
+WH_MIN_ROWS = int(os.environ.get("DLLAMA_WH_MIN_ROWS", "768"))             # resident copy: free to use
+WH_MIN_ROWS_SCRATCH = int(os.environ.get("DLLAMA_WH_MIN_ROWS_SCRATCH", "2048"))   # per-call expansion: ~13 % of the GEMM time at 2048 rows
 PAGE = K.PAGE_SIZE
 
 
@@ -93,7 +99,7 @@ class LlamaEngine:
                  n_slots: int = 4, max_seq_len: int = 2048, kv_dtype: torch.dtype = torch.float16,
                  sync_q80: bool = True, use_pdl: bool = True, use_graphs: bool = True, n_pages: Optional[int] = None,
                  device: Optional[torch.device] = None, verbose: bool = False, bucket_rows: bool = False,
-                 use_mega: Optional[bool] = None):
+                 use_mega: Optional[bool] = None, prefill_wh: str = "auto"):
         self.mf = ModelFile(model_path, max_seq_len=max_seq_len)
         h = self.h = self.mf.header
         if h.weight_type != quant.Q40:
@@ -131,6 +137,7 @@ class LlamaEngine:
 
         # ---- weights ---------------------------------------------------------------------------
         self._load_weights(verbose)
+        self._init_wh(os.environ.get("DLLAMA_PREFILL_WH", prefill_wh))
 
         # ---- activations -----------------------------------------------------------------------
         R = max_rows
@@ -244,7 +251,10 @@ class LlamaEngine:
             self.pages.free_slots.remove(self._pad_slot)
             self.pages.ensure(self._pad_slot, 1)
         self.max_splits = 32
-        self.att_scratch = torch.zeros(K.attention_scratch_bytes(R, self.n_heads_loc, self.hs, self.max_splits),
+        # split-KV partials exist only for batches small enough to leave SMs idle (M * splits(M) <= ~n_sms / n_kv):
+        # size the scratch for the largest M * splits product, not for max_rows x max_splits (2 GB at 4096 rows)
+        att_rows = max(m * self._attention_splits(m) for m in range(1, min(R, self.n_sms) + 1))
+        self.att_scratch = torch.zeros(K.attention_scratch_bytes(max(att_rows, R), self.n_heads_loc, self.hs, 1),
                                        dtype=torch.uint8, device=dev)
         self.argmax_scratch = torch.zeros(int(K.cuda_lib().dl_argmax_scratch_bytes(256)), dtype=torch.uint8,
                                           device=dev)
@@ -416,6 +426,33 @@ class LlamaEngine:
         self.wcls = wcls
         torch.cuda.synchronize()
 
+    def _init_wh(self, mode: str):
+        """fp16 copies of the layer matrices for prompt-sized batches.  'resident': expanded once and kept (8B: 14 GB of
+        the 180 GB); 'scratch': one buffer of the largest matrix, expanded before every use; 'off'; 'auto': resident
+        when the engine can see batches that large and the copies take less than a quarter of the free memory."""
+        h = self.h
+        shapes = {"qkv": (self.qkv_d, h.dim), "wo": (h.dim, self.q_loc), "w13": (2 * self.hid_loc, h.dim), "w2": (h.dim, self.hid_loc)}
+        self._wh_shapes = shapes
+        self._wh, self._wh_scratch, self.wh_mode = {}, None, "off"
+        if mode == "off" or self.device.type != "cuda" or self.max_rows < min(WH_MIN_ROWS, WH_MIN_ROWS_SCRATCH):
+            return
+        per_layer = sum(K.wh_bytes(d, n) for d, n in shapes.values())
+        if mode == "auto":
+            free_b, _ = torch.cuda.mem_get_info(self.device)
+            mode = "resident" if per_layer * h.n_layers <= free_b // 4 else "scratch"
+        if mode == "resident" and self.max_rows >= WH_MIN_ROWS:
+            for L in self.layers:
+                for name, (d, n) in shapes.items():
+                    self._wh[L[name].data_ptr()] = K.q40t_to_wh(L[name], d, n)
+            torch.cuda.synchronize()
+            self.wh_mode = "resident"
+        elif mode == "scratch" and self.max_rows >= WH_MIN_ROWS_SCRATCH:
+            self._wh_scratch = torch.empty(max(K.wh_bytes(d, n) for d, n in shapes.values()), dtype=torch.uint8, device=self.device)
+            self.wh_mode = "scratch"
+
+    def wh_bytes(self) -> int:
+        return sum(t.numel() for t in self._wh.values()) + (self._wh_scratch.numel() if self._wh_scratch is not None else 0)
+
     def weight_bytes(self) -> int:
         """Q40T bytes streamed per forward on this rank (roofline numerator)."""
         n = sum(t.numel() for L in self.layers for k, t in L.items() if t.dtype == torch.uint8)
@@ -451,6 +488,11 @@ class LlamaEngine:
             R, S, T = K.choose_splits(d, n, kind, self.n_sms, M)
             K.gemv_q40(w, d, n, None if norm is not None else xq, M, epi, R, S, norm=norm, pdl=self.use_pdl,
                        tiles_per_cta=T)
+        elif self.wh_mode == "resident" and M >= WH_MIN_ROWS and w.data_ptr() in self._wh:
+            K.gemm_wh_tc(self._wh[w.data_ptr()], d, n, xh, self.ncap, M, epi, pdl=self.use_pdl)
+        elif self.wh_mode == "scratch" and M >= WH_MIN_ROWS_SCRATCH and w is not self.wcls:
+            K.q40t_to_wh(w, d, n, self._wh_scratch)      # plain launch: starts after the previous user of the scratch has finished
+            K.gemm_wh_tc(self._wh_scratch, d, n, xh, self.ncap, M, epi, pdl=self.use_pdl)
         else:
             assert norm is None
             S = K.choose_tc_split(d, n, M, self.n_sms)
@@ -683,7 +725,11 @@ class LlamaEngine:
                 hd[3, b:e] = 1
                 hd[4, 1 + 2 * k] = b
                 hd[4, 2 + 2 * k] = e
-        for s, p in zip(slots, positions):
+        need = {}
+        for s, p in zip(slots, positions):           # one ensure per sequence (a 4096-row prompt is one sequence)
+            if p >= need.get(s, -1):
+                need[s] = p
+        for s, p in need.items():
             self.pages.ensure(int(s), int(p) + 1)
         self._sync_block_table()
         if segs:

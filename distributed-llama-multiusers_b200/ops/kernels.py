@@ -189,6 +189,28 @@ def gemm_q40_tc(w: torch.Tensor, d: int, n: int, xh: torch.Tensor, ncap: int, M:
     lib.count_launch()
 
 
+def wh_bytes(d: int, n: int) -> int:
+    return int(cuda_lib().dl_wh_bytes(d, n))
+
+
+def q40t_to_wh(q40t: torch.Tensor, d: int, n: int, out: torch.Tensor = None) -> torch.Tensor:
+    """Q40T image -> WH (fp16 tiles in the UMMA core-matrix image) for gemm_wh_tc; `out` = caller's scratch."""
+    if out is None:
+        out = torch.empty(wh_bytes(d, n), dtype=torch.uint8, device=q40t.device)
+    assert out.numel() >= wh_bytes(d, n)
+    check(cuda_lib().dl_q40t_to_wh(q40t.data_ptr(), d, n, out.data_ptr(), _stream()), "dl_q40t_to_wh")
+    lib.count_launch()
+    return out
+
+
+def gemm_wh_tc(wh: torch.Tensor, d: int, n: int, xh: torch.Tensor, ncap: int, M: int, epi: DlEpilogue,
+               force_cg: int = 0, pdl: bool = False):
+    """Prompt-sized batches: persistent fp16 SS-mode tcgen05 GEMM on pre-expanded weights (CTA pairs)."""
+    check(cuda_lib().dl_gemm_wh_tc(wh.data_ptr(), d, n, xh.data_ptr(), ncap, M, C.byref(epi), force_cg,
+                                   1 if pdl else 0, _stream()), "dl_gemm_wh_tc")
+    lib.count_launch()
+
+
 def attention_scratch_bytes(M: int, n_heads: int, head_size: int, max_splits: int) -> int:
     return int(cuda_lib().dl_attention_scratch_bytes(M, n_heads, head_size, max_splits))
 

@@ -146,6 +146,14 @@ long long dl_gemv_q40_smem_bytes(int n, int M, int k_split);
  * TMEM accumulators (reference: llamafile_sgemm Q40xQ80, src/nn/llamafile/sgemm.cpp:593-783) */
 int dl_gemm_q40_tc(const uint8_t* w_q40t, int d, int n, const uint8_t* xh, int ncap, int M, int k_split,
                    const DlEpilogue* epi /*host*/, int pdl, void* stream);
+/* prompt-sized batches, two phases: the Q40T image is expanded once into WH (fp16 tiles of 128 x 128 in the UMMA
+ * K-major core-matrix image, dl_wh_bytes(d, n) bytes), then a persistent SS-mode tcgen05 GEMM with CTA pairs
+ * (cta_group::2, 256 x 256 tiles, double-buffered TMEM accumulators) runs on it; same epilogues as above.
+ * force_cg: 0 = CTA pairs when the number of 128-row tiles is even, 1 = single CTAs */
+long long dl_wh_bytes(int d, int n);
+int dl_q40t_to_wh(const uint8_t* w_q40t, int d, int n, uint8_t* wh, void* stream);
+int dl_gemm_wh_tc(const uint8_t* wh, int d, int n, const uint8_t* xh, int ncap, int M, const DlEpilogue* epi /*host*/,
+                  int force_cg, int pdl, void* stream);
 
 /* ---- attention ---------------------------------------------------------------------------- */
 /* per-row paged GQA attention over positions 0..pos[m] (decode rows and prefill-chunk rows alike);

@@ -37,6 +37,9 @@ def main():
     ap.add_argument("--iters", type=int, default=24)
     ap.add_argument("--gemv-m", default="1,2,4,8")
     ap.add_argument("--tc-m", default="8,16,32,64,128,256")
+    ap.add_argument("--wh-m", default="", help="rows for the two-phase prompt GEMM (gemm_wh_tc), e.g. 256,512,1024,2048,4096")
+    ap.add_argument("--wh-cg", type=int, default=0, help="1 = force single CTAs (no cta_group::2 pairs)")
+    ap.add_argument("--wh-dbg", type=int, default=0, help="timing experiments of gemm_wh_tc (results invalid): 1 no epilogue, 2 no MMAs, 4 no activation copies")
     ap.add_argument("--out", default="")
     ap.add_argument("--shapes", default="qkv,wo,w13,w2,wcls")
     a = ap.parse_args()
@@ -46,6 +49,8 @@ def main():
     shapes = {"qkv": (6144 // N, dim), "wo": (dim, dim // N), "w13": (2 * hid // N, dim), "w2": (dim, hid // N),
               "wcls": (128256 // N, dim)}
     n_sms = K.cuda_lib().dl_device_sm_count()
+    if a.wh_dbg:
+        K.cuda_lib().dl_debug_set_wh_mode(a.wh_dbg)
     rows = []
     for name, (d, n) in shapes.items():
         if name not in a.shapes.split(","):
@@ -56,7 +61,8 @@ def main():
         for w in ws:      # sane fp16 scales (avoid inf/nan patterns)
             v = w.view(-1, 9216)[:, 8192:].view(torch.float16)
             v.copy_(torch.full_like(v, 0.01))
-        y = torch.zeros(256, d, device="cuda")
+        max_m = max([256] + [int(x) for x in (a.tc_m + "," + a.wh_m).split(",") if x])
+        y = torch.zeros(max_m, d, device="cuda")
         epi = K.epi_store([y.data_ptr()], d)
         for M in [int(x) for x in a.gemv_m.split(",") if x]:
             xq = K.alloc_xq(n, M, "cuda")
@@ -88,6 +94,33 @@ def main():
                              gbs=round(wbytes / us / 1e3, 1), frac_hbm=round(wbytes / us / 1e3 / hbm, 3),
                              tflops=round(2.0 * d * n * M / us / 1e6, 1)))
             print(rows[-1], flush=True)
+        wh_ms = [int(x) for x in a.wh_m.split(",") if x]
+        if wh_ms:
+            whs = [K.q40t_to_wh(ws[i], d, n) for i in range(2)]
+            it = [0]
+
+            def run_deq():
+                K.q40t_to_wh(ws[it[0] % copies], d, n, whs[it[0] % 2])
+                it[0] += 1
+            us = timed(run_deq, a.iters)
+            rows.append(dict(kernel="q40t_to_wh", shape=name, d=d, n=n, us=round(us, 2),
+                             gbs=round((wbytes + K.wh_bytes(d, n)) / us / 1e3, 1)))
+            print(rows[-1], flush=True)
+            for M in wh_ms:
+                ncap = (M + 255) // 256 * 256
+                xh = K.alloc_xh(n, ncap, "cuda")
+                x = torch.randn(M, n, device="cuda")
+                K.quant_q80(x, M, n, ncap, None, xh)
+                it = [0]
+
+                def run_wh():
+                    K.gemm_wh_tc(whs[it[0] % 2], d, n, xh, ncap, M, epi, a.wh_cg)
+                    it[0] += 1
+                us = timed(run_wh, a.iters)
+                rows.append(dict(kernel="wh_tc", shape=name, d=d, n=n, M=M, cg=1 if (a.wh_cg == 1 or ((d + 127) // 128) % 2) else 2,
+                                 us=round(us, 2), tflops=round(2.0 * d * n * M / us / 1e6, 1)))
+                print(rows[-1], flush=True)
+            del whs
         del ws
         torch.cuda.empty_cache()
     if a.out:

@@ -164,6 +164,67 @@ def test_gemm_q40_tc_matches_reference(d, n, M, S):
     np.testing.assert_allclose(got, ref, rtol=2e-3, atol=2e-3 * scale)
 
 
+def _decode_wh(wh: torch.Tensor, d: int, n: int) -> np.ndarray:
+    """WH image -> [d_pad][n] fp16 values in natural K order (inverse of the layout in gemm_wh_tc.cu / xh_slot)."""
+    rt, kt = (d + 127) // 128, n // 128
+    a = wh.cpu().numpy().view(np.float16).reshape(rt, kt, 16, 16, 8, 8)        # [rt][kt][row group][chunk][row][slot]
+    slot_of = np.zeros(32, dtype=np.int64)
+    chunk_of = np.zeros(32, dtype=np.int64)
+    for e in range(32):
+        hi, e2 = e >> 4, e & 15
+        w, r = e2 >> 2, e2 & 3
+        chunk_of[e], slot_of[e] = w, hi * 4 + (2 if r == 1 else 1 if r == 2 else r)
+    out = np.zeros((rt * 128, n), dtype=np.float32)
+    for kb in range(4):
+        for e in range(32):
+            v = a[:, :, :, kb * 4 + chunk_of[e], :, slot_of[e]]                 # [rt][kt][16][8]
+            out.reshape(rt, 128, kt, 128)[:, :, :, kb * 32 + e] = v.transpose(0, 2, 3, 1).reshape(rt, 128, kt)
+    return out
+
+
+def test_q40t_to_wh_matches_dequant():
+    k = K()
+    d, n = 300, 512
+    raw, wdq = _rand_q40(d, n, 5)
+    w = k.make_q40t(torch.from_numpy(raw).cuda(), d, n)
+    wh = k.q40t_to_wh(w, d, n)
+    torch.cuda.synchronize()
+    got = _decode_wh(wh, d, n)
+    np.testing.assert_array_equal(got[:d], wdq.astype(np.float16).astype(np.float32))
+    assert not got[d:].any()
+
+
+def _gemm_wh_case(d, n, M, ncap, force_cg, seed):
+    k = K()
+    raw, wdq = _rand_q40(d, n, seed)
+    w = k.make_q40t(torch.from_numpy(raw).cuda(), d, n)
+    wh = k.q40t_to_wh(w, d, n)
+    rng = np.random.default_rng(seed + 1)
+    x = rng.standard_normal((M, n), dtype=np.float32)
+    xh = k.alloc_xh(n, ncap, "cuda")
+    k.quant_q80(torch.from_numpy(x).cuda(), M, n, ncap, None, xh)
+    ref = quant.q80_roundtrip(x).astype(np.float64) @ wdq.astype(np.float64).T
+    y = torch.full((M, d), float("nan"), device="cuda")
+    k.gemm_wh_tc(wh, d, n, xh, ncap, M, k.epi_store([y.data_ptr()], d, 0, False), force_cg)
+    torch.cuda.synchronize()
+    return y.cpu().numpy(), ref
+
+
+@pytest.mark.parametrize("d,n,M,ncap,force_cg", [
+    (256, 256, 256, 256, 1), (256, 256, 256, 256, 0), (128, 512, 40, 64, 0), (512, 1024, 300, 384, 0),
+    (512, 1024, 300, 384, 1), (384, 384, 700, 768, 0), (200, 256, 256, 256, 0),
+    # more tiles than CTAs / clusters: the persistent loop, both accumulators, barrier phases wrapping several times
+    (9728, 1024, 1100, 1152, 0), (9600, 512, 520, 640, 0), (38912, 256, 260, 384, 0), (19456, 128, 512, 512, 1),
+])
+def test_gemm_wh_tc_matches_reference(d, n, M, ncap, force_cg):
+    """Prompt-sized GEMM on pre-expanded weights: CTA pairs (cta_group::2) and single CTAs, partial activation tiles,
+    padded weight rows, several tiles per CTA."""
+    got, ref = _gemm_wh_case(d, n, M, ncap, force_cg, seed=d + n + M)
+    assert not np.isnan(got).any()
+    scale = np.abs(ref).max()
+    np.testing.assert_allclose(got, ref, rtol=2e-3, atol=2e-3 * scale)
+
+
 def _tc_tile(d, M, S, ncap, n_sms=148):
     """The activation tile width dl_gemm_q40_tc picks (mirror of gemm_q40_tc.cu:388-396), so the wide-tile tests
     below fail loudly if a change of the heuristic stops exercising the plans they are meant to cover."""

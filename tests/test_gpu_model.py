@@ -79,6 +79,39 @@ def test_wide_prefill_chunk_matches_oracle(tiny_model_path):
     e.close()
 
 
+@pytest.mark.parametrize("mode", ["resident", "scratch"])
+def test_prompt_sized_batch_on_expanded_weights(tiny_tp_model_path, mode, monkeypatch):
+    """One 500-row prompt forward through the two-phase GEMM (fp16-expanded weights, CTA pairs): same logits as the
+    fused dequantising kernel (identical operand values, different summation order), the oracle at sampled rows, and
+    a decode step that reads the KV cache the big batch wrote."""
+    import dllama_b200.models.llama as LL
+    monkeypatch.setattr(LL, "WH_MIN_ROWS", 256)
+    monkeypatch.setattr(LL, "WH_MIN_ROWS_SCRATCH", 256)
+    o = _oracle(tiny_tp_model_path)
+    rng = np.random.default_rng(11)
+    n = 500
+    prompt = rng.integers(1, 2048, n).tolist()
+    outs = {}
+    for wh in (mode, "off"):
+        e = _engine(tiny_tp_model_path, max_rows=512, n_slots=2, use_graphs=True, use_pdl=True, prefill_wh=wh)
+        assert e.wh_mode == wh
+        slot = e.alloc_slot()
+        lg = e.forward(prompt, list(range(n)), [slot] * n, logits_from=n - 4).float().cpu().numpy()
+        nxt = e.forward([5], [n], [slot]).float().cpu().numpy()
+        outs[wh] = (lg, nxt)
+        e.close()
+    ref = o.forward(prompt, 0).numpy()
+    ref1 = o.forward([5], n).numpy()
+    errs = {wh: [_rel_err(outs[wh][0][i], ref[t]) for i, t in enumerate(range(n - 4, n))] + [_rel_err(outs[wh][1][0], ref1[0])]
+            for wh in outs}
+    cross = [_rel_err(outs[mode][0], outs["off"][0]), _rel_err(outs[mode][1], outs["off"][1])]
+    print("errors vs oracle:", errs, "between the two kernels:", cross)
+    assert max(errs[mode]) < 3e-2, errs
+    # the two kernels see identical operand values and differ only in summation order; a Q80 rounding flip downstream
+    # is worth up to 1/127 of a block's range, so they agree to about the same tolerance as with the oracle
+    assert max(cross) < 2e-2, cross
+
+
 def test_prompt_chunk_mixed_with_decode_rows(tiny_model_path):
     """A batch holding a 40-row prompt chunk of one sequence plus decode rows of two others: the chunk goes
     through the tensor-core prefill attention, the other rows through the per-row kernel (row_skip)."""
