@@ -375,7 +375,8 @@ extern "C" int dl_attention(const float* q, int M, int n_heads, int n_kv_heads, 
     a.q = q; a.k_cache = k_cache; a.v_cache = v_cache; a.pos = pos; a.slot = slot; a.block_table = block_table;
     a.row_skip = row_skip;
     a.M = M; a.n_heads = n_heads; a.n_kv_heads = n_kv_heads; a.max_pages = max_pages; a.n_splits = n_splits;
-    if (n_splits > 1 && (long long)M * n_kv_heads * 4 > ATT_COUNTER_BYTES) {      // counters are only touched by split rows dl_set_error("dl_attention: M*n_kv_heads too large"); return -1; }
+    // the completion counters are only touched by rows that are split
+    if (n_splits > 1 && (long long)M * n_kv_heads * 4 > ATT_COUNTER_BYTES) { dl_set_error("dl_attention: M*n_kv_heads too large"); return -1; }
     long long o = ((long long)M * n_heads * n_splits * head_size * 4 + 255) / 256 * 256;
     a.counters = reinterpret_cast<unsigned*>(scratch);
     a.part_o = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(scratch) + ATT_COUNTER_BYTES);

@@ -407,20 +407,29 @@ extern "C" int dl_argmax(const float* logits, int M, int vocab, int ld, int* tok
     a.scratch = reinterpret_cast<uint8_t*>(scratch);
     a.tr = dl_trace_next(TR_ARGMAX);
     if (history != nullptr && step_counter == nullptr) { dl_set_error("dl_argmax: history needs step_counter"); return -1; }
-    if (scratch == nullptr || M > 256) { dl_set_error("dl_argmax: needs zero-initialised scratch (dl_argmax_scratch_bytes) and M <= 256"); return -1; }
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(ARGMAX_CHUNKS, M);
-    cfg.blockDim = dim3(ARGMAX_THREADS);
-    cfg.stream = (cudaStream_t)stream;
-    cudaLaunchAttribute attr[1];
-    if (pdl) {
-        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-        attr[0].val.programmaticStreamSerializationAllowed = 1;
-        cfg.attrs = attr;
-        cfg.numAttrs = 1;
+    if (scratch == nullptr) { dl_set_error("dl_argmax: needs zero-initialised scratch (dl_argmax_scratch_bytes(min(M, 256)))"); return -1; }
+    if (M > 256 && history != nullptr) { dl_set_error("dl_argmax: the device-loop history supports M <= 256"); return -1; }
+    // the scratch holds 256 rows of counters and chunk winners: larger batches go through it 256 rows at a time
+    // (launches on one stream run in order, and the counters return to zero)
+    for (int m0 = 0; m0 < M; m0 += 256) {
+        const int mb = (M - m0 < 256) ? M - m0 : 256;
+        a.logits = logits + (size_t)m0 * ld;
+        a.tokens_out = tokens_out + m0;
+        a.pos_inc = pos_inc != nullptr ? pos_inc + m0 : nullptr;
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(ARGMAX_CHUNKS, mb);
+        cfg.blockDim = dim3(ARGMAX_THREADS);
+        cfg.stream = (cudaStream_t)stream;
+        cudaLaunchAttribute attr[1];
+        if (pdl && m0 == 0) {
+            attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            attr[0].val.programmaticStreamSerializationAllowed = 1;
+            cfg.attrs = attr;
+            cfg.numAttrs = 1;
+        }
+        cudaError_t e = cudaLaunchKernelEx(&cfg, argmax_kernel, a);
+        if (e != cudaSuccess) { dl_set_error("dl_argmax: %s", cudaGetErrorString(e)); return -(int)e; }
     }
-    cudaError_t e = cudaLaunchKernelEx(&cfg, argmax_kernel, a);
-    if (e != cudaSuccess) { dl_set_error("dl_argmax: %s", cudaGetErrorString(e)); return -(int)e; }
     return 0;
 }
 

@@ -669,6 +669,11 @@ def test_argmax_and_embedding():
     got = out.cpu().numpy()
     assert got[2] == 17 and got[3] == 0
     np.testing.assert_array_equal(got[[0, 1, 4]], ref[[0, 1, 4]])
+    big = torch.randn(600, 777, device="cuda")          # more rows than the scratch holds at once: 256-row passes
+    out = torch.zeros(600, dtype=torch.int32, device="cuda")
+    k.argmax(big, 600, 777, 777, out)
+    torch.cuda.synchronize()
+    np.testing.assert_array_equal(out.cpu().numpy(), big.argmax(dim=-1).cpu().numpy())
     table = torch.randn(50, 256, device="cuda")
     toks = torch.tensor([3, 49, 0], dtype=torch.int32, device="cuda")
     x = torch.zeros(3, 256, device="cuda")
