@@ -637,8 +637,41 @@ class LlamaEngine:
         if logits_from == M - 1:              # prompt chunk or single decode row: only the last row's logits
             self._run(Mp, Mp - 1, greedy)
             return 0
+        tail = self._tail_rows(Mp)
+        if tail and M - logits_from <= tail:  # prompt rows + a few sampling rows: logits of the last `tail` rows only
+            self._run(Mp, Mp - tail, greedy)
+            return tail - (M - logits_from)
         self._run(Mp, 0, greedy)              # logits of every row; the caller's rows are the tail
         return (Mp - M) + logits_from
+
+    def _bucket(self, M: int) -> int:
+        """Padded row count of a bucket_rows batch: powers of two up to 256, then multiples of 256 (a 1091-row batch
+        runs as 1280 rows, not 2048)."""
+        if M <= 256:
+            Mp = 1
+            while Mp < M:
+                Mp *= 2
+        else:
+            Mp = _round_up(M, 256)
+        return min(Mp, self.max_rows)
+
+    def _buckets(self) -> List[int]:
+        out, m = [], 1
+        while m < min(256, self.max_rows):
+            out.append(m)
+            m *= 2
+        out += list(range(256, self.max_rows + 1, 256)) if self.max_rows >= 256 else []
+        if not out or out[-1] != self.max_rows:
+            out.append(self.max_rows)
+        return out
+
+    def _tail_rows(self, Mp: int) -> int:
+        """Large mixed batches (prompt rows of many requests + their sampling rows): the wcls matmul, the logits write
+        and the argmax run on the last `tail` rows (>= one row per sequence slot) instead of on every row."""
+        tail = 1
+        while tail < min(self.n_slots, 256):
+            tail *= 2
+        return tail if Mp >= 2 * tail else 0
 
     def warmup_graphs(self):
         """Capture every CUDA graph a bucket_rows engine can ask for (power-of-two row counts x {all-row
@@ -646,26 +679,24 @@ class LlamaEngine:
         ever waits for a capture.  Every rank must call it at the same point (it runs real forwards)."""
         assert self.bucket_rows and self.use_graphs
         hd = self.h_desc.numpy()
-        Mp = 1
-        while True:
-            Mp = min(Mp, self.max_rows)
+        for Mp in self._buckets():
             hd[0, :Mp] = 0
             hd[1, :Mp] = 0
             hd[2, :Mp] = self._pad_slot
             self.desc.copy_(self.h_desc, non_blocking=True)
-            for row0 in sorted({0, Mp - 1}):
-                for greedy in (False, True):
-                    self._run(Mp, row0, greedy, chunk=False)
+            tail = self._tail_rows(Mp)
+            row0s = sorted({0, Mp - 1} | ({Mp - tail} if tail else set()))
+            if Mp <= 256:                                    # decode-sized batches without prompt chunks
+                for row0 in row0s:
+                    for greedy in (False, True):
+                        self._run(Mp, row0, greedy, chunk=False)
             if self.prefill_attention and Mp >= 16:          # batches that contain prompt chunks
                 hd[3, :Mp] = 0
                 hd[4, 0] = 0                                 # no segment: both kernels run, the prefill one exits at once
                 self.desc.copy_(self.h_desc, non_blocking=True)
-                for row0 in sorted({0, Mp - 1}):
+                for row0 in row0s:
                     for greedy in (False, True):
                         self._run(Mp, row0, greedy, chunk=True)
-            if Mp >= self.max_rows:
-                break
-            Mp *= 2
         torch.cuda.synchronize()
 
     # ------------------------------------------------------------------------------------------------
@@ -694,10 +725,7 @@ class LlamaEngine:
             return 1
         off = 0
         if self.bucket_rows:
-            Mp = 1
-            while Mp < M:
-                Mp *= 2
-            Mp = min(Mp, self.max_rows)
+            Mp = self._bucket(M)
             off = Mp - M                      # padding rows first, real rows last (the last row stays last)
             hd[0, :off] = 0
             hd[1, :off] = 0

@@ -14,6 +14,7 @@ from __future__ import annotations
 import ctypes as C
 import os
 import threading
+import time
 from typing import Optional
 
 import torch
@@ -69,6 +70,8 @@ class NativeApiServer:
         self._stop = threading.Event()
         self._thread: Optional[threading.Thread] = None
         self.n_errors = 0
+        # DLLAMA_STEP_LOG=1: (start time, rows, first logits row, sampled rows, seconds) of every step, for load tests
+        self.step_log = [] if os.environ.get("DLLAMA_STEP_LOG") == "1" else None
 
     # ---- lifecycle -------------------------------------------------------------------------------------
     def warmup(self):
@@ -137,6 +140,7 @@ class NativeApiServer:
         """One scheduler step = one forward pass.  Returns the number of rows run."""
         L, h, eng, R = self._L, self._h, self.engine, self.max_rows
         p = self._ptrs
+        t_step = time.perf_counter() if self.step_log is not None else 0.0
         n = L.dl_srv_next_batch(h, p[0], p[1], p[2], R, C.byref(self._lf), C.byref(self._ns), p[3], p[4], p[5],
                                 int(self._device_sampler), C.byref(self._greedy), C.addressof(self._released), 256,
                                 C.byref(self._nrel))
@@ -177,4 +181,6 @@ class NativeApiServer:
             rc = L.dl_srv_commit(h, n_s, self._h_tok.data_ptr())
         if rc < 0:
             raise RuntimeError(f"dl_srv_commit failed ({rc})")
+        if self.step_log is not None:
+            self.step_log.append((t_step, n, lf, n_s, time.perf_counter() - t_step))
         return n

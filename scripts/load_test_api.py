@@ -96,6 +96,9 @@ def _client_proc(port, users, first_user, max_tokens, prompt_words, temperature,
                         ntok[k] = json.loads(ev[6:])["usage"]["completion_tokens"]
 
     threads = [threading.Thread(target=user, args=(k,)) for k in range(users)]
+    # first use of urllib in a fresh interpreter imports http.client, email, socket ... (60+ ms): keep that out of
+    # the users' time to first token
+    urllib.request.urlopen(f"http://127.0.0.1:{port}/health", timeout=30).read()
     q.put("ready")
     go.wait()                      # interpreter start-up (imports) stays outside the timed window
     [t.start() for t in threads]
@@ -192,6 +195,12 @@ def main():
         got = [q.get(timeout=900) for _ in procs]
         wall = time.perf_counter() - t0
         [p.join() for p in procs]
+        log = getattr(srv, "step_log", None)
+        if log and rnd == a.rounds - 1:
+            mine = [e for e in log if e[0] >= t0]
+            print("first steps of the last round (ms after go, rows, first logits row, sampled rows, step ms):")
+            for e in mine[:24]:
+                print(f"   {1e3 * (e[0] - t0):8.2f}  rows {e[1]:5d}  logits_from {e[2]:5d}  sampled {e[3]:3d}  {1e3 * e[4]:7.2f} ms")
         tt = sorted(x for g in got for x in g[0] if x is not None)
         c1 = counters()
         total = c1[0] - c0[0]              # server-side counter (also exported at /metrics)
