@@ -35,6 +35,8 @@ struct WhArgs {
     const uint8_t* xh;                 // [KT][ncap/8][2048]
     int d_real, row_tiles, KT, ncap, M, m_tiles, n_tiles;
     int n_epi_ctas;
+    int piece;                         // bytes per bulk copy (4096 / 8192 / 16384)
+    int pf_dist, pf_mask;              // weight tiles are pulled into L2 pf_dist k-steps ahead by the CTAs whose activation tile index & pf_mask == 0
     int dbg;                           // timing experiments (results invalid): 1 = no epilogue work, 2 = no MMAs, 4 = no activation copies
     unsigned long long* tr;
     DlEpilogue epi;
@@ -107,7 +109,6 @@ __global__ void __launch_bounds__(WT_THREADS, 1) gemm_wh_tc_kernel(const __grid_
     constexpr int NS = (CG == 1) ? 2 : 3;                 // stages of one 128-wide k step
     constexpr int B_ROWS = WT_NT / CG;                    // activation rows staged by this CTA
     constexpr int STAGE = WH_TILE_BYTES + B_ROWS * 256;   // 96 KB / 64 KB
-    constexpr int NPIECE = STAGE / WT_PIECE;              // 6 / 4 issuing lanes
     trace_begin(a.tr);
     const unsigned long long t0 = globaltimer_ns();
     float* out_s = reinterpret_cast<float*>(smem + NS * STAGE);          // [32][128]
@@ -148,8 +149,10 @@ __global__ void __launch_bounds__(WT_THREADS, 1) gemm_wh_tc_kernel(const __grid_
 
     if (warp == 0) {
         // ------------------------------------ producer ------------------------------------
-        // lanes 0,1: the two halves of the weight tile; lanes 2..: 64-row pieces of the activation slab
-        if (lane < NPIECE) {
+        // the stage is fetched as `piece`-byte bulk copies, one per lane: first the weight tile, then row groups of the
+        // activation slab (many requests in flight: one bulk copy streams at only ~16 B/clk)
+        const int piece = a.piece, npiece = STAGE / piece, na = WH_TILE_BYTES / piece, prow = piece / 256;
+        if (lane < npiece) {
             pdl_wait();
             const size_t x_kt_stride = (size_t)(a.ncap >> 3) * XH_ROWGROUP_BYTES;
             uint32_t it = 0;
@@ -161,22 +164,33 @@ __global__ void __launch_bounds__(WT_THREADS, 1) gemm_wh_tc_kernel(const __grid_
                 const uint8_t* src;
                 size_t stride;
                 uint32_t bytes;
-                if (lane < 2) {
-                    src = a.wh + (size_t)rt * KT * WH_TILE_BYTES + lane * WT_PIECE;
+                if (lane < na) {
+                    src = a.wh + (size_t)rt * KT * WH_TILE_BYTES + lane * piece;
                     stride = WH_TILE_BYTES;
-                    bytes = WT_PIECE;
+                    bytes = piece;
                 } else {
-                    const int r0 = (lane - 2) * 64;
+                    const int r0 = (lane - na) * prow;
                     src = a.xh + (size_t)((mrow0 + r0) >> 3) * XH_ROWGROUP_BYTES;
                     stride = x_kt_stride;
-                    bytes = (a.dbg & 4) ? 0u : (uint32_t)max(0, min(64, b_rows - r0)) * 256u;
+                    bytes = (a.dbg & 4) ? 0u : (uint32_t)max(0, min(prow, b_rows - r0)) * 256u;
                 }
                 const uint32_t total = WH_TILE_BYTES + ((a.dbg & 4) ? 0u : (uint32_t)b_rows * 256u);
+                const bool pf = lane < na && a.pf_dist > 0 && (mt & a.pf_mask) == 0;
                 for (int kt = 0; kt < KT; kt++, it++) {
+                    if (pf) {      // optional: pull the weight tile pf_dist k-steps ahead into L2 (measured: no gain, off by default)
+                        int j = kt + a.pf_dist, tt = t;
+                        while (j >= KT) { j -= KT; tt += ncl; }
+                        if (tt < a.n_tiles) {
+                            const int rt2 = (tt / m_tiles) * CG + (int)crank;
+                            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a.wh + ((size_t)rt2 * KT + j) * WH_TILE_BYTES + lane * piece),
+                                         "r"(piece)
+                                         : "memory");
+                        }
+                    }
                     const uint32_t s = it % NS;
                     if (it >= NS) wt_wait(&empty[s], ((it / NS) & 1) ^ 1, t0);
                     if (lane == 0) mbar_arrive_expect_tx(&full[s], total);
-                    if (bytes) bulk_g2s(smem + s * STAGE + lane * WT_PIECE, src + (size_t)kt * stride, bytes, &full[s]);
+                    if (bytes) bulk_g2s(smem + s * STAGE + lane * piece, src + (size_t)kt * stride, bytes, &full[s]);
                 }
             }
         }
@@ -314,8 +328,10 @@ __global__ void __launch_bounds__(512) q40t_to_wh_kernel(const uint8_t* __restri
 extern void dl_set_error(const char* fmt, ...);
 extern "C" int dl_device_sm_count();
 
-static int g_wh_dbg = 0;
+static int g_wh_dbg = 0, g_wh_pf_dist = 0, g_wh_pf_mask = 0, g_wh_piece = 16384;
+extern "C" void dl_debug_set_wh_piece(int b) { if (b == 4096 || b == 8192 || b == 16384) g_wh_piece = b; }
 extern "C" void dl_debug_set_wh_mode(int m) { g_wh_dbg = m; }
+extern "C" void dl_debug_set_wh_prefetch(int dist, int mask) { g_wh_pf_dist = dist; g_wh_pf_mask = mask; }
 
 extern "C" long long dl_wh_bytes(int d, int n) { return (long long)((d + 127) / 128) * (n / 128) * WH_TILE_BYTES; }
 
@@ -347,6 +363,9 @@ extern "C" int dl_gemm_wh_tc(const uint8_t* wh, int d, int n, const uint8_t* xh,
     a.n_epi_ctas = grid;
     a.epi = *epi;
     a.dbg = g_wh_dbg;
+    a.pf_dist = g_wh_pf_dist < a.KT ? g_wh_pf_dist : 0;
+    a.pf_mask = g_wh_pf_mask;
+    a.piece = g_wh_piece;
     a.tr = dl_trace_next(TR_TC);
     const size_t smem = 196608 + WT_EPI_CHUNK * 128 * 4 + 16 * 8 + 16;
     static bool attr_set = false;

@@ -40,6 +40,8 @@ def main():
     ap.add_argument("--wh-m", default="", help="rows for the two-phase prompt GEMM (gemm_wh_tc), e.g. 256,512,1024,2048,4096")
     ap.add_argument("--wh-cg", type=int, default=0, help="1 = force single CTAs (no cta_group::2 pairs)")
     ap.add_argument("--wh-dbg", type=int, default=0, help="timing experiments of gemm_wh_tc (results invalid): 1 no epilogue, 2 no MMAs, 4 no activation copies")
+    ap.add_argument("--wh-pf", default="", help="gemm_wh_tc L2 prefetch: distance,mask (k-steps ahead, activation-tile mask)")
+    ap.add_argument("--wh-piece", type=int, default=0, help="gemm_wh_tc bytes per bulk copy (4096, 8192, 16384)")
     ap.add_argument("--out", default="")
     ap.add_argument("--shapes", default="qkv,wo,w13,w2,wcls")
     a = ap.parse_args()
@@ -51,6 +53,10 @@ def main():
     n_sms = K.cuda_lib().dl_device_sm_count()
     if a.wh_dbg:
         K.cuda_lib().dl_debug_set_wh_mode(a.wh_dbg)
+    if a.wh_piece:
+        K.cuda_lib().dl_debug_set_wh_piece(a.wh_piece)
+    if a.wh_pf:
+        K.cuda_lib().dl_debug_set_wh_prefetch(*[int(x) for x in a.wh_pf.split(",")])
     rows = []
     for name, (d, n) in shapes.items():
         if name not in a.shapes.split(","):
