@@ -1,0 +1,431 @@
+// Causal attention for long prompt chunks on the 5th-gen tensor cores (head size 128): the same job as
+// attention_prefill.cu (segments of consecutive positions of one sequence, listed in `meta`), with both products
+// as tcgen05.mma and the score / probability / output tiles in TENSOR MEMORY instead of registers.
+//
+// A CTA owns 128 query rows x one query head and walks the KV history 128 tokens (four pages) at a time:
+//   S = Q K^T     SS-mode MMA, M = 128 rows, N = 128 tokens, K = 128: Q staged once (fp16, K-major core matrices),
+//                 K pages copied with cp.async into the same core-matrix image; S (f32) lands in TMEM, double-buffered
+//   softmax       one thread per query row (= TMEM lane): two passes over S with tcgen05.ld (row maximum, then
+//                 exp2 -> fp16 probabilities written back to TMEM with tcgen05.st); running maximum with LAZY
+//                 rescaling: the reference maximum only moves when a row's maximum grew by more than 2^8, so in the
+//                 steady state the output accumulator is never touched by the softmax threads
+//   O += P V      TS-mode MMA: A = P straight from TMEM, B = V pages in shared memory as an MN-major operand (V is
+//                 [token][head dim] in the cache, i.e. N-contiguous: no transpose anywhere), accumulating in TMEM
+// The MMA warp issues S(j+1) before P(j) V(j), so the tensor core works on the next scores while the softmax threads
+// are busy with the current ones.  Output: O / l -> shared memory -> Q80 cast into the XQ / XH slabs of the wo matmul.
+//
+// Warp roles (288 threads): warp 0 MMA issuer + TMEM owner, warps 1-4 softmax (row = TMEM lane), warps 5-8 KV producers.
+// TMEM columns: S0 [0,128) S1 [128,256) P0 [256,320) P1 [320,384) O [384,512).
+// Reference semantics: multiheadAtt_F32 (src/nn/nn-cpu-ops.cpp:749-784), softmax in f32, output cast as OP_CAST
+// (src/llm.cpp:296-301).  KV cache: fp16 pages [page][kv_head][32][128].
+#include "epilogue.cuh"
+
+#define PT_HS 128
+#define PT_ROWS 128
+#define PT_KV 128                      // tokens per step
+#define PT_THREADS 288
+#define PT_MAX_SEG 8
+#define PT_TILE_BYTES 32768            // 128 x 128 fp16
+#define PT_STAGES 3                    // KV tiles in flight (K + V: 64 KB each)
+#define PT_OUT_LD 129
+#define PT_DEADLINE_NS 4000000000ull
+
+struct PtArgs {
+    const float* q;            // [M][n_heads*128]
+    const __half* k_cache;     // [pages][n_kv][32][128]
+    const __half* v_cache;
+    const int* pos;
+    const int* slot;
+    const int* block_table;
+    const int* meta;           // meta[0] = n_seg, then [begin, end) pairs
+    int M, n_heads, n_kv_heads, max_pages;
+    uint8_t* xq_out;
+    uint8_t* xh_out;
+    int out_mcap;
+    float* y_out;
+    long long* stamps;         // debug: clock64 stamps of CTA (0, 0), [tile][8]
+    int dbg;                   // timing experiments (results invalid): 1 = no softmax arithmetic, 2 = no KV copies, 4 = no MMAs
+    unsigned long long* tr;
+};
+
+DL_DEVINL void pt_wait(uint64_t* bar, uint32_t parity, unsigned long long t0) {
+    unsigned n = 0;
+    while (!mbar_try_wait(bar, parity)) {
+        if ((++n & 0x3FFu) == 0 && globaltimer_ns() - t0 > PT_DEADLINE_NS) __trap();
+    }
+}
+DL_DEVINL void pt_cp_async16(uint32_t smem_dst, const void* gsrc) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_dst), "l"(gsrc) : "memory");
+}
+DL_DEVINL void tmem_ld_32x32b_x32(uint32_t taddr, uint32_t (&v)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, %17, %18, %19, "
+        "%20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
+          "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]),
+          "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]),
+          "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr)
+        : "memory");
+}
+DL_DEVINL void tmem_st_32x32b_x32(uint32_t taddr, const uint32_t (&v)[32]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, %17, %18, %19, "
+        "%20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};" ::"r"(taddr),
+        "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]), "r"(v[9]), "r"(v[10]),
+        "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]), "r"(v[16]), "r"(v[17]), "r"(v[18]), "r"(v[19]), "r"(v[20]),
+        "r"(v[21]), "r"(v[22]), "r"(v[23]), "r"(v[24]), "r"(v[25]), "r"(v[26]), "r"(v[27]), "r"(v[28]), "r"(v[29]), "r"(v[30]),
+        "r"(v[31])
+        : "memory");
+}
+// instruction descriptor, kind::f16: A fp16 K-major (or TMEM), B fp16 with selectable major-ness, D f32
+DL_DEVINL uint32_t pt_idesc(int M, int N, int b_mn_major) {
+    uint32_t d = 0;
+    d |= 1u << 4;                                  // D = f32
+    d |= (uint32_t)(b_mn_major & 1) << 16;         // b_major: 0 = K, 1 = MN
+    d |= (uint32_t)(N >> 3) << 17;
+    d |= (uint32_t)(M >> 4) << 24;
+    return d;
+}
+#define PT_STAMP(slot, j) do { if (a.stamps && blockIdx.x == 0 && blockIdx.y == 0 && (j) < 64) a.stamps[(j) * 8 + (slot)] = clock64(); } while (0)
+
+DL_DEVINL float pt_ex2(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+DL_DEVINL uint32_t pt_pack_half2(float lo, float hi) {
+    __half2 h = __floats2half2_rn(lo, hi);
+    return *reinterpret_cast<uint32_t*>(&h);
+}
+
+// 32 scores (masked ones are -inf) -> exp2(s * sc - ref) as 16 packed fp16 pairs into TMEM; returns their sum
+DL_DEVINL float pt_probs(const uint32_t (&v)[32], float sc, float ref, uint32_t taddr) {
+    uint32_t pk[16];
+    float sum = 0.0f;
+#pragma unroll
+    for (int e = 0; e < 32; e += 2) {
+        const float pa = pt_ex2(fmaf(__uint_as_float(v[e]), sc, -ref));
+        const float pb = pt_ex2(fmaf(__uint_as_float(v[e + 1]), sc, -ref));
+        sum += pa + pb;
+        pk[e >> 1] = pt_pack_half2(pa, pb);
+    }
+    tmem_st_32x32b_x16(taddr, pk);
+    return sum;
+}
+
+__global__ void __launch_bounds__(PT_THREADS, 1) attention_prefill_tc_kernel(const __grid_constant__ PtArgs a) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    trace_begin(a.tr);
+    const unsigned long long t0 = globaltimer_ns();
+    uint8_t* q_s = smem;                                        // Q tile, K-major core matrices
+    uint8_t* k_s = smem + PT_TILE_BYTES;                        // [3] K tiles (tokens x head dim, K-major)
+    uint8_t* v_s = k_s + PT_STAGES * PT_TILE_BYTES;             // [3] V tiles (tokens x head dim, MN-major for P V)
+    float* out_s = reinterpret_cast<float*>(k_s);               // [128][129] f32, reuses the KV stages after the loop
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (1 + 2 * PT_STAGES) * PT_TILE_BYTES);
+    uint64_t* kv_full = bars;            // [3] 128 producer arrivals
+    uint64_t* kv_empty = bars + 3;       // [3] P V of the tile has retired
+    uint64_t* q_full = bars + 6;
+    uint64_t* s_full = bars + 7;         // [2] scores complete
+    uint64_t* p_full = bars + 9;         // [2] probabilities written (and the score buffer read)
+    uint64_t* o_full = bars + 11;        // [2] P V of tile j complete (barrier j & 1)
+    uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(bars + 13);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int head = blockIdx.y;
+    const int kvh = head / (a.n_heads / a.n_kv_heads);
+    pdl_launch_dependents();
+    pdl_wait();                                                  // q, this chunk's KV rows and meta come from earlier kernels
+    // which (segment, 128-row tile) is this CTA?  Large tiles (late rows: long histories) are handed out first.
+    int tile = blockIdx.x, begin = 0, end = 0;
+    {
+        const int n_seg = min(a.meta[0], PT_MAX_SEG);
+        int i = 0;
+        for (; i < n_seg; i++) {
+            begin = a.meta[1 + 2 * i];
+            end = a.meta[2 + 2 * i];
+            const int nt = (end - begin + PT_ROWS - 1) / PT_ROWS;
+            if (tile < nt) { tile = nt - 1 - tile; break; }
+            tile -= nt;
+        }
+        if (i == n_seg) { trace_end(a.tr); return; }
+    }
+    const int n_rows = end - begin;
+    const int r_first = tile * PT_ROWS;
+    const int rows_here = min(PT_ROWS, n_rows - r_first);
+    const int p0 = a.pos[begin];
+    const int* bt = a.block_table + (size_t)a.slot[begin] * a.max_pages;
+    const int last_pos = p0 + r_first + rows_here - 1;
+    const int seq_end = p0 + n_rows;                             // tokens of this sequence that exist
+    const int n_tiles = last_pos / PT_KV + 1;
+
+    if (tid == 0) {
+        for (int s = 0; s < PT_STAGES; s++) {
+            mbar_init(&kv_full[s], 128);
+            mbar_init(&kv_empty[s], 1);
+        }
+        for (int s = 0; s < 2; s++) {
+            mbar_init(&s_full[s], 1);
+            mbar_init(&p_full[s], 128);
+            mbar_init(&o_full[s], 1);
+        }
+        mbar_init(q_full, 128);
+        mbar_fence_init();
+    }
+    if (warp == 0) tmem_alloc(tmem_holder, 512);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_holder;
+    const uint32_t T_S = tmem_base, T_P = tmem_base + 256, T_O = tmem_base + 384;
+
+    if (warp == 0) {
+        // ------------------------------------ MMA issuer ------------------------------------
+        const uint32_t idesc_s = pt_idesc(PT_ROWS, PT_KV, 0), idesc_pv = pt_idesc(PT_ROWS, PT_HS, 1);
+        const uint32_t desc_hi = (2048u >> 4) | (1u << 14);
+        auto desc_lo = [](const void* p) { return ((smem_u32(p) & 0x3FFFFu) >> 4) | ((128u >> 4) << 16); };
+        auto issue_pv = [&](int i) {
+            pt_wait(&p_full[i & 1], (i >> 1) & 1, t0);
+            if (lane == 0) PT_STAMP(2, i);
+            tc_fence_after();
+            if (elect_one()) {
+                const uint32_t b_lo = desc_lo(v_s + (i % PT_STAGES) * PT_TILE_BYTES);
+#pragma unroll
+                for (int k = 0; k < 8; k++) {      // 16 tokens per MMA: 8 TMEM columns of P, two token groups (256 B) of V
+                    uint64_t db;
+                    asm("mov.b64 %0, {%1, %2};" : "=l"(db) : "r"(b_lo + k * 16), "r"(desc_hi));
+                    if (!(a.dbg & 4)) umma_f16_ts(T_O, T_P + (i & 1) * 64 + k * 8, db, idesc_pv, (i > 0 || k > 0) ? 1u : 0u);
+                }
+                umma_commit(&o_full[i & 1]);
+                umma_commit(&kv_empty[i % PT_STAGES]);
+            }
+            __syncwarp();
+        };
+        pt_wait(q_full, 0, t0);
+        for (int j = 0; j < n_tiles; j++) {
+            pt_wait(&kv_full[j % PT_STAGES], (j / PT_STAGES) & 1, t0);
+            if (lane == 0) PT_STAMP(0, j);
+            if (j >= 2) pt_wait(&p_full[j & 1], ((j - 2) >> 1) & 1, t0);      // softmax(j-2) has read this score buffer
+            tc_fence_after();
+            if (elect_one()) {
+                const uint32_t a_lo = desc_lo(q_s), b_lo = desc_lo(k_s + (j % PT_STAGES) * PT_TILE_BYTES);
+#pragma unroll
+                for (int k = 0; k < 8; k++) {
+                    uint64_t da, db;
+                    asm("mov.b64 %0, {%1, %2};" : "=l"(da) : "r"(a_lo + k * 16), "r"(desc_hi));
+                    asm("mov.b64 %0, {%1, %2};" : "=l"(db) : "r"(b_lo + k * 16), "r"(desc_hi));
+                    if (!(a.dbg & 4)) umma_f16_ss(T_S + (j & 1) * 128, da, db, idesc_s, k > 0 ? 1u : 0u);
+                }
+                umma_commit(&s_full[j & 1]);
+            }
+            __syncwarp();
+            if (lane == 0) PT_STAMP(1, j);
+            if (j >= 1) issue_pv(j - 1);
+        }
+        issue_pv(n_tiles - 1);
+    } else if (warp <= 4) {
+        // ------------------------------------ softmax: thread = query row = TMEM lane ------------------------------------
+        const int quarter = warp & 3, row = quarter * 32 + lane;
+        const int r_abs = r_first + row;
+        {
+            const float* qg = a.q + (size_t)(begin + min(r_abs, n_rows - 1)) * a.n_heads * PT_HS + head * PT_HS;
+            uint8_t* qd = q_s + (row >> 3) * 2048 + (row & 7) * 16;
+#pragma unroll 4
+            for (int c = 0; c < 16; c++) {
+                const float4 x = reinterpret_cast<const float4*>(qg)[2 * c], y = reinterpret_cast<const float4*>(qg)[2 * c + 1];
+                uint4 u;
+                u.x = pt_pack_half2(x.x, x.y); u.y = pt_pack_half2(x.z, x.w);
+                u.z = pt_pack_half2(y.x, y.y); u.w = pt_pack_half2(y.z, y.w);
+                *reinterpret_cast<uint4*>(qd + c * 128) = u;
+            }
+            fence_proxy_async_smem();
+            mbar_arrive(q_full);
+        }
+        const int pos_r = p0 + r_abs;
+        const uint32_t lane_base = (uint32_t)(quarter * 32) << 16;
+        const float sc = 1.4426950408889634f * rsqrtf((float)PT_HS);      // scores in the log2 domain
+        float m_used = -INFINITY, l = 0.0f;
+        uint32_t v0[32], v1[32], v2[32], v3[32];
+        for (int j = 0; j < n_tiles; j++) {
+            pt_wait(&s_full[j & 1], (j >> 1) & 1, t0);
+            if (tid == 32) PT_STAMP(3, j);
+            tc_fence_after();
+            const uint32_t t_s = T_S + lane_base + (j & 1) * 128;
+            const int tok0 = j * PT_KV;
+            if (a.dbg & 1) { tc_fence_before(); mbar_arrive(&p_full[j & 1]); continue; }
+            // the whole score row in registers: four loads in flight, one wait
+            tmem_ld_32x32b_x32(t_s, v0);
+            tmem_ld_32x32b_x32(t_s + 32, v1);
+            tmem_ld_32x32b_x32(t_s + 64, v2);
+            tmem_ld_32x32b_x32(t_s + 96, v3);
+            tmem_ld_wait();
+            const int lim = pos_r - tok0;                    // columns e <= lim are visible to this row
+            const bool full = lim >= PT_KV - 1;              // no masking in this tile (all but the last tile or two)
+            float mx = -INFINITY;
+            if (full) {
+#pragma unroll
+                for (int e = 0; e < 32; e++)
+                    mx = fmaxf(mx, fmaxf(fmaxf(__uint_as_float(v0[e]), __uint_as_float(v1[e])), fmaxf(__uint_as_float(v2[e]), __uint_as_float(v3[e]))));
+            } else {
+#pragma unroll
+                for (int e = 0; e < 32; e++) {
+                    if (e > lim) v0[e] = 0xff800000u;        // -inf
+                    if (e + 32 > lim) v1[e] = 0xff800000u;
+                    if (e + 64 > lim) v2[e] = 0xff800000u;
+                    if (e + 96 > lim) v3[e] = 0xff800000u;
+                    mx = fmaxf(mx, fmaxf(fmaxf(__uint_as_float(v0[e]), __uint_as_float(v1[e])), fmaxf(__uint_as_float(v2[e]), __uint_as_float(v3[e]))));
+                }
+            }
+            if (tid == 32) PT_STAMP(4, j);
+            mx *= sc;
+            const bool need = mx > m_used + 8.0f;
+            if (__any_sync(0xffffffffu, need)) {
+                const float m_new = need ? mx : m_used;
+                const float alpha = need ? pt_ex2(m_used - m_new) : 1.0f;
+                if (j > 0) {      // the accumulated output moves to the new reference (rare after the first tiles)
+                    pt_wait(&o_full[(j - 1) & 1], ((j - 1) >> 1) & 1, t0);
+                    tc_fence_after();
+                    uint32_t w[32];
+#pragma unroll 1
+                    for (int ch = 0; ch < 4; ch++) {
+                        tmem_ld_32x32b_x32(T_O + lane_base + ch * 32, w);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int e = 0; e < 32; e++) w[e] = __float_as_uint(__uint_as_float(w[e]) * alpha);
+                        tmem_st_32x32b_x32(T_O + lane_base + ch * 32, w);
+                    }
+                    tmem_st_wait();
+                }
+                l *= alpha;
+                m_used = m_new;
+            }
+            const float ref = (m_used == -INFINITY) ? 0.0f : m_used;
+            const uint32_t t_p = T_P + lane_base + (j & 1) * 64;
+            l += pt_probs(v0, sc, ref, t_p);
+            l += pt_probs(v1, sc, ref, t_p + 16);
+            l += pt_probs(v2, sc, ref, t_p + 32);
+            l += pt_probs(v3, sc, ref, t_p + 48);
+            tmem_st_wait();
+            tc_fence_before();
+            mbar_arrive(&p_full[j & 1]);
+            if (tid == 32) PT_STAMP(5, j);
+        }
+        // ---- finish: O / l -> shared memory -> Q80 cast into the slabs of the wo matmul ----
+        pt_wait(&o_full[(n_tiles - 1) & 1], ((n_tiles - 1) >> 1) & 1, t0);
+        tc_fence_after();
+        const float inv = l > 0.0f ? 1.0f / l : 0.0f;
+#pragma unroll 1
+        for (int ch = 0; ch < 4; ch++) {
+            tmem_ld_32x32b_x32(T_O + lane_base + ch * 32, v0);
+            tmem_ld_wait();
+#pragma unroll
+            for (int e = 0; e < 32; e++) out_s[row * PT_OUT_LD + ch * 32 + e] = __uint_as_float(v0[e]) * inv;
+        }
+        __syncwarp();                                            // a warp only re-reads the 32 rows it wrote
+        for (int rr = 0; rr < 32; rr++) {
+            const int rc = r_first + quarter * 32 + rr;
+            if (rc >= n_rows) break;
+            const int m = begin + rc;
+#pragma unroll
+            for (int b = 0; b < PT_HS / 32; b++) {
+                const float val = out_s[(quarter * 32 + rr) * PT_OUT_LD + b * 32 + lane];
+                q80_block_store(val, lane, m, (head * PT_HS) / 32 + b, a.out_mcap, a.xq_out, a.xh_out);
+                if (a.y_out != nullptr) a.y_out[(size_t)m * a.n_heads * PT_HS + head * PT_HS + b * 32 + lane] = val;
+            }
+        }
+    } else {
+        // ------------------------------------ KV producers (128 threads) ------------------------------------
+        // a warp's 32 copies cover 8 token rows x 4 chunks: 64-byte runs in global memory, and the 16-byte writes of a
+        // wavefront fall on 8 distinct bank groups ((token & 7) * 16 selects the bank in both tile images)
+        const int ptid = tid - 160;
+        const int t_lo = ptid & 7, c_sub = (ptid >> 3) & 3, w4 = ptid >> 5;
+        const uint32_t k_base = smem_u32(k_s), v_base = smem_u32(v_s);
+        for (int j = 0; j < n_tiles; j++) {
+            const int st = j % PT_STAGES;
+            if (j >= 1) {      // tile j-1 has landed: hand it over BEFORE waiting for a free stage (its consumer frees it)
+                asm volatile("cp.async.wait_group 0;" ::: "memory");
+                fence_proxy_async_smem();
+                mbar_arrive(&kv_full[(j - 1) % PT_STAGES]);
+            }
+            if (j >= PT_STAGES) pt_wait(&kv_empty[st], ((j / PT_STAGES) & 1) ^ 1, t0);
+            if (ptid == 0) PT_STAMP(6, j);
+            // the four pages of this tile (token t lives in page t >> 5 = i >> 2 of the tile): one table read each
+            int pg[4];
+#pragma unroll
+            for (int p4 = 0; p4 < 4; p4++) pg[p4] = (j * PT_KV + p4 * 32 < seq_end) ? bt[4 * j + p4] : 0;
+#pragma unroll
+            for (int i = 0; i < 16; i++) {
+                const int combo = i * 4 + w4, tg = combo >> 2, c = (combo & 3) * 4 + c_sub;
+                const int t = tg * 8 + t_lo;
+                const uint32_t kd = k_base + st * PT_TILE_BYTES + tg * 2048 + c * 128 + t_lo * 16;
+                const uint32_t vd = v_base + st * PT_TILE_BYTES + c * 2048 + tg * 128 + t_lo * 16;
+                if (a.dbg & 2) continue;
+                if (j * PT_KV + t < seq_end) {
+                    const size_t g = (((size_t)pg[i >> 2] * a.n_kv_heads + kvh) * 32 + (t & 31)) * PT_HS + c * 8;
+                    pt_cp_async16(kd, a.k_cache + g);
+                    pt_cp_async16(vd, a.v_cache + g);
+                } else {
+                    // tokens past the end of the sequence were never written: their scores are masked, but a zero
+                    // probability times a non-finite V would still poison the product -> feed zeros
+                    asm volatile("st.shared.v4.u32 [%0], {%1, %1, %1, %1};" ::"r"(kd), "r"(0) : "memory");
+                    asm volatile("st.shared.v4.u32 [%0], {%1, %1, %1, %1};" ::"r"(vd), "r"(0) : "memory");
+                }
+            }
+            asm volatile("cp.async.commit_group;" ::: "memory");
+            if (ptid == 0) PT_STAMP(7, j);
+        }
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        fence_proxy_async_smem();
+        mbar_arrive(&kv_full[(n_tiles - 1) % PT_STAGES]);
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
+    }
+    trace_end(a.tr);
+}
+
+extern void dl_set_error(const char* fmt, ...);
+static int g_pt_dbg = 0;
+static long long* g_pt_stamps = nullptr;
+extern "C" void dl_debug_set_pt_mode(int m) { g_pt_dbg = m; }
+extern "C" void dl_debug_set_pt_trace(long long* p) { g_pt_stamps = p; }
+
+extern "C" int dl_attention_prefill_tc(const float* q, int M, int n_heads, int n_kv_heads, int head_size, const void* k_cache,
+                                       const void* v_cache, const int* pos, const int* slot, const int* block_table,
+                                       int max_pages, int page_size, const int* meta, uint8_t* xq_out, uint8_t* xh_out,
+                                       int out_mcap, float* y_out, int pdl, void* stream) {
+    if (page_size != 32 || head_size != PT_HS) { dl_set_error("dl_attention_prefill_tc: page size 32 and head size 128 only"); return -1; }
+    if (n_heads % n_kv_heads != 0) { dl_set_error("dl_attention_prefill_tc: bad head grouping"); return -1; }
+    PtArgs a;
+    a.q = q; a.k_cache = (const __half*)k_cache; a.v_cache = (const __half*)v_cache; a.pos = pos; a.slot = slot;
+    a.block_table = block_table; a.meta = meta; a.M = M; a.n_heads = n_heads; a.n_kv_heads = n_kv_heads;
+    a.max_pages = max_pages; a.xq_out = xq_out; a.xh_out = xh_out; a.out_mcap = out_mcap; a.y_out = y_out;
+    a.dbg = g_pt_dbg;
+    a.stamps = g_pt_stamps;
+    a.tr = dl_trace_next(TR_ATT);
+    const size_t smem = (1 + 2 * PT_STAGES) * PT_TILE_BYTES + 16 * 8;
+    static bool set = false;
+    if (!set) {
+        cudaError_t e = cudaFuncSetAttribute(attention_prefill_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) { dl_set_error("attention_prefill_tc smem attr: %s", cudaGetErrorString(e)); return -(int)e; }
+        set = true;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)((M + PT_ROWS - 1) / PT_ROWS + PT_MAX_SEG), (unsigned)n_heads);      // upper bound of the tiles of all segments
+    cfg.blockDim = dim3(PT_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = (cudaStream_t)stream;
+    cudaLaunchAttribute attr[1];
+    if (pdl) {
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+    }
+    cudaError_t e = cudaLaunchKernelEx(&cfg, attention_prefill_tc_kernel, a);
+    if (e != cudaSuccess) { dl_set_error("attention_prefill_tc launch: %s", cudaGetErrorString(e)); return -(int)e; }
+    return 0;
+}

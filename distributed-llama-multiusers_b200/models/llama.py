@@ -46,6 +46,9 @@ PREFILL_MAX_SEG = 8          # prompt-chunk segments per batch (attention_prefil
 # wo / w2 break even at 1024 rows and gain 17-21 % at 2048.  The expansion itself runs at 4.3-6.0 TB/s (w13: 50 us).
 WH_MIN_ROWS = int(os.environ.get("DLLAMA_WH_MIN_ROWS", "768"))             # resident copy: free to use
 WH_MIN_ROWS_SCRATCH = int(os.environ.get("DLLAMA_WH_MIN_ROWS_SCRATCH", "2048"))   # per-call expansion: ~13 % of the GEMM time at 2048 rows
+# batches from this many rows run their prompt chunks on the tcgen05 attention kernel (attention_prefill_tc.cu, 128-row
+# tiles, head size 128); smaller ones on the mma.sync kernel with 64-row tiles
+PREFILL_TC_MIN_ROWS = int(os.environ.get("DLLAMA_PREFILL_TC_MIN_ROWS", "2048"))
 PAGE = K.PAGE_SIZE
 
 
@@ -568,13 +571,14 @@ class LlamaEngine:
             epi = K.epi_qkv_rope(self.q, self.q_loc, self.kv_loc, self.hs, self.rope_freqs, self.pos, self.slot,
                                  self.block_table, self.max_pages, self.n_kv_loc, self.k_cache[l], self.v_cache[l])
             norm_then(W["rms_att"], pending, l, W["qkv"], self.qkv_d, EPI_QKV_ROPE, epi)
-            K.attention(self.q, M, self.n_heads_loc, self.n_kv_loc, self.hs, self.k_cache[l], self.v_cache[l], self.pos,
-                        self.slot, self.block_table, self.max_pages, n_splits, self.att_scratch, xq(self.xq_att),
-                        xh(self.xh_att), mcap, pdl=pdl, row_skip=self.row_skip if chunk else None)
+            if chunk != 2:
+                K.attention(self.q, M, self.n_heads_loc, self.n_kv_loc, self.hs, self.k_cache[l], self.v_cache[l], self.pos,
+                            self.slot, self.block_table, self.max_pages, n_splits, self.att_scratch, xq(self.xq_att),
+                            xh(self.xh_att), mcap, pdl=pdl, row_skip=self.row_skip if chunk else None)
             if chunk:        # prompt-chunk rows (skipped above) on the tensor cores
                 K.attention_prefill(self.q, M, self.n_heads_loc, self.n_kv_loc, self.hs, self.k_cache[l], self.v_cache[l],
                                     self.pos, self.slot, self.block_table, self.max_pages, self.meta, xq(self.xq_att),
-                                    xh(self.xh_att), mcap, pdl=pdl)
+                                    xh(self.xh_att), mcap, pdl=pdl, tc=self.hs == 128 and M >= PREFILL_TC_MIN_ROWS)
             self._matmul(W["wo"], h.dim, self.q_loc, M, self.xq_att, self.xh_att,
                          push(part_att, self.flags_att_peer, l + 1, self.cta_counters[0]), EPI_STORE)
             pending = (part_att, self.flags_att_local)
@@ -607,7 +611,7 @@ class LlamaEngine:
         return int(min(want, max_by_ctx, self.max_splits))
 
     def _run(self, M: int, row0: int, greedy: bool, device_loop: bool = False, chunk: Optional[bool] = None):
-        chunk = (self._chunk and not device_loop) if chunk is None else chunk
+        chunk = (0 if device_loop else self._chunk) if chunk is None else chunk
         key = (M, row0, greedy, device_loop, chunk)
         if not self.use_graphs:
             self._launch_forward(M, row0, greedy, device_loop, chunk)
@@ -745,7 +749,9 @@ class LlamaEngine:
                 if j - i >= 16 and len(segs) < PREFILL_MAX_SEG:
                     segs.append((off + i, off + j))
                 i = j
-        self._chunk = bool(segs)
+        # 0 = no prompt chunk, 1 = chunks mixed with other rows, 2 = every row belongs to a chunk (a long prompt run as
+        # one batch): then the per-row kernel has nothing to do and is not launched
+        self._chunk = (2 if (off == 0 and sum(e - b for b, e in segs) == M) else 1) if segs else 0
         if segs:
             hd[3, :off + M] = 0
             hd[4, 0] = len(segs)

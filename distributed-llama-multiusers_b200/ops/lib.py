@@ -170,6 +170,7 @@ def cuda_lib():
     L.dl_attention.argtypes = [vp, i32, i32, i32, i32, vp, vp, i32, vp, vp, vp, i32, i32, i32, vp, vp, vp,
                                i32, vp, vp, i32, vp]
     L.dl_attention_prefill.argtypes = [vp, i32, i32, i32, i32, vp, vp, vp, vp, vp, i32, i32, vp, vp, vp, i32, vp, i32, vp]
+    L.dl_attention_prefill_tc.argtypes = L.dl_attention_prefill.argtypes
     L.dl_argmax.argtypes = [vp, i32, i32, i32, vp, vp, i32, vp, u32, u32, vp, vp, i32, vp, i32, vp]
     L.dl_argmax_scratch_bytes.restype = i64
     L.dl_argmax_scratch_bytes.argtypes = [i32]
@@ -191,7 +192,7 @@ def cuda_lib():
     L.dl_decode_mega_plan.argtypes = [i32, i32, i32, i32, i32, C.POINTER(i32), C.POINTER(i32), C.POINTER(i32)]
     L.dl_decode_mega_plan.restype = i32
     for name in ("dl_q40_repack", "dl_q40t_dequant", "dl_reduce_norm_quant", "dl_quant_q80", "dl_embedding",
-                 "dl_sample_rows", "dl_gemm_f32", "dl_gemv_q40", "dl_gemm_q40_tc", "dl_q40t_to_wh", "dl_gemm_wh_tc", "dl_attention", "dl_attention_prefill", "dl_argmax", "dl_ipc_alloc", "dl_ipc_open",
+                 "dl_sample_rows", "dl_gemm_f32", "dl_gemv_q40", "dl_gemm_q40_tc", "dl_q40t_to_wh", "dl_gemm_wh_tc", "dl_attention", "dl_attention_prefill", "dl_attention_prefill_tc", "dl_argmax", "dl_ipc_alloc", "dl_ipc_open",
                  "dl_ipc_close", "dl_ipc_free", "dl_peer_barrier", "dl_wait_flags"):
         getattr(L, name).restype = i32
     _cuda = L

@@ -175,6 +175,13 @@ int dl_attention_prefill(const float* q, int M, int n_heads, int n_kv_heads, int
                          int page_size, const int* meta /*device*/, uint8_t* xq_out, uint8_t* xh_out, int out_mcap,
                          float* y_out, int pdl, void* stream);
 
+/* same job on tcgen05 (head_size 128): S = Q K^T and O += P V as UMMA with the score / probability / output tiles in
+ * tensor memory, 128 query rows x one head per CTA, 128 tokens per step, lazy softmax rescaling */
+int dl_attention_prefill_tc(const float* q, int M, int n_heads, int n_kv_heads, int head_size, const void* k_cache,
+                            const void* v_cache, const int* pos, const int* slot, const int* block_table, int max_pages,
+                            int page_size, const int* meta /*device*/, uint8_t* xq_out, uint8_t* xh_out, int out_mcap,
+                            float* y_out, int pdl, void* stream);
+
 /* ---- sampling helpers --------------------------------------------------------------------- */
 /* argmax over logits[m][0..vocab) -> tokens[m]  (reference: Sampler::sample temperature==0,
  * src/tokenizer.cpp:472-502) */

@@ -441,11 +441,16 @@ def test_attention_matches_reference(n_heads, n_kv, hs, positions, n_splits, kv_
         np.testing.assert_allclose(dq, quant.q80_roundtrip(got), rtol=0, atol=np.abs(got).max() / 127 * 1.01)
 
 
-@pytest.mark.parametrize("n_heads,n_kv,hs,segs", [
-    (4, 1, 128, [(0, 0, 16)]), (8, 2, 128, [(0, 37, 100)]), (4, 4, 64, [(3, 5, 70)]), (2, 1, 128, [(62, 200, 130)]),
-    (2, 2, 64, [(31, 31, 33)]), (4, 2, 128, [(2, 10, 40), (45, 0, 90)]),
+@pytest.mark.parametrize("n_heads,n_kv,hs,segs,tc", [
+    (4, 1, 128, [(0, 0, 16)], False), (8, 2, 128, [(0, 37, 100)], False), (4, 4, 64, [(3, 5, 70)], False),
+    (2, 1, 128, [(62, 200, 130)], False), (2, 2, 64, [(31, 31, 33)], False), (4, 2, 128, [(2, 10, 40), (45, 0, 90)], False),
+    # the tcgen05 / TMEM kernel: one tile, partial tiles, several KV steps (lazy rescaling, both score buffers, stage
+    # reuse), a chunk that starts deep inside a sequence, two segments
+    (4, 1, 128, [(0, 0, 16)], True), (8, 2, 128, [(0, 37, 100)], True), (2, 1, 128, [(62, 200, 130)], True),
+    (4, 2, 128, [(2, 10, 40), (45, 0, 90)], True), (4, 4, 128, [(0, 0, 700)], True), (2, 1, 128, [(5, 900, 300)], True),
+    (8, 2, 128, [(0, 0, 257), (260, 130, 384)], True),
 ])
-def test_attention_prefill_matches_reference(n_heads, n_kv, hs, segs):
+def test_attention_prefill_matches_reference(n_heads, n_kv, hs, segs, tc):
     """Tensor-core prompt-chunk attention.  segs = [(first row, first position, rows)]: every segment is a run of
     consecutive positions of its own sequence; rows outside the segments must not be touched (the per-row kernel
     serves them).  Compared with the f64 reference."""
@@ -486,7 +491,7 @@ def test_attention_prefill_matches_reference(n_heads, n_kv, hs, segs):
     ncap = (M + 127) // 128 * 128
     xh = k.alloc_xh(n_heads * hs, ncap, "cuda") if (n_heads * hs) % 128 == 0 else None
     k.attention_prefill(torch.from_numpy(q).cuda(), M, n_heads, n_kv, hs, Kc, Vc, pos_t, slot_t, bt_t, max_pages, meta_t,
-                        None, xh, ncap, y)
+                        None, xh, ncap, y, tc=tc)
     torch.cuda.synchronize()
     got = y.cpu().numpy()
     covered = np.zeros(M, dtype=bool)
