@@ -3,8 +3,9 @@
 // as tcgen05.mma and the score / probability / output tiles in TENSOR MEMORY instead of registers.
 //
 // A CTA owns 128 query rows x one query head and walks the KV history 128 tokens (four pages) at a time:
-//   S = Q K^T     SS-mode MMA, M = 128 rows, N = 128 tokens, K = 128: Q staged once (fp16, K-major core matrices),
-//                 K pages copied with cp.async into the same core-matrix image; S (f32) lands in TMEM, double-buffered
+//   S = Q K^T     SS-mode MMA, M = 128 rows, N = 128 tokens, K = 128: Q staged once (fp16, K-major, 128-byte swizzle);
+//                 K pages arrive by TMA tensor copies (cp.async.bulk.tensor.2d over this GPU's KV cache, box 64 x 32,
+//                 hardware 128-byte swizzle); S (f32) lands in TMEM, double-buffered
 //   softmax       one thread per query row (= TMEM lane): two passes over S with tcgen05.ld (row maximum, then
 //                 exp2 -> fp16 probabilities written back to TMEM with tcgen05.st); running maximum with LAZY
 //                 rescaling: the reference maximum only moves when a row's maximum grew by more than 2^8, so in the
@@ -14,16 +15,22 @@
 // The MMA warp issues S(j+1) before P(j) V(j), so the tensor core works on the next scores while the softmax threads
 // are busy with the current ones.  Output: O / l -> shared memory -> Q80 cast into the XQ / XH slabs of the wo matmul.
 //
-// Warp roles (288 threads): warp 0 MMA issuer + TMEM owner, warps 1-4 softmax (row = TMEM lane), warps 5-8 KV producers.
+// Warp roles (224 threads): warp 0 issues the S MMAs (+ TMEM owner), warp 6 the P V MMAs (an issuing thread spends ~700 clk
+// per group of 8 MMAs, so one thread for both would cap a step at ~1500 clk), warps 1-4 softmax (row = TMEM lane), warp 5
+// K producer and warp 7 V producer (one lane each issues 8 tensor copies of 4 KB per step: 4 pages x 2 halves of the head
+// dimension; K and V have their own 3-stage rings, so a K stage is free again as soon as its scores are complete).
+// (The first version copied K/V with cp.async in 16-byte pieces into un-swizzled core matrices: 4096 LDGSTS per step
+// cost 3500 clk of issue time, three times the MMAs -- scripts/trace_attention_tc.py.)
 // TMEM columns: S0 [0,128) S1 [128,256) P0 [256,320) P1 [320,384) O [384,512).
 // Reference semantics: multiheadAtt_F32 (src/nn/nn-cpu-ops.cpp:749-784), softmax in f32, output cast as OP_CAST
 // (src/llm.cpp:296-301).  KV cache: fp16 pages [page][kv_head][32][128].
+#include <cuda.h>
 #include "epilogue.cuh"
 
 #define PT_HS 128
 #define PT_ROWS 128
 #define PT_KV 128                      // tokens per step
-#define PT_THREADS 288
+#define PT_THREADS 256
 #define PT_MAX_SEG 8
 #define PT_TILE_BYTES 32768            // 128 x 128 fp16
 #define PT_STAGES 3                    // KV tiles in flight (K + V: 64 KB each)
@@ -114,7 +121,8 @@ DL_DEVINL float pt_probs(const uint32_t (&v)[32], float sc, float ref, uint32_t 
     return sum;
 }
 
-__global__ void __launch_bounds__(PT_THREADS, 1) attention_prefill_tc_kernel(const __grid_constant__ PtArgs a) {
+__global__ void __launch_bounds__(PT_THREADS, 1) attention_prefill_tc_kernel(const __grid_constant__ PtArgs a, const __grid_constant__ CUtensorMap kmap,
+                                                                                const __grid_constant__ CUtensorMap vmap) {
     extern __shared__ __align__(1024) uint8_t smem[];
     trace_begin(a.tr);
     const unsigned long long t0 = globaltimer_ns();
@@ -123,13 +131,16 @@ __global__ void __launch_bounds__(PT_THREADS, 1) attention_prefill_tc_kernel(con
     uint8_t* v_s = k_s + PT_STAGES * PT_TILE_BYTES;             // [3] V tiles (tokens x head dim, MN-major for P V)
     float* out_s = reinterpret_cast<float*>(k_s);               // [128][129] f32, reuses the KV stages after the loop
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (1 + 2 * PT_STAGES) * PT_TILE_BYTES);
-    uint64_t* kv_full = bars;            // [3] 128 producer arrivals
-    uint64_t* kv_empty = bars + 3;       // [3] P V of the tile has retired
-    uint64_t* q_full = bars + 6;
-    uint64_t* s_full = bars + 7;         // [2] scores complete
-    uint64_t* p_full = bars + 9;         // [2] probabilities written (and the score buffer read)
-    uint64_t* o_full = bars + 11;        // [2] P V of tile j complete (barrier j & 1)
-    uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(bars + 13);
+    uint64_t* k_full = bars;             // [3] transaction bytes of the step's K copies
+    uint64_t* k_empty = bars + 3;        // [3] the scores that read the stage are complete
+    uint64_t* v_full = bars + 6;         // [3] transaction bytes of the step's V copies
+    uint64_t* v_empty = bars + 9;        // [3] P V of the step has retired
+    uint64_t* q_full = bars + 12;
+    uint64_t* s_full = bars + 13;        // [2] scores complete
+    uint64_t* p_full = bars + 15;        // [2] probabilities written (and the score buffer read)
+    uint64_t* o_full = bars + 17;        // [2] P V of tile j complete (barrier j & 1)
+    uint64_t* s_empty = bars + 19;       // [2] the score buffer has been read into registers
+    uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(bars + 21);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int head = blockIdx.y;
@@ -161,11 +172,14 @@ __global__ void __launch_bounds__(PT_THREADS, 1) attention_prefill_tc_kernel(con
 
     if (tid == 0) {
         for (int s = 0; s < PT_STAGES; s++) {
-            mbar_init(&kv_full[s], 128);
-            mbar_init(&kv_empty[s], 1);
+            mbar_init(&k_full[s], 1);
+            mbar_init(&k_empty[s], 1);
+            mbar_init(&v_full[s], 1);
+            mbar_init(&v_empty[s], 1);
         }
         for (int s = 0; s < 2; s++) {
             mbar_init(&s_full[s], 1);
+            mbar_init(&s_empty[s], 128);
             mbar_init(&p_full[s], 128);
             mbar_init(&o_full[s], 1);
         }
@@ -179,64 +193,84 @@ __global__ void __launch_bounds__(PT_THREADS, 1) attention_prefill_tc_kernel(con
     const uint32_t tmem_base = *tmem_holder;
     const uint32_t T_S = tmem_base, T_P = tmem_base + 256, T_O = tmem_base + 384;
 
+    // 128-byte-swizzled operands: rows of 128 B (64 halfs), 8-row groups 1024 B apart; the head dimension is split in
+    // two such half tiles 16 KB apart.  K-major (Q, K): LBO unused (1), SBO 1024.  MN-major (V as B of P V): LBO =
+    // distance between the two 64-wide halves of N (16 KB), SBO = distance between 8-token groups (1024 B).
+    const uint32_t desc_hi = (1024u >> 4) | (1u << 14) | (2u << 29);
     if (warp == 0) {
-        // ------------------------------------ MMA issuer ------------------------------------
-        const uint32_t idesc_s = pt_idesc(PT_ROWS, PT_KV, 0), idesc_pv = pt_idesc(PT_ROWS, PT_HS, 1);
-        const uint32_t desc_hi = (2048u >> 4) | (1u << 14);
-        auto desc_lo = [](const void* p) { return ((smem_u32(p) & 0x3FFFFu) >> 4) | ((128u >> 4) << 16); };
-        auto issue_pv = [&](int i) {
+        // ------------------------------------ S = Q K^T issuer ------------------------------------
+        const uint32_t idesc_s = pt_idesc(PT_ROWS, PT_KV, 0);
+        auto lo_k = [](const void* p) { return ((smem_u32(p) & 0x3FFFFu) >> 4) | (1u << 16); };
+        pt_wait(q_full, 0, t0);
+        for (int j = 0; j < n_tiles; j++) {
+            pt_wait(&k_full[j % PT_STAGES], (j / PT_STAGES) & 1, t0);
+            if (lane == 0) PT_STAMP(0, j);
+            if (j >= 2) pt_wait(&s_empty[j & 1], ((j - 2) >> 1) & 1, t0);     // softmax(j-2) has this score buffer in registers
+            tc_fence_after();
+            if (elect_one()) {
+                const uint32_t a_lo = lo_k(q_s), b_lo = lo_k(k_s + (j % PT_STAGES) * PT_TILE_BYTES);
+#pragma unroll
+                for (int k = 0; k < 8; k++) {      // K = 16 per MMA: 32 B inside the swizzled row, the second half tile after four
+                    const uint32_t off = (uint32_t)((k >> 2) * (16384 >> 4) + (k & 3) * 2);
+                    uint64_t da, db;
+                    asm("mov.b64 %0, {%1, %2};" : "=l"(da) : "r"(a_lo + off), "r"(desc_hi));
+                    asm("mov.b64 %0, {%1, %2};" : "=l"(db) : "r"(b_lo + off), "r"(desc_hi));
+                    if (!(a.dbg & 4)) umma_f16_ss(T_S + (j & 1) * 128, da, db, idesc_s, k > 0 ? 1u : 0u);
+                }
+                umma_commit(&s_full[j & 1]);
+                umma_commit(&k_empty[j % PT_STAGES]);
+            }
+            __syncwarp();
+            if (lane == 0) PT_STAMP(1, j);
+        }
+    } else if (warp == 6) {
+        // ------------------------------------ O += P V issuer ------------------------------------
+        const uint32_t idesc_pv = pt_idesc(PT_ROWS, PT_HS, 1);
+        for (int i = 0; i < n_tiles; i++) {
+            uint8_t* vz = v_s + (i % PT_STAGES) * PT_TILE_BYTES;
+            if ((i + 1) * PT_KV > seq_end) {
+                // the step that contains the end of the sequence: rows past it were never written (or not copied at all);
+                // their scores are masked, but a zero probability times a non-finite V would poison the product -> zero them
+                pt_wait(&v_full[i % PT_STAGES], (i / PT_STAGES) & 1, t0);
+                const int r0 = max(0, seq_end - i * PT_KV);
+                for (int idx = r0 * 16 + lane; idx < PT_KV * 16; idx += 32) {      // 16 pieces of 16 B per token row (two halves)
+                    const int r = idx >> 4, c = idx & 15;
+                    *reinterpret_cast<uint4*>(vz + (c >> 3) * 16384 + r * 128 + (c & 7) * 16) = make_uint4(0, 0, 0, 0);
+                }
+                fence_proxy_async_smem();
+                __syncwarp();
+            }
+            pt_wait(&v_full[i % PT_STAGES], (i / PT_STAGES) & 1, t0);
             pt_wait(&p_full[i & 1], (i >> 1) & 1, t0);
             if (lane == 0) PT_STAMP(2, i);
             tc_fence_after();
             if (elect_one()) {
-                const uint32_t b_lo = desc_lo(v_s + (i % PT_STAGES) * PT_TILE_BYTES);
+                const uint32_t b_lo = ((smem_u32(vz) & 0x3FFFFu) >> 4) | ((16384u >> 4) << 16);
 #pragma unroll
-                for (int k = 0; k < 8; k++) {      // 16 tokens per MMA: 8 TMEM columns of P, two token groups (256 B) of V
+                for (int k = 0; k < 8; k++) {      // 16 tokens per MMA: 8 TMEM columns of P, two 8-token groups (2048 B) of V
                     uint64_t db;
-                    asm("mov.b64 %0, {%1, %2};" : "=l"(db) : "r"(b_lo + k * 16), "r"(desc_hi));
+                    asm("mov.b64 %0, {%1, %2};" : "=l"(db) : "r"(b_lo + k * 128), "r"(desc_hi));
                     if (!(a.dbg & 4)) umma_f16_ts(T_O, T_P + (i & 1) * 64 + k * 8, db, idesc_pv, (i > 0 || k > 0) ? 1u : 0u);
                 }
                 umma_commit(&o_full[i & 1]);
-                umma_commit(&kv_empty[i % PT_STAGES]);
+                umma_commit(&v_empty[i % PT_STAGES]);
             }
             __syncwarp();
-        };
-        pt_wait(q_full, 0, t0);
-        for (int j = 0; j < n_tiles; j++) {
-            pt_wait(&kv_full[j % PT_STAGES], (j / PT_STAGES) & 1, t0);
-            if (lane == 0) PT_STAMP(0, j);
-            if (j >= 2) pt_wait(&p_full[j & 1], ((j - 2) >> 1) & 1, t0);      // softmax(j-2) has read this score buffer
-            tc_fence_after();
-            if (elect_one()) {
-                const uint32_t a_lo = desc_lo(q_s), b_lo = desc_lo(k_s + (j % PT_STAGES) * PT_TILE_BYTES);
-#pragma unroll
-                for (int k = 0; k < 8; k++) {
-                    uint64_t da, db;
-                    asm("mov.b64 %0, {%1, %2};" : "=l"(da) : "r"(a_lo + k * 16), "r"(desc_hi));
-                    asm("mov.b64 %0, {%1, %2};" : "=l"(db) : "r"(b_lo + k * 16), "r"(desc_hi));
-                    if (!(a.dbg & 4)) umma_f16_ss(T_S + (j & 1) * 128, da, db, idesc_s, k > 0 ? 1u : 0u);
-                }
-                umma_commit(&s_full[j & 1]);
-            }
-            __syncwarp();
-            if (lane == 0) PT_STAMP(1, j);
-            if (j >= 1) issue_pv(j - 1);
         }
-        issue_pv(n_tiles - 1);
     } else if (warp <= 4) {
         // ------------------------------------ softmax: thread = query row = TMEM lane ------------------------------------
         const int quarter = warp & 3, row = quarter * 32 + lane;
         const int r_abs = r_first + row;
         {
             const float* qg = a.q + (size_t)(begin + min(r_abs, n_rows - 1)) * a.n_heads * PT_HS + head * PT_HS;
-            uint8_t* qd = q_s + (row >> 3) * 2048 + (row & 7) * 16;
+            uint8_t* qd = q_s + row * 128;
 #pragma unroll 4
-            for (int c = 0; c < 16; c++) {
+            for (int c = 0; c < 16; c++) {      // 16-byte piece c of the row: half tile c >> 3, swizzled slot (c & 7) ^ (row & 7)
                 const float4 x = reinterpret_cast<const float4*>(qg)[2 * c], y = reinterpret_cast<const float4*>(qg)[2 * c + 1];
                 uint4 u;
                 u.x = pt_pack_half2(x.x, x.y); u.y = pt_pack_half2(x.z, x.w);
                 u.z = pt_pack_half2(y.x, y.y); u.w = pt_pack_half2(y.z, y.w);
-                *reinterpret_cast<uint4*>(qd + c * 128) = u;
+                *reinterpret_cast<uint4*>(qd + (c >> 3) * 16384 + (((c & 7) ^ (row & 7)) << 4)) = u;
             }
             fence_proxy_async_smem();
             mbar_arrive(q_full);
@@ -259,6 +293,8 @@ __global__ void __launch_bounds__(PT_THREADS, 1) attention_prefill_tc_kernel(con
             tmem_ld_32x32b_x32(t_s + 64, v2);
             tmem_ld_32x32b_x32(t_s + 96, v3);
             tmem_ld_wait();
+            tc_fence_before();
+            mbar_arrive(&s_empty[j & 1]);                    // the scores of step j+2 may overwrite the buffer now
             const int lim = pos_r - tok0;                    // columns e <= lim are visible to this row
             const bool full = lim >= PT_KV - 1;              // no masking in this tile (all but the last tile or two)
             float mx = -INFINITY;
@@ -301,6 +337,10 @@ __global__ void __launch_bounds__(PT_THREADS, 1) attention_prefill_tc_kernel(con
             }
             const float ref = (m_used == -INFINITY) ? 0.0f : m_used;
             const uint32_t t_p = T_P + lane_base + (j & 1) * 64;
+            if (j >= 2) {      // P V(j-2) has consumed this probability buffer (long done; the wait keeps it a guarantee)
+                pt_wait(&o_full[j & 1], ((j - 2) >> 1) & 1, t0);
+                tc_fence_after();
+            }
             l += pt_probs(v0, sc, ref, t_p);
             l += pt_probs(v1, sc, ref, t_p + 16);
             l += pt_probs(v2, sc, ref, t_p + 32);
@@ -333,50 +373,46 @@ __global__ void __launch_bounds__(PT_THREADS, 1) attention_prefill_tc_kernel(con
                 if (a.y_out != nullptr) a.y_out[(size_t)m * a.n_heads * PT_HS + head * PT_HS + b * 32 + lane] = val;
             }
         }
-    } else {
-        // ------------------------------------ KV producers (128 threads) ------------------------------------
-        // a warp's 32 copies cover 8 token rows x 4 chunks: 64-byte runs in global memory, and the 16-byte writes of a
-        // wavefront fall on 8 distinct bank groups ((token & 7) * 16 selects the bank in both tile images)
-        const int ptid = tid - 160;
-        const int t_lo = ptid & 7, c_sub = (ptid >> 3) & 3, w4 = ptid >> 5;
-        const uint32_t k_base = smem_u32(k_s), v_base = smem_u32(v_s);
-        for (int j = 0; j < n_tiles; j++) {
-            const int st = j % PT_STAGES;
-            if (j >= 1) {      // tile j-1 has landed: hand it over BEFORE waiting for a free stage (its consumer frees it)
-                asm volatile("cp.async.wait_group 0;" ::: "memory");
-                fence_proxy_async_smem();
-                mbar_arrive(&kv_full[(j - 1) % PT_STAGES]);
-            }
-            if (j >= PT_STAGES) pt_wait(&kv_empty[st], ((j / PT_STAGES) & 1) ^ 1, t0);
-            if (ptid == 0) PT_STAMP(6, j);
-            // the four pages of this tile (token t lives in page t >> 5 = i >> 2 of the tile): one table read each
-            int pg[4];
+    } else if (warp == 5 || warp == 7) {
+        // ------------------------------------ K producer (warp 5) / V producer (warp 7), one lane each ------------------------------------
+        if (lane == 0) {
+            const bool is_k = warp == 5;
+            const uint64_t map = is_k ? reinterpret_cast<uint64_t>(&kmap) : reinterpret_cast<uint64_t>(&vmap);
+            uint64_t* full = is_k ? k_full : v_full;
+            uint64_t* empty = is_k ? k_empty : v_empty;
+            uint8_t* ring = is_k ? k_s : v_s;
+            const int total_pages = (seq_end + 31) / 32;
+            // the page ids of a step are fetched one step ahead, so the table reads (dependent global loads) overlap the
+            // wait for a free stage instead of delaying the copies
+            int pg[4], pg_next[4];
 #pragma unroll
-            for (int p4 = 0; p4 < 4; p4++) pg[p4] = (j * PT_KV + p4 * 32 < seq_end) ? bt[4 * j + p4] : 0;
+            for (int p4 = 0; p4 < 4; p4++) pg_next[p4] = (p4 < total_pages) ? bt[p4] : 0;
+            for (int j = 0; j < n_tiles; j++) {
+                const int st = j % PT_STAGES;
 #pragma unroll
-            for (int i = 0; i < 16; i++) {
-                const int combo = i * 4 + w4, tg = combo >> 2, c = (combo & 3) * 4 + c_sub;
-                const int t = tg * 8 + t_lo;
-                const uint32_t kd = k_base + st * PT_TILE_BYTES + tg * 2048 + c * 128 + t_lo * 16;
-                const uint32_t vd = v_base + st * PT_TILE_BYTES + c * 2048 + tg * 128 + t_lo * 16;
-                if (a.dbg & 2) continue;
-                if (j * PT_KV + t < seq_end) {
-                    const size_t g = (((size_t)pg[i >> 2] * a.n_kv_heads + kvh) * 32 + (t & 31)) * PT_HS + c * 8;
-                    pt_cp_async16(kd, a.k_cache + g);
-                    pt_cp_async16(vd, a.v_cache + g);
-                } else {
-                    // tokens past the end of the sequence were never written: their scores are masked, but a zero
-                    // probability times a non-finite V would still poison the product -> feed zeros
-                    asm volatile("st.shared.v4.u32 [%0], {%1, %1, %1, %1};" ::"r"(kd), "r"(0) : "memory");
-                    asm volatile("st.shared.v4.u32 [%0], {%1, %1, %1, %1};" ::"r"(vd), "r"(0) : "memory");
+                for (int p4 = 0; p4 < 4; p4++) {
+                    pg[p4] = pg_next[p4];
+                    pg_next[p4] = (4 * (j + 1) + p4 < total_pages) ? bt[4 * (j + 1) + p4] : 0;
                 }
+                if (j >= PT_STAGES) pt_wait(&empty[st], ((j / PT_STAGES) & 1) ^ 1, t0);
+                if (is_k) PT_STAMP(6, j);
+                const int n_pg = (a.dbg & 2) ? 0 : min(4, (seq_end - j * PT_KV + 31) / 32);      // pages of this step that exist
+                mbar_arrive_expect_tx(&full[st], (uint32_t)n_pg * 2u * 4096u);
+                const uint32_t dst = smem_u32(ring + st * PT_TILE_BYTES), bar = smem_u32(&full[st]);
+#pragma unroll
+                for (int p4 = 0; p4 < 4; p4++) {
+                    if (p4 >= n_pg) break;
+                    const int y = (pg[p4] * a.n_kv_heads + kvh) * 32;      // first row of the page in the [rows][128] view
+#pragma unroll
+                    for (int h = 0; h < 2; h++)
+                        asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
+                                         dst + h * 16384 + p4 * 4096),
+                                     "l"(map), "r"(h * 64), "r"(y), "r"(bar)
+                                     : "memory");
+                }
+                if (is_k) PT_STAMP(7, j);
             }
-            asm volatile("cp.async.commit_group;" ::: "memory");
-            if (ptid == 0) PT_STAMP(7, j);
         }
-        asm volatile("cp.async.wait_group 0;" ::: "memory");
-        fence_proxy_async_smem();
-        mbar_arrive(&kv_full[(n_tiles - 1) % PT_STAGES]);
     }
     tc_fence_before();
     __syncthreads();
@@ -393,12 +429,39 @@ static long long* g_pt_stamps = nullptr;
 extern "C" void dl_debug_set_pt_mode(int m) { g_pt_dbg = m; }
 extern "C" void dl_debug_set_pt_trace(long long* p) { g_pt_stamps = p; }
 
+typedef CUresult (*PtEncodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+// [rows][128] fp16 view of a KV cache on THIS GPU (rows = pages x kv heads x 32), box = 64 columns x 32 rows (one page of
+// one head, half of the head dimension), 128-byte swizzle: the image tcgen05.mma reads as a swizzled K- or MN-major tile
+static int pt_make_map(CUtensorMap* m, const void* base, long long rows) {
+    static PtEncodeTiled enc = nullptr;
+    if (enc == nullptr) {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult qr;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qr) != cudaSuccess || fn == nullptr) {
+            dl_set_error("attention_prefill_tc: cuTensorMapEncodeTiled not available");
+            return -1;
+        }
+        enc = (PtEncodeTiled)fn;
+    }
+    const cuuint64_t dims[2] = {PT_HS, (cuuint64_t)rows};
+    const cuuint64_t strides[1] = {PT_HS * 2};
+    const cuuint32_t box[2] = {64, 32}, es[2] = {1, 1};
+    const CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(base), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                           CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { dl_set_error("attention_prefill_tc: cuTensorMapEncodeTiled failed (%d)", (int)r); return -1; }
+    return 0;
+}
+
 extern "C" int dl_attention_prefill_tc(const float* q, int M, int n_heads, int n_kv_heads, int head_size, const void* k_cache,
                                        const void* v_cache, const int* pos, const int* slot, const int* block_table,
                                        int max_pages, int page_size, const int* meta, uint8_t* xq_out, uint8_t* xh_out,
-                                       int out_mcap, float* y_out, int pdl, void* stream) {
+                                       int out_mcap, float* y_out, int n_cache_pages, int pdl, void* stream) {
     if (page_size != 32 || head_size != PT_HS) { dl_set_error("dl_attention_prefill_tc: page size 32 and head size 128 only"); return -1; }
     if (n_heads % n_kv_heads != 0) { dl_set_error("dl_attention_prefill_tc: bad head grouping"); return -1; }
+    if (n_cache_pages < 1) { dl_set_error("dl_attention_prefill_tc: n_cache_pages < 1"); return -1; }
     PtArgs a;
     a.q = q; a.k_cache = (const __half*)k_cache; a.v_cache = (const __half*)v_cache; a.pos = pos; a.slot = slot;
     a.block_table = block_table; a.meta = meta; a.M = M; a.n_heads = n_heads; a.n_kv_heads = n_kv_heads;
@@ -406,7 +469,10 @@ extern "C" int dl_attention_prefill_tc(const float* q, int M, int n_heads, int n
     a.dbg = g_pt_dbg;
     a.stamps = g_pt_stamps;
     a.tr = dl_trace_next(TR_ATT);
-    const size_t smem = (1 + 2 * PT_STAGES) * PT_TILE_BYTES + 16 * 8;
+    alignas(64) CUtensorMap kmap, vmap;
+    const long long rows = (long long)n_cache_pages * n_kv_heads * 32;
+    if (pt_make_map(&kmap, k_cache, rows) != 0 || pt_make_map(&vmap, v_cache, rows) != 0) return -1;
+    const size_t smem = (1 + 2 * PT_STAGES) * PT_TILE_BYTES + 24 * 8;
     static bool set = false;
     if (!set) {
         cudaError_t e = cudaFuncSetAttribute(attention_prefill_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -425,7 +491,7 @@ extern "C" int dl_attention_prefill_tc(const float* q, int M, int n_heads, int n
         cfg.attrs = attr;
         cfg.numAttrs = 1;
     }
-    cudaError_t e = cudaLaunchKernelEx(&cfg, attention_prefill_tc_kernel, a);
+    cudaError_t e = cudaLaunchKernelEx(&cfg, attention_prefill_tc_kernel, a, kmap, vmap);
     if (e != cudaSuccess) { dl_set_error("attention_prefill_tc launch: %s", cudaGetErrorString(e)); return -(int)e; }
     return 0;
 }

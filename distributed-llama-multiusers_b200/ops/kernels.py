@@ -230,11 +230,13 @@ def attention_prefill(q, M, n_heads, n_kv_heads, head_size, k_cache, v_cache, po
     """Tensor-core causal attention of prompt chunks: meta = [n_seg, begin0, end0, ...] (device int32), each
     range being consecutive positions of one sequence.  tc=True: the tcgen05 / TMEM kernel (head size 128)."""
     assert k_cache.dtype == torch.float16
-    fn = cuda_lib().dl_attention_prefill_tc if tc else cuda_lib().dl_attention_prefill
-    check(fn(q.data_ptr(), M, n_heads, n_kv_heads, head_size, k_cache.data_ptr(),
-                                          v_cache.data_ptr(), pos.data_ptr(), slot.data_ptr(), block_table.data_ptr(),
-                                          max_pages, PAGE_SIZE, meta.data_ptr(), _p(xq_out), _p(xh_out), out_mcap,
-                                          _p(y_out), 1 if pdl else 0, _stream()), "dl_attention_prefill")
+    args = (q.data_ptr(), M, n_heads, n_kv_heads, head_size, k_cache.data_ptr(), v_cache.data_ptr(), pos.data_ptr(),
+            slot.data_ptr(), block_table.data_ptr(), max_pages, PAGE_SIZE, meta.data_ptr(), _p(xq_out), _p(xh_out), out_mcap,
+            _p(y_out))
+    if tc:
+        check(cuda_lib().dl_attention_prefill_tc(*args, int(k_cache.shape[0]), 1 if pdl else 0, _stream()), "dl_attention_prefill_tc")
+    else:
+        check(cuda_lib().dl_attention_prefill(*args, 1 if pdl else 0, _stream()), "dl_attention_prefill")
     lib.count_launch()
 
 

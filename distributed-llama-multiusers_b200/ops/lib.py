@@ -170,7 +170,7 @@ def cuda_lib():
     L.dl_attention.argtypes = [vp, i32, i32, i32, i32, vp, vp, i32, vp, vp, vp, i32, i32, i32, vp, vp, vp,
                                i32, vp, vp, i32, vp]
     L.dl_attention_prefill.argtypes = [vp, i32, i32, i32, i32, vp, vp, vp, vp, vp, i32, i32, vp, vp, vp, i32, vp, i32, vp]
-    L.dl_attention_prefill_tc.argtypes = L.dl_attention_prefill.argtypes
+    L.dl_attention_prefill_tc.argtypes = [vp, i32, i32, i32, i32, vp, vp, vp, vp, vp, i32, i32, vp, vp, vp, i32, vp, i32, i32, vp]
     L.dl_argmax.argtypes = [vp, i32, i32, i32, vp, vp, i32, vp, u32, u32, vp, vp, i32, vp, i32, vp]
     L.dl_argmax_scratch_bytes.restype = i64
     L.dl_argmax_scratch_bytes.argtypes = [i32]

@@ -180,7 +180,8 @@ int dl_attention_prefill(const float* q, int M, int n_heads, int n_kv_heads, int
 int dl_attention_prefill_tc(const float* q, int M, int n_heads, int n_kv_heads, int head_size, const void* k_cache,
                             const void* v_cache, const int* pos, const int* slot, const int* block_table, int max_pages,
                             int page_size, const int* meta /*device*/, uint8_t* xq_out, uint8_t* xh_out, int out_mcap,
-                            float* y_out, int pdl, void* stream);
+                            float* y_out, int n_cache_pages /*pages in k_cache / v_cache: bounds of the TMA tensor maps*/,
+                            int pdl, void* stream);
 
 /* ---- sampling helpers --------------------------------------------------------------------- */
 /* argmax over logits[m][0..vocab) -> tokens[m]  (reference: Sampler::sample temperature==0,
