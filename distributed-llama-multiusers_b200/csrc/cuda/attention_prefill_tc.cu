@@ -15,8 +15,9 @@
 // The MMA warp issues S(j+1) before P(j) V(j), so the tensor core works on the next scores while the softmax threads
 // are busy with the current ones.  Output: O / l -> shared memory -> Q80 cast into the XQ / XH slabs of the wo matmul.
 //
-// Warp roles (224 threads): warp 0 issues the S MMAs (+ TMEM owner), warp 6 the P V MMAs (an issuing thread spends ~700 clk
-// per group of 8 MMAs, so one thread for both would cap a step at ~1500 clk), warps 1-4 softmax (row = TMEM lane), warp 5
+// Warp roles (384 threads): warp 0 issues the S MMAs (+ TMEM owner), warp 6 the P V MMAs (an issuing thread spends ~700 clk
+// per group of 8 MMAs, so one thread for both would cap a step at ~1500 clk), warps 1-4 and 8-11 softmax (two threads per
+// row = TMEM lane, 64 columns each; the row maximum is exchanged through shared memory), warp 5
 // K producer and warp 7 V producer (one lane each issues 8 tensor copies of 4 KB per step: 4 pages x 2 halves of the head
 // dimension; K and V have their own 3-stage rings, so a K stage is free again as soon as its scores are complete).
 // (The first version copied K/V with cp.async in 16-byte pieces into un-swizzled core matrices: 4096 LDGSTS per step
@@ -30,7 +31,7 @@
 #define PT_HS 128
 #define PT_ROWS 128
 #define PT_KV 128                      // tokens per step
-#define PT_THREADS 256
+#define PT_THREADS 384
 #define PT_MAX_SEG 8
 #define PT_TILE_BYTES 32768            // 128 x 128 fp16
 #define PT_STAGES 3                    // KV tiles in flight (K + V: 64 KB each)
@@ -106,6 +107,17 @@ DL_DEVINL uint32_t pt_pack_half2(float lo, float hi) {
     return *reinterpret_cast<uint32_t*>(&h);
 }
 
+// exp2 on the FMA pipe (Cody-Waite split + degree-3 polynomial, relative error 8e-5 -- the result is rounded to fp16,
+// 5e-4, right after): the softmax is bound by the 16 MUFU results per clock and SM (128 x 128 exp2 per step = 1024 clk,
+// as long as the MMAs of the step), so every fourth element takes this path instead
+DL_DEVINL float pt_ex2_poly(float x) {
+    const float xc = fmaxf(x, -126.0f);
+    const float t = xc + 12582912.0f;              // 1.5 * 2^23: round(x) lands in the low mantissa bits
+    const float f = xc - (t - 12582912.0f);        // [-0.5, 0.5]
+    const float p = fmaf(fmaf(fmaf(0.0550886838f, f, 0.242604051f), f, 0.693276242f), f, 0.99992894f);
+    return __int_as_float(__float_as_int(p) + (__float_as_int(t) << 23));
+}
+
 // 32 scores (masked ones are -inf) -> exp2(s * sc - ref) as 16 packed fp16 pairs into TMEM; returns their sum
 DL_DEVINL float pt_probs(const uint32_t (&v)[32], float sc, float ref, uint32_t taddr) {
     uint32_t pk[16];
@@ -113,7 +125,8 @@ DL_DEVINL float pt_probs(const uint32_t (&v)[32], float sc, float ref, uint32_t 
 #pragma unroll
     for (int e = 0; e < 32; e += 2) {
         const float pa = pt_ex2(fmaf(__uint_as_float(v[e]), sc, -ref));
-        const float pb = pt_ex2(fmaf(__uint_as_float(v[e + 1]), sc, -ref));
+        const float xb = fmaf(__uint_as_float(v[e + 1]), sc, -ref);
+        const float pb = (e & 2) ? pt_ex2_poly(xb) : pt_ex2(xb);
         sum += pa + pb;
         pk[e >> 1] = pt_pack_half2(pa, pb);
     }
@@ -141,6 +154,7 @@ __global__ void __launch_bounds__(PT_THREADS, 1) attention_prefill_tc_kernel(con
     uint64_t* o_full = bars + 17;        // [2] P V of tile j complete (barrier j & 1)
     uint64_t* s_empty = bars + 19;       // [2] the score buffer has been read into registers
     uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(bars + 21);
+    float* mx_s = reinterpret_cast<float*>(bars + 24);          // [2 step parities][2 halves][128 rows] row maxima (and row sums at the end)
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int head = blockIdx.y;
@@ -179,11 +193,11 @@ __global__ void __launch_bounds__(PT_THREADS, 1) attention_prefill_tc_kernel(con
         }
         for (int s = 0; s < 2; s++) {
             mbar_init(&s_full[s], 1);
-            mbar_init(&s_empty[s], 128);
-            mbar_init(&p_full[s], 128);
+            mbar_init(&s_empty[s], 256);
+            mbar_init(&p_full[s], 256);
             mbar_init(&o_full[s], 1);
         }
-        mbar_init(q_full, 128);
+        mbar_init(q_full, 256);
         mbar_fence_init();
     }
     if (warp == 0) tmem_alloc(tmem_holder, 512);
@@ -257,20 +271,22 @@ __global__ void __launch_bounds__(PT_THREADS, 1) attention_prefill_tc_kernel(con
             }
             __syncwarp();
         }
-    } else if (warp <= 4) {
-        // ------------------------------------ softmax: thread = query row = TMEM lane ------------------------------------
-        const int quarter = warp & 3, row = quarter * 32 + lane;
+    } else if (warp <= 4 || warp >= 8) {
+        // ---------------- softmax: two threads per query row (= TMEM lane), 64 score columns each ----------------
+        // warps 1-4 take columns [0, 64) of their lane quarter, warps 8-11 columns [64, 128): the MUFU work of a step
+        // (128 x 128 exp2) is fixed, but with two warps per scheduler the loads, maxima, packs and stores overlap it
+        const int quarter = warp & 3, row = quarter * 32 + lane, hf = warp >= 8 ? 1 : 0;
         const int r_abs = r_first + row;
         {
-            const float* qg = a.q + (size_t)(begin + min(r_abs, n_rows - 1)) * a.n_heads * PT_HS + head * PT_HS;
-            uint8_t* qd = q_s + row * 128;
+            const float* qg = a.q + (size_t)(begin + min(r_abs, n_rows - 1)) * a.n_heads * PT_HS + head * PT_HS + hf * 64;
+            uint8_t* qd = q_s + hf * 16384 + row * 128;
 #pragma unroll 4
-            for (int c = 0; c < 16; c++) {      // 16-byte piece c of the row: half tile c >> 3, swizzled slot (c & 7) ^ (row & 7)
+            for (int c = 0; c < 8; c++) {       // 16-byte piece c of this half of the row -> swizzled slot c ^ (row & 7)
                 const float4 x = reinterpret_cast<const float4*>(qg)[2 * c], y = reinterpret_cast<const float4*>(qg)[2 * c + 1];
                 uint4 u;
                 u.x = pt_pack_half2(x.x, x.y); u.y = pt_pack_half2(x.z, x.w);
                 u.z = pt_pack_half2(y.x, y.y); u.w = pt_pack_half2(y.z, y.w);
-                *reinterpret_cast<uint4*>(qd + (c >> 3) * 16384 + (((c & 7) ^ (row & 7)) << 4)) = u;
+                *reinterpret_cast<uint4*>(qd + ((c ^ (row & 7)) << 4)) = u;
             }
             fence_proxy_async_smem();
             mbar_arrive(q_full);
@@ -279,39 +295,41 @@ __global__ void __launch_bounds__(PT_THREADS, 1) attention_prefill_tc_kernel(con
         const uint32_t lane_base = (uint32_t)(quarter * 32) << 16;
         const float sc = 1.4426950408889634f * rsqrtf((float)PT_HS);      // scores in the log2 domain
         float m_used = -INFINITY, l = 0.0f;
-        uint32_t v0[32], v1[32], v2[32], v3[32];
+        uint32_t v0[32], v1[32];
         for (int j = 0; j < n_tiles; j++) {
             pt_wait(&s_full[j & 1], (j >> 1) & 1, t0);
             if (tid == 32) PT_STAMP(3, j);
             tc_fence_after();
-            const uint32_t t_s = T_S + lane_base + (j & 1) * 128;
-            const int tok0 = j * PT_KV;
-            if (a.dbg & 1) { tc_fence_before(); mbar_arrive(&p_full[j & 1]); continue; }
-            // the whole score row in registers: four loads in flight, one wait
+            const uint32_t t_s = T_S + lane_base + (j & 1) * 128 + hf * 64;
+            const int tok0 = j * PT_KV + hf * 64;
+            if (a.dbg & 1) { tc_fence_before(); mbar_arrive(&s_empty[j & 1]); mbar_arrive(&p_full[j & 1]); continue; }
             tmem_ld_32x32b_x32(t_s, v0);
             tmem_ld_32x32b_x32(t_s + 32, v1);
-            tmem_ld_32x32b_x32(t_s + 64, v2);
-            tmem_ld_32x32b_x32(t_s + 96, v3);
             tmem_ld_wait();
             tc_fence_before();
             mbar_arrive(&s_empty[j & 1]);                    // the scores of step j+2 may overwrite the buffer now
-            const int lim = pos_r - tok0;                    // columns e <= lim are visible to this row
-            const bool full = lim >= PT_KV - 1;              // no masking in this tile (all but the last tile or two)
-            float mx = -INFINITY;
-            if (full) {
+            const int lim = pos_r - tok0;                    // columns e <= lim of this half are visible to this row
+            float ma = -INFINITY, mb = -INFINITY;
+            if (lim >= 63) {
 #pragma unroll
-                for (int e = 0; e < 32; e++)
-                    mx = fmaxf(mx, fmaxf(fmaxf(__uint_as_float(v0[e]), __uint_as_float(v1[e])), fmaxf(__uint_as_float(v2[e]), __uint_as_float(v3[e]))));
+                for (int e = 0; e < 32; e += 2) {
+                    ma = fmaxf(ma, fmaxf(__uint_as_float(v0[e]), __uint_as_float(v1[e])));
+                    mb = fmaxf(mb, fmaxf(__uint_as_float(v0[e + 1]), __uint_as_float(v1[e + 1])));
+                }
             } else {
 #pragma unroll
                 for (int e = 0; e < 32; e++) {
                     if (e > lim) v0[e] = 0xff800000u;        // -inf
                     if (e + 32 > lim) v1[e] = 0xff800000u;
-                    if (e + 64 > lim) v2[e] = 0xff800000u;
-                    if (e + 96 > lim) v3[e] = 0xff800000u;
-                    mx = fmaxf(mx, fmaxf(fmaxf(__uint_as_float(v0[e]), __uint_as_float(v1[e])), fmaxf(__uint_as_float(v2[e]), __uint_as_float(v3[e]))));
+                    ma = fmaxf(ma, fmaxf(__uint_as_float(v0[e]), __uint_as_float(v1[e])));
                 }
             }
+            // row maximum over both halves: exchange through shared memory (slot of step parity: the next write to it
+            // comes two steps later, after everybody has passed the barrier of the step in between)
+            float mx = fmaxf(ma, mb);
+            mx_s[((j & 1) * 2 + hf) * PT_ROWS + row] = mx;
+            asm volatile("bar.sync 2, 256;" ::: "memory");
+            mx = fmaxf(mx, mx_s[((j & 1) * 2 + (hf ^ 1)) * PT_ROWS + row]);
             if (tid == 32) PT_STAMP(4, j);
             mx *= sc;
             const bool need = mx > m_used + 8.0f;
@@ -323,12 +341,12 @@ __global__ void __launch_bounds__(PT_THREADS, 1) attention_prefill_tc_kernel(con
                     tc_fence_after();
                     uint32_t w[32];
 #pragma unroll 1
-                    for (int ch = 0; ch < 4; ch++) {
-                        tmem_ld_32x32b_x32(T_O + lane_base + ch * 32, w);
+                    for (int ch = 0; ch < 2; ch++) {
+                        tmem_ld_32x32b_x32(T_O + lane_base + hf * 64 + ch * 32, w);
                         tmem_ld_wait();
 #pragma unroll
                         for (int e = 0; e < 32; e++) w[e] = __float_as_uint(__uint_as_float(w[e]) * alpha);
-                        tmem_st_32x32b_x32(T_O + lane_base + ch * 32, w);
+                        tmem_st_32x32b_x32(T_O + lane_base + hf * 64 + ch * 32, w);
                     }
                     tmem_st_wait();
                 }
@@ -336,15 +354,13 @@ __global__ void __launch_bounds__(PT_THREADS, 1) attention_prefill_tc_kernel(con
                 m_used = m_new;
             }
             const float ref = (m_used == -INFINITY) ? 0.0f : m_used;
-            const uint32_t t_p = T_P + lane_base + (j & 1) * 64;
+            const uint32_t t_p = T_P + lane_base + (j & 1) * 64 + hf * 32;
             if (j >= 2) {      // P V(j-2) has consumed this probability buffer (long done; the wait keeps it a guarantee)
                 pt_wait(&o_full[j & 1], ((j - 2) >> 1) & 1, t0);
                 tc_fence_after();
             }
             l += pt_probs(v0, sc, ref, t_p);
             l += pt_probs(v1, sc, ref, t_p + 16);
-            l += pt_probs(v2, sc, ref, t_p + 32);
-            l += pt_probs(v3, sc, ref, t_p + 48);
             tmem_st_wait();
             tc_fence_before();
             mbar_arrive(&p_full[j & 1]);
@@ -353,24 +369,30 @@ __global__ void __launch_bounds__(PT_THREADS, 1) attention_prefill_tc_kernel(con
         // ---- finish: O / l -> shared memory -> Q80 cast into the slabs of the wo matmul ----
         pt_wait(&o_full[(n_tiles - 1) & 1], ((n_tiles - 1) >> 1) & 1, t0);
         tc_fence_after();
+        // the two halves of the row sum, through the exchange slots the LAST step did not use (their previous readers
+        // have all passed that step's barrier)
+        const int fs = (n_tiles & 1) * 2;
+        mx_s[(fs + hf) * PT_ROWS + row] = l;
+        asm volatile("bar.sync 2, 256;" ::: "memory");
+        l += mx_s[(fs + (hf ^ 1)) * PT_ROWS + row];
         const float inv = l > 0.0f ? 1.0f / l : 0.0f;
 #pragma unroll 1
-        for (int ch = 0; ch < 4; ch++) {
-            tmem_ld_32x32b_x32(T_O + lane_base + ch * 32, v0);
+        for (int ch = 0; ch < 2; ch++) {
+            tmem_ld_32x32b_x32(T_O + lane_base + hf * 64 + ch * 32, v0);
             tmem_ld_wait();
 #pragma unroll
-            for (int e = 0; e < 32; e++) out_s[row * PT_OUT_LD + ch * 32 + e] = __uint_as_float(v0[e]) * inv;
+            for (int e = 0; e < 32; e++) out_s[row * PT_OUT_LD + hf * 64 + ch * 32 + e] = __uint_as_float(v0[e]) * inv;
         }
-        __syncwarp();                                            // a warp only re-reads the 32 rows it wrote
+        __syncwarp();                                            // a warp only re-reads the 32 rows x 64 columns it wrote
         for (int rr = 0; rr < 32; rr++) {
             const int rc = r_first + quarter * 32 + rr;
             if (rc >= n_rows) break;
             const int m = begin + rc;
 #pragma unroll
-            for (int b = 0; b < PT_HS / 32; b++) {
-                const float val = out_s[(quarter * 32 + rr) * PT_OUT_LD + b * 32 + lane];
-                q80_block_store(val, lane, m, (head * PT_HS) / 32 + b, a.out_mcap, a.xq_out, a.xh_out);
-                if (a.y_out != nullptr) a.y_out[(size_t)m * a.n_heads * PT_HS + head * PT_HS + b * 32 + lane] = val;
+            for (int b = 0; b < 2; b++) {
+                const float val = out_s[(quarter * 32 + rr) * PT_OUT_LD + hf * 64 + b * 32 + lane];
+                q80_block_store(val, lane, m, (head * PT_HS) / 32 + hf * 2 + b, a.out_mcap, a.xq_out, a.xh_out);
+                if (a.y_out != nullptr) a.y_out[(size_t)m * a.n_heads * PT_HS + head * PT_HS + hf * 64 + b * 32 + lane] = val;
             }
         }
     } else if (warp == 5 || warp == 7) {
@@ -472,7 +494,7 @@ extern "C" int dl_attention_prefill_tc(const float* q, int M, int n_heads, int n
     alignas(64) CUtensorMap kmap, vmap;
     const long long rows = (long long)n_cache_pages * n_kv_heads * 32;
     if (pt_make_map(&kmap, k_cache, rows) != 0 || pt_make_map(&vmap, v_cache, rows) != 0) return -1;
-    const size_t smem = (1 + 2 * PT_STAGES) * PT_TILE_BYTES + 24 * 8;
+    const size_t smem = (1 + 2 * PT_STAGES) * PT_TILE_BYTES + 24 * 8 + 4 * PT_ROWS * 4;
     static bool set = false;
     if (!set) {
         cudaError_t e = cudaFuncSetAttribute(attention_prefill_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

@@ -48,7 +48,7 @@ WH_MIN_ROWS = int(os.environ.get("DLLAMA_WH_MIN_ROWS", "768"))             # res
 WH_MIN_ROWS_SCRATCH = int(os.environ.get("DLLAMA_WH_MIN_ROWS_SCRATCH", "2048"))   # per-call expansion: ~13 % of the GEMM time at 2048 rows
 # batches from this many rows run their prompt chunks on the tcgen05 attention kernel (attention_prefill_tc.cu, 128-row
 # tiles, head size 128); smaller ones on the mma.sync kernel with 64-row tiles
-PREFILL_TC_MIN_ROWS = int(os.environ.get("DLLAMA_PREFILL_TC_MIN_ROWS", "2048"))
+PREFILL_TC_MIN_ROWS = int(os.environ.get("DLLAMA_PREFILL_TC_MIN_ROWS", "128"))
 PAGE = K.PAGE_SIZE
 
 
