@@ -116,12 +116,12 @@ class LlamaEngine:
         self.sync_q80 = sync_q80
         # Decode batches of <= 4 rows can run as ONE persistent cooperative kernel (csrc/cuda/decode_mega.cu) instead of the
         # launch sequence below.  Measured on 8B single-stream decode (tok/s, launch sequence vs persistent kernel):
-        # 1 GPU 592 / 477, 2 GPUs 628 / 573, 4 GPUs 573 / 586, 8 GPUs 463 / 517 -- a step is a chain of ~8 grid-wide
+        # 1 GPU 593 / 477, 2 GPUs 628 / 573, 4 GPUs 575 / 555, 8 GPUs 464 / 573 -- a step is a chain of ~8 grid-wide
         # hand-offs per layer either way; the persistent kernel wins where the launch sequence's fence + counter + flag
-        # exchange dominates.  Default: on for world >= 4.  DLLAMA_MEGA=1 / 0 or use_mega=True / False force it.
+        # exchange dominates.  Default: on for world >= 8.  DLLAMA_MEGA=1 / 0 or use_mega=True / False force it.
         env_mega = os.environ.get("DLLAMA_MEGA", "auto")
         if use_mega is None:
-            use_mega = (world >= 4) if env_mega == "auto" else (env_mega != "0")
+            use_mega = (world >= 8) if env_mega == "auto" else (env_mega != "0")
         self.use_mega = bool(use_mega)
         self.seq_len = min(h.seq_len, max_seq_len)
         self.n_sms = K.cuda_lib().dl_device_sm_count()
