@@ -80,7 +80,7 @@ DL_DEVINL void epilogue_rows(const DlEpilogue& e, const float* out_s, int out_ld
                         d0[m * ld] = v;
                     }
                 }
-            } else if (e.ll) {
+            } else if (e.ll == 1) {
                 // tensor-parallel push, LL words: value and epoch travel in one 8-byte store per peer; the consumer
                 // polls the words themselves, so there is nothing to fence and no flag to release afterwards
                 const uint32_t epoch = ld_volatile_u32(e.step_counter) * e.flag_mul + e.flag_add;
@@ -91,6 +91,29 @@ DL_DEVINL void epilogue_rows(const DlEpilogue& e, const float* out_s, int out_ld
                         const size_t off = off0 + m * ld;
 #pragma unroll 1
                         for (int p = 0; p < nd; p++) ll_store(e.dst[p], off, v, epoch);
+                    }
+                }
+            } else if (e.ll == 2) {
+                // tensor-parallel push in the reference's own wire format: Q80 blocks (int8 values + one fp16 scale per
+                // 32, src/nn/nn-quants.hpp:64-72) instead of the f32 of their round trip -- 1.06 instead of 4 bytes per
+                // value on NVLink, which is what bounds prompt-sized exchanges.  Row R = element offset / ld of the f32
+                // layout; a wire row is ld int8 followed by ld/32 fp16 scales.  A warp = one 32-value block.
+                const size_t rowb = (size_t)ld + (ld >> 4);
+                const size_t row0 = ((size_t)e.dst_off + (size_t)m0 * ld) / ld;
+                for (int m = m_first; m < M; m += m_step) {
+                    const float v = out_s[m * out_ld + tid];
+                    const float amax = warp_max(fabsf(v));
+                    const float d = amax / 127.0f;
+                    const float id = (d != 0.0f) ? (1.0f / d) : 0.0f;
+                    const int q = __float2int_rn(v * id);
+                    if (live) {
+                        const size_t rb = (row0 + m) * rowb;
+#pragma unroll 1
+                        for (int p = 0; p < nd; p++) {
+                            uint8_t* wrow = reinterpret_cast<uint8_t*>(e.dst[p]) + rb;
+                            reinterpret_cast<int8_t*>(wrow)[grow] = (int8_t)q;
+                            if (lane == 0) *reinterpret_cast<__half*>(wrow + ld + ((grow >> 5) << 1)) = __float2half_rn(d);
+                        }
                     }
                 }
             } else {

@@ -174,7 +174,10 @@ __global__ void __launch_bounds__(RNQ_THREADS) reduce_norm_quant_kernel(const __
         }
         __syncthreads();
     }
-    const int ll = a.ll;
+    const int ll = (a.ll == 1) ? 1 : 0;
+    const bool wire = a.ll == 2;      // partials are Q80 wire rows: dim int8 + dim/32 fp16 scales (see epilogue.cuh)
+    const size_t rowb = (size_t)a.dim + (a.dim >> 4);
+    const size_t src_rows = (size_t)a.src_stride / a.dim;
     const uint32_t ll_epoch = ll ? ld_volatile_u32(a.step_counter) * a.flag_mul + a.flag_add : 0u;
     // pass 1: merged residual (float4, coalesced) -> x_out, sum of squares
     constexpr int nwarps = RNQ_THREADS / 32;
@@ -183,7 +186,16 @@ __global__ void __launch_bounds__(RNQ_THREADS) reduce_norm_quant_kernel(const __
     for (int i4 = tid; i4 < a.dim / 4; i4 += RNQ_THREADS) {
         float4 v = reinterpret_cast<const float4*>(a.x_in + row)[i4];
         for (int s = 0; s < a.n_src; s++) {
-            const float4 p = part_load4(a.partials, (size_t)s * a.src_stride + row + 4 * (size_t)i4, ll, ll_epoch);
+            float4 p;
+            if (wire) {
+                const uint8_t* wr = reinterpret_cast<const uint8_t*>(a.partials) + ((size_t)s * src_rows + m) * rowb;
+                const int q4 = *reinterpret_cast<const int*>(wr + 4 * i4);
+                const float d = __half2float(*reinterpret_cast<const __half*>(wr + a.dim + ((i4 >> 3) << 1)));
+                p = make_float4((float)(int8_t)(q4 & 0xff) * d, (float)(int8_t)((q4 >> 8) & 0xff) * d,
+                                (float)(int8_t)((q4 >> 16) & 0xff) * d, (float)(q4 >> 24) * d);
+            } else {
+                p = part_load4(a.partials, (size_t)s * a.src_stride + row + 4 * (size_t)i4, ll, ll_epoch);
+            }
             v.x += p.x; v.y += p.y; v.z += p.z; v.w += p.w;
         }
         if (a.x_out != nullptr) reinterpret_cast<float4*>(a.x_out + row)[i4] = v;
@@ -206,6 +218,19 @@ __global__ void __launch_bounds__(RNQ_THREADS) reduce_norm_quant_kernel(const __
 #pragma unroll
         for (int j = 0; j < 8; j++) v[j] = reinterpret_cast<const float4*>(a.x_in + e)[j];
         for (int s = 0; s < a.n_src; s++) {
+            if (wire) {
+                const uint8_t* wr = reinterpret_cast<const uint8_t*>(a.partials) + ((size_t)s * src_rows + m) * rowb;
+                const uint4 qa = *reinterpret_cast<const uint4*>(wr + b * 32), qb = *reinterpret_cast<const uint4*>(wr + b * 32 + 16);
+                const float d = __half2float(*reinterpret_cast<const __half*>(wr + a.dim + (b << 1)));
+                const uint32_t w8[8] = {qa.x, qa.y, qa.z, qa.w, qb.x, qb.y, qb.z, qb.w};
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                    const int q4 = (int)w8[j];
+                    v[j].x += (float)(int8_t)(q4 & 0xff) * d; v[j].y += (float)(int8_t)((q4 >> 8) & 0xff) * d;
+                    v[j].z += (float)(int8_t)((q4 >> 16) & 0xff) * d; v[j].w += (float)(q4 >> 24) * d;
+                }
+                continue;
+            }
             const size_t pe = (size_t)s * a.src_stride + e;
 #pragma unroll
             for (int j = 0; j < 8; j++) {

@@ -49,6 +49,7 @@ WH_MIN_ROWS_SCRATCH = int(os.environ.get("DLLAMA_WH_MIN_ROWS_SCRATCH", "2048")) 
 # batches from this many rows run their prompt chunks on the tcgen05 attention kernel (attention_prefill_tc.cu, 128-row
 # tiles, head size 128); smaller ones on the mma.sync kernel with 64-row tiles
 PREFILL_TC_MIN_ROWS = int(os.environ.get("DLLAMA_PREFILL_TC_MIN_ROWS", "128"))
+WIRE_Q80 = os.environ.get("DLLAMA_WIRE_Q80", "1") != "0"
 PAGE = K.PAGE_SIZE
 
 
@@ -516,6 +517,9 @@ class LlamaEngine:
         L = h.n_layers
         multi = N > 1
         ll_fwd = self.use_ll and M <= self._ll_rows          # this forward exchanges LL words (same choice on every rank)
+        # batches on the tensor-core path that use the flag protocol ship Q80 rows (int8 + fp16 scales) instead of f32:
+        # 3.8x fewer NVLink bytes, which is what bounds prompt-sized exchanges (DLLAMA_WIRE_Q80=0: f32 as before)
+        wire = (N > 1) and not gemv and not ll_fwd and self.sync_q80 and WIRE_Q80
         src_stride = (self._ll_rows if ll_fwd else self.max_rows) * h.dim
         part_att = self.part_att_ll if ll_fwd else self.part_att
         part_ffn = self.part_ffn_ll if ll_fwd else self.part_ffn
@@ -536,21 +540,25 @@ class LlamaEngine:
             x_in = _Off(self.x[cur], x_off)
             x_out = _Off(self.x[cur ^ 1], x_off) if merge else None
             ll = ll_fwd and merge
-            parts = (pending[0][self.rank] + x_off * (2 if ll else 1)) if merge else None
+            wq = wire and merge
+            if wq:       # Q80 wire rows: dim int8 + dim/32 fp16 scales per row
+                parts = pending[0][self.rank] + (x_off // (h.dim * 4)) * (h.dim + h.dim // 16)
+            else:
+                parts = (pending[0][self.rank] + x_off * (2 if ll else 1)) if merge else None
             flags = pending[1] if (merge and multi and not ll) else None
             fuse = False
-            if rows <= GEMV_PATH_MAX_M:
+            if rows <= GEMV_PATH_MAX_M and not wq:
                 fuse = True          # the grid never exceeds one CTA per SM: the repeated prologue is cheap
             if fuse:
                 nm = K.norm_prolog(x_in, x_out, parts, N, src_stride, flags, sc, L, flag_add, w_norm, eps, ll=ll)
                 self._matmul(weight, d, h.dim, rows, None, None, epi, kind, norm=nm)
             elif rows <= GEMV_PATH_MAX_M:
                 K.reduce_norm_quant(x_in, x_out, parts, N if merge else 0, src_stride, flags, sc, L, flag_add, w_norm,
-                                    eps, h.dim, rows, rows, self.xq_dim, None, pdl=pdl, ll=ll)
+                                    eps, h.dim, rows, rows, self.xq_dim, None, pdl=pdl, ll=ll, wire_q80=wq)
                 self._matmul(weight, d, h.dim, rows, self.xq_dim, None, epi, kind)
             else:
                 K.reduce_norm_quant(x_in, x_out, parts, N if merge else 0, src_stride, flags, sc, L, flag_add, w_norm,
-                                    eps, h.dim, rows, self.ncap, None, self.xh_dim, pdl=pdl, ll=ll)
+                                    eps, h.dim, rows, self.ncap, None, self.xh_dim, pdl=pdl, ll=ll, wire_q80=wq)
                 self._matmul(weight, d, h.dim, rows, None, self.xh_dim, epi, kind)
             if merge:
                 cur ^= 1
@@ -563,7 +571,7 @@ class LlamaEngine:
                 return K.epi_store(buf_ptrs, h.dim, self.rank * src_stride, self.sync_q80, None, sc, L, flag_add,
                                    ll=True)
             return K.epi_store(buf_ptrs, h.dim, self.rank * src_stride, self.sync_q80,
-                               flags_peer if multi else None, sc, L, flag_add, counter)
+                               flags_peer if multi else None, sc, L, flag_add, counter, wire_q80=wire)
 
         pending = None
         for l, W in enumerate(self.layers):

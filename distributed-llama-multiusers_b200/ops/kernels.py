@@ -75,12 +75,16 @@ def make_q40t(raw_q40: torch.Tensor, d: int, n: int) -> torch.Tensor:
 def epi_store(dst: Sequence[int], ld: int, dst_off: int = 0, q80_roundtrip: bool = False,
               flags: Optional[Sequence[int]] = None, step_counter: Optional[int] = None, flag_mul: int = 0,
               flag_add: int = 0, cta_counter: Optional[int] = None, residual: Optional[int] = None,
-              residual_ld: int = 0, ll: bool = False) -> DlEpilogue:
+              residual_ld: int = 0, ll: bool = False, wire_q80: bool = False) -> DlEpilogue:
     """ll=True: dst[] hold LL words {f32 bits, epoch} (tensor-parallel partial sums); step_counter / flag_mul /
-    flag_add define the epoch and no flags are released."""
+    flag_add define the epoch and no flags are released.  wire_q80=True (with flags): the partial sums travel as Q80
+    rows (ld int8 + ld/32 fp16 scales) instead of f32; dst_off / ld keep their f32-layout meaning (row = offset / ld)."""
     e = DlEpilogue()
     e.kind = EPI_STORE
-    e.ll = 1 if ll else 0
+    assert not (ll and wire_q80)
+    e.ll = 1 if ll else (2 if wire_q80 else 0)
+    if wire_q80:
+        assert q80_roundtrip and residual is None and dst_off % ld == 0
     if ll:
         assert flags is None and step_counter is not None
         e.step_counter = step_counter
@@ -133,9 +137,10 @@ def epi_silu_mul(xq_out: Optional[torch.Tensor], xh_out: Optional[torch.Tensor],
 
 # ---- launches ------------------------------------------------------------------------------------
 def reduce_norm_quant(x_in, x_out, partials, n_src, src_stride, flags, step_counter, flag_mul, flag_add, norm_w,
-                      eps, dim, M, mcap, xq_out, xh_out, y_out=None, pdl=False, ll=False):
+                      eps, dim, M, mcap, xq_out, xh_out, y_out=None, pdl=False, ll=False, wire_q80=False):
+    mode = (1 if ll else (2 if wire_q80 else 0)) if (partials and n_src) else 0
     check(cuda_lib().dl_reduce_norm_quant(_p(x_in), _p(x_out), partials, n_src, src_stride, flags, step_counter,
-                                          flag_mul, flag_add, 1 if (ll and partials and n_src) else 0, _p(norm_w), eps,
+                                          flag_mul, flag_add, mode, _p(norm_w), eps,
                                           dim, M, mcap, _p(xq_out),
                                           _p(xh_out), _p(y_out), 1 if pdl else 0, _stream()),
           "dl_reduce_norm_quant")

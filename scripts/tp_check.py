@@ -45,7 +45,7 @@ def main():
             print(f"[rank {rank}] {'PASS' if cond else 'FAIL'} {name} {detail}", flush=True)
 
     for graphs in (False, True):
-        eng = LlamaEngine(path, rank=rank, world=world, max_rows=32, n_slots=3, max_seq_len=256,
+        eng = LlamaEngine(path, rank=rank, world=world, max_rows=64, n_slots=4, max_seq_len=256,
                           use_graphs=graphs, use_pdl=not a.no_pdl)
         oracle = OracleLlama(mfile.ModelFile(path), n_nodes=world, max_seq_len=256) if rank == 0 else None
         rng = np.random.default_rng(1)
@@ -79,6 +79,17 @@ def main():
             ref2 = oracle.forward(p2, 0).numpy()
             err = float(np.abs(lg2 - ref2).max() / np.abs(ref2).max())
             check(f"tcgen05 20-row chunk logits (graphs={graphs})", err < 4e-2, f"rel err {err:.2e}")
+        # --- 50-row chunk: more rows than the LL exchange takes, so the partial sums travel as Q80 wire rows under the
+        #     flag protocol at every world size; logits of the last 3 rows only (offset into the exchange rows) ---
+        slot3 = eng.alloc_slot()
+        p3 = rng.integers(1, vocab, 50).tolist()
+        lg3 = eng.forward(p3, list(range(50)), [slot3] * 50, logits_from=47).float().cpu().numpy()
+        if rank == 0:
+            oracle.reset()
+            ref3 = oracle.forward(p3, 0).numpy()[47:]
+            err = float(np.abs(lg3 - ref3).max() / np.abs(ref3).max())
+            check(f"50-row chunk, Q80 wire exchange, last-3 logits (graphs={graphs})", err < 4e-2, f"rel err {err:.2e}")
+        eng.free_slot(slot3)
         # --- device-resident greedy loop: all ranks must produce identical tokens ---
         t0 = int(np.argmax(lg2[-1]))
         eng.ensure_capacity(slot2, 20 + 12)

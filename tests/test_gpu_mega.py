@@ -14,6 +14,8 @@ def _plan(d, n, align, grid):
     (6144, 4096, 2, 148), (4096, 4096, 32, 148), (28672, 4096, 2, 148), (4096, 14336, 32, 148),
     (128256, 4096, 2, 148), (768, 4096, 2, 148), (4096, 512, 32, 148), (3584, 4096, 2, 148), (16032, 4096, 2, 148),
     (512, 256, 2, 148), (256, 256, 32, 148), (1024, 256, 2, 148), (1024, 256, 2, 7), (256, 512, 32, 1),
+    # Llama-3.3-70B on 8 ranks: qkv 1280 x 8192, wo 8192 x 1024, w1|w3 7168 x 8192, w2 8192 x 3584, wcls 16032 x 8192
+    (1280, 8192, 2, 148), (8192, 1024, 32, 148), (7168, 8192, 2, 148), (8192, 3584, 32, 148), (16032, 8192, 2, 148),
 ])
 def test_mega_plan_covers_every_row_once(d, n, align, grid):
     """Every row of a matmul phase belongs to exactly one CTA, ranges are aligned, and the busiest CTA is within one
