@@ -9,7 +9,7 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "distributed-llama-multiusers_b200", "lib", "libdllama_b200_cuda.so")
-KEYS = ["UTCHMMA", "UTCBAR", "UTCATOMSWS", "LDTM", "STTM", "UBLKCP", "SYNCS", "ACQBULK", "IDP.4A", "UCGABAR", "MAPA", "ELECT",
+KEYS = ["UTCHMMA", "UTCBAR", "UTCATOMSWS", "LDTM", "STTM", "UBLKCP", "UTMALDG", "SYNCS", "ACQBULK", "IDP.4A", "UCGABAR", "MAPA", "ELECT",
         "NANOSLEEP", "ST.E.STRONG.SYS", "LD.E.STRONG.SYS", "MEMBAR", "CCTL", "HMMA", "HFMA2", "HMUL2", "HADD2", "LDS.128", "STS.128",
         "REDUX", "SHFL", "ATOMG", "RED."]
 
@@ -92,7 +92,7 @@ def main():
                     break
     lines = ["SASS mnemonic counts per kernel (cuobjdump -sass libdllama_b200_cuda.so), sm_100a; regenerate with scripts/sass_evidence.py",
              "UTCHMMA = tcgen05.mma kind::f16 (operand `tmem[..]` in the A slot = A from tensor memory), STTM = tcgen05.st, LDTM = tcgen05.ld,",
-             "UTCATOMSWS = tcgen05.alloc/dealloc, UTCBAR = tcgen05.commit, UBLKCP = cp.async.bulk (TMA 1-D), SYNCS = mbarrier ops,",
+             "UTCATOMSWS = tcgen05.alloc/dealloc, UTCBAR = tcgen05.commit, UBLKCP = cp.async.bulk (TMA 1-D), UTMALDG = cp.async.bulk.tensor (TMA tensor copy), SYNCS = mbarrier ops,",
              "IDP.4A = dp4a, UCGABAR = cluster barrier, MAPA = DSMEM address map, ELECT = elect.sync, ST/LD.E.STRONG.SYS = system-scope flags", ""]
     for name, c in kernels.items():
         lines.append(name)
