@@ -107,6 +107,9 @@ class AppArgs:
                     raise ValueError("GPU segments expected in the format <from>:<to>")
                 f, t = value.split(":", 1)
                 a.gpu_segment_from, a.gpu_segment_to = int(f), int(t)
+                # the reference splits a layer's ops between CPU and Vulkan segments; here every op of a rank runs on
+                # its one GPU (or all on the host backend), so there is nothing to segment
+                print(f"💡 --gpu-segments {value} accepted and ignored: all ops of a rank run on one device", flush=True)
             elif name == "--net-turbo": a.net_turbo = int(value) == 1
             elif name == "--max-batch": a.max_batch = int(value)
             elif name == "--n-slots": a.n_slots = int(value)

@@ -31,7 +31,8 @@ DL_DEVINL void q80_block_store(float val, int lane, int m, int kblock, int mcap,
         xh_slot(lane, w, s);
         size_t off = (size_t)kt * (size_t)(mcap >> 3) * XH_ROWGROUP_BYTES + (size_t)(m >> 3) * XH_ROWGROUP_BYTES +
                      (size_t)(kb * 4 + w) * 128 + (size_t)(m & 7) * 16 + (size_t)s * 2;
-        *reinterpret_cast<__half*>(xh + off) = __float2half_rn((float)q * df);
+        // fp16 operand of the tcgen05 path: a block whose scale exceeds 515 (|x| > 65405) saturates instead of becoming inf
+        *reinterpret_cast<__half*>(xh + off) = __float2half_rn((float)q * fminf(df, 515.0f));
     }
 }
 

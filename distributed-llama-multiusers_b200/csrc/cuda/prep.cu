@@ -282,13 +282,14 @@ __global__ void __launch_bounds__(RNQ_THREADS) reduce_norm_quant_kernel(const __
             // chunk w holds elements [4w, 4w+2, 4w+1, 4w+3, 4w+16, 4w+18, 4w+17, 4w+19] (see xh_slot)
             uint8_t* base = a.xh_out + (size_t)kt * (size_t)(a.mcap >> 3) * XH_ROWGROUP_BYTES +
                             (size_t)(m >> 3) * XH_ROWGROUP_BYTES + (size_t)(kb * 4) * 128 + (size_t)(m & 7) * 16;
+            const float dfh = fminf(df, 515.0f);       // fp16 operand: saturate (|x| > 65405) instead of producing inf
 #pragma unroll
             for (int w = 0; w < 4; w++) {
                 const int o = 4 * w;
-                __half2 h0 = __floats2half2_rn((float)q[o] * df, (float)q[o + 2] * df);
-                __half2 h1 = __floats2half2_rn((float)q[o + 1] * df, (float)q[o + 3] * df);
-                __half2 h2 = __floats2half2_rn((float)q[o + 16] * df, (float)q[o + 18] * df);
-                __half2 h3 = __floats2half2_rn((float)q[o + 17] * df, (float)q[o + 19] * df);
+                __half2 h0 = __floats2half2_rn((float)q[o] * dfh, (float)q[o + 2] * dfh);
+                __half2 h1 = __floats2half2_rn((float)q[o + 1] * dfh, (float)q[o + 3] * dfh);
+                __half2 h2 = __floats2half2_rn((float)q[o + 16] * dfh, (float)q[o + 18] * dfh);
+                __half2 h3 = __floats2half2_rn((float)q[o + 17] * dfh, (float)q[o + 19] * dfh);
                 uint4 u;
                 u.x = *reinterpret_cast<uint32_t*>(&h0); u.y = *reinterpret_cast<uint32_t*>(&h1);
                 u.z = *reinterpret_cast<uint32_t*>(&h2); u.w = *reinterpret_cast<uint32_t*>(&h3);

@@ -1439,11 +1439,15 @@ int dl_cpu_worker_serve(int port, int n_threads, char* err, int errlen) {
         setsockopt(lfd, SOL_SOCKET, SO_REUSEADDR, &one, sizeof one);
         sockaddr_in a{};
         a.sin_family = AF_INET;
+        // DLLAMA_BIND_ADDR: listen on one interface only (default: all, like the reference's worker)
+        const char* bind_addr = getenv("DLLAMA_BIND_ADDR");
         a.sin_addr.s_addr = htonl(INADDR_ANY);
+        if (bind_addr != nullptr && *bind_addr && inet_pton(AF_INET, bind_addr, &a.sin_addr) != 1)
+            throw std::runtime_error(std::string("DLLAMA_BIND_ADDR is not an IPv4 address: ") + bind_addr);
         a.sin_port = htons((uint16_t)port);
         if (bind(lfd, (sockaddr*)&a, sizeof a) != 0 || listen(lfd, 16) != 0)
             throw std::runtime_error(std::string("cannot listen on port ") + std::to_string(port) + ": " + strerror(errno));
-        printf("Listening on 0.0.0.0:%d...\n", port);
+        printf("Listening on %s:%d...\n", (bind_addr != nullptr && *bind_addr) ? bind_addr : "0.0.0.0", port);
         fflush(stdout);
         Node nd;
         const int rfd = accept(lfd, nullptr, nullptr);
@@ -1453,7 +1457,21 @@ int dl_cpu_worker_serve(int port, int n_threads, char* err, int errlen) {
         recv_all(rfd, hello, sizeof hello, nullptr);
         if (hello[0] != kHello) throw std::runtime_error("bad handshake from the root");
         const int n_workers = hello[1];
+        if (n_workers < 1 || n_workers > 63) throw std::runtime_error("bad worker count in the handshake");
         recv_all(rfd, &nd.c, sizeof nd.c, &nd.mesh.stats);
+        {
+            // everything below is sized from this packet: refuse values that cannot describe a model before any buffer
+            // is allocated or indexed with them (the peer is trusted like the reference trusts its root, but a wrong
+            // packet must end in an error message, not in memory corruption)
+            const Header& hh = nd.c.h;
+            const bool ok = nd.c.n_nodes == n_workers + 1 && nd.c.node >= 1 && nd.c.node < nd.c.n_nodes &&
+                            nd.c.max_rows >= 1 && nd.c.max_rows <= (1 << 16) && nd.c.n_slots >= 1 && nd.c.n_slots <= (1 << 16) &&
+                            hh.dim >= 32 && hh.dim <= (1 << 17) && hh.hidden_dim >= 32 && hh.hidden_dim <= (1 << 20) &&
+                            hh.n_layers >= 1 && hh.n_layers <= 1024 && hh.n_heads >= 1 && hh.n_heads <= 1024 &&
+                            hh.n_kv_heads >= 1 && hh.n_kv_heads <= hh.n_heads && hh.vocab >= 1 && hh.vocab <= (1 << 22) &&
+                            hh.seq_len >= 1 && hh.seq_len <= (1 << 22) && hh.dim % hh.n_heads == 0;
+            if (!ok) throw std::runtime_error("bad node configuration from the root");
+        }
         if (n_threads > 0) nd.c.n_threads = n_threads;
         std::vector<std::string> hosts(n_workers);
         std::vector<int> ports(n_workers);
@@ -1488,10 +1506,28 @@ int dl_cpu_worker_serve(int port, int n_threads, char* err, int errlen) {
             if (nb < 0 || (per_layer && (l < 0 || l >= nd.c.h.n_layers))) throw std::runtime_error("malformed weight record");
             auto read_mat = [&](Mat& m) {
                 m.d = hd[2]; m.n = hd[3]; m.q40 = hd[4] != 0;
+                // the slice this node owns is fixed by the header and the node count: anything else is a corrupt record
+                const Header& hh = nd.c.h;
+                const int qd = hh.dim / n, kvd = hh.kv_dim() / n, hid = hh.hidden_dim / n;
+                int ed = 0, en = 0;
+                switch (tag) {
+                    case T_WQ: ed = qd; en = hh.dim; break;
+                    case T_WK: case T_WV: ed = kvd; en = hh.dim; break;
+                    case T_WO: ed = hh.dim; en = qd; break;
+                    case T_W1: case T_W3: ed = hid; en = hh.dim; break;
+                    case T_W2: ed = hh.dim; en = hid; break;
+                    default: ed = hh.vocab / n; en = hh.dim; break;      // T_WCLS
+                }
+                const long long want = m.q40 ? (long long)ed * (en / QK) * Q40_BYTES : (long long)ed * en * 4;
+                if (m.d != ed || m.n != en || nb != want) throw std::runtime_error("weight record does not match the model header");
                 if (m.q40) { m.q.resize((size_t)nb); recv_all(rfd, m.q.data(), (size_t)nb, &nd.mesh.stats); }
                 else { m.f.resize((size_t)nb / 4); recv_all(rfd, m.f.data(), (size_t)nb, &nd.mesh.stats); }
             };
-            auto read_vec = [&](std::vector<float>& v) { v.resize((size_t)nb / 4); recv_all(rfd, v.data(), (size_t)nb, &nd.mesh.stats); };
+            auto read_vec = [&](std::vector<float>& v) {
+                if (nb != (long long)nd.c.h.dim * 4) throw std::runtime_error("norm record does not match the model header");
+                v.resize((size_t)nb / 4);
+                recv_all(rfd, v.data(), (size_t)nb, &nd.mesh.stats);
+            };
             switch (tag) {
                 case T_WQ: read_mat(nd.layers[l].wq); break;
                 case T_WK: read_mat(nd.layers[l].wk); break;

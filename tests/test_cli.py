@@ -197,3 +197,22 @@ def test_cpu_worker_serves_a_second_root_after_the_first_left(tiny_model_path, t
         worker.terminate()
         out = worker.communicate(timeout=30)[0]
     assert out.count("Worker is ready") == 3 and out.count("waiting for a new one") >= 2, out
+
+
+def test_every_environment_variable_is_documented():
+    """utils/envvars.py lists every DLLAMA_* variable the sources read (Python, C++, scripts)."""
+    import os
+    import re
+    from dllama_b200.utils import ENV_VARS
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    seen = set()
+    for base in ("distributed-llama-multiusers_b200", "scripts", "baseline"):
+        for dp, _, files in os.walk(os.path.join(root, base)):
+            if "_ref" in dp:
+                continue
+            for f in files:
+                if f.endswith((".py", ".cpp", ".cu", ".cuh", ".h", ".hpp")):
+                    seen |= set(re.findall(r"DLLAMA_[A-Z0-9_]+", open(os.path.join(dp, f), errors="ignore").read()))
+    seen |= set(re.findall(r"DLLAMA_[A-Z0-9_]+", open(os.path.join(root, "bench.py")).read()))
+    missing = sorted(v for v in seen if v not in ENV_VARS)
+    assert not missing, f"undocumented environment variables: {missing}"

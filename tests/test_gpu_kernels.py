@@ -97,6 +97,25 @@ def test_quant_q80_matches_numpy(M, Kdim):
     np.testing.assert_allclose(got_h, ref, rtol=1e-3, atol=1e-6)    # fp16 rounding of q*d
 
 
+def test_xh_saturates():
+    """fp16 activations of the tensor-core path: a block beyond the fp16 range saturates (no inf), everything else is
+    the plain Q80 round trip."""
+    k = K()
+    x = np.zeros((2, 256), dtype=np.float32)
+    x[0, :32] = np.linspace(-3e5, 3e5, 32)          # block scale 2362: far beyond fp16
+    x[0, 32:64] = np.linspace(-100, 100, 32)
+    x[1] = np.random.default_rng(3).standard_normal(256)
+    xh = k.alloc_xh(256, 16, "cuda")
+    k.quant_q80(torch.from_numpy(x).cuda(), 2, 256, 16, None, xh)
+    torch.cuda.synchronize()
+    got = _decode_xh(xh, 256, 16, 2)
+    assert np.isfinite(got).all() and np.abs(got).max() <= 65504
+    assert abs(got[0, 31]) > 6e4 and np.sign(got[0, 0]) == -1
+    ref = quant.q80_roundtrip(x)
+    np.testing.assert_allclose(got[0, 32:], ref[0, 32:], rtol=1e-3, atol=1e-6)
+    np.testing.assert_allclose(got[1], ref[1], rtol=1e-3, atol=1e-6)
+
+
 def _gemv_case(d, n, M, R, S, q80rt=False, seed=0):
     k = K()
     raw, wdq = _rand_q40(d, n, seed)
