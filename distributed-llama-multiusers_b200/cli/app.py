@@ -58,7 +58,7 @@ class AppArgs:
     gpu_index: int = -1
     gpu_segment_from: int = -1
     gpu_segment_to: int = -1
-    max_batch: int = 32
+    max_batch: int = 0          # 0 = chosen from the entry point and the device (see AppArgs.parse)
     n_slots: int = 0
     device: str = "auto"
     api_backend: str = "native"
@@ -121,6 +121,11 @@ class AppArgs:
             else:
                 raise ValueError(f"Unknown option: {name}")
             i += 2
+        if a.max_batch <= 0:
+            # rows of one forward pass.  On a GPU a large value costs memory only (activations, and from 768 rows the
+            # fp16 copy of the weights), and lets simultaneous prompts share one pass: dllama-api (require_mode False)
+            # 1024, the CLI 256; the host backends stay at 32
+            a.max_batch = (256 if require_mode else 1024) if use_cuda_device(a.device) else 32
         return a
 
 

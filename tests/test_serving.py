@@ -360,3 +360,24 @@ def test_scheduler_randomised_simulation_keeps_its_invariants():
     s.pop_released()
     assert s.stats() == {"waiting": 0, "running": 0, "free_slots": S}
     assert len(done) + len(cancelled) >= 300 and len(done) > 150
+
+
+def test_engine_row_buckets_and_logits_tail():
+    """Serving batch shapes (LlamaEngine._bucket / _buckets / _tail_rows, pure host logic): powers of two up to 256 rows,
+    multiples of 256 above, never beyond max_rows; every bucket a batch can ask for is in the warm-up list; the logits
+    tail covers one row per sequence slot and is only used when it saves at least half of the rows."""
+    from types import SimpleNamespace
+    from dllama_b200.models.llama import LlamaEngine
+    for max_rows, n_slots in ((32, 8), (64, 34), (256, 34), (1000, 34), (2048, 34), (2048, 300)):
+        e = SimpleNamespace(max_rows=max_rows, n_slots=n_slots)
+        buckets = LlamaEngine._buckets(e)
+        assert buckets == sorted(set(buckets)) and buckets[-1] == max_rows
+        for M in range(1, max_rows + 1):
+            Mp = LlamaEngine._bucket(e, M)
+            assert M <= Mp <= max_rows and Mp in buckets, (max_rows, M, Mp)
+            assert Mp < 2 * M or Mp <= 1 or Mp == max_rows or M <= 256          # padding never doubles a large batch
+            if M > 256:
+                assert Mp - M < 256
+        for Mp in buckets:
+            tail = LlamaEngine._tail_rows(e, Mp)
+            assert tail == 0 or (tail >= min(n_slots, 256) and 2 * tail <= Mp and tail & (tail - 1) == 0)
