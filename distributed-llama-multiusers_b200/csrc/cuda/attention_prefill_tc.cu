@@ -6,14 +6,15 @@
 //   S = Q K^T     SS-mode MMA, M = 128 rows, N = 128 tokens, K = 128: Q staged once (fp16, K-major, 128-byte swizzle);
 //                 K pages arrive by TMA tensor copies (cp.async.bulk.tensor.2d over this GPU's KV cache, box 64 x 32,
 //                 hardware 128-byte swizzle); S (f32) lands in TMEM, double-buffered
-//   softmax       one thread per query row (= TMEM lane): two passes over S with tcgen05.ld (row maximum, then
-//                 exp2 -> fp16 probabilities written back to TMEM with tcgen05.st); running maximum with LAZY
-//                 rescaling: the reference maximum only moves when a row's maximum grew by more than 2^8, so in the
-//                 steady state the output accumulator is never touched by the softmax threads
+//   softmax       two threads per query row (= TMEM lane), 64 score columns each, read into registers with tcgen05.ld
+//                 in one pass (the score buffer is handed back at once); the row maximum is exchanged through shared
+//                 memory; exp2 -> fp16 probabilities written back to TMEM with tcgen05.st (every fourth exp2 on the
+//                 FMA pipe: the step is MUFU-bound); running maximum with LAZY rescaling: the reference maximum only
+//                 moves when a row's maximum grew by more than 2^8, so in the steady state the output accumulator is
+//                 never touched by the softmax threads
 //   O += P V      TS-mode MMA: A = P straight from TMEM, B = V pages in shared memory as an MN-major operand (V is
 //                 [token][head dim] in the cache, i.e. N-contiguous: no transpose anywhere), accumulating in TMEM
-// The MMA warp issues S(j+1) before P(j) V(j), so the tensor core works on the next scores while the softmax threads
-// are busy with the current ones.  Output: O / l -> shared memory -> Q80 cast into the XQ / XH slabs of the wo matmul.
+// S(j+1) and S(j+2) are issued while the softmax threads are busy with step j, so the tensor core works ahead of them.  Output: O / l -> shared memory -> Q80 cast into the XQ / XH slabs of the wo matmul.
 //
 // Warp roles (384 threads): warp 0 issues the S MMAs (+ TMEM owner), warp 6 the P V MMAs (an issuing thread spends ~700 clk
 // per group of 8 MMAs, so one thread for both would cap a step at ~1500 clk), warps 1-4 and 8-11 softmax (two threads per

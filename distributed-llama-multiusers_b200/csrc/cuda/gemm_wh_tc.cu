@@ -19,7 +19,7 @@
 // weight panel in L2); each CTA owns 128 TMEM lanes x 2 accumulators of 256 columns, so the epilogue of tile i
 // (TMEM -> registers -> smem chunk -> the shared fused epilogues of epilogue.cuh) overlaps the MMAs of tile i+1.
 //
-// Warp roles (576 threads): warp 0 producer (lanes issue 16 KB pieces), warp 1 MMA issuer + TMEM owner (in the
+// Warp roles (576 threads): warp 0 producer (4-6 lanes issue one 16 KB bulk copy each per stage), warp 1 MMA issuer + TMEM owner (in the
 // second CTA of a pair: forwards "my half of the stage has landed" to the leader's barrier), warps 2-17 epilogue.
 // Reference semantics: matmul_Q80_Q40_F32 (src/nn/nn-cpu-ops.cpp:352-377), llamafile sgemm (src/nn/llamafile/sgemm.cpp:593-783).
 #include "epilogue.cuh"
@@ -28,7 +28,6 @@
 #define WT_NT 256                      // activation rows per tile
 #define WT_THREADS 576
 #define WT_EPI_CHUNK 32
-#define WT_PIECE 16384                 // bytes per bulk copy
 
 struct WhArgs {
     const uint8_t* wh;                 // [row_tiles][KT][32 KB]
@@ -328,7 +327,7 @@ __global__ void __launch_bounds__(512) q40t_to_wh_kernel(const uint8_t* __restri
 extern void dl_set_error(const char* fmt, ...);
 extern "C" int dl_device_sm_count();
 
-static int g_wh_dbg = 0, g_wh_pf_dist = 0, g_wh_pf_mask = 0, g_wh_piece = 16384;
+static int g_wh_dbg = 0, g_wh_pf_dist = 0, g_wh_pf_mask = 0, g_wh_piece = 16384;      // bytes per bulk copy: 16 KB pieces (4 / 8 KB measured: no gain)
 extern "C" void dl_debug_set_wh_piece(int b) { if (b == 4096 || b == 8192 || b == 16384) g_wh_piece = b; }
 extern "C" void dl_debug_set_wh_mode(int m) { g_wh_dbg = m; }
 extern "C" void dl_debug_set_wh_prefetch(int dist, int mask) { g_wh_pf_dist = dist; g_wh_pf_mask = mask; }
