@@ -624,6 +624,58 @@ def test_reduce_norm_quant_with_partials():
     np.testing.assert_allclose(got, quant.q80_roundtrip(yout.cpu().numpy()), rtol=0, atol=1e-6)
 
 
+def test_q80_wire_rows_producer_to_consumer():
+    """Tensor-parallel hand-off of tensor-core batches under the flag protocol: the matmul epilogue pushes its partial
+    sums as Q80 wire rows (ld int8 + ld/32 fp16 scales per row) into N destination buffers (standing in for the peers)
+    and releases their flags; reduce_norm_quant waits for the flags and merges the rows.  Must equal the f32 exchange
+    of the Q80 round trip bit for bit (q * d is exact in f32)."""
+    k = K()
+    M, d, n, n_src, rows_cap = 40, 512, 256, 2, 64
+    rng = np.random.default_rng(71)
+    step = torch.tensor([3], dtype=torch.int32, device="cuda")
+    flag_mul, flag_add = 10, 4
+    rowb = d + d // 16
+    src_stride = rows_cap * d                                     # elements between sources in the f32 layout
+    bufs = [torch.zeros(n_src * rows_cap * rowb + 64, dtype=torch.uint8, device="cuda") for _ in range(2)]
+    flags = [torch.zeros(8, dtype=torch.int32, device="cuda") for _ in range(2)]
+    counter = torch.zeros(1, dtype=torch.int32, device="cuda")
+    ncap = 64
+    parts_ref = []
+    for src in range(n_src):                                      # source `src` writes its slot in both destinations
+        raw, wdq = _rand_q40(d, n, 80 + src)
+        w = k.make_q40t(torch.from_numpy(raw).cuda(), d, n)
+        xa = rng.standard_normal((M, n), dtype=np.float32)
+        xh = k.alloc_xh(n, ncap, "cuda")
+        k.quant_q80(torch.from_numpy(xa).cuda(), M, n, ncap, None, xh)
+        epi = k.epi_store([b.data_ptr() for b in bufs], d, src * src_stride, True, [f.data_ptr() + 4 * src for f in flags],
+                          step.data_ptr(), flag_mul, flag_add, counter.data_ptr(), wire_q80=True)
+        k.gemm_q40_tc(w, d, n, xh, ncap, M, epi, 1)
+        y = torch.zeros(M, d, device="cuda")                      # the same product through the plain f32 epilogue
+        k.gemm_q40_tc(w, d, n, xh, ncap, M, k.epi_store([y.data_ptr()], d, 0, True), 1)
+        parts_ref.append(y)
+    torch.cuda.synchronize()
+    assert all(int(f[s]) == 3 * flag_mul + flag_add for f in flags for s in range(n_src))
+    x = rng.standard_normal((M, d), dtype=np.float32)
+    wn = (1.0 + 0.1 * rng.standard_normal(d)).astype(np.float32)
+    outs = []
+    for b, f in zip(bufs, flags):
+        xout = torch.zeros(M, d, device="cuda")
+        yout = torch.zeros(M, d, device="cuda")
+        k.reduce_norm_quant(torch.from_numpy(x).cuda(), xout, b.data_ptr(), n_src, src_stride, f.data_ptr(), step.data_ptr(),
+                            flag_mul, flag_add, torch.from_numpy(wn).cuda(), 1e-5, d, M, ncap, None, k.alloc_xh(d, ncap, "cuda"),
+                            yout, wire_q80=True)
+        outs.append((xout, yout))
+    torch.cuda.synchronize()
+    xs = torch.from_numpy(x).cuda()
+    for p in parts_ref:                                            # rank order, like the kernel
+        xs = xs + p
+    for xout, yout in outs:
+        assert torch.equal(xout, xs)
+        xr = xs.cpu().numpy()
+        yref = wn * (xr / np.sqrt((xr * xr).mean(-1, keepdims=True) + 1e-5))
+        np.testing.assert_allclose(yout.cpu().numpy(), yref, rtol=1e-5, atol=1e-5)
+
+
 def test_ll_exchange_words_producer_to_consumers():
     """Tensor-parallel hand-off in LL words: a matmul epilogue pushes {value, epoch} pairs into N destination
     buffers (standing in for the peers), then the fused GEMV prologue and the stand-alone rnq kernel consume
