@@ -36,11 +36,19 @@ def required_memory(h: LlmHeader, n_nodes: int = 1, max_rows: int = 32, n_slots:
     # residual stream, normalised / quantised activations, q/k/v, hidden, logits, exchange area (N slices per sync)
     act = max_rows * (4 * dim * 4 + (dim + 2 * kv) // N * 4 + 3 * (hid // N) * 4 + vocab * 4 + 2 * N * dim * 8)
     out = {"weights": weights, "embedding": embedding, "kv_cache": kv_cache, "activations": act}
+    # fp16 copy of the layer matrices for prompt-sized batches (LlamaEngine prefill_wh="resident": 2 bytes per weight,
+    # rows padded to 128); only engines that can see >= 768-row batches build it, and "auto" declines it when it would
+    # take more than a quarter of the free memory
+    if backend == "cuda" and wt == quant.Q40 and max_rows >= 768:
+        pad = lambda r: (r + 127) // 128 * 128
+        out["fp16_weight_copy"] = 2 * L * (pad((dim + 2 * kv) // N) * dim + pad(dim) * (dim // N)
+                                           + pad(2 * hid // N) * dim + pad(dim) * (hid // N))
     out["total"] = sum(out.values())
     return out
 
 
 def describe(m: Dict[str, int]) -> str:
     mb = lambda b: f"{b / 2 ** 20:.0f} MB"
+    extra = f", fp16 weight copy {mb(m['fp16_weight_copy'])}" if m.get("fp16_weight_copy") else ""
     return (f"📀 RequiredMemory: {mb(m['total'])} (weights {mb(m['weights'])}, embedding {mb(m['embedding'])}, "
-            f"kv {mb(m['kv_cache'])}, activations {mb(m['activations'])})")
+            f"kv {mb(m['kv_cache'])}, activations {mb(m['activations'])}{extra})")

@@ -242,3 +242,15 @@ def test_native_random_model_writer_produces_a_valid_equivalent_file(tmp_path):
     lg = eng.forward([1, 2, 3], [0, 1, 2], [0, 0, 0]).numpy()
     assert np.isfinite(lg).all() and lg.std() > 0
     eng.close()
+
+
+def test_required_memory_counts_the_fp16_weight_copy():
+    """Engines that can see >= 768-row batches keep an fp16 copy of the layer matrices (2 bytes per weight): the
+    measured sizes were 13.96 GB for the 8B model on one GPU and 17.11 GB per rank for the 70B model on 8."""
+    from dllama_b200.models.memory import required_memory
+    for name, n, measured in (("llama3.1-8b", 1, 13958643712), ("llama3.1-8b", 2, 6979321856), ("llama3.3-70b", 8, 17112760320)):
+        s = mfile.MODEL_SHAPES[name]
+        h = mfile.LlmHeader(dim=s["dim"], hidden_dim=s["hidden_dim"], n_layers=s["n_layers"], n_heads=s["n_heads"],
+                            n_kv_heads=s["n_kv_heads"], vocab_size=s["vocab_size"], seq_len=4096, weight_type=quant.Q40)
+        assert required_memory(h, n, max_rows=4096, backend="cuda")["fp16_weight_copy"] == measured
+        assert "fp16_weight_copy" not in required_memory(h, n, max_rows=256, backend="cuda")
